@@ -81,7 +81,7 @@ MISC = {"P1": 0, "P2": 1, "Pass": 0, "Move": 1, "Switch": 2, "None": 0,
 
 class _L:
     def __getattr__(self, name):
-        return Lit(name)
+        return Lit(name.rstrip("_"))
 
 
 L = _L()
@@ -98,7 +98,7 @@ class _Enum:
         self._t = table
 
     def __getattr__(self, name):
-        return self._t[name]
+        return self._t[name.rstrip("_")]
 
 
 Move = _Enum(MOVE_ID)
@@ -275,6 +275,7 @@ class View:
         struct.pack_into("<" + fmt, self._b, self._o + off, int(v) & mask)
 
     def __getattr__(self, name):
+        name = name.rstrip("_")
         f = type(self).FIELDS.get(name)
         if f is None:
             raise AttributeError(name)
@@ -283,6 +284,7 @@ class View:
         return f[1](self._b, self._o + f[0])
 
     def __setattr__(self, name, v):
+        name = name.rstrip("_")
         f = type(self).FIELDS.get(name)
         if f is None:
             raise AttributeError(name)
@@ -414,11 +416,13 @@ class BoostsV:
         object.__setattr__(self, "_o", off)
 
     def __getattr__(self, name):
+        name = name.rstrip("_")
         v = struct.unpack_from("<I", self._b, self._o)[0]
         x = (v >> (4 * BOOST_FIELDS.index(name))) & 15
         return x - 16 if x >= 8 else x
 
     def __setattr__(self, name, val):
+        name = name.rstrip("_")
         v = struct.unpack_from("<I", self._b, self._o)[0]
         s = 4 * BOOST_FIELDS.index(name)
         v = (v & ~(15 << s)) | ((int(val) & 15) << s)
@@ -533,7 +537,7 @@ def build_pokemon(buf, off, p):
     level = int(p.get("level", 100))
     dvs = {"atk": 15, "def": 15, "spe": 15, "spc": 15}
     if isinstance(p.get("dvs"), dict):
-        dvs.update({k: int(v) for k, v in p["dvs"].items()})
+        dvs.update({k.rstrip("_"): int(v) for k, v in p["dvs"].items()})
     dvs["hp"] = (dvs["atk"] & 1) << 3 | (dvs["def"] & 1) << 2 | (dvs["spe"] & 1) << 1 | (dvs["spc"] & 1)
     exp = {"hp": 0xFFFF, "atk": 0xFFFF, "def": 0xFFFF, "spe": 0xFFFF, "spc": 0xFFFF}
     st = p.get("stats")
@@ -541,7 +545,7 @@ def build_pokemon(buf, off, p):
         exp = dict.fromkeys(exp, 0)
     elif isinstance(st, dict):
         exp = dict.fromkeys(exp, 0)
-        exp.update({k: int(v) for k, v in st.items()})
+        exp.update({k.rstrip("_"): int(v) for k, v in st.items()})
     pk = PokemonV(buf, off)
     for i, k in enumerate(["hp", "atk", "def", "spe", "spc"]):
         setattr(pk.stats, k, calc_stat(k == "hp", sd["stats"][i], dvs[k], exp[k], level))
@@ -693,3 +697,40 @@ def namespace():
              expectEqualSlices=expectEqualSlices, showdown=True, SkipCase=SkipCase, Choice=None,
              choices=[0] * 16)
     return g
+
+NULL = None
+CHOICES_SIZE = 16
+choices = [0] * 16
+Choice = None
+EXP = 0xFFFF
+def repeat(xs, n):
+    return list(xs) * n
+
+
+class Battle:
+    @staticmethod
+    def fixed(rolls, p1, p2):
+        return TestCase(rolls, p1, p2).battle.actual
+
+options = None
+
+
+class _ZeroVolatiles:
+    def __eq__(self, o):
+        return o._get() == 0
+
+
+class _DataNS:
+    @staticmethod
+    def Volatiles():
+        return _ZeroVolatiles()
+
+    @staticmethod
+    def Boosts():
+        class Z:
+            def __eq__(self, o):
+                return struct.unpack_from("<I", o._b, o._o)[0] == 0
+        return Z()
+
+
+data = _DataNS
