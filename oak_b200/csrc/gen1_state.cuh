@@ -1,0 +1,181 @@
+// Battle-state access for the B200 engine.
+//
+// HBM layout: the reference's own records, untouched — battle[n][384] (libpkmn Battle, reference
+// engine/src/lib/gen1/data.zig:54-68), durations[n][8] (gen1/chance.zig:255-318), result[n] (u8).
+// On-chip layout: one battle per thread, its 96 32-bit words stored as a COLUMN of a word-transposed
+// shared-memory tile, word w of the battle owned by thread t at tile[w * STRIDE + t]. Thread t
+// therefore always hits bank (t mod 32) whatever field it touches, so the data-dependent field
+// addressing of the simulator (party slot, move slot, player) is bank-conflict-free by construction.
+//
+// Everything here is `OAK_HD`: under nvcc it is __device__ (device only), under a plain host compiler it is
+// ordinary inline C++ with STRIDE = 1 so that tests can differential-test the very same engine source
+// against the oracle without a GPU (tests only; the product has no CPU path).
+#pragma once
+
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define OAK_HD __device__ __forceinline__
+#define OAK_HD_NOINLINE __device__ __noinline__
+#else
+#define OAK_HD inline
+#define OAK_HD_NOINLINE inline
+#endif
+
+#include "gen1_tables.cuh"
+
+namespace oakb200 {
+
+// ---- byte offsets inside the 384-byte battle (reference cpp/include/libpkmn/layout.h:17-96)
+enum : int {
+  SIDE_SIZE = 184,
+  PK_SIZE = 24,
+  PK_STATS = 0,  // hp, atk, def, spe, spc (u16 each)
+  PK_MOVES = 10,  // 4 x {id, pp}
+  PK_HP = 18,
+  PK_STATUS = 20,
+  PK_SPECIES = 21,
+  PK_TYPES = 22,
+  PK_LEVEL = 23,
+  S_ACTIVE = 144,
+  A_STATS = S_ACTIVE + 0,
+  A_SPECIES = S_ACTIVE + 10,
+  A_TYPES = S_ACTIVE + 11,
+  A_BOOSTS = S_ACTIVE + 12,
+  A_VOL = S_ACTIVE + 16,
+  A_MOVES = S_ACTIVE + 24,
+  S_ORDER = 176,
+  S_LAST_SELECTED = 182,
+  S_LAST_USED = 183,
+  B_TURN = 368,
+  B_LAST_DAMAGE = 370,
+  B_LAST_MOVES = 372,  // per player {index u8, counterable u8}
+  B_RNG = 376,
+  ST_HP = 0, ST_ATK = 2, ST_DEF = 4, ST_SPE = 6, ST_SPC = 8,
+};
+
+enum : uint8_t { CH_PASS = 0, CH_MOVE = 1, CH_SWITCH = 2 };
+enum : uint8_t { RES_NONE = 0, RES_WIN = 1, RES_LOSE = 2, RES_TIE = 3, RES_ERROR = 4, RESULT_DEFAULT = 0x50 };
+
+// Status byte (data.zig:235-301)
+enum : uint8_t { SB_PSN = 1u << 3, SB_BRN = 1u << 4, SB_FRZ = 1u << 5, SB_PAR = 1u << 6, SB_EXT = 1u << 7, SB_TOX = 0x88 };
+
+// Volatiles (data.zig:325-383), as masks on the packed u64
+#define OAK_VBIT(n) (1ull << (n))
+static const uint64_t V_BIDE = OAK_VBIT(0), V_THRASHING = OAK_VBIT(1), V_MULTIHIT = OAK_VBIT(2), V_FLINCH = OAK_VBIT(3),
+                      V_CHARGING = OAK_VBIT(4), V_BINDING = OAK_VBIT(5), V_INVULNERABLE = OAK_VBIT(6),
+                      V_CONFUSION = OAK_VBIT(7), V_MIST = OAK_VBIT(8), V_FOCUS_ENERGY = OAK_VBIT(9),
+                      V_SUBSTITUTE = OAK_VBIT(10), V_RECHARGING = OAK_VBIT(11), V_RAGE = OAK_VBIT(12),
+                      V_LEECH_SEED = OAK_VBIT(13), V_TOXIC = OAK_VBIT(14), V_LIGHT_SCREEN = OAK_VBIT(15),
+                      V_REFLECT = OAK_VBIT(16), V_TRANSFORM = OAK_VBIT(17);
+// multi-bit fields: shift, width
+#define VF_CONFUSION 18, 3
+#define VF_ATTACKS 21, 3
+#define VF_STATE 24, 16
+#define VF_SUBSTITUTE 40, 8
+#define VF_TRANSFORM 48, 4
+#define VF_DISABLE_DURATION 52, 4
+#define VF_DISABLE_MOVE 56, 3
+#define VF_TOXIC 59, 5
+
+OAK_HD uint32_t vf_get(uint64_t v, int shift, int bits) { return (uint32_t)((v >> shift) & ((1ull << bits) - 1)); }
+OAK_HD uint64_t vf_set(uint64_t v, int shift, int bits, uint32_t x) {
+  const uint64_t m = ((1ull << bits) - 1) << shift;
+  return (v & ~m) | (((uint64_t)x << shift) & m);
+}
+
+// Boost nibbles (data.zig:448-463)
+enum : int { BO_ATK = 0, BO_DEF = 1, BO_SPE = 2, BO_SPC = 3, BO_ACC = 4, BO_EVA = 5 };
+OAK_HD int boost_get(uint32_t b, int which) {
+  const int v = (int)((b >> (4 * which)) & 15u);
+  return v >= 8 ? v - 16 : v;
+}
+OAK_HD uint32_t boost_set(uint32_t b, int which, int v) {
+  return (b & ~(15u << (4 * which))) | (((uint32_t)v & 15u) << (4 * which));
+}
+
+// chance Action fields (chance.zig:160-206): shift, width
+#define AF_DAMAGE 0, 8
+#define AF_HIT 8, 2
+#define AF_CRIT 10, 2
+#define AF_SECONDARY 12, 2
+#define AF_SPEED_TIE 14, 2
+#define AF_CONFUSED 16, 2
+#define AF_PARALYZED 18, 2
+#define AF_DURATION 20, 4
+#define AF_SLEEP 24, 3
+#define AF_CONFUSION 27, 4
+#define AF_DISABLE 31, 3
+#define AF_ATTACKING 34, 2
+#define AF_BINDING 36, 2
+#define AF_MOVE_SLOT 38, 3
+#define AF_MULTI_HIT 41, 3
+#define AF_PP 44, 4
+#define AF_PSYWAVE 48, 8
+#define AF_METRONOME 56, 8
+enum : uint32_t { OPT_NONE = 0, OPT_FALSE = 1, OPT_TRUE = 2 };
+enum : uint32_t { OBS_NONE = 0, OBS_STARTED = 1, OBS_CONTINUING = 2, OBS_ENDED = 3, OBS_OVERWRITTEN = 4 };
+
+// chance Duration fields (chance.zig:279-287): sleeps 6x3 bits, then these
+#define DF_CONFUSION 18, 3
+#define DF_DISABLE 21, 4
+#define DF_ATTACKING 25, 3
+#define DF_BINDING 28, 3
+OAK_HD uint32_t bf_get(uint32_t d, int shift, int bits) { return (d >> shift) & ((1u << bits) - 1); }
+OAK_HD uint32_t bf_set(uint32_t d, int shift, int bits, uint32_t x) {
+  const uint32_t m = ((1u << bits) - 1) << shift;
+  return (d & ~m) | ((x << shift) & m);
+}
+
+// ---- constant tables (generated; reference moves.zig / species.zig / types.zig)
+OAK_HD uint32_t move_word(uint32_t id) { return GEN1_MOVE_DATA[id]; }
+OAK_HD uint32_t mv_effect(uint32_t w) { return w & 255u; }
+OAK_HD uint32_t mv_bp(uint32_t w) { return (w >> 8) & 255u; }
+OAK_HD uint32_t mv_accuracy(uint32_t w) { return (w >> 16) & 255u; }
+OAK_HD uint32_t mv_type(uint32_t w) { return (w >> 24) & 15u; }
+OAK_HD bool mv_self(uint32_t w) { return ((w >> 28) & 1u) != 0; }
+OAK_HD uint32_t type_eff(uint32_t atk, uint32_t def) { return GEN1_TYPE_CHART[atk * 15 + def]; }
+OAK_HD bool types_include(uint32_t types, uint32_t t) { return (types & 15u) == t || (types >> 4) == t; }
+
+// Effect ordinal ranges (moves.zig:1600-1640)
+OAK_HD bool eff_onBegin(uint32_t e) { return e - 1u < 16u; }
+OAK_HD bool eff_isStatDown(uint32_t e) { return e - 17u < 5u; }
+OAK_HD bool eff_onEnd(uint32_t e) { return e - 17u < 15u; }
+OAK_HD bool eff_alwaysHappens(uint32_t e) { return e - 32u < 7u; }
+OAK_HD bool eff_isSpecial(uint32_t e) { return e - 32u < 15u; }
+OAK_HD bool eff_isMulti(uint32_t e) { return e - 45u < 3u; }
+OAK_HD bool eff_isStatDownChance(uint32_t e) { return e - 48u < 4u; }
+
+// Stat-stage multipliers num/den (mechanics.zig:34-48), index = stage + 6
+OAK_HD uint32_t boost_num(int stage) {
+  // 25 28 33 40 50 66 1 15 2 25 3 35 4 packed 8 bits each would not fit one word; two words
+  const uint64_t lo = 0x0F01423228211C19ull;  // stages -6..+1: 25,28,33,40,50,66,1,15
+  const uint64_t hi = 0x0000000423031902ull;  // stages +2..+6: 2,25,3,35,4
+  const int i = stage + 6;
+  return (uint32_t)(((i < 8 ? lo >> (8 * i) : hi >> (8 * (i - 8)))) & 255u);
+}
+OAK_HD uint32_t boost_den(int stage) {
+  // 100 x6, 1, 10, 1, 10, 1, 10, 1
+  return stage < 0 ? 100u : ((stage & 1) ? 10u : 1u);
+}
+
+// ---- the per-battle memory window
+template <int STRIDE>
+struct Mem {
+  uint8_t* base;  // address of byte 0 of word 0 of this battle's column
+
+  OAK_HD uint8_t* at(int off) const { return base + (size_t)(off >> 2) * (STRIDE * 4) + (off & 3); }
+  OAK_HD uint32_t ld8(int off) const { return *at(off); }
+  OAK_HD void st8(int off, uint32_t v) const { *at(off) = (uint8_t)v; }
+  OAK_HD uint32_t ld16(int off) const { return *reinterpret_cast<const uint16_t*>(at(off)); }
+  OAK_HD void st16(int off, uint32_t v) const { *reinterpret_cast<uint16_t*>(at(off)) = (uint16_t)v; }
+  OAK_HD uint32_t ld32(int off) const { return *reinterpret_cast<const uint32_t*>(at(off)); }
+  OAK_HD void st32(int off, uint32_t v) const { *reinterpret_cast<uint32_t*>(at(off)) = v; }
+  OAK_HD uint64_t ld64(int off) const { return (uint64_t)ld32(off) | ((uint64_t)ld32(off + 4) << 32); }
+  OAK_HD void st64(int off, uint64_t v) const {
+    st32(off, (uint32_t)v);
+    st32(off + 4, (uint32_t)(v >> 32));
+  }
+};
+
+}  // namespace oakb200

@@ -1,0 +1,46 @@
+// TEST-ONLY: compiles the CUDA engine source (oak_b200/csrc/gen1_engine.cuh) with the host compiler
+// (STRIDE = 1 over a plain 384-byte record) so that it can be differential-tested against the oracle
+// in the GPU-less build container. Nothing in the product links this.
+#include <cstring>
+
+#include "../../oak_b200/csrc/gen1_engine.cuh"
+
+using namespace oakb200;
+
+template <bool CALC, bool CHANCE>
+static uint8_t run_update(uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, uint8_t* actions, const uint8_t* overrides) {
+  Engine<1, CALC, CHANCE> e;
+  uint32_t d[2];
+  memcpy(d, durations, 8);
+  e.begin(battle, d[0], d[1]);
+  if (CALC && overrides) memcpy(e.ovr, overrides, 16);
+  const uint32_t r = e.update(c1, c2);
+  e.end();
+  d[0] = e.dur[0];
+  d[1] = e.dur[1];
+  memcpy(durations, d, 8);
+  if (actions) memcpy(actions, e.act, 16);
+  return (uint8_t)r;
+}
+
+extern "C" {
+uint8_t shim_update(uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, uint8_t* actions, const uint8_t* overrides) {
+  return overrides ? run_update<true, true>(battle, c1, c2, durations, actions, overrides)
+                   : run_update<false, true>(battle, c1, c2, durations, actions, nullptr);
+}
+uint8_t shim_update_nochance(uint8_t* battle, uint8_t c1, uint8_t c2) {
+  uint8_t d[8] = {0};
+  return run_update<false, false>(battle, c1, c2, d, nullptr, nullptr);
+}
+uint8_t shim_choices(const uint8_t* battle, int player, int request, uint8_t* out) {
+  Engine<1, false, true> e;
+  e.begin(const_cast<uint8_t*>(battle), 0, 0);
+  int n;
+  const uint64_t list = e.choices(player, request, &n);
+  for (int i = 0; i < n; i++) {
+    const uint32_t c = Engine<1, false, true>::choice_at(list, i);
+    out[i] = (uint8_t)(((c >> 2) << 2) | (c & 3));
+  }
+  return (uint8_t)n;
+}
+}

@@ -1,0 +1,123 @@
+"""ctypes bindings to the ORACLE (oracle/liboracle.so) and to the test-only host build of the CUDA
+engine source (tests/host_shim). Test infrastructure only."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MASK64 = (1 << 64) - 1
+
+
+def splitmix64(x):
+    z = (x + 0x9E3779B97F4A7C15) & MASK64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & MASK64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & MASK64
+    return z ^ (z >> 31)
+
+
+def sample_seed(i):
+    return ((i + 1) * 0x9E3779B97F4A7C15) & MASK64
+
+
+def pick_word(seed, step):
+    return splitmix64(seed ^ ((0xD1B54A32D192ED03 * step) & MASK64))
+
+
+class Oracle:
+    def __init__(self):
+        path = os.path.join(ROOT, "oracle", "liboracle.so")
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+        self.lib = lib = ctypes.CDLL(path)
+        lib.oracle_gen1_update.restype = ctypes.c_uint8
+        lib.oracle_gen1_choices.restype = ctypes.c_uint8
+        lib.oracle_oak_step.restype = ctypes.c_uint8
+        lib.oracle_oak_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint64,
+                                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.oracle_oak_sample_battle.argtypes = [ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.oracle_oak_rollout.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
+                                           ctypes.c_uint32, ctypes.c_void_p]
+        lib.oracle_oak_battle_init.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_uint64, ctypes.c_void_p]
+        lib.oracle_oak_randomize_hidden.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+
+    @staticmethod
+    def _p(a):
+        return a.ctypes.data_as(ctypes.c_void_p)
+
+    def sample_battle(self, i):
+        b = np.zeros(384, np.uint8)
+        d = np.zeros(8, np.uint8)
+        r = np.zeros(1, np.uint8)
+        self.lib.oracle_oak_sample_battle(i, self._p(b), self._p(d), self._p(r))
+        return b, d, int(r[0])
+
+    def battle_init(self, p1_species, p1_moves, p2_species, p2_moves, seed):
+        b = np.zeros(384, np.uint8)
+        a = [np.ascontiguousarray(x, np.uint8) for x in (p1_species, p1_moves, p2_species, p2_moves)]
+        self.lib.oracle_oak_battle_init(*[self._p(x) for x in a], seed, self._p(b))
+        return b
+
+    def choices(self, battle, player, request):
+        out = np.zeros(16, np.uint8)
+        n = self.lib.oracle_gen1_choices(self._p(battle), player, request, self._p(out))
+        return [int(x) for x in out[:n]]
+
+    def update(self, battle, c1, c2, durations, overrides=None):
+        """options_set(null[, calc]) + update. battle/durations updated in place. Returns (result, actions[16])."""
+        opt = np.zeros(40, np.uint8)
+        opt[16:24] = durations
+        if overrides is not None:
+            opt[24:40] = overrides
+        r = self.lib.oracle_gen1_update(self._p(battle), c1, c2, self._p(opt))
+        durations[:] = opt[16:24]
+        return int(r), opt[0:16].copy()
+
+    def step(self, battle, durations, result, pick):
+        act = np.zeros(16, np.uint8)
+        c = np.zeros(2, np.uint8)
+        r = self.lib.oracle_oak_step(self._p(battle), self._p(durations), result, pick, self._p(act),
+                                     self._p(c[0:1]), self._p(c[1:2]))
+        return int(r), act, int(c[0]), int(c[1])
+
+    def rollout(self, battle, durations, result, seed, max_steps=100000):
+        r = np.array([result], np.uint8)
+        steps = np.zeros(1, np.uint32)
+        self.lib.oracle_oak_rollout(self._p(battle), self._p(durations), self._p(r), seed, max_steps, self._p(steps))
+        return int(r[0]), int(steps[0])
+
+    def randomize_hidden(self, battle, durations):
+        self.lib.oracle_oak_randomize_hidden(self._p(battle), self._p(durations))
+
+
+class HostShim:
+    """The CUDA engine source compiled for the host (tests only)."""
+
+    def __init__(self):
+        d = os.path.join(ROOT, "tests", "host_shim")
+        so = os.path.join(d, "libengine_host.so")
+        src = os.path.join(d, "engine_host_shim.cpp")
+        deps = [src] + [os.path.join(ROOT, "oak_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "oak_b200", "csrc"))]
+        if not os.path.exists(so) or any(os.path.getmtime(x) > os.path.getmtime(so) for x in deps):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
+        self.lib = lib = ctypes.CDLL(so)
+        lib.shim_update.restype = ctypes.c_uint8
+        lib.shim_update.argtypes = [ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint8, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.shim_update_nochance.restype = ctypes.c_uint8
+        lib.shim_update_nochance.argtypes = [ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint8]
+        lib.shim_choices.restype = ctypes.c_uint8
+        lib.shim_choices.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+
+    def choices(self, battle, player, request):
+        out = np.zeros(16, np.uint8)
+        n = self.lib.shim_choices(battle.ctypes.data, player, request, out.ctypes.data)
+        return [int(x) for x in out[:n]]
+
+    def update(self, battle, c1, c2, durations, overrides=None):
+        act = np.zeros(16, np.uint8)
+        ov = None if overrides is None else np.ascontiguousarray(overrides, np.uint8).ctypes.data
+        r = self.lib.shim_update(battle.ctypes.data, c1, c2, durations.ctypes.data, act.ctypes.data, ov)
+        return int(r), act
+
+    def update_nochance(self, battle, c1, c2):
+        return int(self.lib.shim_update_nochance(battle.ctypes.data, c1, c2))

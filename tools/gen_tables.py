@@ -162,7 +162,7 @@ def main():
         f.write(hdr + "#pragma once\n\n" + enum_txt + "\n" + body("static const"))
     with open(f"{ROOT}/oak_b200/csrc/gen1_tables.cuh", "w") as f:
         f.write(hdr + "#pragma once\n\n" + enum_txt.replace("Gen1Effect", "Effect").replace("Gen1Move", "Move").replace("Gen1Type", "Type")
-                + "\n#ifdef __CUDACC__\n#define OAK_TABLE __device__ __constant__ const\n#else\n#define OAK_TABLE static const\n#endif\n\n"
+                + "\n#ifdef __CUDACC__\n#define OAK_TABLE static __device__ const\n#else\n#define OAK_TABLE static const\n#endif\n\n"
                 + body("OAK_TABLE"))
     with open(f"{ROOT}/tests/golden/gen1_names.json", "w") as f:
         json.dump(dict(moves=moves, species=species, types=types, effects=effects,
