@@ -1,0 +1,115 @@
+/* oakb200 — B200-native batched Generation I battle engine: C ABI.
+ *
+ * Drop-in boundary for the data-parallel hot path of lab-oak/oak. Host buffers keep the reference's
+ * own array-of-records formats so existing Oak buffers pass through untouched:
+ *   battle    384 bytes  pkmn_gen1_battle            (reference engine/src/include/pkmn.h:150-160,
+ *                                                     layout engine/src/lib/gen1/data.zig:54-68)
+ *   durations   8 bytes  pkmn_gen1_chance_durations  (engine/src/lib/gen1/chance.zig:255-318)
+ *   actions    16 bytes  pkmn_gen1_chance_actions    (chance.zig:30-38,160-206)
+ *   overrides  16 bytes  pkmn_gen1_calc_options.overrides (bindings/c.zig:101-103)
+ *   choice      1 byte   pkmn_choice  (type | data << 2, common/data.zig:56-72)
+ *   result      1 byte   pkmn_result  (type | p1 << 4 | p2 << 6, common/data.zig:84-112)
+ * Engine semantics are libpkmn's as Oak builds it (reference dev/libpkmn:9: -Dshowdown, miss=false,
+ * advance=false, ebc=false, key=true, -Dchance, -Dcalc).
+ *
+ * Every entry point returns 0 on success or a negative OAKB200_E* code; oakb200_last_error() gives
+ * the text. Nothing throws across the ABI. One context per GPU; calls on one context are serialised
+ * by the caller (the reference's own contract is one search object per thread, cpp/include/search/
+ * mcts.h:135-139). There is no CPU fallback: without a CUDA device oakb200_create fails.
+ *
+ * Entry points ending in _device take DEVICE pointers and enqueue on the context stream without
+ * synchronising; the others take HOST pointers, copy, run and synchronise.
+ */
+#ifndef OAKB200_H
+#define OAKB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OAKB200_BATTLE_SIZE 384    /* PKMN_GEN1_BATTLE_SIZE, pkmn.h:150 */
+#define OAKB200_DURATIONS_SIZE 8   /* PKMN_GEN1_CHANCE_DURATIONS_SIZE */
+#define OAKB200_ACTIONS_SIZE 16    /* PKMN_GEN1_CHANCE_ACTIONS_SIZE */
+#define OAKB200_MAX_CHOICES 9      /* PKMN_GEN1_MAX_CHOICES, pkmn.h:163 */
+
+#define OAKB200_OK 0
+#define OAKB200_ENODEVICE (-1)
+#define OAKB200_ECUDA (-2)
+#define OAKB200_EINVAL (-3)
+#define OAKB200_ECAPACITY (-4)
+
+typedef struct oakb200_ctx oakb200_ctx;
+
+/* rollout flags */
+#define OAKB200_ROLLOUT_WRITE_STATE 1u /* write final battle/durations/result back (parity checks) */
+#define OAKB200_ROLLOUT_TRACK_CHANCE 2u /* maintain chance durations during playouts, as the reference's
+                                           options-enabled update does (mcts.h:462-479); the outputs
+                                           (score, turns, steps) do not depend on it */
+
+int oakb200_create(int device, size_t n_max, oakb200_ctx** out);
+void oakb200_destroy(oakb200_ctx* ctx);
+const char* oakb200_last_error(const oakb200_ctx* ctx);
+int oakb200_device(const oakb200_ctx* ctx);
+/* Use an existing cudaStream_t (e.g. the caller's framework stream) instead of the context's own. */
+int oakb200_set_stream(oakb200_ctx* ctx, void* cuda_stream);
+int oakb200_synchronize(oakb200_ctx* ctx);
+/* Number of kernels this library has launched on the context since creation. */
+uint64_t oakb200_launch_count(const oakb200_ctx* ctx);
+
+/* ---- resident batch -------------------------------------------------------------------------
+ * upload: make `n` battles resident (durations NULL = zeros, results NULL = 0x50 "both move").
+ * Replaces: building a std::vector of MCTS::Input / Frames rows (cpp/include/search/mcts.h:62-66,
+ * cpp/include/py/battle/frames.h:22-27). */
+int oakb200_upload(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results);
+int oakb200_download(oakb200_ctx* ctx, size_t n, uint8_t* battles, uint8_t* durations, uint8_t* results);
+/* Device pointers of the resident arrays (battle[n][384], durations[n][8], result[n]). */
+int oakb200_resident(oakb200_ctx* ctx, void** battles, void** durations, void** results, size_t* n);
+
+/* ---- pkmn_gen1_battle_choices for a batch (pkmn.h:283-288; mechanics.zig:3139-3251) ------------
+ * For every resident battle and both players, given the request kinds held in the resident result
+ * byte: out[n][2][9] choices (switches first, then moves) and counts[n][2]. HOST outputs. */
+int oakb200_choices(oakb200_ctx* ctx, uint8_t* out, uint8_t* counts);
+int oakb200_choices_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* results, void* out, void* counts);
+
+/* ---- pkmn_gen1_battle_options_set + pkmn_gen1_battle_update for a batch (pkmn.h:225-229,264-268) -
+ * c1/c2[n]: the players' choices. overrides[n][16] or NULL: calc overrides (Oak writes bytes 0 and 8,
+ * mcts.h:569-590); NULL = options_set(calc = null). Resident battle/durations/result are updated in
+ * place; results_out[n] and actions_out[n][16] (each nullable) receive copies. HOST pointers. */
+int oakb200_step(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const uint8_t* overrides,
+                 uint8_t* results_out, uint8_t* actions_out);
+int oakb200_step_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
+                        const void* c2, const void* overrides, void* actions_out);
+/* One random-playout step (body of the loop at mcts.h:467-479): choices for both players, then
+ * c1 = choices1[pick % m], c2 = choices2[(pick >> 32) % n], options_set(null), update.
+ * pick for battle i = splitmix64(seeds[i] ^ (0xD1B54A32D192ED03 * step_index)). */
+int oakb200_step_random_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results,
+                               const void* seeds, uint32_t step_index, void* actions_out, void* chosen_out);
+
+/* ---- random playouts to a terminal result (MCTS::init_stats_and_rollout, mcts.h:448-496) ------
+ * For every resident battle i play picks splitmix64(seeds[i] ^ (K * step)), step = 0, 1, ... until
+ * the result type is non-zero or max_steps updates were made. score2_out[n]: 2 win / 1 tie / 0 lose
+ * for player 1 (PKMN::score2, cpp/include/libpkmn/pkmn.h:192-208; 255 if max_steps hit);
+ * turns_out[n] (u16): battle turn counter at the end; steps_out[n] (u32): updates made. Any of the
+ * three may be NULL. The resident state is left untouched unless OAKB200_ROLLOUT_WRITE_STATE. */
+int oakb200_rollout(oakb200_ctx* ctx, const uint64_t* seeds, uint32_t max_steps, uint32_t flags, uint8_t* score2_out,
+                    uint16_t* turns_out, uint32_t* steps_out);
+int oakb200_rollout_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                           uint32_t max_steps, uint32_t flags, void* score2_out, void* turns_out, void* steps_out);
+/* Sum of updates performed by all rollout launches on this context (device counter, synchronises). */
+int oakb200_total_steps(oakb200_ctx* ctx, uint64_t* out);
+
+/* ---- MCTS::randomize_hidden_variables for a batch (cpp/include/search/durations.h:25-97) ------- */
+int oakb200_randomize_hidden_device(oakb200_ctx* ctx, size_t n, void* battles, const void* durations);
+
+/* ---- PKMN::battle + update(0,0) for a batch (pkmn.h:50-57, init.h:90-154, generate.cc:238-240) --
+ * teams[n][2][6][5] = {species, move x4}; seeds[n]; builds level-100 max-stat battles on the device
+ * into the resident arrays, sends out the leads, durations = 0. HOST pointers. */
+int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, const uint64_t* seeds);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

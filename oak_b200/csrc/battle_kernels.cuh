@@ -1,0 +1,314 @@
+// sm_100a kernels for batched Generation I battles. One battle per thread; each CTA stages its
+// battles as columns of a word-transposed shared-memory tile (gen1_state.cuh) and runs the engine
+// (gen1_engine.cuh) on them. Global memory holds the reference's AoS records.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gen1_engine.cuh"
+
+namespace oakb200 {
+
+static const int BATTLE_WORDS = 96;
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  uint64_t z = x + 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+// pick word of playout step `step`: the shape of mcts.h:456-461 with a counter-based stream
+__device__ __forceinline__ uint64_t pick_word(uint64_t seed, uint32_t step) {
+  return splitmix64(seed ^ (0xD1B54A32D192ED03ull * (uint64_t)step));
+}
+// 64-bit value mod a small divisor (1..9) without a 64-bit division
+__device__ __forceinline__ uint32_t mod_small(uint64_t v, uint32_t d) {
+  const uint32_t hi = (uint32_t)(v >> 32) % d, lo = (uint32_t)v % d;
+  const uint32_t two32 = (uint32_t)(0x100000000ull % d);
+  return (hi * two32 + lo) % d;
+}
+
+// AoS record (384 B, 16-byte aligned) -> this thread's column
+template <int STRIDE>
+__device__ __forceinline__ void load_column(uint32_t* col, const uint8_t* record) {
+  const uint4* src = reinterpret_cast<const uint4*>(record);
+#pragma unroll 6
+  for (int k = 0; k < BATTLE_WORDS / 4; k++) {
+    const uint4 v = src[k];
+    col[(4 * k + 0) * STRIDE] = v.x;
+    col[(4 * k + 1) * STRIDE] = v.y;
+    col[(4 * k + 2) * STRIDE] = v.z;
+    col[(4 * k + 3) * STRIDE] = v.w;
+  }
+}
+template <int STRIDE>
+__device__ __forceinline__ void store_column(const uint32_t* col, uint8_t* record) {
+  uint4* dst = reinterpret_cast<uint4*>(record);
+#pragma unroll 6
+  for (int k = 0; k < BATTLE_WORDS / 4; k++) {
+    uint4 v;
+    v.x = col[(4 * k + 0) * STRIDE];
+    v.y = col[(4 * k + 1) * STRIDE];
+    v.z = col[(4 * k + 2) * STRIDE];
+    v.w = col[(4 * k + 3) * STRIDE];
+    dst[k] = v;
+  }
+}
+
+// Both players' legal choices for `result`'s request kinds, then the playout pick (mcts.h:467-477)
+template <class E>
+__device__ __forceinline__ void pick_choices(const E& e, uint32_t result, uint64_t pick, uint32_t& c1, uint32_t& c2) {
+  int m, n;
+  const uint64_t l1 = e.choices(0, (result >> 4) & 3, &m);
+  const uint64_t l2 = e.choices(1, (result >> 6) & 3, &n);
+  c1 = E::choice_at(l1, (int)mod_small(pick, (uint32_t)m));
+  c2 = E::choice_at(l2, (int)((uint32_t)(pick >> 32) % (uint32_t)n));
+}
+
+// ---------------------------------------------------------------------------------------------
+// choices_kernel: pkmn_gen1_battle_choices for both players of every battle
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) choices_kernel(const uint8_t* __restrict__ battles, const uint8_t* __restrict__ results,
+                                                         uint8_t* __restrict__ out, uint8_t* __restrict__ counts, uint32_t n) {
+  extern __shared__ uint32_t tile[];
+  const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  uint32_t* col = tile + threadIdx.x;
+  load_column<BLOCK>(col, battles + (size_t)i * 384);
+  Engine<BLOCK, false, false> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+  const uint32_t r = results[i];
+#pragma unroll
+  for (int p = 0; p < 2; p++) {
+    int k;
+    const uint64_t list = e.choices(p, (r >> (4 + 2 * p)) & 3, &k);
+    for (int j = 0; j < 9; j++) out[(size_t)i * 18 + p * 9 + j] = j < k ? (uint8_t)Engine<BLOCK, false, false>::choice_at(list, j) : 0;
+    counts[(size_t)i * 2 + p] = (uint8_t)k;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// step_kernel: one update per battle, in place.
+//   RANDOM = false: choices from c1[]/c2[];  RANDOM = true: playout pick from seeds[] and step_index
+//   CALC: per-battle 16-byte calc overrides
+template <int BLOCK, bool RANDOM, bool CALC>
+__global__ void __launch_bounds__(BLOCK, 3)
+step_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+            const uint8_t* __restrict__ c1s, const uint8_t* __restrict__ c2s, const uint64_t* __restrict__ seeds,
+            uint32_t step_index, const uint8_t* __restrict__ overrides, uint8_t* __restrict__ actions_out,
+            uint8_t* __restrict__ chosen_out, uint32_t n) {
+  extern __shared__ uint32_t tile[];
+  const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  uint32_t* col = tile + threadIdx.x;
+  load_column<BLOCK>(col, battles + (size_t)i * 384);
+  const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+  Engine<BLOCK, CALC, true> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
+  const uint32_t prev = results[i];
+  uint32_t c1, c2;
+  if (RANDOM) {
+    pick_choices(e, prev, pick_word(seeds[i], step_index), c1, c2);
+    if (chosen_out) {
+      chosen_out[(size_t)i * 2] = (uint8_t)c1;
+      chosen_out[(size_t)i * 2 + 1] = (uint8_t)c2;
+    }
+  } else {
+    c1 = c1s[i];
+    c2 = c2s[i];
+  }
+  if (CALC) {
+    const uint4 o = *reinterpret_cast<const uint4*>(overrides + (size_t)i * 16);
+    e.ovr[0] = (uint64_t)o.x | ((uint64_t)o.y << 32);
+    e.ovr[1] = (uint64_t)o.z | ((uint64_t)o.w << 32);
+  }
+  uint32_t r = prev;
+  if ((prev & 15u) == 0) {  // a finished battle is frozen
+    r = e.update(c1, c2);
+    e.end();
+    store_column<BLOCK>(col, battles + (size_t)i * 384);
+    *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
+    results[i] = (uint8_t)r;
+  }
+  if (actions_out) {
+    uint4 a;
+    a.x = (uint32_t)e.act[0];
+    a.y = (uint32_t)(e.act[0] >> 32);
+    a.z = (uint32_t)e.act[1];
+    a.w = (uint32_t)(e.act[1] >> 32);
+    *reinterpret_cast<uint4*>(actions_out + (size_t)i * 16) = a;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rollout_kernel: random playouts to a terminal result. Persistent CTAs; every lane pulls its next
+// battle from a global ticket counter the moment its current one ends (lane refill), so a warp
+// stays full although playout lengths differ by an order of magnitude. The loop body is
+// "maybe refill, then exactly one update" so that all lanes re-converge once per update.
+template <int BLOCK, bool CHANCE, bool WRITE_STATE>
+__global__ void __launch_bounds__(BLOCK, 3)
+rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+               const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
+               uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
+               unsigned long long* __restrict__ total_steps) {
+  extern __shared__ uint32_t tile[];
+  uint32_t* col = tile + threadIdx.x;
+  Engine<BLOCK, false, CHANCE> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+
+  uint32_t i = 0, result = 0, step = 0;
+  uint64_t seed = 0;
+  bool have = false, exhausted = false;
+  uint32_t my_steps = 0;
+
+  for (;;) {
+    if (!have && !exhausted) {
+      i = atomicAdd(ticket, 1u);
+      if (i < n) {
+        load_column<BLOCK>(col, battles + (size_t)i * 384);
+        const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+        e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
+        result = results[i];
+        seed = seeds[i];
+        step = 0;
+        have = true;
+      } else {
+        exhausted = true;
+      }
+    }
+    if (__all_sync(0xFFFFFFFFu, !have)) break;
+    if (have) {
+      const bool live = (result & 15u) == 0 && step < max_steps;
+      if (live) {
+        uint32_t c1, c2;
+        pick_choices(e, result, pick_word(seed, step), c1, c2);
+        e.act[0] = e.act[1] = 0;  // pkmn_gen1_battle_options_set(null, null, null) (mcts.h:478)
+        result = e.update(c1, c2);
+        step++;
+      }
+      if (!live || (result & 15u) != 0 || step >= max_steps) {
+        const uint32_t t = result & 15u;
+        if (score2_out) score2_out[i] = t == RES_WIN ? 2 : (t == RES_TIE ? 1 : (t == RES_LOSE ? 0 : 255));
+        if (turns_out) turns_out[i] = (uint16_t)e.m.ld16(B_TURN);
+        if (steps_out) steps_out[i] = step;
+        if (WRITE_STATE) {
+          e.end();
+          store_column<BLOCK>(col, battles + (size_t)i * 384);
+          *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
+          results[i] = (uint8_t)result;
+        }
+        my_steps += step;
+        have = false;
+      }
+    }
+  }
+  // one atomic per warp
+  uint32_t s = my_steps;
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+  if ((threadIdx.x & 31) == 0 && total_steps) atomicAdd(total_steps, (unsigned long long)s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// MCTS::randomize_hidden_variables (reference cpp/include/search/durations.h:25-97). Touches a few
+// bytes per battle, so it works on the AoS records in place. Every draw uses the same battle.rng.
+__device__ __constant__ uint64_t HIDDEN_BINDING_CUM[4] = {
+    // thresholds (cumulative counts out of 40) of the 4x40 lookup rows, 8 bits each: n(<=1), n(<=2), n(<=3)
+    15ull | (30ull << 8) | (36ull << 16), 24ull | (32ull << 8) | (40ull << 16), 20ull | (40ull << 8) | (40ull << 16),
+    40ull | (40ull << 8) | (40ull << 16)};
+
+__global__ void randomize_hidden_kernel(uint8_t* __restrict__ battles, const uint8_t* __restrict__ durations, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint8_t* b = battles + (size_t)i * 384;
+  const uint64_t rng = *reinterpret_cast<const uint64_t*>(b + B_RNG);
+  const uint2 dd = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+  for (int s = 0; s < 2; s++) {
+    const uint32_t d = s == 0 ? dd.x : dd.y;
+    if (d == 0) continue;
+    uint8_t* side = b + s * SIDE_SIZE;
+    uint64_t v = *reinterpret_cast<uint64_t*>(side + A_VOL);
+    const uint32_t confusion = bf_get(d, DF_CONFUSION);
+    if (confusion) {
+      const uint32_t one = confusion == 1;
+      const uint32_t max = 6 - (confusion + one);
+      v = vf_set(v, VF_CONFUSION, (uint32_t)(rng % max) + 1 + one);
+    }
+    const uint32_t disable = bf_get(d, DF_DISABLE);
+    if (disable) v = vf_set(v, VF_DISABLE_DURATION, (uint32_t)(rng % (9 - disable)) + 1);
+    const uint32_t attacking = bf_get(d, DF_ATTACKING);
+    if (attacking && (v & (V_BIDE | V_THRASHING))) {
+      v = vf_set(v, VF_ATTACKS, attacking == 3 ? 1u : 4u - (attacking + (uint32_t)(rng % 2)));
+    }
+    const uint32_t binding = bf_get(d, DF_BINDING);
+    if (binding) {
+      const uint32_t idx = (uint32_t)(rng % 40);
+      const uint64_t cum = HIDDEN_BINDING_CUM[binding - 1];
+      const uint32_t a = 1 + (idx >= (cum & 255)) + (idx >= ((cum >> 8) & 255)) + (idx >= ((cum >> 16) & 255));
+      v = vf_set(v, VF_ATTACKS, a);
+    }
+    *reinterpret_cast<uint64_t*>(side + A_VOL) = v;
+    for (int k = 0; k < 6; k++) {
+      const uint32_t sleep = (d >> (3 * k)) & 7u;
+      if (!sleep) continue;
+      uint8_t* pk = side + ((int)side[S_ORDER + k] - 1) * PK_SIZE;
+      const uint32_t st = pk[PK_STATUS];
+      if ((st & 7u) && !(st & SB_EXT)) pk[PK_STATUS] = (uint8_t)((st & 0xF8u) | ((uint32_t)(rng % (8 - sleep)) + 1));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// build_kernel: PKMN::battle(p1, p2, seed) + update(0, 0) (reference cpp/include/libpkmn/pkmn.h:50-57,
+// init.h:35-40,90-154, data/moves.h:1794-1796, cpp/src/generate.cc:238-240).
+// teams[n][2][6][5] = {species, move x4}; level 100, DV 15, max stat experience.
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) build_kernel(const uint8_t* __restrict__ teams, const uint64_t* __restrict__ seeds,
+                                                       uint8_t* __restrict__ battles, uint8_t* __restrict__ durations,
+                                                       uint8_t* __restrict__ results, uint32_t n) {
+  extern __shared__ uint32_t tile[];
+  const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  uint32_t* col = tile + threadIdx.x;
+  for (int w = 0; w < BATTLE_WORDS; w++) col[w * BLOCK] = 0;
+  Mem<BLOCK> m;
+  m.base = reinterpret_cast<uint8_t*>(col);
+  const uint8_t* t = teams + (size_t)i * 60;
+  for (int s = 0; s < 2; s++) {
+    for (int k = 0; k < 6; k++) {
+      const uint8_t* set = t + (s * 6 + k) * 5;
+      const uint32_t species = set[0];
+      const int pk = s * SIDE_SIZE + k * PK_SIZE;
+      if (species == 0) {
+        if (k == 0) m.st8(s * SIDE_SIZE + S_ORDER, 1);
+        continue;
+      }
+      for (int q = 0; q < 5; q++) {
+        const uint32_t base = GEN1_SPECIES_STATS[5 * species + q];
+        const uint32_t core = 2 * (base + 15) + 63;
+        m.st16(pk + PK_STATS + 2 * q, core * 100 / 100 + (q == 0 ? 110u : 5u));
+      }
+      for (int q = 0; q < 4; q++) {
+        const uint32_t mv = set[1 + q];
+        const uint32_t pp = GEN1_MOVE_PP[mv] / 5 * 8;
+        m.st8(pk + PK_MOVES + 2 * q, mv);
+        m.st8(pk + PK_MOVES + 2 * q + 1, mv ? (pp < 61 ? pp : 61) : 0);
+      }
+      m.st16(pk + PK_HP, m.ld16(pk + PK_STATS));
+      m.st8(pk + PK_SPECIES, species);
+      m.st8(pk + PK_TYPES, GEN1_SPECIES_TYPES[species]);
+      m.st8(pk + PK_LEVEL, 100);
+      m.st8(s * SIDE_SIZE + S_ORDER + k, k + 1);
+    }
+  }
+  m.st64(B_RNG, seeds[i]);
+  Engine<BLOCK, false, true> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+  const uint32_t r = e.update(0, 0);
+  e.end();
+  store_column<BLOCK>(col, battles + (size_t)i * 384);
+  *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
+  results[i] = (uint8_t)r;
+}
+
+}  // namespace oakb200

@@ -1,0 +1,352 @@
+// C ABI of the B200 battle engine (include/oakb200.h). Host side: context, resident buffers,
+// launches. No CPU compute path: every entry point either launches sm_100a kernels or fails.
+#include "../../include/oakb200.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "battle_kernels.cuh"
+
+using namespace oakb200;
+
+namespace {
+const int BLOCK = 128;                                  // battles per CTA
+const size_t TILE_BYTES = (size_t)BATTLE_WORDS * BLOCK * 4;  // 48 KB shared-memory tile
+}  // namespace
+
+struct oakb200_ctx {
+  int device = -1;
+  int sm_count = 0;
+  size_t n_max = 0, n = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint8_t *battles = nullptr, *durations = nullptr, *results = nullptr;
+  // scratch for the host-pointer entry points
+  uint8_t *c1 = nullptr, *c2 = nullptr, *overrides = nullptr, *actions = nullptr, *choices = nullptr, *counts = nullptr;
+  uint64_t* seeds = nullptr;
+  uint8_t* score2 = nullptr;
+  uint16_t* turns = nullptr;
+  uint32_t* steps = nullptr;
+  uint8_t* teams = nullptr;
+  uint32_t* ticket = nullptr;
+  unsigned long long* total_steps = nullptr;
+  uint64_t launches = 0;
+  std::string error;
+};
+
+namespace {
+
+int fail(oakb200_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess) {
+  if (ctx) {
+    ctx->error = what;
+    if (e != cudaSuccess) {
+      ctx->error += ": ";
+      ctx->error += cudaGetErrorString(e);
+    }
+  }
+  return code;
+}
+
+#define CU(ctx, call)                                              \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return fail(ctx, OAKB200_ECUDA, #call, e__); \
+  } while (0)
+
+template <class K>
+cudaError_t allow_smem(K kernel) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TILE_BYTES);
+}
+
+unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
+
+template <bool RANDOM, bool CALC>
+cudaError_t launch_step(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
+                        const void* c2, const void* seeds, uint32_t step_index, const void* overrides, void* actions,
+                        void* chosen) {
+  auto k = step_kernel<BLOCK, RANDOM, CALC>;
+  cudaError_t e = allow_smem(k);
+  if (e != cudaSuccess) return e;
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
+                                                     (const uint8_t*)c1, (const uint8_t*)c2, (const uint64_t*)seeds,
+                                                     step_index, (const uint8_t*)overrides, (uint8_t*)actions,
+                                                     (uint8_t*)chosen, (uint32_t)n);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
+template <bool CHANCE, bool WRITE>
+cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                           uint32_t max_steps, void* score2, void* turns, void* steps) {
+  auto k = rollout_kernel<BLOCK, CHANCE, WRITE>;
+  cudaError_t e = allow_smem(k);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, TILE_BYTES);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  // persistent grid: exactly the resident CTAs of the chip (a multiple of the SM count), never more
+  // CTAs than there is work
+  unsigned grid = (unsigned)(ctx->sm_count * per_sm);
+  const unsigned need = grid_for(n);
+  if (grid > need) grid = need;
+  e = cudaMemsetAsync(ctx->ticket, 0, sizeof(uint32_t), ctx->stream);
+  if (e != cudaSuccess) return e;
+  k<<<grid, BLOCK, TILE_BYTES, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
+                                              (const uint64_t*)seeds, max_steps, (uint32_t)n, ctx->ticket,
+                                              (uint8_t*)score2, (uint16_t*)turns, (uint32_t*)steps, ctx->total_steps);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
+  if (!out || n_max == 0 || n_max > 0x7FFFFFFFull) return OAKB200_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || device < 0 || device >= count) return OAKB200_ENODEVICE;
+  oakb200_ctx* ctx = new (std::nothrow) oakb200_ctx();
+  if (!ctx) return OAKB200_ECAPACITY;
+  ctx->device = device;
+  ctx->n_max = n_max;
+  *out = ctx;
+  CU(ctx, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(ctx, cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail(ctx, OAKB200_ENODEVICE, "device is not sm_100 class");
+  ctx->sm_count = prop.multiProcessorCount;
+  CU(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  ctx->own_stream = true;
+  CU(ctx, cudaMalloc(&ctx->battles, n_max * 384));
+  CU(ctx, cudaMalloc(&ctx->durations, n_max * 8));
+  CU(ctx, cudaMalloc(&ctx->results, n_max));
+  CU(ctx, cudaMalloc(&ctx->c1, n_max));
+  CU(ctx, cudaMalloc(&ctx->c2, n_max));
+  CU(ctx, cudaMalloc(&ctx->overrides, n_max * 16));
+  CU(ctx, cudaMalloc(&ctx->actions, n_max * 16));
+  CU(ctx, cudaMalloc(&ctx->choices, n_max * 18));
+  CU(ctx, cudaMalloc(&ctx->counts, n_max * 2));
+  CU(ctx, cudaMalloc(&ctx->seeds, n_max * 8));
+  CU(ctx, cudaMalloc(&ctx->score2, n_max));
+  CU(ctx, cudaMalloc(&ctx->turns, n_max * 2));
+  CU(ctx, cudaMalloc(&ctx->steps, n_max * 4));
+  CU(ctx, cudaMalloc(&ctx->teams, n_max * 60));
+  CU(ctx, cudaMalloc(&ctx->ticket, sizeof(uint32_t)));
+  CU(ctx, cudaMalloc(&ctx->total_steps, sizeof(unsigned long long)));
+  CU(ctx, cudaMemset(ctx->total_steps, 0, sizeof(unsigned long long)));
+  return OAKB200_OK;
+}
+
+void oakb200_destroy(oakb200_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  void* bufs[] = {ctx->battles, ctx->durations, ctx->results, ctx->c1,    ctx->c2,    ctx->overrides, ctx->actions, ctx->choices,
+                  ctx->counts,  ctx->seeds,     ctx->score2,  ctx->turns, ctx->steps, ctx->teams,     ctx->ticket,  ctx->total_steps};
+  for (void* b : bufs)
+    if (b) cudaFree(b);
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* oakb200_last_error(const oakb200_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+int oakb200_device(const oakb200_ctx* ctx) { return ctx ? ctx->device : -1; }
+uint64_t oakb200_launch_count(const oakb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int oakb200_set_stream(oakb200_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return OAKB200_EINVAL;
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+  ctx->stream = (cudaStream_t)cuda_stream;
+  ctx->own_stream = false;
+  return OAKB200_OK;
+}
+
+int oakb200_synchronize(oakb200_ctx* ctx) {
+  if (!ctx) return OAKB200_EINVAL;
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+int oakb200_upload(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results) {
+  if (!ctx || !battles) return fail(ctx, OAKB200_EINVAL, "upload: null argument");
+  if (n > ctx->n_max) return fail(ctx, OAKB200_ECAPACITY, "upload: n exceeds n_max");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ctx->battles, battles, n * 384, cudaMemcpyHostToDevice, ctx->stream));
+  if (durations) {
+    CU(ctx, cudaMemcpyAsync(ctx->durations, durations, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    CU(ctx, cudaMemsetAsync(ctx->durations, 0, n * 8, ctx->stream));
+  }
+  if (results) {
+    CU(ctx, cudaMemcpyAsync(ctx->results, results, n, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    CU(ctx, cudaMemsetAsync(ctx->results, RESULT_DEFAULT, n, ctx->stream));
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->n = n;
+  return OAKB200_OK;
+}
+
+int oakb200_download(oakb200_ctx* ctx, size_t n, uint8_t* battles, uint8_t* durations, uint8_t* results) {
+  if (!ctx) return OAKB200_EINVAL;
+  if (n > ctx->n) return fail(ctx, OAKB200_EINVAL, "download: n exceeds resident count");
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (battles) CU(ctx, cudaMemcpyAsync(battles, ctx->battles, n * 384, cudaMemcpyDeviceToHost, ctx->stream));
+  if (durations) CU(ctx, cudaMemcpyAsync(durations, ctx->durations, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (results) CU(ctx, cudaMemcpyAsync(results, ctx->results, n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+int oakb200_resident(oakb200_ctx* ctx, void** battles, void** durations, void** results, size_t* n) {
+  if (!ctx) return OAKB200_EINVAL;
+  if (battles) *battles = ctx->battles;
+  if (durations) *durations = ctx->durations;
+  if (results) *results = ctx->results;
+  if (n) *n = ctx->n;
+  return OAKB200_OK;
+}
+
+int oakb200_choices_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* results, void* out, void* counts) {
+  if (!ctx || !battles || !results || !out || !counts) return fail(ctx, OAKB200_EINVAL, "choices: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  auto k = choices_kernel<BLOCK>;
+  CU(ctx, allow_smem(k));
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>((const uint8_t*)battles, (const uint8_t*)results, (uint8_t*)out,
+                                                     (uint8_t*)counts, (uint32_t)n);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
+  return OAKB200_OK;
+}
+
+int oakb200_choices(oakb200_ctx* ctx, uint8_t* out, uint8_t* counts) {
+  if (!ctx || !out || !counts) return fail(ctx, OAKB200_EINVAL, "choices: null argument");
+  const size_t n = ctx->n;
+  int rc = oakb200_choices_device(ctx, n, ctx->battles, ctx->results, ctx->choices, ctx->counts);
+  if (rc) return rc;
+  CU(ctx, cudaMemcpyAsync(out, ctx->choices, n * 18, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(counts, ctx->counts, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+int oakb200_step_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
+                        const void* c2, const void* overrides, void* actions_out) {
+  if (!ctx || !battles || !durations || !results || !c1 || !c2) return fail(ctx, OAKB200_EINVAL, "step: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (overrides) {
+    CU(ctx, (launch_step<false, true>(ctx, n, battles, durations, results, c1, c2, nullptr, 0, overrides, actions_out, nullptr)));
+  } else {
+    CU(ctx, (launch_step<false, false>(ctx, n, battles, durations, results, c1, c2, nullptr, 0, nullptr, actions_out, nullptr)));
+  }
+  return OAKB200_OK;
+}
+
+int oakb200_step(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const uint8_t* overrides, uint8_t* results_out,
+                 uint8_t* actions_out) {
+  if (!ctx || !c1 || !c2) return fail(ctx, OAKB200_EINVAL, "step: null argument");
+  const size_t n = ctx->n;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ctx->c1, c1, n, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(ctx->c2, c2, n, cudaMemcpyHostToDevice, ctx->stream));
+  if (overrides) CU(ctx, cudaMemcpyAsync(ctx->overrides, overrides, n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = oakb200_step_device(ctx, n, ctx->battles, ctx->durations, ctx->results, ctx->c1, ctx->c2,
+                               overrides ? ctx->overrides : nullptr, actions_out ? ctx->actions : nullptr);
+  if (rc) return rc;
+  if (results_out) CU(ctx, cudaMemcpyAsync(results_out, ctx->results, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (actions_out) CU(ctx, cudaMemcpyAsync(actions_out, ctx->actions, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+int oakb200_step_random_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                               uint32_t step_index, void* actions_out, void* chosen_out) {
+  if (!ctx || !battles || !durations || !results || !seeds) return fail(ctx, OAKB200_EINVAL, "step_random: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, (launch_step<true, false>(ctx, n, battles, durations, results, nullptr, nullptr, seeds, step_index, nullptr,
+                                    actions_out, chosen_out)));
+  return OAKB200_OK;
+}
+
+int oakb200_rollout_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                           uint32_t max_steps, uint32_t flags, void* score2_out, void* turns_out, void* steps_out) {
+  if (!ctx || !battles || !durations || !results || !seeds) return fail(ctx, OAKB200_EINVAL, "rollout: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  const bool write = (flags & OAKB200_ROLLOUT_WRITE_STATE) != 0;
+  const bool chance = (flags & OAKB200_ROLLOUT_TRACK_CHANCE) != 0;
+  cudaError_t e;
+  if (write) {
+    e = chance ? launch_rollout<true, true>(ctx, n, battles, durations, results, seeds, max_steps, score2_out, turns_out, steps_out)
+               : launch_rollout<false, true>(ctx, n, battles, durations, results, seeds, max_steps, score2_out, turns_out, steps_out);
+  } else {
+    e = chance ? launch_rollout<true, false>(ctx, n, battles, durations, results, seeds, max_steps, score2_out, turns_out, steps_out)
+               : launch_rollout<false, false>(ctx, n, battles, durations, results, seeds, max_steps, score2_out, turns_out, steps_out);
+  }
+  CU(ctx, e);
+  return OAKB200_OK;
+}
+
+int oakb200_rollout(oakb200_ctx* ctx, const uint64_t* seeds, uint32_t max_steps, uint32_t flags, uint8_t* score2_out,
+                    uint16_t* turns_out, uint32_t* steps_out) {
+  if (!ctx || !seeds) return fail(ctx, OAKB200_EINVAL, "rollout: null argument");
+  const size_t n = ctx->n;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ctx->seeds, seeds, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = oakb200_rollout_device(ctx, n, ctx->battles, ctx->durations, ctx->results, ctx->seeds, max_steps, flags,
+                                  ctx->score2, ctx->turns, ctx->steps);
+  if (rc) return rc;
+  if (score2_out) CU(ctx, cudaMemcpyAsync(score2_out, ctx->score2, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (turns_out) CU(ctx, cudaMemcpyAsync(turns_out, ctx->turns, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  if (steps_out) CU(ctx, cudaMemcpyAsync(steps_out, ctx->steps, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+int oakb200_total_steps(oakb200_ctx* ctx, uint64_t* out) {
+  if (!ctx || !out) return OAKB200_EINVAL;
+  CU(ctx, cudaSetDevice(ctx->device));
+  unsigned long long v = 0;
+  CU(ctx, cudaMemcpyAsync(&v, ctx->total_steps, sizeof(v), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  *out = v;
+  return OAKB200_OK;
+}
+
+int oakb200_randomize_hidden_device(oakb200_ctx* ctx, size_t n, void* battles, const void* durations) {
+  if (!ctx || !battles || !durations) return fail(ctx, OAKB200_EINVAL, "randomize_hidden: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  randomize_hidden_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((uint8_t*)battles, (const uint8_t*)durations, (uint32_t)n);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
+  return OAKB200_OK;
+}
+
+int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, const uint64_t* seeds) {
+  if (!ctx || !teams || !seeds) return fail(ctx, OAKB200_EINVAL, "build_battles: null argument");
+  if (n > ctx->n_max) return fail(ctx, OAKB200_ECAPACITY, "build_battles: n exceeds n_max");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(ctx->teams, teams, n * 60, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(ctx->seeds, seeds, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  auto k = build_kernel<BLOCK>;
+  CU(ctx, allow_smem(k));
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>(ctx->teams, ctx->seeds, ctx->battles, ctx->durations, ctx->results, (uint32_t)n);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->n = n;
+  return OAKB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,213 @@
+"""Host-side mirror of the reference's battle interface over the oakb200 C ABI.
+
+Reference interface being mirrored (same argument meaning and error behaviour):
+  PKMN::choices / pkmn_gen1_battle_choices   cpp/include/libpkmn/pkmn.h:141-156, engine pkmn.h:283-288
+  PKMN::update  / pkmn_gen1_battle_update    cpp/include/libpkmn/pkmn.h:106-139, engine pkmn.h:264-268
+  MCTS rollout                                cpp/include/search/mcts.h:448-496
+  PKMN::battle(p1, p2, seed) + update(0, 0)  cpp/include/libpkmn/pkmn.h:50-57, cpp/src/generate.cc:238-240
+Batches are numpy uint8 arrays in the reference's AoS record formats ([n,384] battles, [n,8]
+durations, [n] results), or torch CUDA tensors for the *_device calls.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liboakb200.so")
+
+ROLLOUT_WRITE_STATE = 1
+ROLLOUT_TRACK_CHANCE = 2
+
+_lib = None
+
+
+class OakB200Error(RuntimeError):
+    pass
+
+
+def load_library():
+    """dlopen oak_b200/liboakb200.so (built in-tree by oak_b200.build). Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OakB200Error(f"{LIB_PATH} is missing: run `python -m oak_b200.build` (needs nvcc). "
+                           "oak_b200 has no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, sz, u32, i32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int
+    sig = {
+        "oakb200_create": (i32, [i32, sz, ctypes.POINTER(vp)]),
+        "oakb200_destroy": (None, [vp]),
+        "oakb200_last_error": (ctypes.c_char_p, [vp]),
+        "oakb200_device": (i32, [vp]),
+        "oakb200_set_stream": (i32, [vp, vp]),
+        "oakb200_synchronize": (i32, [vp]),
+        "oakb200_launch_count": (ctypes.c_uint64, [vp]),
+        "oakb200_upload": (i32, [vp, sz, vp, vp, vp]),
+        "oakb200_download": (i32, [vp, sz, vp, vp, vp]),
+        "oakb200_resident": (i32, [vp, ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+        "oakb200_choices": (i32, [vp, vp, vp]),
+        "oakb200_choices_device": (i32, [vp, sz, vp, vp, vp, vp]),
+        "oakb200_step": (i32, [vp, vp, vp, vp, vp, vp]),
+        "oakb200_step_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp]),
+        "oakb200_step_random_device": (i32, [vp, sz, vp, vp, vp, vp, u32, vp, vp]),
+        "oakb200_rollout": (i32, [vp, vp, u32, u32, vp, vp, vp]),
+        "oakb200_rollout_device": (i32, [vp, sz, vp, vp, vp, vp, u32, u32, vp, vp, vp]),
+        "oakb200_total_steps": (i32, [vp, ctypes.POINTER(ctypes.c_uint64)]),
+        "oakb200_randomize_hidden_device": (i32, [vp, sz, vp, vp]),
+        "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _np(a, dtype, shape=None):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    if shape is not None and tuple(a.shape) != tuple(shape):
+        raise ValueError(f"expected shape {shape}, got {a.shape}")
+    return a
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+class BattleEngine:
+    """One context per GPU holding a resident batch of battles (include/oakb200.h)."""
+
+    def __init__(self, n_max, device=0):
+        self.lib = load_library()
+        h = ctypes.c_void_p()
+        rc = self.lib.oakb200_create(int(device), int(n_max), ctypes.byref(h))
+        self._h = h if h.value else None
+        if rc != 0:
+            msg = self.lib.oakb200_last_error(h).decode() if h.value else "no CUDA device (oak_b200 has no CPU fallback)"
+            if h.value:
+                self.lib.oakb200_destroy(h)
+                self._h = None
+            raise OakB200Error(f"oakb200_create failed ({rc}): {msg}")
+        self.n_max = int(n_max)
+        self.n = 0
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.oakb200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise OakB200Error(f"oakb200 error {rc}: {self.lib.oakb200_last_error(self._h).decode()}")
+
+    # ---------------------------------------------------------------- plumbing
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self.lib.oakb200_set_stream(self._h, ctypes.c_void_p(cuda_stream_ptr)))
+
+    def synchronize(self):
+        self._check(self.lib.oakb200_synchronize(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.oakb200_launch_count(self._h))
+
+    def total_steps(self):
+        v = ctypes.c_uint64()
+        self._check(self.lib.oakb200_total_steps(self._h, ctypes.byref(v)))
+        return v.value
+
+    # ---------------------------------------------------------------- resident batch (host arrays)
+    def upload(self, battles, durations=None, results=None):
+        battles = _np(battles, np.uint8)
+        n = battles.shape[0]
+        battles = _np(battles, np.uint8, (n, 384))
+        durations = None if durations is None else _np(durations, np.uint8, (n, 8))
+        results = None if results is None else _np(results, np.uint8, (n,))
+        self._check(self.lib.oakb200_upload(self._h, n, _ptr(battles), _ptr(durations), _ptr(results)))
+        self.n = n
+
+    def download(self):
+        n = self.n
+        b = np.empty((n, 384), np.uint8)
+        d = np.empty((n, 8), np.uint8)
+        r = np.empty((n,), np.uint8)
+        self._check(self.lib.oakb200_download(self._h, n, _ptr(b), _ptr(d), _ptr(r)))
+        return b, d, r
+
+    def build_battles(self, teams, seeds):
+        """teams[n,2,6,5] = {species, move x4}; seeds[n] u64. PKMN::battle + update(0,0) on the device."""
+        teams = _np(teams, np.uint8)
+        n = teams.shape[0]
+        teams = _np(teams, np.uint8, (n, 2, 6, 5))
+        seeds = _np(seeds, np.uint64, (n,))
+        self._check(self.lib.oakb200_build_battles(self._h, n, _ptr(teams), _ptr(seeds)))
+        self.n = n
+
+    def choices(self):
+        """-> (choices[n,2,9] u8, counts[n,2] u8): pkmn_gen1_battle_choices for both players."""
+        out = np.empty((self.n, 2, 9), np.uint8)
+        cnt = np.empty((self.n, 2), np.uint8)
+        self._check(self.lib.oakb200_choices(self._h, _ptr(out), _ptr(cnt)))
+        return out, cnt
+
+    def update(self, c1, c2, overrides=None, want_actions=False):
+        """options_set(null[, calc overrides]) + pkmn_gen1_battle_update for every resident battle."""
+        n = self.n
+        c1 = _np(c1, np.uint8, (n,))
+        c2 = _np(c2, np.uint8, (n,))
+        overrides = None if overrides is None else _np(overrides, np.uint8, (n, 16))
+        res = np.empty((n,), np.uint8)
+        act = np.empty((n, 16), np.uint8) if want_actions else None
+        self._check(self.lib.oakb200_step(self._h, _ptr(c1), _ptr(c2), _ptr(overrides), _ptr(res), _ptr(act)))
+        return (res, act) if want_actions else res
+
+    def rollout(self, seeds, max_steps=100000, write_state=False, track_chance=False):
+        """Random playouts to a terminal result -> (score2[n] u8, turns[n] u16, steps[n] u32)."""
+        n = self.n
+        seeds = _np(seeds, np.uint64, (n,))
+        score = np.empty((n,), np.uint8)
+        turns = np.empty((n,), np.uint16)
+        steps = np.empty((n,), np.uint32)
+        flags = (ROLLOUT_WRITE_STATE if write_state else 0) | (ROLLOUT_TRACK_CHANCE if track_chance else 0)
+        self._check(self.lib.oakb200_rollout(self._h, _ptr(seeds), int(max_steps), flags, _ptr(score), _ptr(turns), _ptr(steps)))
+        return score, turns, steps
+
+    # ---------------------------------------------------------------- device-pointer calls (torch CUDA tensors)
+    def resident(self):
+        b, d, r, n = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_size_t()
+        self._check(self.lib.oakb200_resident(self._h, ctypes.byref(b), ctypes.byref(d), ctypes.byref(r), ctypes.byref(n)))
+        return b.value, d.value, r.value, n.value
+
+    def choices_device(self, battles, results, out, counts):
+        self._check(self.lib.oakb200_choices_device(self._h, battles.shape[0], _ptr(battles), _ptr(results), _ptr(out), _ptr(counts)))
+
+    def step_device(self, battles, durations, results, c1, c2, overrides=None, actions_out=None):
+        self._check(self.lib.oakb200_step_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                 _ptr(c1), _ptr(c2), _ptr(overrides), _ptr(actions_out)))
+
+    def step_random_device(self, battles, durations, results, seeds, step_index, actions_out=None, chosen_out=None):
+        self._check(self.lib.oakb200_step_random_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                        _ptr(seeds), int(step_index), _ptr(actions_out), _ptr(chosen_out)))
+
+    def rollout_device(self, battles, durations, results, seeds, max_steps=100000, flags=0, score2_out=None, turns_out=None,
+                       steps_out=None):
+        self._check(self.lib.oakb200_rollout_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                    _ptr(seeds), int(max_steps), int(flags), _ptr(score2_out), _ptr(turns_out),
+                                                    _ptr(steps_out)))
+
+    def randomize_hidden_device(self, battles, durations):
+        self._check(self.lib.oakb200_randomize_hidden_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations)))

@@ -1,4 +1,8 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see gen1_oracle.hpp). C entry points for ctypes.
+#include <atomic>
+#include <thread>
+#include <vector>
+
 #include "gen1_oracle.hpp"
 #include "oak_oracle.hpp"
 
@@ -67,5 +71,53 @@ void oracle_oak_rollout(uint8_t* battle, uint8_t* durations, uint8_t* result, ui
 }
 void oracle_oak_randomize_hidden(uint8_t* battle, const uint8_t* durations) {
   oak_randomize_hidden_variables(*reinterpret_cast<Battle*>(battle), durations);
+}
+
+// Batch of random playouts on `threads` host threads (one battle stream per std::thread, as the
+// reference's generate.cc:527-530 does). battles/durations/results are [n][384]/[n][8]/[n] AoS and are
+// advanced in place to their terminal state. Used as the checker at full size and as the timed CPU
+// baseline (bench.py cpu_baseline / --impl reference).
+void oracle_oak_rollout_batch(uint8_t* battles, uint8_t* durations, uint8_t* results, const uint64_t* seeds, size_t n,
+                              uint32_t max_steps, int threads, uint8_t* score2, uint16_t* turns, uint32_t* steps) {
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const size_t i0 = next.fetch_add(256);
+      if (i0 >= n) return;
+      const size_t i1 = i0 + 256 < n ? i0 + 256 : n;
+      for (size_t i = i0; i < i1; i++) {
+        Battle& b = *reinterpret_cast<Battle*>(battles + i * 384);
+        const uint32_t st = oak_rollout(b, durations + i * 8, results + i, seeds[i], max_steps);
+        const uint8_t t = results[i] & 15;
+        if (score2) score2[i] = t == RES_WIN ? 2 : (t == RES_TIE ? 1 : (t == RES_LOSE ? 0 : 255));
+        if (turns) turns[i] = b.turn;
+        if (steps) steps[i] = st;
+      }
+    }
+  };
+  if (threads <= 1) {
+    work();
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++) pool.emplace_back(work);
+  for (auto& t : pool) t.join();
+}
+
+// Synthetic battles first..first+n built on `threads` host threads.
+void oracle_oak_sample_batch(uint64_t first, size_t n, int threads, uint8_t* battles, uint8_t* durations, uint8_t* results) {
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const size_t i0 = next.fetch_add(1024);
+      if (i0 >= n) return;
+      const size_t i1 = i0 + 1024 < n ? i0 + 1024 : n;
+      for (size_t i = i0; i < i1; i++)
+        oak_sample_battle(first + i, *reinterpret_cast<Battle*>(battles + i * 384), durations + i * 8, results + i);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < (threads < 1 ? 1 : threads); t++) pool.emplace_back(work);
+  for (auto& t : pool) t.join();
 }
 }

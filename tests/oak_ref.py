@@ -121,3 +121,44 @@ class HostShim:
 
     def update_nochance(self, battle, c1, c2):
         return int(self.lib.shim_update_nochance(battle.ctypes.data, c1, c2))
+
+
+def oracle_rollout_batch(orc, battles, durations, results, seeds, max_steps=100000, threads=None):
+    """In-place terminal playouts of a whole batch on the host. -> (score2, turns, steps)."""
+    n = battles.shape[0]
+    threads = threads or os.cpu_count() or 1
+    score = np.empty(n, np.uint8)
+    turns = np.empty(n, np.uint16)
+    steps = np.empty(n, np.uint32)
+    f = orc.lib.oracle_oak_rollout_batch
+    f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int] + [ctypes.c_void_p] * 3
+    f.restype = None
+    f(battles.ctypes.data, durations.ctypes.data, results.ctypes.data, seeds.ctypes.data, n, max_steps, threads,
+      score.ctypes.data, turns.ctypes.data, steps.ctypes.data)
+    return score, turns, steps
+
+
+def oracle_sample_batch(orc, first, n, threads=None):
+    threads = threads or os.cpu_count() or 1
+    b = np.empty((n, 384), np.uint8)
+    d = np.empty((n, 8), np.uint8)
+    r = np.empty((n,), np.uint8)
+    f = orc.lib.oracle_oak_sample_batch
+    f.argtypes = [ctypes.c_uint64, ctypes.c_size_t, ctypes.c_int] + [ctypes.c_void_p] * 3
+    f.restype = None
+    f(first, n, threads, b.ctypes.data, d.ctypes.data, r.ctypes.data)
+    return b, d, r
+
+
+def sample_seeds(first, n):
+    i = np.arange(first + 1, first + n + 1, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        return i * np.uint64(0x9E3779B97F4A7C15)
+
+
+def sample_teams(first, n):
+    """teams[n,2,6,5] for synthetic battles first..first+n: teams[i & 15] vs teams[(i >> 4) & 15]."""
+    import json
+    t = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    i = np.arange(first, first + n)
+    return np.stack([t[i & 15], t[(i >> 4) & 15]], axis=1)
