@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(BLOCK) build_kernel(const uint8_t* __restrict_
   uint32_t* col = tile + threadIdx.x;
   for (int w = 0; w < BATTLE_WORDS; w++) col[w * BLOCK] = 0;
   Mem<BLOCK> m;
-  m.base = reinterpret_cast<uint8_t*>(col);
+  m.set(reinterpret_cast<uint8_t*>(col));
   const uint8_t* t = teams + (size_t)i * 60;
   for (int s = 0; s < 2; s++) {
     for (int k = 0; k < 6; k++) {

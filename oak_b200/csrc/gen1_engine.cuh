@@ -15,26 +15,9 @@
 //   * legal choices are packed 5 bits each into one 64-bit register (no per-thread arrays).
 #pragma once
 
-#include "gen1_state.cuh"
+#include "gen1_mem_ops.cuh"
 
 namespace oakb200 {
-
-// volatile flag masks on the LOW word of the packed u64 (bits 0..17), fields confusion/attacks
-enum : uint32_t {
-  VL_BIDE = 1u << 0, VL_THRASHING = 1u << 1, VL_MULTIHIT = 1u << 2, VL_FLINCH = 1u << 3, VL_CHARGING = 1u << 4,
-  VL_BINDING = 1u << 5, VL_INVULNERABLE = 1u << 6, VL_CONFUSION = 1u << 7, VL_MIST = 1u << 8,
-  VL_FOCUS_ENERGY = 1u << 9, VL_SUBSTITUTE = 1u << 10, VL_RECHARGING = 1u << 11, VL_RAGE = 1u << 12,
-  VL_LEECH_SEED = 1u << 13, VL_TOXIC = 1u << 14, VL_LIGHT_SCREEN = 1u << 15, VL_REFLECT = 1u << 16,
-  VL_TRANSFORM = 1u << 17,
-};
-// (shift, width) of fields inside the low / high volatile words
-#define VLO_CONFUSION 18, 3
-#define VLO_ATTACKS 21, 3
-#define VHI_SUBSTITUTE 8, 8
-#define VHI_TRANSFORM 16, 4
-#define VHI_DISABLE_DURATION 20, 4
-#define VHI_DISABLE_MOVE 24, 3
-#define VHI_TOXIC 27, 5
 
 enum { OBSF_SLEEP = 0, OBSF_CONFUSION, OBSF_DISABLE, OBSF_ATTACKING, OBSF_BINDING };
 enum { BM_DONE = 0, BM_SKIP_CAN, BM_SKIP_PP, BM_OK, BM_ERR };
@@ -51,7 +34,7 @@ struct Engine {
 
   // ---------------------------------------------------------------- load / store of register copies
   OAK_HD void begin(uint8_t* column_base, uint32_t d0, uint32_t d1) {
-    m.base = column_base;
+    m.set(column_base);
     rng = m.ld64(B_RNG);
     last_damage = m.ld16(B_LAST_DAMAGE);
     act[0] = act[1] = 0;
@@ -64,32 +47,49 @@ struct Engine {
     m.st16(B_LAST_DAMAGE, last_damage);
   }
 
-  // ---------------------------------------------------------------- field helpers
-  static OAK_HD int sb(int p) { return p * SIDE_SIZE; }
-  OAK_HD int stored(int p) const { return sb(p) + ((int)m.ld8(sb(p) + S_ORDER) - 1) * PK_SIZE; }
-  OAK_HD uint32_t vlo(int p) const { return m.ld32(sb(p) + A_VOL); }
-  OAK_HD void set_vlo(int p, uint32_t v) const { m.st32(sb(p) + A_VOL, v); }
-  OAK_HD uint32_t vhi(int p) const { return m.ld32(sb(p) + A_VOL + 4); }
-  OAK_HD void set_vhi(int p, uint32_t v) const { m.st32(sb(p) + A_VOL + 4, v); }
-  OAK_HD bool vflag(int p, uint32_t mask) const { return (vlo(p) & mask) != 0; }
-  OAK_HD void vclear(int p, uint32_t mask) const { set_vlo(p, vlo(p) & ~mask); }
-  OAK_HD void vraise(int p, uint32_t mask) const { set_vlo(p, vlo(p) | mask); }
-  OAK_HD uint32_t vlo_field(int p, int shift, int bits) const { return bf_get(vlo(p), shift, bits); }
-  OAK_HD void set_vlo_field(int p, int shift, int bits, uint32_t x) const { set_vlo(p, bf_set(vlo(p), shift, bits, x)); }
-  OAK_HD uint32_t vhi_field(int p, int shift, int bits) const { return bf_get(vhi(p), shift, bits); }
-  OAK_HD void set_vhi_field(int p, int shift, int bits, uint32_t x) const { set_vhi(p, bf_set(vhi(p), shift, bits, x)); }
-  OAK_HD uint32_t vstate(int p) const { return (vlo(p) >> 24) | ((vhi(p) & 255u) << 8); }
-  OAK_HD void set_vstate(int p, uint32_t s) const {
-    set_vlo(p, (vlo(p) & 0x00FFFFFFu) | (s << 24));
-    set_vhi(p, (vhi(p) & ~255u) | ((s >> 8) & 255u));
+  // ---------------------------------------------------------------- field helpers (forward to Mem)
+  static OAK_HD H sb(int p) { return Mem<STRIDE>::sb(p); }
+  static OAK_HD H pokemon(int p, int idx) { return Mem<STRIDE>::pokemon(p, idx); }
+  OAK_HD H stored(int p) const { return m.stored(p); }
+  OAK_HD uint32_t vlo(int p) const { return m.vlo(p); }
+  OAK_HD void set_vlo(int p, uint32_t v) const { m.set_vlo(p, v); }
+  OAK_HD uint32_t vhi(int p) const { return m.vhi(p); }
+  OAK_HD void set_vhi(int p, uint32_t v) const { m.set_vhi(p, v); }
+  OAK_HD bool vflag(int p, uint32_t mask) const { return m.vflag(p, mask); }
+  OAK_HD void vclear(int p, uint32_t mask) const { m.vclear(p, mask); }
+  OAK_HD void vraise(int p, uint32_t mask) const { m.vraise(p, mask); }
+  OAK_HD uint32_t vlo_field(int p, int shift, int bits) const { return m.vlo_field(p, shift, bits); }
+  OAK_HD void set_vlo_field(int p, int shift, int bits, uint32_t x) const { m.set_vlo_field(p, shift, bits, x); }
+  OAK_HD uint32_t vhi_field(int p, int shift, int bits) const { return m.vhi_field(p, shift, bits); }
+  OAK_HD void set_vhi_field(int p, int shift, int bits, uint32_t x) const { m.set_vhi_field(p, shift, bits, x); }
+  OAK_HD uint32_t vstate(int p) const { return m.vstate(p); }
+  OAK_HD void set_vstate(int p, uint32_t s) const { m.set_vstate(p, s); }
+  OAK_HD uint32_t status_of(H pk) const { return m.status_of(pk); }
+  OAK_HD uint32_t hp_of(H pk) const { return m.hp_of(pk); }
+  OAK_HD uint32_t last_selected(int p) const { return m.last_selected(p); }
+  OAK_HD uint32_t active_types(int p) const { return m.active_types(p); }
+  OAK_HD uint32_t active_stat(int p, int st) const { return m.active_stat(p, st); }
+  OAK_HD void set_active_stat(int p, int st, uint32_t v) const { m.set_active_stat(p, st, v); }
+  // applyDamage through the shared routine; returns true when a Substitute broke
+  OAK_HD bool applyDamage(int t, int subp) {
+    const uint32_t r = mem_apply_damage(m, t, subp, last_damage);
+    last_damage = r & 0x7FFFFFFFu;
+    return (r >> 31) != 0;
   }
-  OAK_HD uint32_t status_of(int pk) const { return m.ld8(pk + PK_STATUS); }
-  OAK_HD uint32_t hp_of(int pk) const { return m.ld16(pk + PK_HP); }
-  OAK_HD uint32_t last_selected(int p) const { return m.ld8(sb(p) + S_LAST_SELECTED); }
-  OAK_HD uint32_t active_types(int p) const { return m.ld8(sb(p) + A_TYPES); }
-  OAK_HD uint32_t active_stat(int p, int st) const { return m.ld16(sb(p) + A_STATS + st); }
-  OAK_HD void set_active_stat(int p, int st, uint32_t v) const { m.st16(sb(p) + A_STATS + st, v); }
-  OAK_HD uint32_t ident(int p) const { return ((uint32_t)p << 3) | m.ld8(sb(p) + S_ORDER); }
+  OAK_HD void buildRage(int who) { mem_build_rage(m, who); }
+  // applyDamage to the foe with the current last_damage + Rage build-up unless a Substitute took it
+  OAK_HD void hitFoeWithLastDamage(int p) {
+    const int f = p ^ 1;
+    const bool sub = vflag(f, VL_SUBSTITUTE);
+    applyDamage(f, f);
+    if (hp_of(stored(f)) > 0 && !sub) buildRage(f);
+  }
+  OAK_HD uint64_t choices(int p, int request, int* n) const {
+    const uint64_t l = mem_choices(m, p, request);
+    *n = choice_count(l);
+    return l;
+  }
+  static OAK_HD uint32_t choice_at(uint64_t list, int i) { return oakb200::choice_at(list, i); }
 
   // ---------------------------------------------------------------- PRNG (rng.zig:34-59,149-164)
   OAK_HD uint32_t next() {
@@ -240,21 +240,21 @@ struct Engine {
     }
     return n;
   }
-  // moves_off: byte offset of a 4 x {id, pp} array
-  OAK_HD uint32_t roll_moveSlot(int p, int moves_off, uint32_t check_pp) {
+  // moves_off: handle of a (word-aligned) 4 x {id, pp} array
+  OAK_HD uint32_t roll_moveSlot(int p, H moves_off, uint32_t check_pp) {
     const uint32_t ov = overridden(p, AF_MOVE_SLOT);
     uint32_t slot = 0;
-    if (ov && m.ld8(moves_off + 2 * (ov - 1)) != MOVE_None && (check_pp == 0 || m.ld8(moves_off + 2 * (ov - 1) + 1) > 0)) {
+    if (ov && m.ld8(moves_off, 2 * (ov - 1)) != MOVE_None && (check_pp == 0 || m.ld8(moves_off, 2 * (ov - 1) + 1) > 0)) {
       slot = ov;
     } else if (check_pp == 0) {
       int last = 0;
       for (int i = 0; i < 4; i++)
-        if (m.ld8(moves_off + 2 * i) != MOVE_None) last = i + 1;
+        if (m.ld8(moves_off, 2 * i) != MOVE_None) last = i + 1;
       if (last) slot = range(0, (uint32_t)last) + 1;
     } else {
       uint32_t r = range(0, check_pp) + 1;
       for (int i = 0; i < 4; i++) {
-        if (r > 0 && m.ld8(moves_off + 2 * i + 1) > 0) {
+        if (r > 0 && m.ld8(moves_off, 2 * i + 1) > 0) {
           r--;
           if (r == 0) slot = (uint32_t)i + 1;
         }

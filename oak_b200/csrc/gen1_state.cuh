@@ -159,23 +159,114 @@ OAK_HD uint32_t boost_den(int stage) {
   return stage < 0 ? 100u : ((stage & 1) ? 10u : 1u);
 }
 
+// volatile flag masks on the LOW word of the packed u64 (bits 0..17), fields confusion/attacks
+enum : uint32_t {
+  VL_BIDE = 1u << 0, VL_THRASHING = 1u << 1, VL_MULTIHIT = 1u << 2, VL_FLINCH = 1u << 3, VL_CHARGING = 1u << 4,
+  VL_BINDING = 1u << 5, VL_INVULNERABLE = 1u << 6, VL_CONFUSION = 1u << 7, VL_MIST = 1u << 8,
+  VL_FOCUS_ENERGY = 1u << 9, VL_SUBSTITUTE = 1u << 10, VL_RECHARGING = 1u << 11, VL_RAGE = 1u << 12,
+  VL_LEECH_SEED = 1u << 13, VL_TOXIC = 1u << 14, VL_LIGHT_SCREEN = 1u << 15, VL_REFLECT = 1u << 16,
+  VL_TRANSFORM = 1u << 17,
+};
+// (shift, width) of fields inside the low / high volatile words
+#define VLO_CONFUSION 18, 3
+#define VLO_ATTACKS 21, 3
+#define VHI_SUBSTITUTE 8, 8
+#define VHI_TRANSFORM 16, 4
+#define VHI_DISABLE_DURATION 20, 4
+#define VHI_DISABLE_MOVE 24, 3
+#define VHI_TOXIC 27, 5
+
 // ---- the per-battle memory window
+// H is a WORD-ALIGNED position inside the battle record, already scaled to column addressing
+// (word index * STRIDE * 4). Fields are then addressed as (H, constant byte offset): the offset folds
+// into the load/store immediate, so a field access costs one LDS/STS and no address arithmetic.
+// (The first B200 build addressed everything by runtime byte offset and spent ~40% of its
+// instructions on shift/mask/multiply address math.)
+struct H {
+  int v;
+};
+
 template <int STRIDE>
 struct Mem {
-  uint8_t* base;  // address of byte 0 of word 0 of this battle's column
+  static const int W = STRIDE * 4;
+  static OAK_HD int enc(int off) { return (off >> 2) * W + (off & 3); }
 
-  OAK_HD uint8_t* at(int off) const { return base + (size_t)(off >> 2) * (STRIDE * 4) + (off & 3); }
-  OAK_HD uint32_t ld8(int off) const { return *at(off); }
-  OAK_HD void st8(int off, uint32_t v) const { *at(off) = (uint8_t)v; }
-  OAK_HD uint32_t ld16(int off) const { return *reinterpret_cast<const uint16_t*>(at(off)); }
-  OAK_HD void st16(int off, uint32_t v) const { *reinterpret_cast<uint16_t*>(at(off)) = (uint16_t)v; }
-  OAK_HD uint32_t ld32(int off) const { return *reinterpret_cast<const uint32_t*>(at(off)); }
-  OAK_HD void st32(int off, uint32_t v) const { *reinterpret_cast<uint32_t*>(at(off)) = v; }
+#ifdef __CUDA_ARCH__
+  // Device: the column lives in shared memory; keep its 32-bit shared-window address and issue
+  // explicit ld.shared / st.shared so that non-inlined routines (which cannot see where the pointer
+  // came from) still get LDS/STS with the field offset folded in, never generic LD/ST.
+  uint32_t sbase;
+  OAK_HD void set(uint8_t* column) { sbase = (uint32_t)__cvta_generic_to_shared(column); }
+  OAK_HD uint32_t ld8a(uint32_t a) const { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+  OAK_HD uint32_t ld16a(uint32_t a) const { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+  OAK_HD uint32_t ld32a(uint32_t a) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+  OAK_HD void st8a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+  OAK_HD void st16a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+  OAK_HD void st32a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+  OAK_HD uint32_t at(int off) const { return sbase + (uint32_t)enc(off); }
+  OAK_HD uint32_t at(H h, int off) const { return sbase + (uint32_t)(h.v + enc(off)); }
+#else
+  uint8_t* base;  // host (tests only): address of byte 0 of word 0 of this battle's column
+  OAK_HD void set(uint8_t* column) { base = column; }
+  OAK_HD uint32_t ld8a(uint8_t* a) const { return *a; }
+  OAK_HD uint32_t ld16a(uint8_t* a) const { return *reinterpret_cast<const uint16_t*>(a); }
+  OAK_HD uint32_t ld32a(uint8_t* a) const { return *reinterpret_cast<const uint32_t*>(a); }
+  OAK_HD void st8a(uint8_t* a, uint32_t v) const { *a = (uint8_t)v; }
+  OAK_HD void st16a(uint8_t* a, uint32_t v) const { *reinterpret_cast<uint16_t*>(a) = (uint16_t)v; }
+  OAK_HD void st32a(uint8_t* a, uint32_t v) const { *reinterpret_cast<uint32_t*>(a) = v; }
+  OAK_HD uint8_t* at(int off) const { return base + enc(off); }
+  OAK_HD uint8_t* at(H h, int off) const { return base + (h.v + enc(off)); }
+#endif
+  // raw byte offset from the start of the battle (battle-level fields, cold paths)
+  OAK_HD uint32_t ld8(int off) const { return ld8a(at(off)); }
+  OAK_HD void st8(int off, uint32_t v) const { st8a(at(off), v); }
+  OAK_HD uint32_t ld16(int off) const { return ld16a(at(off)); }
+  OAK_HD void st16(int off, uint32_t v) const { st16a(at(off), v); }
+  OAK_HD uint32_t ld32(int off) const { return ld32a(at(off)); }
+  OAK_HD void st32(int off, uint32_t v) const { st32a(at(off), v); }
   OAK_HD uint64_t ld64(int off) const { return (uint64_t)ld32(off) | ((uint64_t)ld32(off + 4) << 32); }
   OAK_HD void st64(int off, uint64_t v) const {
     st32(off, (uint32_t)v);
     st32(off + 4, (uint32_t)(v >> 32));
   }
+  // (aligned handle, byte offset) addressing
+  OAK_HD uint32_t ld8(H h, int off) const { return ld8a(at(h, off)); }
+  OAK_HD void st8(H h, int off, uint32_t v) const { st8a(at(h, off), v); }
+  OAK_HD uint32_t ld16(H h, int off) const { return ld16a(at(h, off)); }
+  OAK_HD void st16(H h, int off, uint32_t v) const { st16a(at(h, off), v); }
+  OAK_HD uint32_t ld32(H h, int off) const { return ld32a(at(h, off)); }
+  OAK_HD void st32(H h, int off, uint32_t v) const { st32a(at(h, off), v); }
+
+  // ---- handles
+  static OAK_HD H sb(int p) { return H{p * ((SIDE_SIZE / 4) * W)}; }                       // side p
+  static OAK_HD H pokemon(int p, int idx) { return H{p * ((SIDE_SIZE / 4) * W) + idx * ((PK_SIZE / 4) * W)}; }  // party index 0..5
+  static OAK_HD H hadd(H h, int aligned_off) { return H{h.v + (aligned_off >> 2) * W}; }   // + word-aligned byte offset
+  OAK_HD H stored(int p) const { return pokemon(p, (int)ld8(sb(p), S_ORDER) - 1); }
+
+  // ---- field helpers
+  OAK_HD uint32_t vlo(int p) const { return ld32(sb(p), A_VOL); }
+  OAK_HD void set_vlo(int p, uint32_t v) const { st32(sb(p), A_VOL, v); }
+  OAK_HD uint32_t vhi(int p) const { return ld32(sb(p), A_VOL + 4); }
+  OAK_HD void set_vhi(int p, uint32_t v) const { st32(sb(p), A_VOL + 4, v); }
+  OAK_HD bool vflag(int p, uint32_t mask) const { return (vlo(p) & mask) != 0; }
+  OAK_HD void vclear(int p, uint32_t mask) const { set_vlo(p, vlo(p) & ~mask); }
+  OAK_HD void vraise(int p, uint32_t mask) const { set_vlo(p, vlo(p) | mask); }
+  OAK_HD uint32_t vlo_field(int p, int shift, int bits) const { return bf_get(vlo(p), shift, bits); }
+  OAK_HD void set_vlo_field(int p, int shift, int bits, uint32_t x) const { set_vlo(p, bf_set(vlo(p), shift, bits, x)); }
+  OAK_HD uint32_t vhi_field(int p, int shift, int bits) const { return bf_get(vhi(p), shift, bits); }
+  OAK_HD void set_vhi_field(int p, int shift, int bits, uint32_t x) const { set_vhi(p, bf_set(vhi(p), shift, bits, x)); }
+  OAK_HD uint32_t vstate(int p) const { return (vlo(p) >> 24) | ((vhi(p) & 255u) << 8); }
+  OAK_HD void set_vstate(int p, uint32_t s) const {
+    set_vlo(p, (vlo(p) & 0x00FFFFFFu) | (s << 24));
+    set_vhi(p, (vhi(p) & ~255u) | ((s >> 8) & 255u));
+  }
+  OAK_HD uint32_t status_of(H pk) const { return ld8(pk, PK_STATUS); }
+  OAK_HD uint32_t hp_of(H pk) const { return ld16(pk, PK_HP); }
+  OAK_HD uint32_t last_selected(int p) const { return ld8(sb(p), S_LAST_SELECTED); }
+  OAK_HD uint32_t active_types(int p) const { return ld8(sb(p), A_TYPES); }
+  OAK_HD uint32_t active_stat(int p, int st) const { return ld16(sb(p), A_STATS + st); }
+  OAK_HD void set_active_stat(int p, int st, uint32_t v) const { st16(sb(p), A_STATS + st, v); }
+  OAK_HD uint32_t ident(int p) const { return ((uint32_t)p << 3) | ld8(sb(p), S_ORDER); }
 };
 
 }  // namespace oakb200

@@ -31,10 +31,11 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise OakB200Error(f"{LIB_PATH} is missing: run `python -m oak_b200.build` (needs nvcc). "
+    path = os.environ.get("OAKB200_LIB", LIB_PATH)
+    if not os.path.exists(path):
+        raise OakB200Error(f"{path} is missing: run `python -m oak_b200.build` (needs nvcc). "
                            "oak_b200 has no CPU fallback.")
-    lib = ctypes.CDLL(LIB_PATH)
+    lib = ctypes.CDLL(path)
     vp, sz, u32, i32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int
     sig = {
         "oakb200_create": (i32, [i32, sz, ctypes.POINTER(vp)]),

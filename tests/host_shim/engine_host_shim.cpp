@@ -1,21 +1,38 @@
 // TEST-ONLY: compiles the CUDA engine source (oak_b200/csrc/gen1_engine.cuh) with the host compiler
-// (STRIDE = 1 over a plain 384-byte record) so that it can be differential-tested against the oracle
-// in the GPU-less build container. Nothing in the product links this.
+// so that it can be differential-tested against the oracle in the GPU-less build container. The
+// record is scattered with STRIDE = 3 words (a 3-thread "column tile" of which we use column 1), so
+// the column addressing (word handles + folded byte offsets) is exercised exactly as on the GPU.
+// Nothing in the product links this.
 #include <cstring>
 
 #include "../../oak_b200/csrc/gen1_engine.cuh"
 
 using namespace oakb200;
 
+static const int ST = 3;
+struct Tile {
+  uint32_t w[96 * ST];
+  explicit Tile(const uint8_t* battle) {
+    memset(w, 0xAB, sizeof(w));
+    for (int i = 0; i < 96; i++) memcpy(&w[i * ST + 1], battle + 4 * i, 4);
+  }
+  void store(uint8_t* battle) const {
+    for (int i = 0; i < 96; i++) memcpy(battle + 4 * i, &w[i * ST + 1], 4);
+  }
+  uint8_t* column() { return reinterpret_cast<uint8_t*>(&w[1]); }
+};
+
 template <bool CALC, bool CHANCE>
 static uint8_t run_update(uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, uint8_t* actions, const uint8_t* overrides) {
-  Engine<1, CALC, CHANCE> e;
+  Engine<ST, CALC, CHANCE> e;
+  Tile tile(battle);
   uint32_t d[2];
   memcpy(d, durations, 8);
-  e.begin(battle, d[0], d[1]);
+  e.begin(tile.column(), d[0], d[1]);
   if (CALC && overrides) memcpy(e.ovr, overrides, 16);
   const uint32_t r = e.update(c1, c2);
   e.end();
+  tile.store(battle);
   d[0] = e.dur[0];
   d[1] = e.dur[1];
   memcpy(durations, d, 8);
@@ -33,12 +50,13 @@ uint8_t shim_update_nochance(uint8_t* battle, uint8_t c1, uint8_t c2) {
   return run_update<false, false>(battle, c1, c2, d, nullptr, nullptr);
 }
 uint8_t shim_choices(const uint8_t* battle, int player, int request, uint8_t* out) {
-  Engine<1, false, true> e;
-  e.begin(const_cast<uint8_t*>(battle), 0, 0);
+  Engine<ST, false, true> e;
+  Tile tile(battle);
+  e.begin(tile.column(), 0, 0);
   int n;
   const uint64_t list = e.choices(player, request, &n);
   for (int i = 0; i < n; i++) {
-    const uint32_t c = Engine<1, false, true>::choice_at(list, i);
+    const uint32_t c = Engine<ST, false, true>::choice_at(list, i);
     out[i] = (uint8_t)(((c >> 2) << 2) | (c & 3));
   }
   return (uint8_t)n;
