@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -83,10 +84,13 @@ template <bool CHANCE, bool WRITE>
 cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
                            uint32_t max_steps, void* score2, void* turns, void* steps) {
   auto k = rollout_kernel<BLOCK, CHANCE, WRITE>;
-  cudaError_t e = allow_smem(k);
+  // tuning/diagnostic knob: pad the dynamic shared memory to lower the resident CTAs per SM
+  size_t tile_bytes = TILE_BYTES;
+  if (const char* pad = getenv("OAKB200_ROLLOUT_SMEM_PAD")) tile_bytes += (size_t)atol(pad);
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, TILE_BYTES);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, tile_bytes);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   // persistent grid: exactly the resident CTAs of the chip (a multiple of the SM count), never more
@@ -96,7 +100,7 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
   if (grid > need) grid = need;
   e = cudaMemsetAsync(ctx->ticket, 0, sizeof(uint32_t), ctx->stream);
   if (e != cudaSuccess) return e;
-  k<<<grid, BLOCK, TILE_BYTES, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
+  k<<<grid, BLOCK, tile_bytes, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
                                               (const uint64_t*)seeds, max_steps, (uint32_t)n, ctx->ticket,
                                               (uint8_t*)score2, (uint16_t*)turns, (uint32_t*)steps, ctx->total_steps);
   ctx->launches++;
