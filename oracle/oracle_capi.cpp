@@ -5,6 +5,7 @@
 
 #include "gen1_oracle.hpp"
 #include "oak_oracle.hpp"
+#include "nn_oracle.hpp"
 
 using namespace oracle;
 
@@ -114,6 +115,94 @@ void oracle_oak_sample_batch(uint64_t first, size_t n, int threads, uint8_t* bat
       const size_t i1 = i0 + 1024 < n ? i0 + 1024 : n;
       for (size_t i = i0; i < i1; i++)
         oak_sample_battle(first + i, *reinterpret_cast<Battle*>(battles + i * 384), durations + i * 8, results + i);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < (threads < 1 ? 1 : threads); t++) pool.emplace_back(work);
+  for (auto& t : pool) t.join();
+}
+
+// ---- leaf evaluation (nn_oracle.hpp)
+uint32_t oracle_enc_pokemon_sparse(const uint8_t* pokemon24, uint8_t sleep, float* values, uint16_t* indices) {
+  Pokemon p;
+  memcpy(&p, pokemon24, 24);
+  Sparse sp;
+  uint16_t off = 0;
+  enc_pokemon(p, sleep, sp, off);
+  memcpy(values, sp.v, sp.n * 4);
+  memcpy(indices, sp.i, sp.n * 2);
+  return sp.n;
+}
+uint32_t oracle_enc_active_pokemon_sparse(const uint8_t* pokemon24, const uint8_t* active32, uint32_t duration, float* values,
+                                          uint16_t* indices) {
+  Pokemon p;
+  Active a;
+  memcpy(&p, pokemon24, 24);
+  memcpy(&a, active32, 32);
+  Sparse sp;
+  enc_active_pokemon(p, a, duration, sp);
+  memcpy(values, sp.v, sp.n * 4);
+  memcpy(indices, sp.i, sp.n * 2);
+  return sp.n;
+}
+uint8_t oracle_pokemon_key(const uint8_t* pokemon24, uint8_t sleep) {
+  Pokemon p;
+  memcpy(&p, pokemon24, 24);
+  return pokemon_key(p, sleep);
+}
+uint16_t oracle_policy_index(const uint8_t* side184, uint8_t choice) {
+  Side s;
+  memcpy(&s, side184, 184);
+  return policy_index(s, choice);
+}
+void* oracle_net_create(const uint8_t* data, size_t len) {
+  BattleNet* n = new BattleNet();
+  if (!n->load(data, len)) {
+    delete n;
+    return nullptr;
+  }
+  return n;
+}
+void oracle_net_destroy(void* h) { delete static_cast<BattleNet*>(h); }
+void oracle_net_dims(void* h, uint32_t* out7) {
+  const BattleNet* n = static_cast<BattleNet*>(h);
+  const uint32_t v[7] = {n->pk0.out, n->pk1.out, n->ac0.out, n->ac1.out, n->fc0.out, n->v2.out, n->p1a.out};
+  memcpy(out7, v, sizeof(v));
+}
+// value_policy_inference for explicit choice lists; embedding_out nullable (2 * side_dim floats)
+float oracle_net_eval(void* h, const uint8_t* battle, const uint8_t* durations, int m, int n, const uint8_t* c1, const uint8_t* c2,
+                      float* l1, float* l2, float* embedding_out) {
+  const BattleNet* net = static_cast<BattleNet*>(h);
+  std::vector<float> emb;
+  const float v = net->eval(*reinterpret_cast<const Battle*>(battle), durations, m, n, c1, c2, l1, l2, embedding_out ? &emb : nullptr);
+  if (embedding_out) memcpy(embedding_out, emb.data(), emb.size() * 4);
+  return v;
+}
+// Batched leaf evaluation as the GPU kernel defines it: legal choices are derived from each battle's
+// result byte (choices x2), then value + logits of those choices. logits[n][2][9], counts[n][2].
+void oracle_net_eval_batch(void* h, const uint8_t* battles, const uint8_t* durations, const uint8_t* results, size_t n, int threads,
+                           float* values, float* logits, uint8_t* counts) {
+  const BattleNet* net = static_cast<BattleNet*>(h);
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const size_t i0 = next.fetch_add(64);
+      if (i0 >= n) return;
+      const size_t i1 = i0 + 64 < n ? i0 + 64 : n;
+      for (size_t i = i0; i < i1; i++) {
+        Battle b;
+        memcpy(&b, battles + i * 384, 384);
+        Options o{};
+        OakEngine e(b, o);
+        uint8_t c1[9], c2[9];
+        const int m = e.choices(P1, (results[i] >> 4) & 3, c1);
+        const int k = e.choices(P2, (results[i] >> 6) & 3, c2);
+        float* lo = logits + i * 18;
+        for (int j = 0; j < 18; j++) lo[j] = 0.0f;
+        values[i] = net->eval(b, durations + i * 8, m, k, c1, c2, lo, lo + 9);
+        counts[2 * i] = (uint8_t)m;
+        counts[2 * i + 1] = (uint8_t)k;
+      }
     }
   };
   std::vector<std::thread> pool;

@@ -162,3 +162,62 @@ def sample_teams(first, n):
     t = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
     i = np.arange(first, first + n)
     return np.stack([t[i & 15], t[(i >> 4) & 15]], axis=1)
+
+
+class NetOracle:
+    """Oracle leaf evaluation (oracle/nn_oracle.hpp) on a parameter blob in the reference's file format."""
+
+    def __init__(self, orc, blob):
+        self.lib = orc.lib
+        blob = np.ascontiguousarray(blob, np.uint8)
+        self.lib.oracle_net_create.restype = ctypes.c_void_p
+        self.lib.oracle_net_create.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+        self.h = self.lib.oracle_net_create(blob.ctypes.data, blob.size)
+        if not self.h:
+            raise ValueError("oracle_net_create: bad parameter blob")
+        dims = np.zeros(7, np.uint32)
+        self.lib.oracle_net_dims.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        self.lib.oracle_net_dims(self.h, dims.ctypes.data)
+        self.phd, self.pod, self.ahd, self.aod, self.hd, self.vhd, self.pohd = (int(x) for x in dims)
+        self.side_dim = (1 + self.aod) + 5 * (1 + self.pod)
+
+    def eval_batch(self, battles, durations, results, threads=None):
+        n = battles.shape[0]
+        v = np.zeros(n, np.float32)
+        lg = np.zeros((n, 2, 9), np.float32)
+        cnt = np.zeros((n, 2), np.uint8)
+        f = self.lib.oracle_net_eval_batch
+        f.restype = None
+        f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_size_t, ctypes.c_int] + [ctypes.c_void_p] * 3
+        f(self.h, battles.ctypes.data, durations.ctypes.data, results.ctypes.data, n, threads or os.cpu_count() or 1,
+          v.ctypes.data, lg.ctypes.data, cnt.ctypes.data)
+        return v, lg, cnt
+
+    def eval_one(self, battle, durations, c1, c2):
+        l1 = np.zeros(9, np.float32)
+        l2 = np.zeros(9, np.float32)
+        emb = np.zeros(2 * self.side_dim, np.float32)
+        a1 = np.array(c1, np.uint8)
+        a2 = np.array(c2, np.uint8)
+        f = self.lib.oracle_net_eval
+        f.restype = ctypes.c_float
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 5
+        v = f(self.h, battle.ctypes.data, durations.ctypes.data, len(c1), len(c2), a1.ctypes.data, a2.ctypes.data, l1.ctypes.data,
+              l2.ctypes.data, emb.ctypes.data)
+        return float(v), l1[:len(c1)], l2[:len(c2)], emb
+
+
+def make_net_blob(rng, phd=128, pod=59, ahd=128, aod=83, hd=64, vhd=32, pohd=64, activation=1, scale=1.0):
+    """Random parameters in the reference's file format (affine.h:34-69, network.h:52-70, search.cc:127-147):
+    U(-1/sqrt(in), 1/sqrt(in)) like Affine::initialize (affine.h:104-114)."""
+    import struct
+    side = (1 + aod) + 5 * (1 + pod)
+    shapes = [(198, phd), (phd, pod), (427, ahd), (ahd, aod), (2 * side, hd), (hd, hd), (hd, vhd), (vhd, 1),
+              (hd, pohd), (pohd, 315), (hd, pohd), (pohd, 315)]
+    out = [struct.pack("<Q", activation - 1)]
+    for i, o in shapes:
+        k = scale / np.sqrt(i)
+        out.append(struct.pack("<II", i, o))
+        out.append(rng.uniform(-k, k, o).astype("<f4").tobytes())
+        out.append(rng.uniform(-k, k, (o, i)).astype("<f4").tobytes())
+    return np.frombuffer(b"".join(out), np.uint8).copy()
