@@ -109,6 +109,23 @@ int oakb200_randomize_hidden_device(oakb200_ctx* ctx, size_t n, void* battles, c
  * into the resident arrays, sends out the leads, durations = 0. HOST pointers. */
 int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, const uint64_t* seeds);
 
+/* ---- leaf evaluation: battle encoding -> embedding nets -> main MLP ------------------------------
+ * Replaces NN::Battle::NetworkImpl::{read_parameters, value_policy_inference} (reference
+ * cpp/include/nn/battle/network.h:52-70,102-123; encoder cpp/include/encode/battle/battle.h; parameter
+ * file = 8-byte header (byte 0: activation - 1; cpp/src/search.cc:127-147) + 12 Affine blocks
+ * {u32 in, u32 out, f32 bias[out], f32 W[out][in]} (cpp/include/nn/affine.h:34-69), must end exactly at
+ * the last block. Evaluation is cache-free (the reference's per-search embedding memo is an
+ * optimisation of the same function, cpp/include/nn/battle/cache.h).
+ * net_load: parse + upload a parameter file image (HOST pointer). Limits: hidden dims <= 128,
+ * embedding dims <= 96, main hidden <= 64, head hidden <= 64; OAKB200_EINVAL otherwise. */
+int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* file_bytes, size_t len);
+/* For every battle: legal choices are derived from its result byte (as choices does), then
+ * value[n] (after the sigmoid, network.h:118), logits[n][2][9] for those choices in choices order
+ * (unused entries 0), counts[n][2]. */
+int oakb200_eval(oakb200_ctx* ctx, float* value_out, float* logits_out, uint8_t* counts_out);
+int oakb200_eval_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* durations, const void* results,
+                        void* value_out, void* logits_out, void* counts_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,56 @@
+// Private host-side context shared by the translation units of liboakb200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+#include "../../include/oakb200.h"
+
+struct oakb200_net;  // device copy of a loaded network (value_net.cu)
+
+struct oakb200_ctx {
+  int device = -1;
+  int sm_count = 0;
+  size_t n_max = 0, n = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint8_t *battles = nullptr, *durations = nullptr, *results = nullptr;
+  // scratch for the host-pointer entry points
+  uint8_t *c1 = nullptr, *c2 = nullptr, *overrides = nullptr, *actions = nullptr, *choices = nullptr, *counts = nullptr;
+  uint64_t* seeds = nullptr;
+  uint8_t* score2 = nullptr;
+  uint16_t* turns = nullptr;
+  uint32_t* steps = nullptr;
+  uint8_t* teams = nullptr;
+  uint32_t* ticket = nullptr;
+  unsigned long long* total_steps = nullptr;
+  uint64_t launches = 0;
+  oakb200_net* net = nullptr;
+  float* eval_values = nullptr;
+  float* eval_logits = nullptr;
+  uint8_t* eval_counts = nullptr;
+  std::string error;
+};
+
+namespace {
+
+inline int fail(oakb200_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess) {
+  if (ctx) {
+    ctx->error = what;
+    if (e != cudaSuccess) {
+      ctx->error += ": ";
+      ctx->error += cudaGetErrorString(e);
+    }
+  }
+  return code;
+}
+
+#define CU(ctx, call)                                              \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return fail(ctx, OAKB200_ECUDA, #call, e__); \
+  } while (0)
+
+}  // namespace

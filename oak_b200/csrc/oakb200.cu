@@ -19,44 +19,11 @@ const int BLOCK = 128;                                  // battles per CTA
 const size_t TILE_BYTES = (size_t)BATTLE_WORDS * BLOCK * 4;  // 48 KB shared-memory tile
 }  // namespace
 
-struct oakb200_ctx {
-  int device = -1;
-  int sm_count = 0;
-  size_t n_max = 0, n = 0;
-  cudaStream_t stream = nullptr;
-  bool own_stream = false;
-  uint8_t *battles = nullptr, *durations = nullptr, *results = nullptr;
-  // scratch for the host-pointer entry points
-  uint8_t *c1 = nullptr, *c2 = nullptr, *overrides = nullptr, *actions = nullptr, *choices = nullptr, *counts = nullptr;
-  uint64_t* seeds = nullptr;
-  uint8_t* score2 = nullptr;
-  uint16_t* turns = nullptr;
-  uint32_t* steps = nullptr;
-  uint8_t* teams = nullptr;
-  uint32_t* ticket = nullptr;
-  unsigned long long* total_steps = nullptr;
-  uint64_t launches = 0;
-  std::string error;
-};
+#include "context.h"
+
+void oakb200_net_release(oakb200_ctx* ctx);  // value_net.cu
 
 namespace {
-
-int fail(oakb200_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess) {
-  if (ctx) {
-    ctx->error = what;
-    if (e != cudaSuccess) {
-      ctx->error += ": ";
-      ctx->error += cudaGetErrorString(e);
-    }
-  }
-  return code;
-}
-
-#define CU(ctx, call)                                              \
-  do {                                                             \
-    cudaError_t e__ = (call);                                      \
-    if (e__ != cudaSuccess) return fail(ctx, OAKB200_ECUDA, #call, e__); \
-  } while (0)
 
 template <class K>
 cudaError_t allow_smem(K kernel) {
@@ -142,6 +109,9 @@ int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
   CU(ctx, cudaMalloc(&ctx->turns, n_max * 2));
   CU(ctx, cudaMalloc(&ctx->steps, n_max * 4));
   CU(ctx, cudaMalloc(&ctx->teams, n_max * 60));
+  CU(ctx, cudaMalloc(&ctx->eval_values, n_max * 4));
+  CU(ctx, cudaMalloc(&ctx->eval_logits, n_max * 18 * 4));
+  CU(ctx, cudaMalloc(&ctx->eval_counts, n_max * 2));
   CU(ctx, cudaMalloc(&ctx->ticket, sizeof(uint32_t)));
   CU(ctx, cudaMalloc(&ctx->total_steps, sizeof(unsigned long long)));
   CU(ctx, cudaMemset(ctx->total_steps, 0, sizeof(unsigned long long)));
@@ -152,7 +122,9 @@ void oakb200_destroy(oakb200_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   void* bufs[] = {ctx->battles, ctx->durations, ctx->results, ctx->c1,    ctx->c2,    ctx->overrides, ctx->actions, ctx->choices,
-                  ctx->counts,  ctx->seeds,     ctx->score2,  ctx->turns, ctx->steps, ctx->teams,     ctx->ticket,  ctx->total_steps};
+                  ctx->counts,  ctx->seeds,     ctx->score2,  ctx->turns, ctx->steps, ctx->teams,     ctx->ticket,  ctx->total_steps,
+                  ctx->eval_values, ctx->eval_logits, ctx->eval_counts};
+  oakb200_net_release(ctx);
   for (void* b : bufs)
     if (b) cudaFree(b);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -58,6 +58,9 @@ def load_library():
         "oakb200_total_steps": (i32, [vp, ctypes.POINTER(ctypes.c_uint64)]),
         "oakb200_randomize_hidden_device": (i32, [vp, sz, vp, vp]),
         "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
+        "oakb200_net_load": (i32, [vp, vp, sz]),
+        "oakb200_eval": (i32, [vp, vp, vp, vp]),
+        "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -186,6 +189,27 @@ class BattleEngine:
         flags = (ROLLOUT_WRITE_STATE if write_state else 0) | (ROLLOUT_TRACK_CHANCE if track_chance else 0)
         self._check(self.lib.oakb200_rollout(self._h, _ptr(seeds), int(max_steps), flags, _ptr(score), _ptr(turns), _ptr(steps)))
         return score, turns, steps
+
+    # ---------------------------------------------------------------- leaf evaluation
+    def load_network(self, blob):
+        """Parameter file image in the reference's format (bytes / uint8 array / path)."""
+        if isinstance(blob, (str, os.PathLike)):
+            blob = np.fromfile(blob, np.uint8)
+        blob = np.frombuffer(bytes(blob), np.uint8) if isinstance(blob, (bytes, bytearray)) else _np(blob, np.uint8)
+        self._check(self.lib.oakb200_net_load(self._h, _ptr(blob), blob.size))
+
+    def evaluate(self):
+        """value_policy_inference for every resident battle -> (value[n] f32, logits[n,2,9] f32, counts[n,2] u8)."""
+        n = self.n
+        v = np.empty((n,), np.float32)
+        lg = np.empty((n, 2, 9), np.float32)
+        cnt = np.empty((n, 2), np.uint8)
+        self._check(self.lib.oakb200_eval(self._h, _ptr(v), _ptr(lg), _ptr(cnt)))
+        return v, lg, cnt
+
+    def evaluate_device(self, battles, durations, results, value_out, logits_out, counts_out):
+        self._check(self.lib.oakb200_eval_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                 _ptr(value_out), _ptr(logits_out), _ptr(counts_out)))
 
     # ---------------------------------------------------------------- device-pointer calls (torch CUDA tensors)
     def resident(self):
