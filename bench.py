@@ -129,7 +129,7 @@ def main():
     ap.add_argument("--battles", type=int, default=1 << 20, help="battles per GPU per step")
     ap.add_argument("--impl", default="oak_b200", choices=["oak_b200", "reference"])
     ap.add_argument("--ref-battles", type=int, default=1 << 18)
-    ap.add_argument("--cpu-sample", type=int, default=1 << 18)
+    ap.add_argument("--cpu-sample", type=int, default=1 << 23)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -156,7 +156,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     n = args.battles
-    first = rank * n  # shard: rank r owns synthetic battles [r*n, (r+1)*n) — no data-path collective
+    from oak_b200.sharding import shard_range
+    first, _ = shard_range(rank, world, n)  # rank r owns synthetic battles [r*n, (r+1)*n): no data-path collective
     eng = oak_b200.BattleEngine(n, device=local)
     stream = torch.cuda.current_stream(dev)
     eng.set_stream(stream.cuda_stream)
@@ -251,6 +252,37 @@ def main():
     lock_ms = le0.elapsed_time(le1) / LOCK
     launches += LOCK + 3
 
+    # ---- secondary: batched leaf evaluation (BASELINE configs[2]: batch 64K, default network dims)
+    from oak_ref import make_net_blob
+    EV = min(1 << 16, n)
+    blob = make_net_blob(np.random.default_rng(1234))
+    eng.load_network(blob)
+    ev_v = torch.empty(EV, dtype=torch.float32, device=dev)
+    ev_l = torch.empty((EV, 2, 9), dtype=torch.float32, device=dev)
+    ev_c = torch.empty((EV, 2), dtype=torch.uint8, device=dev)
+    eb, ed, er = lock_b[:EV], lock_d[:EV], lock_r[:EV]  # states after 19 random-playout steps
+    for _ in range(3):
+        eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
+    torch.cuda.synchronize(dev)
+    ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    EVIT = 10
+    ee0.record(stream)
+    for _ in range(EVIT):
+        eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
+    ee1.record(stream)
+    torch.cuda.synchronize(dev)
+    eval_ms = ee0.elapsed_time(ee1) / EVIT
+    launches += EVIT + 3
+    eval_cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oak_ref import NetOracle, Oracle as _O
+        _orc = _O()
+        _net = NetOracle(_orc, blob)
+        cb, cd, cr = (x.cpu().numpy() for x in (eb, ed, er))
+        t0 = time.perf_counter()
+        _net.eval_batch(cb, cd, cr, threads=os.cpu_count() or 1)
+        eval_cpu = EV / (time.perf_counter() - t0)
+
     # ---- reduce over ranks: max time, sum of work
     t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms], dtype=torch.float64, device=dev)
     w = torch.tensor([steps_per_pass * args.steps, n * args.steps, e2e_steps * e2e_iters, launches, n], dtype=torch.float64, device=dev)
@@ -269,7 +301,10 @@ def main():
         if not args.no_cpu_baseline:
             from oak_ref import Oracle
             threads = os.cpu_count() or 1
-            s, dt = cpu_rollouts(Oracle(), 0, args.cpu_sample, threads)
+            orc_, s, dt = Oracle(), 0, 0.0
+            for chunk in range(max(1, args.cpu_sample >> 20)):  # 2^20-playout chunks (412 MB each)
+                s_, dt_ = cpu_rollouts(orc_, chunk << 20, min(args.cpu_sample, 1 << 20), threads)
+                s, dt = s + s_, dt + dt_
             cpu = {"value": s / dt, "unit": "battle-steps/s", "cores": threads, "kind": "port",
                    "rollouts_per_s": args.cpu_sample / dt,
                    "sample": f"{args.cpu_sample} playouts ({s} battle-steps, {dt:.1f} s) of the same synthetic workload; "
@@ -298,6 +333,11 @@ def main():
                                      "achieved_gbs": B_STEP * n / (lock_ms * 1e-3) / 1e9,
                                      "frac_of_hbm_peak": B_STEP * n / (lock_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                                      "live_fraction_at_start": live_before / n},
+            "leaf_eval": {"evals_per_s": world * EV / (eval_ms * 1e-3), "batch_per_gpu": EV, "ms_per_batch": eval_ms,
+                          "network": "default dims 198/427->128->59/83, 768->64->64, value 32, policy 64->315 (legal rows), relu, fp32",
+                          "kernel": "eval_kernel (fp32 CUDA cores, warp per eval)",
+                          "executed_gflops": 2 * 27e3 * EV / (eval_ms * 1e-3) / 1e9 + 322e3 * EV / (eval_ms * 1e-3) / 1e9,
+                          "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (cache-free, sparse first layers), all host cores"},
             "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(tot_launches),
         }
         print(json.dumps(line), flush=True)
