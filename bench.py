@@ -31,6 +31,9 @@ import numpy as np  # noqa: E402
 
 B_ROLLOUT = 404  # algorithmic bytes per fused rollout: read 384+8+1+8, write 1+2
 B_STEP = 787     # algorithmic bytes per battle-step for the one-launch-per-step kernel
+F_EVAL = 1048384      # dense-equivalent FLOP per leaf evaluation
+F_EVAL_TC = 2625536   # FLOP per evaluation the tensor-core kernel actually issues: 32 * sum(N * MMAs) over its chunk
+                      # program, i.e. three products per split-bf16 GEMM and the K/N padding included
 
 
 def peaks():
@@ -261,18 +264,33 @@ def main():
     ev_l = torch.empty((EV, 2, 9), dtype=torch.float32, device=dev)
     ev_c = torch.empty((EV, 2), dtype=torch.uint8, device=dev)
     eb, ed, er = lock_b[:EV], lock_d[:EV], lock_r[:EV]  # states after 19 random-playout steps
-    for _ in range(3):
-        eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
-    torch.cuda.synchronize(dev)
-    ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    eval_ms_mode = {}
     EVIT = 10
-    ee0.record(stream)
-    for _ in range(EVIT):
-        eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
-    ee1.record(stream)
-    torch.cuda.synchronize(dev)
-    eval_ms = ee0.elapsed_time(ee1) / EVIT
-    launches += EVIT + 3
+    for mode in (1, 2):  # 1 = fp32 CUDA-core kernel, 2 = tcgen05 tensor-core kernel (the default path)
+        eng.set_eval_mode(mode)
+        for _ in range(3):
+            eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
+        torch.cuda.synchronize(dev)
+        ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ee0.record(stream)
+        for _ in range(EVIT):
+            eng.evaluate_device(eb, ed, er, ev_v, ev_l, ev_c)
+        ee1.record(stream)
+        torch.cuda.synchronize(dev)
+        eval_ms_mode[mode] = ee0.elapsed_time(ee1) / EVIT
+        launches += EVIT + 3
+    eng.set_eval_mode(0)
+    eval_ms = eval_ms_mode[2]
+    # end to end through the host API: pageable host records in, value/logits/counts out
+    hb_e, hd_e, hr_e = (x.cpu().numpy() for x in (eb, ed, er))
+    eng.upload(hb_e, hd_e, hr_e)
+    eng.evaluate()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        eng.upload(hb_e, hd_e, hr_e)
+        eng.evaluate()
+    eval_e2e_s = (time.perf_counter() - t0) / 3
+    launches += 4
     eval_cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         from oak_ref import NetOracle, Oracle as _O
@@ -334,9 +352,19 @@ def main():
                                      "frac_of_hbm_peak": B_STEP * n / (lock_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                                      "live_fraction_at_start": live_before / n},
             "leaf_eval": {"evals_per_s": world * EV / (eval_ms * 1e-3), "batch_per_gpu": EV, "ms_per_batch": eval_ms,
-                          "network": "default dims 198/427->128->59/83, 768->64->64, value 32, policy 64->315 (legal rows), relu, fp32",
-                          "kernel": "eval_kernel (fp32 CUDA cores, warp per eval)",
-                          "executed_gflops": 2 * 27e3 * EV / (eval_ms * 1e-3) / 1e9 + 322e3 * EV / (eval_ms * 1e-3) / 1e9,
+                          "network": "default dims 198/427->128->59/83, 768->64->64, value 32, policy 64->315 (legal rows), relu",
+                          "kernel": "eval_tc_kernel (tcgen05.mma kind::f16 on split-bf16 operand pairs, fp32 accumulate in TMEM; "
+                                    "one-hot first layers as dense tiles)",
+                          "e2e_evals_per_s": world * EV / eval_e2e_s,
+                          "e2e_note": "host records in (393 B/eval H2D), value + logits + counts out (78 B/eval D2H), wall clock",
+                          "fp32_cuda_core_kernel_evals_per_s": world * EV / (eval_ms_mode[1] * 1e-3),
+                          "roofline": {"bound": "tensor", "achieved": F_EVAL_TC * EV / (eval_ms * 1e-3) / 1e12,
+                                       "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                                       "frac": F_EVAL_TC * EV / (eval_ms * 1e-3) / 1e12 / pk["bf16_tflops"], "peak_source": pk_src,
+                                       "flops_per_eval_executed": F_EVAL_TC, "flops_per_eval_dense_equivalent": F_EVAL,
+                                       "dense_equivalent_tflops": F_EVAL * EV / (eval_ms * 1e-3) / 1e12,
+                                       "note": "executed = every tcgen05.mma issued (3 products per split-bf16 GEMM, K and N "
+                                               "padding included); dense-equivalent = SURVEY 8d F_eval"},
                           "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (cache-free, sparse first layers), all host cores"},
             "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(tot_launches),
         }

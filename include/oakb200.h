@@ -119,6 +119,11 @@ int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, cons
  * net_load: parse + upload a parameter file image (HOST pointer). Limits: hidden dims <= 128,
  * embedding dims <= 96, main hidden <= 64, head hidden <= 64; OAKB200_EINVAL otherwise. */
 int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* file_bytes, size_t len);
+/* Which kernel evaluates: 0 = auto (the tcgen05 tensor-core kernel whenever the layer shapes fit: hidden <= 128,
+ * pokemon/active embedding <= 63/95, main hidden <= 64, value hidden <= 32, policy hidden <= 64 and a multiple
+ * of 4 -- the reference's defaults do), 1 = the fp32 CUDA-core kernel, 2 = tensor cores or OAKB200_EINVAL.
+ * Both compute the same function; the tensor-core kernel uses split-bf16 operands (~1e-5 relative). */
+int oakb200_eval_set_mode(oakb200_ctx* ctx, int mode);
 /* For every battle: legal choices are derived from its result byte (as choices does), then
  * value[n] (after the sigmoid, network.h:118), logits[n][2][9] for those choices in choices order
  * (unused entries 0), counts[n][2]. */

@@ -28,6 +28,7 @@ struct oakb200_ctx {
   unsigned long long* total_steps = nullptr;
   uint64_t launches = 0;
   oakb200_net* net = nullptr;
+  int eval_mode = 0;  // 0 auto (tensor cores when the shape fits), 1 fp32 CUDA-core kernel, 2 tensor cores or fail
   float* eval_values = nullptr;
   float* eval_logits = nullptr;
   uint8_t* eval_counts = nullptr;

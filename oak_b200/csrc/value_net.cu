@@ -35,6 +35,12 @@ struct oakb200_net {
   size_t pk0T, pk0b, pk1T, pk1b, ac0T, ac0b, ac1T, ac1b, fc0T, fc0b, fc1T, fc1b, v2T, v2b, v3w, v3b, p1aT, p1ab, p1bW, p1bb, p2aT,
       p2ab, p2bW, p2bb;
   size_t floats = 0;
+  // tensor-core path (value_net_tc.cuh): packed split-bf16 weight chunks, chunk program, fp32 constants
+  bool tc_ok = false;
+  uint8_t* tc_wpack = nullptr;
+  void* tc_prog = nullptr;
+  float* tc_consts = nullptr;
+  int tc_nchunks = 0;
 };
 
 namespace {
@@ -77,11 +83,17 @@ size_t put_raw(std::vector<float>& blob, const float* src, size_t n) {
   return off;
 }
 
+// builds the tensor-core path's packed weights / program (defined at the end of this file)
+cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d);
+
 }  // namespace
 
 void oakb200_net_release(oakb200_ctx* ctx) {
   if (ctx && ctx->net) {
     if (ctx->net->blob) cudaFree(ctx->net->blob);
+    if (ctx->net->tc_wpack) cudaFree(ctx->net->tc_wpack);
+    if (ctx->net->tc_prog) cudaFree(ctx->net->tc_prog);
+    if (ctx->net->tc_consts) cudaFree(ctx->net->tc_consts);
     delete ctx->net;
     ctx->net = nullptr;
   }
@@ -132,6 +144,11 @@ extern "C" int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* bytes, size_t l
     return fail(ctx, OAKB200_ECUDA, "net_load: upload", e);
   }
   ctx->net = n;
+  e = tc_pack(n, a, d);
+  if (e != cudaSuccess) {
+    oakb200_net_release(ctx);
+    return fail(ctx, OAKB200_ECUDA, "net_load: tensor-core weight upload", e);
+  }
   return OAKB200_OK;
 }
 
@@ -426,6 +443,186 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
 
 }  // namespace
 
+#include "value_net_tc.cuh"
+
+namespace {
+
+uint16_t f2bf(float x) {  // round-to-nearest-even, as __float2bfloat16_rn
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
+  u += 0x7FFFu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+float bf2f(uint16_t h) {
+  const uint32_t u = (uint32_t)h << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+float rdf(const float* base, size_t i) {  // the parameter image need not be 4-byte aligned
+  float v;
+  memcpy(&v, reinterpret_cast<const uint8_t*>(base) + i * 4, 4);
+  return v;
+}
+
+struct PackedMatrix {
+  int N = 0;
+  struct Piece { uint32_t gofs16, bytes16, ksteps, k0; };
+  std::vector<Piece> pieces;
+};
+
+struct Packer {
+  std::vector<uint16_t> w;
+  std::vector<tc::Chunk> prog;
+
+  // B[N][K] (K a multiple of 16, N of 16) -> split-bf16 chunks of at most one ring slot each
+  template <class F>
+  PackedMatrix matrix(int N, int K, F get) {
+    PackedMatrix pm;
+    pm.N = N;
+    const int total = K / 16;
+    int cs = (int)tc::RING_SLOT / (N * 64);
+    if (cs < 1) cs = 1;
+    for (int k0 = 0; k0 < total; k0 += cs) {
+      const int ks = total - k0 < cs ? total - k0 : cs;
+      const size_t base = w.size(), plane = (size_t)ks * N * 16;
+      w.resize(base + 2 * plane);
+      for (int kk = 0; kk < ks * 16; kk++)
+        for (int nn = 0; nn < N; nn++) {
+          const float v = get(nn, k0 * 16 + kk);
+          const uint16_t hi = f2bf(v), lo = f2bf(v - bf2f(hi));
+          const size_t idx = ((size_t)(kk >> 3) * N + nn) * 8 + (kk & 7);
+          w[base + idx] = hi;
+          w[base + plane + idx] = lo;
+        }
+      pm.pieces.push_back({(uint32_t)(base / 8), (uint32_t)(2 * plane / 8), (uint32_t)ks, (uint32_t)k0});
+    }
+    return pm;
+  }
+
+  void stage(const PackedMatrix& pm, uint32_t a_hi, uint32_t a_lo, int lo_ksteps, uint32_t dcol, bool overwrite, uint8_t end_flag) {
+    for (size_t j = 0; j < pm.pieces.size(); j++) {
+      const auto& pc = pm.pieces[j];
+      tc::Chunk c;
+      c.gofs16 = pc.gofs16;
+      c.bytes16 = (uint16_t)pc.bytes16;
+      c.ksteps = (uint8_t)pc.ksteps;
+      c.n8 = (uint8_t)(pm.N / 8);
+      c.a_off16 = (uint16_t)((a_hi + pc.k0 * 2 * tc::CORE) / 16);
+      c.alo_off16 = (uint16_t)((a_lo + pc.k0 * 2 * tc::CORE) / 16);
+      int lo = lo_ksteps - (int)pc.k0;
+      if (lo < 0) lo = 0;
+      if (lo > (int)pc.ksteps) lo = (int)pc.ksteps;
+      c.lo_steps = (uint8_t)lo;
+      c.flags = (uint8_t)((j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
+                          (j + 1 == pm.pieces.size() ? end_flag : 0));
+      c.dcol = (uint16_t)dcol;
+      prog.push_back(c);
+    }
+  }
+};
+
+cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
+  n->tc_ok = d.phd <= 128 && d.ahd <= 128 && d.pod <= 63 && d.aod <= 95 && d.hd <= 64 && d.vhd <= 32 && d.pohd <= 64 && (d.pohd & 3) == 0;
+  if (!n->tc_ok) return cudaSuccess;  // the fp32 kernel serves unusual shapes
+  static_assert(sizeof(tc::Chunk) == 16, "chunk program entries are 16 bytes");
+  Packer P;
+  int inv_act[tc::K_ACT];
+  for (int k = 0; k < tc::K_ACT; k++) inv_act[k] = -1;
+  for (int idx = 0; idx < 229; idx++) inv_act[tc::act_col(idx)] = idx;
+  const int phd = d.phd, pod = d.pod, ahd = d.ahd, aod = d.aod, hd = d.hd, in = d.in;
+  const PackedMatrix ac0a = P.matrix(128, tc::K_ACT, [&](int o, int k) { return o < ahd && inv_act[k] >= 0 ? rdf(a[2].w, (size_t)o * 427 + inv_act[k]) : 0.0f; });
+  const PackedMatrix ac0p = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < ahd && k < 198 ? rdf(a[2].w, (size_t)o * 427 + 229 + k) : 0.0f; });
+  const PackedMatrix pk0 = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < phd && k < 198 ? rdf(a[0].w, (size_t)o * 198 + k) : 0.0f; });
+  const PackedMatrix pk1 = P.matrix(64, 128, [&](int o, int k) { return o < pod && k < phd ? rdf(a[1].w, (size_t)o * phd + k) : 0.0f; });
+  const PackedMatrix ac1 = P.matrix(96, 128, [&](int o, int k) { return o < aod && k < ahd ? rdf(a[3].w, (size_t)o * ahd + k) : 0.0f; });
+  // fc0 column slices: operand column k < od is embedding output k, column od is the hp fraction (network.h:131-175)
+  auto fc0_slice = [&](int K, int od, int base) {
+    return P.matrix(64, K, [&](int o, int k) {
+      if (o >= hd || k > od) return 0.0f;
+      return rdf(a[4].w, (size_t)o * in + (k < od ? base + 1 + k : base));
+    });
+  };
+  PackedMatrix fa[2], fp[2][5];
+  for (int s = 0; s < 2; s++) {
+    fa[s] = fc0_slice(96, aod, s * d.side);
+    for (int p = 0; p < 5; p++) fp[s][p] = fc0_slice(64, pod, s * d.side + (1 + aod) + p * (1 + pod));
+  }
+  const PackedMatrix fc1 = P.matrix(64, 64, [&](int o, int k) { return o < hd && k < hd ? rdf(a[5].w, (size_t)o * hd + k) : 0.0f; });
+  const PackedMatrix heads = P.matrix(160, 64, [&](int o, int k) {
+    if (k >= hd) return 0.0f;
+    if (o < 32) return o < d.vhd ? rdf(a[6].w, (size_t)o * hd + k) : 0.0f;
+    if (o < 96) return o - 32 < d.pohd ? rdf(a[8].w, (size_t)(o - 32) * hd + k) : 0.0f;
+    return o - 96 < d.pohd ? rdf(a[10].w, (size_t)(o - 96) * hd + k) : 0.0f;
+  });
+  for (int s = 0; s < 2; s++) {
+    P.stage(ac0a, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+    P.stage(ac0p, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, false, tc::F_END_D);
+    P.stage(ac1, tc::A2_HI, tc::A2_LO, 8, tc::D_WORK, true, tc::F_END_D);
+    P.stage(fa[s], tc::AEA_HI, tc::AEA_LO, 6, tc::D_TRUNK, s == 0, tc::F_END_T);
+    for (int p = 0; p < 5; p++) {
+      P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+      P.stage(pk1, tc::A2_HI, tc::A2_LO, 8, tc::D_WORK, true, tc::F_END_D);
+      P.stage(fp[s][p], tc::AEP_HI, tc::AEP_LO, 4, tc::D_TRUNK, false, tc::F_END_T);
+    }
+  }
+  P.stage(fc1, tc::AT_HI, tc::AT_LO, 4, tc::D_WORK, true, tc::F_END_D);
+  P.stage(heads, tc::AEP_HI, tc::AEP_LO, 4, tc::D_WORK, true, tc::F_END_D);
+  if (P.prog.size() > tc::PROG_MAX) {
+    n->tc_ok = false;
+    return cudaSuccess;
+  }
+  std::vector<float> c(tc::CONST_FLOATS, 0.0f);
+  for (int i = 0; i < phd; i++) c[tc::C_PK0 + i] = rdf(a[0].bias, i);
+  for (int i = 0; i < pod; i++) c[tc::C_PK1 + i] = rdf(a[1].bias, i);
+  for (int i = 0; i < ahd; i++) c[tc::C_AC0 + i] = rdf(a[2].bias, i);
+  for (int i = 0; i < aod; i++) c[tc::C_AC1 + i] = rdf(a[3].bias, i);
+  for (int i = 0; i < hd; i++) c[tc::C_FC0 + i] = rdf(a[4].bias, i);
+  for (int i = 0; i < hd; i++) c[tc::C_FC1 + i] = rdf(a[5].bias, i);
+  for (int i = 0; i < d.vhd; i++) c[tc::C_HEADS + i] = rdf(a[6].bias, i);
+  for (int i = 0; i < d.pohd; i++) c[tc::C_HEADS + 32 + i] = rdf(a[8].bias, i);
+  for (int i = 0; i < d.pohd; i++) c[tc::C_HEADS + 96 + i] = rdf(a[10].bias, i);
+  for (int i = 0; i < d.vhd; i++) c[tc::C_V3W + i] = rdf(a[7].w, i);
+  c[tc::C_V3B] = rdf(a[7].bias, 0);
+  cudaError_t e = cudaMalloc(&n->tc_wpack, P.w.size() * 2);
+  if (e == cudaSuccess) e = cudaMemcpy(n->tc_wpack, P.w.data(), P.w.size() * 2, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&n->tc_prog, P.prog.size() * sizeof(tc::Chunk));
+  if (e == cudaSuccess) e = cudaMemcpy(n->tc_prog, P.prog.data(), P.prog.size() * sizeof(tc::Chunk), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&n->tc_consts, c.size() * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(n->tc_consts, c.data(), c.size() * 4, cudaMemcpyHostToDevice);
+  n->tc_nchunks = (int)P.prog.size();
+  return e;
+}
+
+int launch_eval_tc(oakb200_ctx* ctx, size_t n, const void* battles, const void* durations, const void* results, void* value_out,
+                   void* logits_out, void* counts_out) {
+  const oakb200_net& N = *ctx->net;
+  tc::Params P;
+  P.wpack = N.tc_wpack;
+  P.prog = reinterpret_cast<const tc::Chunk*>(N.tc_prog);
+  P.consts = N.tc_consts;
+  P.p1bW = N.blob + N.p1bW; P.p1bb = N.blob + N.p1bb; P.p2bW = N.blob + N.p2bW; P.p2bb = N.blob + N.p2bb;
+  P.nchunks = N.tc_nchunks; P.act = N.d.act; P.pod = N.d.pod; P.aod = N.d.aod; P.vhd = N.d.vhd; P.pohd = N.d.pohd;
+  CU(ctx, cudaFuncSetAttribute(tc::eval_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_BYTES));
+  const unsigned tiles = (unsigned)((n + tc::ROWS - 1) / tc::ROWS);
+  const unsigned grid = tiles < (unsigned)ctx->sm_count ? tiles : (unsigned)ctx->sm_count;  // persistent: one CTA per SM
+  tc::eval_tc_kernel<<<grid, tc::THREADS, tc::SMEM_BYTES, ctx->stream>>>(P, (const uint8_t*)battles, (const uint8_t*)durations,
+                                                                        (const uint8_t*)results, (float*)value_out, (float*)logits_out,
+                                                                        (uint8_t*)counts_out, (uint32_t)n);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
+  return OAKB200_OK;
+}
+
+}  // namespace
+
+extern "C" int oakb200_eval_set_mode(oakb200_ctx* ctx, int mode) {
+  if (!ctx || mode < 0 || mode > 2) return fail(ctx, OAKB200_EINVAL, "eval_set_mode: mode is 0 (auto), 1 (fp32 CUDA cores) or 2 (tensor cores)");
+  ctx->eval_mode = mode;
+  return OAKB200_OK;
+}
+
 extern "C" int oakb200_eval_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* durations, const void* results,
                                    void* value_out, void* logits_out, void* counts_out) {
   if (!ctx || !battles || !durations || !results || !value_out || !logits_out || !counts_out)
@@ -434,6 +631,8 @@ extern "C" int oakb200_eval_device(oakb200_ctx* ctx, size_t n, const void* battl
   if (n == 0) return OAKB200_OK;
   CU(ctx, cudaSetDevice(ctx->device));
   const oakb200_net& N = *ctx->net;
+  if (ctx->eval_mode == 2 && !N.tc_ok) return fail(ctx, OAKB200_EINVAL, "eval: network shape is outside the tensor-core kernel's limits");
+  if (ctx->eval_mode != 1 && N.tc_ok) return launch_eval_tc(ctx, n, battles, durations, results, value_out, logits_out, counts_out);
   NetView v;
   v.d = N.d;
   const float* b = N.blob;

@@ -1,0 +1,509 @@
+// Tensor-core leaf evaluation for sm_100a (tcgen05 + Tensor Memory), included by value_net.cu.
+//
+// Same function as eval_kernel (value_net.cu) and as the reference's
+// NN::Battle::NetworkImpl::value_policy_inference (cpp/include/nn/battle/network.h:102-175), organised as
+// batched GEMMs so that every dense contraction runs on the 5th-generation tensor cores:
+//
+//   CTA tile = 128 evaluations; thread r of the four worker warps owns evaluation r = TMEM lane r.
+//   For each of the 12 party slots (2 sides x {active, 5 benched}):
+//     L1  hidden[128 x 128]  = onehot-ish features[128 x K] * W0^T   K = 208 (Pokemon) or 240 + 208 (Active)
+//     L2  embed [128 x 64|96] = act(hidden + b0) * W1^T
+//     T   trunk [128 x 64]  += [embed | hp] * fc0[:, slot columns]^T  (the 768-wide battle embedding never exists)
+//   then fc1, and one N = 160 GEMM for the three head hidden layers (value 32 | policy p1 64 | policy p2 64).
+//   The last layers (value 32 -> 1, policy 64 -> the <= 9 legal rows of 315) are per-thread fp32 dot products.
+//
+// Precision: operands are split bf16 pairs x = hi + lo (umma::split_bf16); each GEMM issues
+// A_hi*B_hi + A_hi*B_lo + A_lo*B_hi into one fp32 accumulator, i.e. ~16 mantissa bits per operand
+// (error ~1e-5 relative, well inside the 1e-3 of the north star) at the smem footprint of one tf32 plane.
+// One-hot feature columns are exact in bf16, so the first layer needs its A_lo plane only for the 14 real-valued
+// columns, which the host-side packing permutes to the front of K.
+//
+// Roles: warps 0-3 workers (encode, epilogues), warp 4 lane 0 streams weight chunks L2 -> shared memory with
+// cp.async.bulk through a 4-slot mbarrier ring (and owns the TMEM allocation), warp 5 lane 0 issues tcgen05.mma.
+// The per-tile schedule is a static chunk program built on the host at oakb200_net_load.
+#pragma once
+
+#include "gen1_mem_ops.cuh"
+#include "umma.cuh"
+
+namespace tc {
+
+using namespace oakb200;
+
+struct Chunk {        // 16 bytes; one weight chunk = `ksteps` K=16 steps of a [N x K] matrix, hi plane then lo plane
+  uint32_t gofs16;    // offset in the packed weight buffer, 16-byte units
+  uint16_t bytes16;   // chunk bytes / 16
+  uint8_t ksteps;
+  uint8_t n8;         // N / 8
+  uint16_t a_off16;   // shared-memory offset / 16 of the A hi plane at this chunk's first K step
+  uint16_t alo_off16; // same for the A lo plane
+  uint8_t lo_steps;   // leading K steps of this chunk for which an A lo plane exists
+  uint8_t flags;
+  uint16_t dcol;      // TMEM column of D
+};
+enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8 };
+
+const int ROWS = 128;
+const int THREADS = 192;
+const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden) / active embedding / trunk input
+const uint32_t OFF_EMB = 65536;      // benched-Pokemon embedding / second trunk operand
+const uint32_t OFF_TILE = 98304;     // 128 battle records as word-transposed columns (gen1_state.cuh)
+const uint32_t OFF_RING = 147456;    // weight chunk ring
+const uint32_t RING_SLOT = 16384, RING_SLOTS = 4;
+const uint32_t OFF_PROG = OFF_RING + RING_SLOTS * RING_SLOT;
+const uint32_t PROG_MAX = 192;
+const uint32_t OFF_CONST = OFF_PROG + PROG_MAX * 16;
+const uint32_t CONST_FLOATS = 740;
+const uint32_t OFF_BAR = OFF_CONST + CONST_FLOATS * 4;  // full[4], empty[4], a_ready, d_ready, t_done
+const uint32_t OFF_TMEM_SLOT = OFF_BAR + 11 * 8;
+const uint32_t SMEM_BYTES = OFF_TMEM_SLOT + 8;
+static_assert(OFF_BAR % 8 == 0, "mbarriers are 8-byte aligned");
+static_assert(SMEM_BYTES <= 232448, "fits the 227 KB of one CTA");
+
+// operand planes (byte offsets from the start of dynamic shared memory); one core column = 128 rows x 16 B
+const uint32_t CORE = ROWS * 16;
+const uint32_t A1_HI = OFF_UNION, A1_LO = OFF_UNION + 30 * CORE;   // K <= 240 hi, 16 lo
+const uint32_t A2_HI = OFF_UNION, A2_LO = OFF_UNION + 16 * CORE;   // K = 128
+const uint32_t AEA_HI = OFF_UNION, AEA_LO = OFF_UNION + 12 * CORE; // active embedding, K = 96
+const uint32_t AT_HI = OFF_UNION, AT_LO = OFF_UNION + 8 * CORE;    // trunk hidden, K = 64
+const uint32_t AEP_HI = OFF_EMB, AEP_LO = OFF_EMB + 8 * CORE;      // benched embedding / second trunk operand, K = 64
+// TMEM columns
+const uint32_t TMEM_COLS = 256, D_WORK = 0, D_TRUNK = 192;
+// constants block (floats)
+const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
+const int K_POK = 208, K_ACT = 240;
+
+// feature column of the Active block after the host-side permutation (real-valued columns first)
+__host__ __device__ inline int act_col(int idx) {
+  if (idx < 5) return idx;         // stats
+  if (idx < 20) return idx + 11;   // types      5..19  -> 16..30
+  if (idx < 26) return idx - 15;   // boosts    20..25  ->  5..10
+  if (idx < 42) return idx + 5;    // flags     26..41  -> 31..46
+  if (idx < 45) return idx - 31;   // state/substitute/toxic 42..44 -> 11..13
+  return idx + 2;                  // moves, durations  45..228 -> 47..230
+}
+
+struct Params {
+  const uint8_t* wpack;
+  const Chunk* prog;
+  const float* consts;
+  const float *p1bW, *p1bb, *p2bW, *p2bb;
+  int nchunks, act, pod, aod, vhd, pohd;
+};
+
+// AoS record (384 B, 16-byte aligned) -> this thread's column of the word-transposed tile
+__device__ __forceinline__ void load_record(uint32_t* col, const uint8_t* record) {
+  const uint4* src = reinterpret_cast<const uint4*>(record);
+#pragma unroll 6
+  for (int k = 0; k < 24; k++) {
+    const uint4 v = __ldg(src + k);
+    col[(4 * k + 0) * ROWS] = v.x;
+    col[(4 * k + 1) * ROWS] = v.y;
+    col[(4 * k + 2) * ROWS] = v.z;
+    col[(4 * k + 3) * ROWS] = v.w;
+  }
+}
+
+__device__ __forceinline__ void st16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory"); }
+__device__ __forceinline__ void stv4(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ uint32_t elem(uint32_t plane, int r, int k) { return plane + (uint32_t)((((k >> 3) * ROWS + r) << 4) + ((k & 7) << 1)); }
+__device__ __forceinline__ float actf(float x, int act) {
+  x = fmaxf(x, 0.0f);
+  return act == 2 ? fminf(x, 1.0f) : x;
+}
+__device__ __forceinline__ uint32_t bf16_count(int c) {  // 1.0, 2.0, 3.0, 4.0
+  return c == 1 ? 0x3F80u : c == 2 ? 0x4000u : c == 3 ? 0x4040u : 0x4080u;
+}
+
+// eight consecutive K elements of one row -> one 16-byte store per plane
+struct Row8 {
+  uint32_t h[4], l[4];
+  __device__ __forceinline__ void set(int i, float x) {
+    uint32_t hi, lo;
+    umma::split_bf16(x, hi, lo);
+    if (i & 1) { h[i >> 1] |= hi << 16; l[i >> 1] |= lo << 16; }
+    else { h[i >> 1] = hi; l[i >> 1] = lo; }
+  }
+  __device__ __forceinline__ void store(uint32_t hi_plane, uint32_t lo_plane, int core, int r) const {
+    const uint32_t o = (uint32_t)((core * ROWS + r) << 4);
+    stv4(hi_plane + o, h[0], h[1], h[2], h[3]);
+    stv4(lo_plane + o, l[0], l[1], l[2], l[3]);
+  }
+};
+
+// one-hot entries for up to four move slots, summing duplicates as the reference's sparse list does
+__device__ __forceinline__ void put_moves(uint32_t plane, int r, int col0, const uint32_t (&id)[4], const uint32_t (&pp)[4]) {
+  bool ok[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) ok[k] = id[k] != MOVE_None && id[k] != MOVE_Struggle && pp[k] != 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    if (!ok[k]) continue;
+    int cnt = 0;
+    bool first = true;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const bool same = ok[j] && id[j] == id[k];
+      cnt += same ? 1 : 0;
+      if (j < k && same) first = false;
+    }
+    if (first) st16(elem(plane, r, col0 + (int)id[k] - 1), bf16_count(cnt));
+  }
+}
+
+// Pokemon block (battle.h:208-214): K = 208, columns as in the reference (stats 0-4 are the real-valued ones)
+__device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<ROWS>& m, H pk, uint32_t sleep, bool alive) {
+  const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+#pragma unroll 5
+  for (int c = 1; c < K_POK / 8; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
+  stv4(lo + (uint32_t)((ROWS + r) << 4), 0, 0, 0, 0);
+  Row8 q;
+  q.h[2] = q.h[3] = q.l[2] = q.l[3] = 0;
+  if (!alive) {
+    q.h[0] = q.h[1] = q.l[0] = q.l[1] = 0;
+    q.store(hi, lo, 0, r);
+    return;
+  }
+#pragma unroll
+  for (int c = 0; c < 5; c++) q.set(c, (float)m.ld16(pk, PK_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
+  q.store(hi, lo, 0, r);
+  uint32_t id[4], pp[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    id[k] = m.ld8(pk, PK_MOVES + 2 * k);
+    pp[k] = m.ld8(pk, PK_MOVES + 2 * k + 1);
+  }
+  put_moves(hi, r, 5, id, pp);
+  const uint32_t st = m.ld8(pk, PK_STATUS);
+  if (st) st16(elem(hi, r, 169 + status_index(st, sleep)), 0x3F80u);
+  const uint32_t ty = m.ld8(pk, PK_TYPES), t1 = ty & 15u, t2 = ty >> 4;
+  st16(elem(hi, r, 183 + (int)t1), 0x3F80u);
+  if (t2 != t1) st16(elem(hi, r, 183 + (int)t2), 0x3F80u);
+}
+
+// Active block (battle.h:480-489) with the act_col() column order: K = 240, real-valued columns 0-13
+__device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROWS>& m, int s, uint32_t dur, bool alive) {
+  const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+#pragma unroll 4
+  for (int c = 2; c < K_ACT / 8; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
+  Row8 q0, q1;
+  if (!alive) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) q0.h[i] = q0.l[i] = q1.h[i] = q1.l[i] = 0;
+    q0.store(hi, lo, 0, r);
+    q1.store(hi, lo, 1, r);
+    return;
+  }
+  const H sb = Mem<ROWS>::sb(s);
+#pragma unroll
+  for (int c = 0; c < 5; c++) q0.set(c, (float)m.ld16(sb, A_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
+  const uint32_t b = m.ld32(sb, A_BOOSTS) & 0xFFFFFFu;
+  float bv[6];
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const int stage = boost_get(b, k);
+    bv[k] = ((float)boost_num(stage) / (float)boost_den(stage)) * (k < 4 ? 0.25f : (1.0f / 3.0f));
+  }
+  q0.set(5, bv[0]);
+  q0.set(6, bv[1]);
+  q0.set(7, bv[2]);
+  q1.set(0, bv[3]);
+  q1.set(1, bv[4]);
+  q1.set(2, bv[5]);
+  const uint32_t vlo = m.vlo(s), vhi = m.vhi(s);
+  q1.set(3, (float)((vlo >> 24) | ((vhi & 255u) << 8)) / 65535.0f);
+  q1.set(4, (float)bf_get(vhi, VHI_SUBSTITUTE) / 177.0f);
+  q1.set(5, (float)bf_get(vhi, VHI_TOXIC) / 16.0f);
+  q1.h[3] = q1.l[3] = 0;
+  q0.store(hi, lo, 0, r);
+  q1.store(hi, lo, 1, r);
+  const uint32_t ty = m.ld8(sb, A_TYPES), t1 = ty & 15u, t2 = ty >> 4;
+  st16(elem(hi, r, 16 + (int)t1), 0x3F80u);
+  if (t2 != t1) st16(elem(hi, r, 16 + (int)t2), 0x3F80u);
+  // bide thrashing | charging binding invulnerable confusion mist focus_energy substitute recharging rage leech_seed
+  // toxic light_screen reflect transform (MultiHit = bit 2 and Flinch = bit 3 are not encoded)
+  uint32_t fl = (vlo & 3u) | ((vlo >> 2) & 0xFFFCu);
+  while (fl) {
+    const int j = __ffs(fl) - 1;
+    fl &= fl - 1;
+    st16(elem(hi, r, 31 + j), 0x3F80u);
+  }
+  uint32_t id[4], pp[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    id[k] = m.ld8(sb, A_MOVES + 2 * k);
+    pp[k] = m.ld8(sb, A_MOVES + 2 * k + 1);
+  }
+  put_moves(hi, r, 47, id, pp);
+  uint32_t n;
+  if ((n = bf_get(dur, DF_CONFUSION)) != 0) st16(elem(hi, r, 211 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_DISABLE)) != 0) st16(elem(hi, r, 216 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_ATTACKING)) != 0) st16(elem(hi, r, 224 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_BINDING)) != 0) st16(elem(hi, r, 227 + (int)n - 1), 0x3F80u);
+}
+
+// D[:, 0..32*blocks) -> act(D + bias) -> split planes (K = 32 * blocks)
+__device__ __forceinline__ void epilogue_dense(uint32_t taddr, int blocks, const float* bias, int act, uint32_t hi, uint32_t lo, int r) {
+  for (int q = 0; q < blocks; q++) {
+    uint32_t v[32];
+    umma::tmem_ld32(taddr + 32u * q, v);
+    umma::tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      Row8 o;
+#pragma unroll
+      for (int i = 0; i < 8; i++) o.set(i, actf(__uint_as_float(v[8 * g + i]) + bias[32 * q + 8 * g + i], act));
+      o.store(hi, lo, 4 * q + g, r);
+    }
+  }
+}
+
+// embedding epilogue: columns 0..od-1 = act(D + bias), column od = hp / max hp, the rest 0; all 0 for an empty slot
+__device__ __forceinline__ void epilogue_embed(uint32_t taddr, int blocks, int od, const float* bias, int act, float hp, bool alive,
+                                               uint32_t hi, uint32_t lo, int r) {
+  for (int q = 0; q < blocks; q++) {
+    uint32_t v[32];
+    umma::tmem_ld32(taddr + 32u * q, v);
+    umma::tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      Row8 o;
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int j = 32 * q + 8 * g + i;
+        float x = 0.0f;
+        if (alive) x = j < od ? actf(__uint_as_float(v[8 * g + i]) + bias[j], act) : (j == od ? hp : 0.0f);
+        o.set(i, x);
+      }
+      o.store(hi, lo, 4 * q + g, r);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __restrict__ durations, const uint8_t* __restrict__ results,
+               float* __restrict__ values, float* __restrict__ logits, uint8_t* __restrict__ counts, uint32_t n) {
+  extern __shared__ __align__(1024) uint8_t dsm[];
+  const uint32_t smem = umma::smem_u32(dsm);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t bar = smem + OFF_BAR;
+  const uint32_t bar_full = bar, bar_empty = bar + 32, bar_a = bar + 64, bar_d = bar + 72, bar_t = bar + 80;
+  const uint32_t ntiles = (n + ROWS - 1) / ROWS;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < (int)RING_SLOTS; i++) {
+      umma::mbar_init(bar_full + 8 * i, 1);
+      umma::mbar_init(bar_empty + 8 * i, 1);
+    }
+    umma::mbar_init(bar_a, ROWS);
+    umma::mbar_init(bar_d, 1);
+    umma::mbar_init(bar_t, 1);
+    umma::mbar_fence_init();
+  }
+  if (warp == 4) umma::tmem_alloc(smem + OFF_TMEM_SLOT, TMEM_COLS);
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(P.prog);
+    uint4* dst = reinterpret_cast<uint4*>(dsm + OFF_PROG);
+    for (int i = threadIdx.x; i < P.nchunks; i += THREADS) dst[i] = src[i];
+    float* cdst = reinterpret_cast<float*>(dsm + OFF_CONST);
+    for (int i = threadIdx.x; i < (int)CONST_FLOATS; i += THREADS) cdst[i] = P.consts[i];
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(dsm + OFF_TMEM_SLOT);
+  const Chunk* prog = reinterpret_cast<const Chunk*>(dsm + OFF_PROG);
+
+  if (warp == 4) {
+    // ===== weight streamer: packed chunks L2 -> ring =====
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        for (int c = 0; c < P.nchunks; c++, g++) {
+          const uint32_t slot = g & (RING_SLOTS - 1);
+          if (g >= RING_SLOTS) umma::mbar_wait(bar_empty + 8 * slot, ((g / RING_SLOTS) - 1) & 1);
+          const uint32_t bytes = (uint32_t)prog[c].bytes16 << 4;
+          umma::mbar_expect_tx(bar_full + 8 * slot, bytes);
+          umma::bulk_g2s(smem + OFF_RING + slot * RING_SLOT, P.wpack + ((size_t)prog[c].gofs16 << 4), bytes, bar_full + 8 * slot);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      uint32_t g = 0, stage = 0;
+      for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        for (int c = 0; c < P.nchunks; c++, g++) {
+          const Chunk ch = prog[c];
+          if (ch.flags & F_STAGE_BEGIN) {
+            umma::mbar_wait(bar_a, stage & 1);
+            stage++;
+          }
+          const uint32_t slot = g & (RING_SLOTS - 1);
+          umma::mbar_wait(bar_full + 8 * slot, (g / RING_SLOTS) & 1);
+          umma::tc_fence_after();
+          const uint32_t N = (uint32_t)ch.n8 << 3;
+          const uint32_t idesc = umma::idesc_bf16_f32(N);
+          const uint32_t kstep_b = N * 32;  // bytes of one K = 16 step of B (two core columns of N rows)
+          const uint32_t b_hi = smem + OFF_RING + slot * RING_SLOT, b_lo = b_hi + ch.ksteps * kstep_b;
+          const uint32_t a_hi = smem + ((uint32_t)ch.a_off16 << 4), a_lo = smem + ((uint32_t)ch.alo_off16 << 4);
+          const uint32_t d = tmem + ch.dcol;
+          for (uint32_t i = 0; i < ch.ksteps; i++) {
+            const uint64_t da = umma::smem_desc(a_hi + i * 2 * CORE, CORE, 128);
+            const uint64_t dbh = umma::smem_desc(b_hi + i * kstep_b, N * 16, 128);
+            const uint64_t dbl = umma::smem_desc(b_lo + i * kstep_b, N * 16, 128);
+            umma::mma_bf16(d, da, dbh, idesc, ((ch.flags & F_OVERWRITE) && i == 0) ? 0u : 1u);
+            umma::mma_bf16(d, da, dbl, idesc, 1u);
+            if (i < ch.lo_steps) umma::mma_bf16(d, umma::smem_desc(a_lo + i * 2 * CORE, CORE, 128), dbh, idesc, 1u);
+          }
+          umma::mma_commit(bar_empty + 8 * slot);
+          if (ch.flags & F_END_D) umma::mma_commit(bar_d);
+          if (ch.flags & F_END_T) umma::mma_commit(bar_t);
+        }
+      }
+    }
+  } else {
+    // ===== workers: thread r = evaluation r of the tile = TMEM lane r =====
+    const int r = threadIdx.x;
+    uint32_t* col = reinterpret_cast<uint32_t*>(dsm + OFF_TILE) + r;
+    Mem<ROWS> m;
+    m.set(reinterpret_cast<uint8_t*>(col));
+    const float* cst = reinterpret_cast<const float*>(dsm + OFF_CONST);
+    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t dphase = 0, tphase = 0;
+    bool t_pending = false;
+    const int act = P.act;
+    auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
+      umma::tc_fence_before();
+      umma::fence_proxy_async();
+      umma::mbar_arrive(bar_a);
+    };
+    auto wait_d = [&]() {
+      umma::mbar_wait(bar_d, dphase & 1);
+      dphase++;
+      umma::tc_fence_after();
+    };
+    auto wait_t = [&]() {
+      if (t_pending) {
+        umma::mbar_wait(bar_t, tphase & 1);
+        tphase++;
+        t_pending = false;
+        umma::tc_fence_after();
+      }
+    };
+    for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      const uint32_t e = t * ROWS + (uint32_t)r;
+      const uint32_t ec = e < n ? e : n - 1;
+      load_record(col, battles + (size_t)ec * 384);
+      const uint2 durw = *reinterpret_cast<const uint2*>(durations + (size_t)ec * 8);
+      for (int s = 0; s < 2; s++) {
+        const H sb = Mem<ROWS>::sb(s);
+        const uint32_t dur = s ? durw.y : durw.x;
+        for (int slot = 1; slot <= 6; slot++) {
+          const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
+          H pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
+          const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
+          const bool alive = hpv != 0;
+          const float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
+          if (slot == 1) {
+            build_active(smem, r, m, s, dur, alive);
+            wait_t();
+            publish();
+            wait_d();
+          }
+          build_pokemon(smem, r, m, pk, sleep, alive);
+          wait_t();
+          publish();
+          wait_d();
+          epilogue_dense(tl + D_WORK, 4, cst + (slot == 1 ? C_AC0 : C_PK0), act, smem + A2_HI, smem + A2_LO, r);
+          publish();
+          wait_d();
+          if (slot == 1) epilogue_embed(tl + D_WORK, 3, P.aod, cst + C_AC1, act, hp, alive, smem + AEA_HI, smem + AEA_LO, r);
+          else epilogue_embed(tl + D_WORK, 2, P.pod, cst + C_PK1, act, hp, alive, smem + AEP_HI, smem + AEP_LO, r);
+          publish();
+          t_pending = true;
+          if (slot == 1) wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
+        }
+      }
+      // ---- trunk (main-net.h:66-107)
+      wait_t();
+      epilogue_dense(tl + D_TRUNK, 2, cst + C_FC0, act, smem + AT_HI, smem + AT_LO, r);
+      publish();
+      wait_d();
+      epilogue_dense(tl + D_WORK, 2, cst + C_FC1, act, smem + AEP_HI, smem + AEP_LO, r);
+      publish();
+      wait_d();
+      {
+        uint32_t v[32];
+        umma::tmem_ld32(tl + D_WORK, v);
+        umma::tmem_ld_wait();
+        float acc = cst[C_V3B];
+#pragma unroll
+        for (int j = 0; j < 32; j++)
+          if (j < P.vhd) acc = fmaf(actf(__uint_as_float(v[j]) + cst[C_HEADS + j], act), cst[C_V3W + j], acc);
+        if (e < n) values[e] = 1.0f / (1.0f + expf(-acc));
+      }
+      const uint32_t res = results[ec];
+      for (int s = 0; s < 2; s++) {
+        float h[64];
+        {
+          uint32_t v[32];
+          umma::tmem_ld32(tl + D_WORK + 32 + 64 * s, v);
+          umma::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j++) h[j] = actf(__uint_as_float(v[j]) + cst[C_HEADS + 32 + 64 * s + j], act);
+          umma::tmem_ld32(tl + D_WORK + 64 + 64 * s, v);
+          umma::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j++) h[32 + j] = actf(__uint_as_float(v[j]) + cst[C_HEADS + 64 + 64 * s + j], act);
+        }
+        const uint64_t list = mem_choices(m, s, (res >> (4 + 2 * s)) & 3);
+        const int cnt = choice_count(list);
+        const float* W = s == 0 ? P.p1bW : P.p2bW;
+        const float* B = s == 0 ? P.p1bb : P.p2bb;
+        const H sb = Mem<ROWS>::sb(s);
+        for (int k = 0; k < 9; k++) {
+          float lg = 0.0f;
+          if (k < cnt) {
+            const uint32_t c = choice_at(list, k);
+            const uint32_t type = c & 3, data = c >> 2;
+            uint32_t idx = 0;  // policy.h:29-58
+            if (type == CH_MOVE) {
+              const uint32_t mid = data >= 1 ? m.ld8(m.stored(s), PK_MOVES + 2 * ((int)data - 1)) : 0;
+              idx = mid == 0 ? 0 : mid - 1;
+            } else if (type == CH_SWITCH) {
+              const uint32_t pid = m.ld8(sb, S_ORDER + (int)data - 1);
+              idx = 164 + m.ld8(Mem<ROWS>::pokemon(s, (int)pid - 1), PK_SPECIES) - 1;
+            }
+            const float4* row = reinterpret_cast<const float4*>(W + (size_t)idx * P.pohd);
+            float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              if (4 * j < P.pohd) {
+                const float4 w = __ldg(row + j);
+                a0 = fmaf(h[4 * j + 0], w.x, a0);
+                a1 = fmaf(h[4 * j + 1], w.y, a1);
+                a0 = fmaf(h[4 * j + 2], w.z, a0);
+                a1 = fmaf(h[4 * j + 3], w.w, a1);
+              }
+            }
+            lg = a0 + a1 + __ldg(B + idx);
+          }
+          if (e < n) logits[(size_t)e * 18 + s * 9 + k] = lg;
+        }
+        if (e < n) counts[(size_t)e * 2 + s] = (uint8_t)cnt;
+      }
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+}  // namespace tc

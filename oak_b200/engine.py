@@ -59,6 +59,7 @@ def load_library():
         "oakb200_randomize_hidden_device": (i32, [vp, sz, vp, vp]),
         "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
         "oakb200_net_load": (i32, [vp, vp, sz]),
+        "oakb200_eval_set_mode": (i32, [vp, i32]),
         "oakb200_eval": (i32, [vp, vp, vp, vp]),
         "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
     }
@@ -197,6 +198,10 @@ class BattleEngine:
             blob = np.fromfile(blob, np.uint8)
         blob = np.frombuffer(bytes(blob), np.uint8) if isinstance(blob, (bytes, bytearray)) else _np(blob, np.uint8)
         self._check(self.lib.oakb200_net_load(self._h, _ptr(blob), blob.size))
+
+    def set_eval_mode(self, mode):
+        """0 auto (tensor cores when the layer shapes fit), 1 fp32 CUDA-core kernel, 2 tensor cores or error."""
+        self._check(self.lib.oakb200_eval_set_mode(self._h, int(mode)))
 
     def evaluate(self):
         """value_policy_inference for every resident battle -> (value[n] f32, logits[n,2,9] f32, counts[n,2] u8)."""
