@@ -18,8 +18,8 @@
 // One-hot feature columns are exact in bf16, so the first layer needs its A_lo plane only for the 14 real-valued
 // columns, which the host-side packing permutes to the front of K.
 //
-// Roles: warps 0-3 workers (encode, epilogues), warp 4 lane 0 streams weight chunks L2 -> shared memory with
-// cp.async.bulk through a 4-slot mbarrier ring (and owns the TMEM allocation), warp 5 lane 0 issues tcgen05.mma.
+// Roles: warps 0-3 workers (encode, epilogues), warps 4-7 a second thread per row (the two split every epilogue by columns), warp 8 lane 0 streams weight chunks L2 -> shared memory with
+// cp.async.bulk through a 4-slot mbarrier ring (and owns the TMEM allocation), warp 9 lane 0 issues tcgen05.mma.
 // The per-tile schedule is a static chunk program built on the host at oakb200_net_load.
 #pragma once
 
@@ -44,7 +44,9 @@ struct Chunk {        // 16 bytes; one weight chunk = `ksteps` K=16 steps of a [
 enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8 };
 
 const int ROWS = 128;
-const int THREADS = 192;
+const int WORKERS = 256;  // two threads per row: they split the epilogue columns
+const int THREADS = WORKERS + 64;
+const int W_STREAM = WORKERS / 32, W_MMA = WORKERS / 32 + 1;
 const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden) / active embedding / trunk input
 const uint32_t OFF_EMB = 65536;      // benched-Pokemon embedding / second trunk operand
 const uint32_t OFF_TILE = 98304;     // 128 battle records as word-transposed columns (gen1_state.cuh)
@@ -91,11 +93,11 @@ struct Params {
   int nchunks, act, pod, aod, vhd, pohd;
 };
 
-// AoS record (384 B, 16-byte aligned) -> this thread's column of the word-transposed tile
-__device__ __forceinline__ void load_record(uint32_t* col, const uint8_t* record) {
+// AoS record (384 B, 16-byte aligned) -> column of the word-transposed tile; the two threads of a row take half each
+__device__ __forceinline__ void load_record_half(uint32_t* col, const uint8_t* record, int half) {
   const uint4* src = reinterpret_cast<const uint4*>(record);
 #pragma unroll 6
-  for (int k = 0; k < 24; k++) {
+  for (int k = 12 * half; k < 12 * half + 12; k++) {
     const uint4 v = __ldg(src + k);
     col[(4 * k + 0) * ROWS] = v.x;
     col[(4 * k + 1) * ROWS] = v.y;
@@ -244,42 +246,47 @@ __device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROW
   if ((n = bf_get(dur, DF_BINDING)) != 0) st16(elem(hi, r, 227 + (int)n - 1), 0x3F80u);
 }
 
-// D[:, 0..32*blocks) -> act(D + bias) -> split planes (K = 32 * blocks)
-__device__ __forceinline__ void epilogue_dense(uint32_t taddr, int blocks, const float* bias, int act, uint32_t hi, uint32_t lo, int r) {
-  for (int q = 0; q < blocks; q++) {
-    uint32_t v[32];
-    umma::tmem_ld32(taddr + 32u * q, v);
-    umma::tmem_ld_wait();
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-      Row8 o;
-#pragma unroll
-      for (int i = 0; i < 8; i++) o.set(i, actf(__uint_as_float(v[8 * g + i]) + bias[32 * q + 8 * g + i], act));
-      o.store(hi, lo, 4 * q + g, r);
-    }
-  }
+// two fp32 -> packed split-bf16: hi = {bf16(x1), bf16(x0)}, lo = the rounded residuals (x0 in the low half)
+__device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(x1), "f"(x0));
+  const float r0 = x0 - __uint_as_float(hi << 16), r1 = x1 - __uint_as_float(hi & 0xFFFF0000u);
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
 }
 
-// embedding epilogue: columns 0..od-1 = act(D + bias), column od = hp / max hp, the rest 0; all 0 for an empty slot
-__device__ __forceinline__ void epilogue_embed(uint32_t taddr, int blocks, int od, const float* bias, int act, float hp, bool alive,
-                                               uint32_t hi, uint32_t lo, int r) {
-  for (int q = 0; q < blocks; q++) {
-    uint32_t v[32];
-    umma::tmem_ld32(taddr + 32u * q, v);
-    umma::tmem_ld_wait();
+// One 32-column block of an accumulator: D[:, 32q .. 32q+31] -> min(max(D + bias, 0), bound) -> split planes, core
+// columns 4q .. 4q+3. bound = 1 for the clamp activation, +inf for ReLU, 0 for an empty slot's row.
+__device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
+  uint32_t v[32];
+  umma::tmem_ld32(taddr + 32u * q, v);
+  umma::tmem_ld_wait();
+  const float4* b4 = reinterpret_cast<const float4*>(bias + 32 * q);
 #pragma unroll
-    for (int g = 0; g < 4; g++) {
-      Row8 o;
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        const int j = 32 * q + 8 * g + i;
-        float x = 0.0f;
-        if (alive) x = j < od ? actf(__uint_as_float(v[8 * g + i]) + bias[j], act) : (j == od ? hp : 0.0f);
-        o.set(i, x);
-      }
-      o.store(hi, lo, 4 * q + g, r);
-    }
+  for (int g = 0; g < 4; g++) {
+    const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
+    const float x0 = fminf(fmaxf(__uint_as_float(v[8 * g + 0]) + ba.x, 0.0f), bound);
+    const float x1 = fminf(fmaxf(__uint_as_float(v[8 * g + 1]) + ba.y, 0.0f), bound);
+    const float x2 = fminf(fmaxf(__uint_as_float(v[8 * g + 2]) + ba.z, 0.0f), bound);
+    const float x3 = fminf(fmaxf(__uint_as_float(v[8 * g + 3]) + ba.w, 0.0f), bound);
+    const float x4 = fminf(fmaxf(__uint_as_float(v[8 * g + 4]) + bb.x, 0.0f), bound);
+    const float x5 = fminf(fmaxf(__uint_as_float(v[8 * g + 5]) + bb.y, 0.0f), bound);
+    const float x6 = fminf(fmaxf(__uint_as_float(v[8 * g + 6]) + bb.z, 0.0f), bound);
+    const float x7 = fminf(fmaxf(__uint_as_float(v[8 * g + 7]) + bb.w, 0.0f), bound);
+    uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
+    split2(x0, x1, h0, l0);
+    split2(x2, x3, h1, l1);
+    split2(x4, x5, h2, l2);
+    split2(x6, x7, h3, l3);
+    const uint32_t o = (uint32_t)(((4 * q + g) * ROWS + r) << 4);
+    stv4(hi + o, h0, h1, h2, h3);
+    stv4(lo + o, l0, l1, l2, l3);
   }
+}
+// the hp / max-hp column of an embedding operand (written after the block stores of the same thread)
+__device__ __forceinline__ void put_hp(uint32_t hi, uint32_t lo, int r, int col, float hp) {
+  uint32_t h, l;
+  umma::split_bf16(hp, h, l);
+  st16(elem(hi, r, col), h);
+  st16(elem(lo, r, col), l);
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -297,12 +304,12 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       umma::mbar_init(bar_full + 8 * i, 1);
       umma::mbar_init(bar_empty + 8 * i, 1);
     }
-    umma::mbar_init(bar_a, ROWS);
+    umma::mbar_init(bar_a, WORKERS);
     umma::mbar_init(bar_d, 1);
     umma::mbar_init(bar_t, 1);
     umma::mbar_fence_init();
   }
-  if (warp == 4) umma::tmem_alloc(smem + OFF_TMEM_SLOT, TMEM_COLS);
+  if (warp == W_STREAM) umma::tmem_alloc(smem + OFF_TMEM_SLOT, TMEM_COLS);
   {
     const uint4* src = reinterpret_cast<const uint4*>(P.prog);
     uint4* dst = reinterpret_cast<uint4*>(dsm + OFF_PROG);
@@ -316,7 +323,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(dsm + OFF_TMEM_SLOT);
   const Chunk* prog = reinterpret_cast<const Chunk*>(dsm + OFF_PROG);
 
-  if (warp == 4) {
+  if (warp == W_STREAM) {
     // ===== weight streamer: packed chunks L2 -> ring =====
     if (lane == 0) {
       uint32_t g = 0;
@@ -330,7 +337,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == W_MMA) {
     // ===== MMA issuer =====
     if (lane == 0) {
       uint32_t g = 0, stage = 0;
@@ -365,16 +372,18 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       }
     }
   } else {
-    // ===== workers: thread r = evaluation r of the tile = TMEM lane r =====
-    const int r = threadIdx.x;
+    // ===== workers: threads r and r + 128 share evaluation r of the tile = TMEM lane r; group 0 encodes, and the
+    // two groups split every epilogue by accumulator columns (a warp may touch TMEM lanes 32 * (warp % 4) .. + 31)
+    const int r = threadIdx.x & (ROWS - 1), grp = threadIdx.x >> 7;
     uint32_t* col = reinterpret_cast<uint32_t*>(dsm + OFF_TILE) + r;
     Mem<ROWS> m;
     m.set(reinterpret_cast<uint8_t*>(col));
     const float* cst = reinterpret_cast<const float*>(dsm + OFF_CONST);
-    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     uint32_t dphase = 0, tphase = 0;
     bool t_pending = false;
     const int act = P.act;
+    const float act_bound = act == 2 ? 1.0f : __int_as_float(0x7F800000);
     auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
       umma::tc_fence_before();
       umma::fence_proxy_async();
@@ -396,8 +405,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const uint32_t e = t * ROWS + (uint32_t)r;
       const uint32_t ec = e < n ? e : n - 1;
-      load_record(col, battles + (size_t)ec * 384);
+      asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory");  // the other group has finished with the previous tile
+      load_record_half(col, battles + (size_t)ec * 384, grp);
       const uint2 durw = *reinterpret_cast<const uint2*>(durations + (size_t)ec * 8);
+      asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory");
       for (int s = 0; s < 2; s++) {
         const H sb = Mem<ROWS>::sb(s);
         const uint32_t dur = s ? durw.y : durw.x;
@@ -407,22 +418,37 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
           const bool alive = hpv != 0;
           const float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
           const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
           if (slot == 1) {
-            build_active(smem, r, m, s, dur, alive);
+            if (grp == 0) build_active(smem, r, m, s, dur, alive);
             wait_t();
             publish();
             wait_d();
           }
-          build_pokemon(smem, r, m, pk, sleep, alive);
+          if (grp == 0) build_pokemon(smem, r, m, pk, sleep, alive);
           wait_t();
           publish();
           wait_d();
-          epilogue_dense(tl + D_WORK, 4, cst + (slot == 1 ? C_AC0 : C_PK0), act, smem + A2_HI, smem + A2_LO, r);
+          {
+            const float* b0 = cst + (slot == 1 ? C_AC0 : C_PK0);
+            epilogue_block(tl + D_WORK, 2 * grp, b0, act_bound, smem + A2_HI, smem + A2_LO, r);
+            epilogue_block(tl + D_WORK, 2 * grp + 1, b0, act_bound, smem + A2_HI, smem + A2_LO, r);
+          }
           publish();
           wait_d();
-          if (slot == 1) epilogue_embed(tl + D_WORK, 3, P.aod, cst + C_AC1, act, hp, alive, smem + AEA_HI, smem + AEA_LO, r);
-          else epilogue_embed(tl + D_WORK, 2, P.pod, cst + C_PK1, act, hp, alive, smem + AEP_HI, smem + AEP_LO, r);
+          if (slot == 1) {  // 96 columns: group 0 takes 0..63, group 1 takes 64..95 (and the hp column aod >= 64 or not)
+            if (grp == 0) {
+              epilogue_block(tl + D_WORK, 0, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
+              epilogue_block(tl + D_WORK, 1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
+            } else {
+              epilogue_block(tl + D_WORK, 2, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
+            }
+            if ((P.aod >= 64) == (grp == 1)) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
+          } else {
+            epilogue_block(tl + D_WORK, grp, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, r);
+            if ((P.pod >= 32) == (grp == 1)) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
+          }
           publish();
           t_pending = true;
           if (slot == 1) wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
@@ -430,13 +456,13 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       }
       // ---- trunk (main-net.h:66-107)
       wait_t();
-      epilogue_dense(tl + D_TRUNK, 2, cst + C_FC0, act, smem + AT_HI, smem + AT_LO, r);
+      epilogue_block(tl + D_TRUNK, grp, cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, r);
       publish();
       wait_d();
-      epilogue_dense(tl + D_WORK, 2, cst + C_FC1, act, smem + AEP_HI, smem + AEP_LO, r);
+      epilogue_block(tl + D_WORK, grp, cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, r);
       publish();
       wait_d();
-      {
+      if (grp == 0) {
         uint32_t v[32];
         umma::tmem_ld32(tl + D_WORK, v);
         umma::tmem_ld_wait();
@@ -446,8 +472,9 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           if (j < P.vhd) acc = fmaf(actf(__uint_as_float(v[j]) + cst[C_HEADS + j], act), cst[C_V3W + j], acc);
         if (e < n) values[e] = 1.0f / (1.0f + expf(-acc));
       }
-      const uint32_t res = results[ec];
-      for (int s = 0; s < 2; s++) {
+      {
+        const int s = grp;  // group 0: player 1's policy head, group 1: player 2's
+        const uint32_t res = results[ec];
         float h[64];
         {
           uint32_t v[32];
@@ -500,7 +527,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   }
   umma::tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == W_STREAM) {
     umma::tc_fence_after();
     umma::tmem_dealloc(tmem, TMEM_COLS);
   }
