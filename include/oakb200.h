@@ -131,6 +131,49 @@ int oakb200_eval(oakb200_ctx* ctx, float* value_out, float* logits_out, uint8_t*
 int oakb200_eval_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* durations, const void* results,
                         void* value_out, void* logits_out, void* counts_out);
 
+/* Rebuild, in place, every battle of the batch whose result byte says it has ended (PKMN::battle + update(0,0) as
+ * oakb200_build_battles; teams[n][2][6][5] and seeds[n] are DEVICE arrays, only the entries of ended slots are read).
+ * Replaces the "next game" step of the generate loop (cpp/src/generate.cc:218-240). */
+int oakb200_respawn_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* teams,
+                           const void* seeds);
+
+/* ---- policy post-processing + sampling (cpp/include/util/policy.h:76-107, util/random.h:41-50, search/util/softmax.h) ----
+ * For every battle and both players: probs = softmax(logits over the legal choices) (fp32); then, in double,
+ * p^temperature renormalised, entries below min_prob zeroed, renormalised; the choice is drawn as sample_pdf does with
+ * u = (splitmix64(seeds[i] ^ 0xD1B54A32D192ED03 * step_index ^ player) >> 11) * 2^-53.
+ * choices[n][2][9], counts[n][2] as oakb200_choices_device writes them; logits[n][2][9] as oakb200_eval_device writes them.
+ * Out: probs_out[n][2][9] f32 (the softmax, unused entries 0), c1_out[n], c2_out[n]. DEVICE pointers. */
+int oakb200_policy_sample_device(oakb200_ctx* ctx, size_t n, const void* choices, const void* counts, const void* logits,
+                                 const void* seeds, uint32_t step_index, double temperature, double min_prob, void* probs_out,
+                                 void* c1_out, void* c2_out);
+
+/* ---- training-frame recorder / writer -----------------------------------------------------------------------------
+ * Replaces Train::Battle::CompressedFrames (cpp/include/train/battle/compressed-frame.h:36-199) and the per-thread
+ * frame buffer of generate (cpp/src/generate.cc:161-188,344-359; cpp/include/util/battle-frame-buffer.h) for `games`
+ * concurrent games, slot i recording the batch's battle i. The stream oakb200_frames_drain returns is the concatenation
+ * of the finished games' records, byte-identical to what the reference appends to an N.battle.data file:
+ *   u32 n_bytes | u16 n_updates | battle[384] | result | { u8 (m-1)|(n-1)<<4, c1, c2, u32 iterations,
+ *   u16 empirical_value, u16 nash_value, u16 p1_empirical[m], p1_nash[m], p2_empirical[n], p2_nash[n] }*
+ * with probabilities and values stored as (uint16)(x * 65535) (compress_probs, compressed-frame.h:12-24).
+ * A game longer than max_updates is dropped when it ends (the reference discards games over --max-battle-length,
+ * generate.cc:268-271,333-336). */
+int oakb200_frames_create(oakb200_ctx* ctx, size_t games, uint32_t max_updates);
+/* Start recording in every idle slot whose battle is not over: snapshots battle[384] (DEVICE pointers). */
+int oakb200_frames_begin_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* results);
+/* Append one update to every recording slot whose battle (result byte BEFORE the update) is still running.
+ * c1/c2[n] the choices made; counts[n][2] the legal-choice counts (m, n); iterations[n] u32 or NULL (0);
+ * empirical_value/nash_value[n] f32; empirical/nash[n][2][9] f32 probabilities in choices order. DEVICE pointers. */
+int oakb200_frames_record_device(oakb200_ctx* ctx, size_t n, const void* results, const void* c1, const void* c2, const void* counts,
+                                 const void* iterations, const void* empirical_value, const void* nash_value,
+                                 const void* empirical, const void* nash);
+/* Close every recording slot whose battle has ended (result byte AFTER the update): header + result. */
+int oakb200_frames_finish_device(oakb200_ctx* ctx, size_t n, const void* results);
+/* Finished games waiting to be drained / games dropped for length so far (synchronises). */
+int oakb200_frames_pending(oakb200_ctx* ctx, uint32_t* finished, uint32_t* dropped);
+/* Pack the finished games in slot order into out[cap] (HOST), free their slots. *bytes = stream length (also set when
+ * the call fails with OAKB200_ECAPACITY), *games = how many games it holds. */
+int oakb200_frames_drain(oakb200_ctx* ctx, uint8_t* out, size_t cap, size_t* bytes, uint32_t* games);
+
 #ifdef __cplusplus
 }
 #endif

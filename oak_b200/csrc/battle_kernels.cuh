@@ -265,10 +265,11 @@ __global__ void randomize_hidden_kernel(uint8_t* __restrict__ battles, const uin
 template <int BLOCK>
 __global__ void __launch_bounds__(BLOCK) build_kernel(const uint8_t* __restrict__ teams, const uint64_t* __restrict__ seeds,
                                                        uint8_t* __restrict__ battles, uint8_t* __restrict__ durations,
-                                                       uint8_t* __restrict__ results, uint32_t n) {
+                                                       uint8_t* __restrict__ results, uint32_t n, uint32_t only_finished) {
   extern __shared__ uint32_t tile[];
   const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
   if (i >= n) return;
+  if (only_finished && (results[i] & 15u) == 0) return;  // respawn: only slots whose battle has ended are rebuilt
   uint32_t* col = tile + threadIdx.x;
   for (int w = 0; w < BATTLE_WORDS; w++) col[w * BLOCK] = 0;
   Mem<BLOCK> m;

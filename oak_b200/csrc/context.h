@@ -8,7 +8,8 @@
 
 #include "../../include/oakb200.h"
 
-struct oakb200_net;  // device copy of a loaded network (value_net.cu)
+struct oakb200_net;     // device copy of a loaded network (value_net.cu)
+struct oakb200_frames;  // training-frame recorder (frame_log.cu)
 
 struct oakb200_ctx {
   int device = -1;
@@ -28,6 +29,7 @@ struct oakb200_ctx {
   unsigned long long* total_steps = nullptr;
   uint64_t launches = 0;
   oakb200_net* net = nullptr;
+  oakb200_frames* frames = nullptr;
   int eval_mode = 0;  // 0 auto (tensor cores when the shape fits), 1 fp32 CUDA-core kernel, 2 tensor cores or fail
   float* eval_values = nullptr;
   float* eval_logits = nullptr;

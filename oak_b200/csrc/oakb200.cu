@@ -21,7 +21,8 @@ const size_t TILE_BYTES = (size_t)BATTLE_WORDS * BLOCK * 4;  // 48 KB shared-mem
 
 #include "context.h"
 
-void oakb200_net_release(oakb200_ctx* ctx);  // value_net.cu
+void oakb200_net_release(oakb200_ctx* ctx);     // value_net.cu
+void oakb200_frames_release(oakb200_ctx* ctx);  // frame_log.cu
 
 namespace {
 
@@ -125,6 +126,7 @@ void oakb200_destroy(oakb200_ctx* ctx) {
                   ctx->counts,  ctx->seeds,     ctx->score2,  ctx->turns, ctx->steps, ctx->teams,     ctx->ticket,  ctx->total_steps,
                   ctx->eval_values, ctx->eval_logits, ctx->eval_counts};
   oakb200_net_release(ctx);
+  oakb200_frames_release(ctx);
   for (void* b : bufs)
     if (b) cudaFree(b);
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -317,11 +319,25 @@ int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, cons
   CU(ctx, cudaMemcpyAsync(ctx->seeds, seeds, n * 8, cudaMemcpyHostToDevice, ctx->stream));
   auto k = build_kernel<BLOCK>;
   CU(ctx, allow_smem(k));
-  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>(ctx->teams, ctx->seeds, ctx->battles, ctx->durations, ctx->results, (uint32_t)n);
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>(ctx->teams, ctx->seeds, ctx->battles, ctx->durations, ctx->results, (uint32_t)n, 0u);
   ctx->launches++;
   CU(ctx, cudaGetLastError());
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->n = n;
+  return OAKB200_OK;
+}
+
+int oakb200_respawn_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* teams,
+                           const void* seeds) {
+  if (!ctx || !battles || !durations || !results || !teams || !seeds) return fail(ctx, OAKB200_EINVAL, "respawn: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  auto k = build_kernel<BLOCK>;
+  CU(ctx, allow_smem(k));
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>((const uint8_t*)teams, (const uint64_t*)seeds, (uint8_t*)battles,
+                                                     (uint8_t*)durations, (uint8_t*)results, (uint32_t)n, 1u);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
   return OAKB200_OK;
 }
 

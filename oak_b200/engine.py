@@ -60,6 +60,14 @@ def load_library():
         "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
         "oakb200_net_load": (i32, [vp, vp, sz]),
         "oakb200_eval_set_mode": (i32, [vp, i32]),
+        "oakb200_respawn_device": (i32, [vp, sz, vp, vp, vp, vp, vp]),
+        "oakb200_policy_sample_device": (i32, [vp, sz, vp, vp, vp, vp, u32, ctypes.c_double, ctypes.c_double, vp, vp, vp]),
+        "oakb200_frames_create": (i32, [vp, sz, u32]),
+        "oakb200_frames_begin_device": (i32, [vp, sz, vp, vp]),
+        "oakb200_frames_record_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "oakb200_frames_finish_device": (i32, [vp, sz, vp]),
+        "oakb200_frames_pending": (i32, [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]),
+        "oakb200_frames_drain": (i32, [vp, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u32)]),
         "oakb200_eval": (i32, [vp, vp, vp, vp]),
         "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
     }
@@ -241,3 +249,47 @@ class BattleEngine:
 
     def randomize_hidden_device(self, battles, durations):
         self._check(self.lib.oakb200_randomize_hidden_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations)))
+
+    def respawn_device(self, battles, durations, results, teams, seeds):
+        """Rebuild in place every battle whose result says it has ended (teams[n,2,6,5], seeds[n] on the device)."""
+        self._check(self.lib.oakb200_respawn_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                    _ptr(teams), _ptr(seeds)))
+
+    # ---------------------------------------------------------------- policy sampling + training frames (device pointers)
+    def policy_sample_device(self, choices, counts, logits, seeds, step_index, probs_out, c1_out, c2_out, temperature=1.0,
+                             min_prob=0.0):
+        self._check(self.lib.oakb200_policy_sample_device(self._h, counts.shape[0], _ptr(choices), _ptr(counts), _ptr(logits),
+                                                          _ptr(seeds), int(step_index), float(temperature), float(min_prob),
+                                                          _ptr(probs_out), _ptr(c1_out), _ptr(c2_out)))
+
+    def frames_create(self, games, max_updates=1024):
+        self._check(self.lib.oakb200_frames_create(self._h, int(games), int(max_updates)))
+
+    def frames_begin_device(self, battles, results):
+        self._check(self.lib.oakb200_frames_begin_device(self._h, results.shape[0], _ptr(battles), _ptr(results)))
+
+    def frames_record_device(self, results, c1, c2, counts, empirical_value, nash_value, empirical, nash, iterations=None):
+        self._check(self.lib.oakb200_frames_record_device(self._h, results.shape[0], _ptr(results), _ptr(c1), _ptr(c2), _ptr(counts),
+                                                          _ptr(iterations), _ptr(empirical_value), _ptr(nash_value),
+                                                          _ptr(empirical), _ptr(nash)))
+
+    def frames_finish_device(self, results):
+        self._check(self.lib.oakb200_frames_finish_device(self._h, results.shape[0], _ptr(results)))
+
+    def frames_pending(self):
+        a, b = ctypes.c_uint32(), ctypes.c_uint32()
+        self._check(self.lib.oakb200_frames_pending(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def frames_drain(self, capacity=None):
+        """-> (stream bytes as a uint8 array, games in it): finished games in slot order, the reference's .battle.data format."""
+        need, games = ctypes.c_size_t(), ctypes.c_uint32()
+        if capacity is None:
+            rc = self.lib.oakb200_frames_drain(self._h, None, 0, ctypes.byref(need), ctypes.byref(games))
+            if need.value == 0:
+                self._check(rc)
+                return np.empty(0, np.uint8), 0
+            capacity = need.value
+        out = np.empty(int(capacity), np.uint8)
+        self._check(self.lib.oakb200_frames_drain(self._h, _ptr(out), out.size, ctypes.byref(need), ctypes.byref(games)))
+        return out[:need.value], games.value

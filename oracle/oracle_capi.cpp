@@ -210,3 +210,16 @@ void oracle_net_eval_batch(void* h, const uint8_t* battles, const uint8_t* durat
   for (auto& t : pool) t.join();
 }
 }
+
+// ---- training frames + policy sampling (frames_oracle.hpp) ----
+#include "frames_oracle.hpp"
+extern "C" {
+uint32_t oracle_frames_write_game(const uint8_t* battle384, uint8_t result, uint32_t n_updates, const uint8_t* k, const uint8_t* choice,
+                                  const uint32_t* iterations, const double* emp_value, const double* nash_value, const double* emp,
+                                  const double* nash, uint8_t* out) {
+  return frames_oracle::write_game(battle384, result, n_updates, k, choice, iterations, emp_value, nash_value, emp, nash, out);
+}
+int oracle_policy_sample(const float* logits, int k, double temp, double floor_p, double u, float* probs9) {
+  return frames_oracle::policy_sample(logits, k, temp, floor_p, u, probs9);
+}
+}

@@ -86,3 +86,45 @@ void ref_init_side(const uint8_t* sets30, uint8_t* side184) {
   memcpy(side184, &side, 184);
 }
 }
+
+// ---- training frames: the reference's own serialiser (train/battle/compressed-frame.h:36-199) ----
+#include <train/battle/compressed-frame.h>
+
+extern "C" {
+// One game -> bytes. k/choice are [n][2]; probabilities [n][2][9] and values are the doubles a search would output.
+uint32_t ref_frames_write_game(const uint8_t* battle384, uint8_t result, uint32_t n_updates, const uint8_t* k, const uint8_t* choice,
+                               const uint32_t* iterations, const double* emp_value, const double* nash_value, const double* emp,
+                               const double* nash, char* out) {
+  using Frames = Train::Battle::CompressedFrames;
+  pkmn_gen1_battle b;
+  memcpy(&b, battle384, 384);
+  Frames frames{b};
+  frames.result = result;
+  for (uint32_t u = 0; u < n_updates; u++) {
+    Frames::Update up{};
+    up.iterations = iterations[u];
+    up.empirical_value = Train::Battle::compress_probs<double, uint16_t>(emp_value[u]);
+    up.nash_value = Train::Battle::compress_probs<double, uint16_t>(nash_value[u]);
+    Frames::Update::Side* sides[2] = {&up.p1, &up.p2};
+    for (int s = 0; s < 2; s++) {
+      sides[s]->k = k[2 * u + s];
+      sides[s]->choice = choice[2 * u + s];
+      for (int i = 0; i < sides[s]->k; i++) {
+        sides[s]->empirical[i] = Train::Battle::compress_probs<double, uint16_t>(emp[(u * 2 + s) * 9 + i]);
+        sides[s]->nash[i] = Train::Battle::compress_probs<double, uint16_t>(nash[(u * 2 + s) * 9 + i]);
+      }
+    }
+    frames.updates.push_back(up);
+  }
+  frames.write(out);
+  return frames.n_bytes();
+}
+// read back through the reference's reader: returns n_updates, fills result and the last update's fields (sanity)
+uint32_t ref_frames_read_game(const char* bytes, uint8_t* battle384, uint8_t* result) {
+  Train::Battle::CompressedFrames frames{};
+  frames.read(bytes);
+  memcpy(battle384, frames.battle.bytes, 384);
+  *result = frames.result;
+  return (uint32_t)frames.updates.size();
+}
+}

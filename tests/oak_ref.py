@@ -221,3 +221,80 @@ def make_net_blob(rng, phd=128, pod=59, ahd=128, aod=83, hd=64, vhd=32, pohd=64,
         out.append(rng.uniform(-k, k, o).astype("<f4").tobytes())
         out.append(rng.uniform(-k, k, (o, i)).astype("<f4").tobytes())
     return np.frombuffer(b"".join(out), np.uint8).copy()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# training frames (oracle/frames_oracle.hpp; the reference's own serialiser through oracle/_ref when it is built)
+def _frames_fn(lib, name):
+    f = getattr(lib, name)
+    f.restype = ctypes.c_uint32
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint32] + [ctypes.c_void_p] * 8
+    return f
+
+
+def frames_write_game(lib, name, battle, result, k, choice, iterations, ev, nv, emp, nash):
+    """One game -> bytes. k/choice [n,2] u8, iterations [n] u32, ev/nv [n] f64, emp/nash [n,2,9] f64."""
+    n = k.shape[0]
+    a = [np.ascontiguousarray(battle, np.uint8), np.ascontiguousarray(k, np.uint8), np.ascontiguousarray(choice, np.uint8),
+         np.ascontiguousarray(iterations, np.uint32), np.ascontiguousarray(ev, np.float64), np.ascontiguousarray(nv, np.float64),
+         np.ascontiguousarray(emp, np.float64), np.ascontiguousarray(nash, np.float64)]
+    out = np.zeros(391 + 83 * n + 16, np.uint8)
+    nb = _frames_fn(lib, name)(a[0].ctypes.data, int(result), n, *[x.ctypes.data for x in a[1:]], out.ctypes.data)
+    return out[:nb].copy()
+
+
+def ref_library():
+    path = os.path.join(ROOT, "oracle", "_ref", "libref_oak.so")
+    return ctypes.CDLL(path) if os.path.exists(path) else None
+
+
+def random_frame_games(rng, games, max_len):
+    """Ragged synthetic games in lockstep layout: dict of [T,G,...] arrays + lengths[G] + battles[G,384] + final results[G]."""
+    L = rng.integers(1, max_len + 1, games)
+    T = int(L.max())
+    k = rng.integers(1, 10, (T, games, 2)).astype(np.uint8)
+    choice = rng.integers(0, 256, (T, games, 2)).astype(np.uint8)
+    iters = rng.integers(0, 1 << 32, (T, games), dtype=np.uint64).astype(np.uint32)
+    ev = rng.random((T, games)).astype(np.float32)
+    nv = rng.random((T, games)).astype(np.float32)
+    emp = rng.random((T, games, 2, 9)).astype(np.float32)
+    nash = rng.random((T, games, 2, 9)).astype(np.float32)
+    emp /= emp.sum(-1, keepdims=True)
+    nash /= nash.sum(-1, keepdims=True)
+    ev[0, :3], nv[0, :3] = 1.0, 0.0  # the ends of the u16 range
+    battles = rng.integers(0, 256, (games, 384)).astype(np.uint8)
+    final = rng.integers(1, 4, games).astype(np.uint8) | 0x50
+    return dict(L=L, T=T, k=k, choice=choice, iters=iters, ev=ev, nv=nv, emp=emp, nash=nash, battles=battles, final=final)
+
+
+def frames_expected_game(lib, name, G, g):
+    n = int(G["L"][g])
+    return frames_write_game(lib, name, G["battles"][g], G["final"][g], G["k"][:n, g], G["choice"][:n, g], G["iters"][:n, g],
+                             G["ev"][:n, g].astype(np.float64), G["nv"][:n, g].astype(np.float64),
+                             G["emp"][:n, g].astype(np.float64), G["nash"][:n, g].astype(np.float64))
+
+
+def parse_battle_data(stream):
+    """Split a .battle.data byte stream into games (the reader of cpp/src/pyoak.cc:43-71 + compressed-frame.h:201-224).
+    -> list of dict(battle, result, updates=[dict(m, n, c1, c2, iterations, ev, nv, p1_emp, p1_nash, p2_emp, p2_nash)])."""
+    stream = bytes(stream)
+    games, at = [], 0
+    while at < len(stream):
+        nb = int.from_bytes(stream[at:at + 4], "little")
+        nu = int.from_bytes(stream[at + 4:at + 6], "little")
+        g = dict(battle=np.frombuffer(stream[at + 6:at + 390], np.uint8).copy(), result=stream[at + 390], updates=[])
+        p, end = at + 391, at + nb
+        while p < end:
+            m, n = (stream[p] & 15) + 1, (stream[p] >> 4) + 1
+            u = dict(m=m, n=n, c1=stream[p + 1], c2=stream[p + 2], iterations=int.from_bytes(stream[p + 3:p + 7], "little"),
+                     ev=int.from_bytes(stream[p + 7:p + 9], "little"), nv=int.from_bytes(stream[p + 9:p + 11], "little"))
+            q = p + 11
+            for name, cnt in (("p1_emp", m), ("p1_nash", m), ("p2_emp", n), ("p2_nash", n)):
+                u[name] = np.frombuffer(stream[q:q + 2 * cnt], np.uint16).copy()
+                q += 2 * cnt
+            g["updates"].append(u)
+            p = q
+        assert p == end and len(g["updates"]) == nu, "corrupt .battle.data stream"
+        games.append(g)
+        at = end
+    return games
