@@ -28,3 +28,52 @@ def reduce_throughput(times_ms, work, device="cpu"):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(w, op=dist.ReduceOp.SUM)
     return t.tolist(), w.tolist()
+
+
+def _group_device(device):
+    return torch.device(device) if device is not None else torch.device("cpu")
+
+
+def broadcast_bytes(data, src=0, device=None):
+    """Broadcast a byte string (e.g. a network parameter file image) from rank `src` to every rank; returns a uint8
+    numpy array on all ranks. NCCL groups need `device` = this rank's CUDA device; gloo groups use the CPU.
+    (Reference analogue: every generate worker re-reads the learner's newest parameter file, cpp/src/generate.cc.)"""
+    import numpy as np
+    dev = _group_device(device)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return np.frombuffer(bytes(data), np.uint8).copy()
+    rank = dist.get_rank()
+    size = torch.tensor([len(data) if rank == src else 0], dtype=torch.int64, device=dev)
+    dist.broadcast(size, src)
+    if rank == src:
+        buf = torch.from_numpy(np.frombuffer(bytes(data), np.uint8).copy()).to(dev)
+    else:
+        buf = torch.empty(int(size.item()), dtype=torch.uint8, device=dev)
+    dist.broadcast(buf, src)
+    return buf.cpu().numpy()
+
+
+def gather_streams(stream, dst=0, device=None):
+    """Gather every rank's frame stream (uint8 array, possibly empty, ragged across ranks) to rank `dst`. Returns the
+    list of per-rank arrays on `dst` (rank order) and None elsewhere. Sizes travel first, payloads are padded to the
+    largest. This is the only collective of the self-play path: the game records themselves are
+    independent, so the writer just concatenates them."""
+    import numpy as np
+    dev = _group_device(device)
+    stream = np.ascontiguousarray(stream, np.uint8)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [stream]
+    world, rank = dist.get_world_size(), dist.get_rank()
+    sizes = torch.zeros(world, dtype=torch.int64, device=dev)
+    sizes[rank] = stream.size
+    dist.all_reduce(sizes, op=dist.ReduceOp.SUM)
+    cap = int(sizes.max().item())
+    if cap == 0:
+        return [np.empty(0, np.uint8) for _ in range(world)] if rank == dst else None
+    mine = torch.zeros(cap, dtype=torch.uint8, device=dev)
+    mine[:stream.size] = torch.from_numpy(stream).to(dev)
+    parts = [torch.empty(cap, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    if rank != dst:
+        return None
+    return [parts[r][:int(sizes[r].item())].cpu().numpy() for r in range(world)]

@@ -1,0 +1,55 @@
+"""Self-play generation on the GPU (config C5, one rank): games are played by the device kernels (choices, tensor-core
+evaluation, policy sampling, update), recorded and packed on the device. Checks, on the produced .battle.data bytes:
+  * every game replays on the ORACLE from its stored initial battle with its stored choices to exactly the stored
+    result and length — the reference's own consistency check (cpp/include/py/battle/encoded-frames.h:117-126);
+  * the stored choices are legal and the stored policies/values are the network's (oracle evaluation of the replayed
+    state, u16-quantised as compress_probs does);
+  * files are flushed by size, finished slots are refilled with fresh games."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oak_ref import ROOT, NetOracle, Oracle, make_net_blob, parse_battle_data
+
+pytestmark = pytest.mark.gpu
+
+
+def test_selfplay_frames_replay_on_oracle(tmp_path):
+    from oak_b200.selfplay import FrameWriter, SelfPlay
+    orc = Oracle()
+    pool = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    blob = make_net_blob(np.random.default_rng(77), scale=3.0)
+    sp = SelfPlay(768, blob, pool, seed=1234, max_updates=400)
+    w = FrameWriter(str(tmp_path), buffer_mb=1)
+    done = sp.run(260, writer=w, collect_every=4)
+    w.flush()
+    sp.close()
+    assert done > 768 and sp.started >= 768 + done  # every finished slot was refilled
+    assert len(w.files) >= 2
+    stream = b"".join(open(f, "rb").read() for f in w.files)
+    games = parse_battle_data(stream)
+    assert len(games) == done
+    net = NetOracle(orc, blob)
+    checked = 0
+    for gi, g in enumerate(games):
+        b, d = g["battle"].copy(), np.zeros(8, np.uint8)
+        r = 0x50  # both players move after the leads are out (PKMN::update(0, 0) result)
+        assert len(g["updates"]) >= 1
+        for ui, u in enumerate(g["updates"]):
+            ch1 = orc.choices(b, 0, (r >> 4) & 3)
+            ch2 = orc.choices(b, 1, (r >> 6) & 3)
+            assert (u["m"], u["n"]) == (len(ch1), len(ch2)) and u["c1"] in ch1 and u["c2"] in ch2 and u["iterations"] == 0
+            if gi % 25 == 0 and ui % 7 == 0:
+                v, l1, l2, _ = net.eval_one(b, d, ch1, ch2)
+                for lg, got in ((l1, u["p1_emp"]), (l2, u["p2_emp"])):
+                    p = np.exp(lg.astype(np.float32))
+                    p = p / p.sum(dtype=np.float32)
+                    assert np.abs((p.astype(np.float64) * 65535.0).astype(np.int64) - got.astype(np.int64)).max() <= 2
+                assert abs(int(v * 65535.0) - u["ev"]) <= 2 and u["ev"] == u["nv"] and np.array_equal(u["p1_emp"], u["p1_nash"])
+                checked += 1
+            r, _ = orc.update(b, u["c1"], u["c2"], d)
+            assert (r & 15) == 0 or ui + 1 == len(g["updates"])
+        assert r == g["result"] and (r & 15) != 0
+    assert checked > 50

@@ -6,7 +6,7 @@ import numpy as np
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from oak_b200.sharding import reduce_throughput, shard_range, split_batch
+from oak_b200.sharding import broadcast_bytes, gather_streams, reduce_throughput, shard_range, split_batch
 
 
 def _free_port():
@@ -53,3 +53,26 @@ def test_split_batch_covers_exactly_once():
                 assert f == pos
                 pos += c
             assert max(c for _, c in parts) - min(c for _, c in parts) <= 1
+
+
+def _io_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    blob = broadcast_bytes(bytes(range(200)) * 3 if rank == 0 else b"", src=0)
+    mine = np.full(1000 * rank + 17, rank + 1, np.uint8)          # ragged per-rank frame streams
+    parts = gather_streams(mine, dst=0)
+    empty = gather_streams(np.empty(0, np.uint8), dst=0)
+    out[rank] = (blob.tobytes(), None if parts is None else [p.tobytes() for p in parts], empty if empty is None else len(empty))
+    dist.destroy_process_group()
+
+
+def test_weight_broadcast_and_frame_gather():
+    """The two collectives of the multi-GPU path: parameter image from rank 0, frame streams to rank 0."""
+    world = 2
+    out = mp.Manager().dict()
+    mp.spawn(_io_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    for r in range(world):
+        assert out[r][0] == bytes(range(200)) * 3
+    assert out[1][1] is None and out[1][2] is None
+    assert out[0][1] == [bytes([1]) * 17, bytes([2]) * 1017] and out[0][2] == 2
