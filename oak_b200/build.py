@@ -12,11 +12,12 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 
 def sources():
-    return [os.path.join(CSRC, "oakb200.cu"), os.path.join(CSRC, "value_net.cu"), os.path.join(CSRC, "frame_log.cu")]
+    return [os.path.join(CSRC, "oakb200.cu"), os.path.join(CSRC, "value_net.cu"), os.path.join(CSRC, "frame_log.cu"),
+            os.path.join(CSRC, "pkmn_compat.cu")]
 
 
 def _deps():
-    out = [os.path.join(HERE, "..", "include", "oakb200.h")]
+    out = [os.path.join(HERE, "..", "include", "oakb200.h"), os.path.join(HERE, "..", "include", "oakb200_pkmn.h")]
     for f in os.listdir(CSRC):
         out.append(os.path.join(CSRC, f))
     return out
