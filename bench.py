@@ -258,7 +258,9 @@ def main():
     # ---- secondary: batched leaf evaluation (BASELINE configs[2]: batch 64K, default network dims)
     from oak_ref import make_net_blob
     EV = min(1 << 16, n)
-    blob = make_net_blob(np.random.default_rng(1234))
+    from oak_b200.sharding import broadcast_bytes, gather_streams
+    # rank 0 owns the parameter image; every other rank receives it over NCCL, then loads it
+    blob = broadcast_bytes(make_net_blob(np.random.default_rng(1234)).tobytes() if rank == 0 else b"", src=0, device=dev)
     eng.load_network(blob)
     ev_v = torch.empty(EV, dtype=torch.float32, device=dev)
     ev_l = torch.empty((EV, 2, 9), dtype=torch.float32, device=dev)
@@ -298,6 +300,32 @@ def main():
         eval_e2e()
     eval_e2e_s = (time.perf_counter() - t0) / 5
     launches += 6
+    # ---- secondary: self-play generation (BASELINE configs[4]): lockstep games, network policy, frames recorded and
+    # packed on the device, drained per rank and gathered to rank 0 (the writer) over NCCL
+    import json as _json
+    from oak_b200.selfplay import SelfPlay
+    pool = np.array(_json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    SP_G, SP_STEPS = 16384, 96
+    sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
+    sp.run(16)  # warm-up
+    barrier()
+    l0 = sp.eng.launch_count
+    t0 = time.perf_counter()
+    sp_streams, sp_games = [], 0
+    for s_ in range(SP_STEPS):
+        sp.step()
+        if (s_ + 1) % 8 == 0:
+            st_, g_ = sp.collect()
+            sp_streams.append(st_)
+            sp_games += g_
+    local_stream = np.concatenate(sp_streams) if sp_streams else np.empty(0, np.uint8)
+    gathered = gather_streams(local_stream, dst=0, device=dev)
+    barrier()
+    sp_s = time.perf_counter() - t0
+    launches += sp.eng.launch_count - l0
+    sp_bytes = sum(len(x) for x in gathered) if gathered is not None else 0
+    sp.close()
+
     eval_cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         from oak_ref import NetOracle, Oracle as _O
@@ -373,6 +401,11 @@ def main():
                                        "note": "executed = every tcgen05.mma issued (3 products per split-bf16 GEMM, K and N "
                                                "padding included); dense-equivalent = SURVEY 8d F_eval"},
                           "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (cache-free, sparse first layers), all host cores"},
+            "selfplay": {"game_updates_per_s": world * SP_G * SP_STEPS / sp_s, "games_per_gpu": SP_G, "steps": SP_STEPS,
+                         "stream_bytes_at_writer": int(sp_bytes),
+                         "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
+                                 "step: choices + tensor-core eval + policy sample + frame record + update + finish kernels; "
+                                 "drain every 8 steps; frame streams gathered to rank 0"},
             "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(tot_launches),
         }
         print(json.dumps(line), flush=True)
