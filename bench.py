@@ -121,10 +121,23 @@ def run_reference(args, rank, world):
                          "sample": f"{args.steps} x {n} playouts, CPU restatement of libpkmn/Oak (Zig toolchain unavailable)"},
         "e2e": {"value": v, "unit": "battle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else a library prints (NCCL's version banner, ...) was
+    sent to stderr by main()."""
+    os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+
+
+_STDOUT_FD = 1
 
 
 def main():
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)  # native libraries writing to fd 1 now land on stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -408,7 +421,7 @@ def main():
                                  "drain every 8 steps; frame streams gathered to rank 0"},
             "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(tot_launches),
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
