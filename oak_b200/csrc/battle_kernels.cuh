@@ -210,6 +210,141 @@ rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, u
 }
 
 // ---------------------------------------------------------------------------------------------
+// rollout_grouped_kernel: the same playouts as rollout_kernel, with the CTA's 128 battles REGROUPED by action
+// class before every update. A battle's state is a shared-memory column, not a thread's registers, so any
+// thread of the CTA can advance any column: each iteration the owner thread t enumerates column t's legal
+// choices and makes the playout pick, the CTA counting-sorts its columns by (class of P1's action, class of
+// P2's action) — pass / switch / move by effect group — and thread u then runs the turn transition of the
+// u-th column in sorted order. Warps therefore execute mostly one kind of turn (switch-switch, move-move of
+// one effect family, ...) instead of the union of all of them, and idle columns collect in whole warps.
+// The first profile of rollout_kernel showed 6.2 of 32 lanes active in executeMove and ~50 % of stall samples
+// waiting on instruction fetch (profiles/r1b_rollout_kernel_by_function.txt).
+__device__ __forceinline__ uint32_t action_class(const Mem<128>& m, int p, uint32_t choice) {
+  const uint32_t type = choice & 3u, data = choice >> 2;
+  if (type == CH_PASS) return 0;
+  if (type == CH_SWITCH) return 1;
+  if (data == 0) return 2;  // Struggle / forced continuation
+  const uint32_t id = m.ld8(Mem<128>::sb(p), A_MOVES + 2 * ((int)data - 1));
+  const uint32_t eff = mv_effect(move_word(id));
+  if (eff == 0) return 2;          // plain damage
+  if (eff <= 16) return 3;         // onBegin family: status / screens / heal / substitute ...
+  if (eff <= 31) return 4;         // stat down, onEnd family
+  if (eff <= 47) return 5;         // always-happens / special / multi-hit
+  return 6;                        // secondary-chance families
+}
+
+template <int BLOCK, bool CHANCE, bool WRITE_STATE>
+__global__ void __launch_bounds__(BLOCK, 3)
+rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+                       const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
+                       uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
+                       unsigned long long* __restrict__ total_steps) {
+  static_assert(BLOCK == 128, "action_class and the sort assume 128 columns");
+  extern __shared__ uint32_t tile[];
+  uint32_t* s_meta = tile + BATTLE_WORDS * BLOCK;  // c1 | c2 << 8 | live << 16
+  uint32_t* s_res = s_meta + BLOCK;
+  uint32_t* s_perm = s_res + BLOCK;
+  uint32_t* s_dur = s_perm + BLOCK;                // 2 per column
+  uint32_t* s_cnt = s_dur + 2 * BLOCK;             // 64 buckets
+  const int t = threadIdx.x;
+  uint32_t* col = tile + t;
+  Mem<BLOCK> m;
+  m.set(reinterpret_cast<uint8_t*>(col));
+
+  uint32_t i = 0, result = 0, step = 0, my_steps = 0;
+  uint64_t seed = 0;
+  bool have = false, exhausted = false;
+
+  for (;;) {
+    // ---- owner: refill, legal choices, playout pick, sort key
+    if (!have && !exhausted) {
+      i = atomicAdd(ticket, 1u);
+      if (i < n) {
+        load_column<BLOCK>(col, battles + (size_t)i * 384);
+        const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+        s_dur[2 * t] = d.x;
+        s_dur[2 * t + 1] = d.y;
+        result = results[i];
+        seed = seeds[i];
+        step = 0;
+        have = true;
+      } else {
+        exhausted = true;
+      }
+    }
+    if (t < 64) s_cnt[t] = 0;
+    const bool live = have && (result & 15u) == 0 && step < max_steps;
+    uint32_t key = 63;
+    if (live) {
+      const uint64_t pick = pick_word(seed, step);
+      const uint64_t l1 = mem_choices(m, 0, (result >> 4) & 3);
+      const uint64_t l2 = mem_choices(m, 1, (result >> 6) & 3);
+      const uint32_t c1 = choice_at(l1, (int)mod_small(pick, (uint32_t)choice_count(l1)));
+      const uint32_t c2 = choice_at(l2, (int)((uint32_t)(pick >> 32) % (uint32_t)choice_count(l2)));
+      s_meta[t] = c1 | (c2 << 8) | (1u << 16);
+      key = action_class(m, 0, c1) * 8 + action_class(m, 1, c2);
+    } else {
+      s_meta[t] = 0;
+    }
+    if (__syncthreads_count(have) == 0) break;
+    // ---- counting sort of the columns by key
+    const uint32_t rank = atomicAdd(&s_cnt[key], 1u);
+    __syncthreads();
+    if (t < 32) {
+      const uint32_t a = s_cnt[2 * t], b = s_cnt[2 * t + 1];
+      uint32_t x = a + b;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+        if (t >= o) x += y;
+      }
+      s_cnt[2 * t] = x - a - b;
+      s_cnt[2 * t + 1] = x - b;
+    }
+    __syncthreads();
+    s_perm[s_cnt[key] + rank] = (uint32_t)t;
+    __syncthreads();
+    // ---- worker: the turn transition of the t-th column in class order
+    {
+      const uint32_t p = s_perm[t];
+      const uint32_t meta = s_meta[p];
+      if (meta >> 16) {
+        Engine<BLOCK, false, CHANCE> e;
+        e.begin(reinterpret_cast<uint8_t*>(tile + p), s_dur[2 * p], s_dur[2 * p + 1]);
+        const uint32_t r = e.update(meta & 255u, (meta >> 8) & 255u);  // begin() cleared the actions (mcts.h:478)
+        e.end();
+        if (CHANCE) {
+          s_dur[2 * p] = e.dur[0];
+          s_dur[2 * p + 1] = e.dur[1];
+        }
+        s_res[p] = r;
+      }
+    }
+    __syncthreads();
+    // ---- owner: bookkeeping, outputs of a finished playout
+    if (live) {
+      result = s_res[t];
+      step++;
+    }
+    if (have && (!live || (result & 15u) != 0 || step >= max_steps)) {
+      const uint32_t ty = result & 15u;
+      if (score2_out) score2_out[i] = ty == RES_WIN ? 2 : (ty == RES_TIE ? 1 : (ty == RES_LOSE ? 0 : 255));
+      if (turns_out) turns_out[i] = (uint16_t)m.ld16(B_TURN);
+      if (steps_out) steps_out[i] = step;
+      if (WRITE_STATE) {
+        store_column<BLOCK>(col, battles + (size_t)i * 384);
+        *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(s_dur[2 * t], s_dur[2 * t + 1]);
+        results[i] = (uint8_t)result;
+      }
+      my_steps += step;
+      have = false;
+    }
+  }
+  uint32_t s = my_steps;
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+  if ((threadIdx.x & 31) == 0 && total_steps) atomicAdd(total_steps, (unsigned long long)s);
+}
+
+// ---------------------------------------------------------------------------------------------
 // MCTS::randomize_hidden_variables (reference cpp/include/search/durations.h:25-97). Touches a few
 // bytes per battle, so it works on the AoS records in place. Every draw uses the same battle.rng.
 __device__ __constant__ uint64_t HIDDEN_BINDING_CUM[4] = {
