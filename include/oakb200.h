@@ -174,6 +174,32 @@ int oakb200_frames_pending(oakb200_ctx* ctx, uint32_t* finished, uint32_t* dropp
  * the call fails with OAKB200_ECAPACITY), *games = how many games it holds. */
 int oakb200_frames_drain(oakb200_ctx* ctx, uint8_t* out, size_t cap, size_t* bytes, uint32_t* games);
 
+/* ---- batched-leaf tree search: host trees + bandits, GPU battle operations -----------------------------------------
+ * Replaces MCTS::Search::run with MonteCarlo evaluation, the joint UCB bandit and a Node heap (reference
+ * cpp/include/search/mcts.h:154-496,569-604; cpp/include/search/bandit/ucb.h; cpp/include/search/joint.h) for many
+ * root positions at once: `roots` x `particles` descents run in lockstep, one kernel launch per tree level (legal
+ * choices by index, clamped-roll update, chance observation), one for the hidden-variable draw and one for all leaf
+ * playouts of a wave. particles = 1 reproduces the reference's sequential search selection for selection given the
+ * same random streams (root seed s, n-th iteration: battle rng = splitmix64(s ^ K(2n+1)), playout seed =
+ * splitmix64(s ^ K(2n+2)), K = 0xD1B54A32D192ED03); particles > 1 batches descents of one tree with virtual visits.
+ * The Nash solve of the root matrix (LRSNash, mcts.h:645-649) stays with the caller: outputs are the matrices. */
+typedef struct oakb200_search oakb200_search;
+int oakb200_search_create(oakb200_ctx* ctx, size_t roots, uint32_t particles, oakb200_search** out);
+void oakb200_search_destroy(oakb200_search* search);
+/* MCTS::Input rows (mcts.h:62-66) + one stream seed per root; resets the trees. HOST pointers. */
+int oakb200_search_set_roots(oakb200_search* search, size_t n, const uint8_t* battles, const uint8_t* durations,
+                             const uint8_t* results, const uint64_t* seeds);
+/* `iterations` more iterations per root (rounded up to a multiple of particles). ucb_c: UCB::Bandit::Params::c;
+ * root_rolls / other_rolls: SearchOptions (1, 2, 3, 20, or 39 = unclamped; the reference default is 3 / 1);
+ * host_threads <= 0: all cores. */
+int oakb200_search_run(oakb200_search* search, uint32_t iterations, float ucb_c, uint32_t root_rolls, uint32_t other_rolls,
+                       int host_threads);
+/* MCTS::Output per root (mcts.h:68-89): k[n][2], choices[n][2][9], visit_matrix[n][9][9] u32, value_matrix[n][9][9] f64,
+ * iterations[n], empirical_value[n] f64, empirical[n][2][9] f64 (process_output, mcts.h:623-661), nodes[n]. Any may be NULL. */
+int oakb200_search_output(oakb200_search* search, uint8_t* k, uint8_t* choices, uint32_t* visit_matrix, double* value_matrix,
+                          uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes);
+int oakb200_search_stats(oakb200_search* search, uint64_t* waves, uint64_t* levels);
+
 #ifdef __cplusplus
 }
 #endif

@@ -345,6 +345,82 @@ rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ dura
 }
 
 // ---------------------------------------------------------------------------------------------
+// Tree-search support (reference cpp/include/search/mcts.h:232-246,304-361,569-604).
+// search_spawn_kernel: particle b of root b / per_root starts from a copy of its root's battle whose rng is replaced by
+// a fresh 64-bit value (run_root_iteration: `rng[0] = device.uniform_64()`); randomize_hidden_kernel then redraws the
+// hidden counters from the root's observed durations.
+__global__ void search_spawn_kernel(const uint8_t* __restrict__ root_battles, const uint8_t* __restrict__ root_durations,
+                                    const uint8_t* __restrict__ root_results, const uint64_t* __restrict__ rng_values,
+                                    uint32_t per_root, uint8_t* __restrict__ battles, uint8_t* __restrict__ durations,
+                                    uint8_t* __restrict__ results, uint32_t n) {
+  const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (g >= n) return;
+  const uint32_t r = g / per_root;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(root_battles + (size_t)r * 384);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(battles + (size_t)g * 384);
+  for (int w = lane; w < BATTLE_WORDS; w += 32) {
+    uint32_t v = src[w];
+    if (w == B_RNG / 4) v = (uint32_t)rng_values[g];
+    if (w == B_RNG / 4 + 1) v = (uint32_t)(rng_values[g] >> 32);
+    dst[w] = v;
+  }
+  if (lane < 2) reinterpret_cast<uint32_t*>(durations + (size_t)g * 8)[lane] = reinterpret_cast<const uint32_t*>(root_durations + (size_t)r * 8)[lane];
+  if (lane == 2) results[g] = root_results[r];
+}
+
+// search_step_kernel: one tree step of every active particle. The host's bandits choose INDICES into the legal-choice
+// lists (mcts.h:334-342); the kernel enumerates the lists, applies Search::battle_options_set's clamped damage rolls
+// (rolls[b] in {1, 2, 3, 20}: both players' damage overrides from bytes 6 and 7 of the battle rng, roll_byte
+// mcts.h:593-604; 39 = no clamping), updates with chance tracking, and returns the result, the 16-byte observation that
+// keys the child node (mcts.h:355-358) and the legal-choice counts of the new state (the child's bandit sizes).
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 3)
+search_step_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+                   const uint8_t* __restrict__ idx1, const uint8_t* __restrict__ idx2, const uint8_t* __restrict__ rolls,
+                   uint8_t* __restrict__ actions_out, uint8_t* __restrict__ counts_out, uint32_t n) {
+  extern __shared__ uint32_t tile[];
+  const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t a = idx1[i], b = idx2[i], prev = results[i];
+  if (a == 255u || (prev & 15u) != 0) return;
+  uint32_t* col = tile + threadIdx.x;
+  load_column<BLOCK>(col, battles + (size_t)i * 384);
+  const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+  Engine<BLOCK, true, true> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
+  int m, k;
+  const uint64_t l1 = e.choices(0, (prev >> 4) & 3, &m);
+  const uint64_t l2 = e.choices(1, (prev >> 6) & 3, &k);
+  const uint32_t c1 = Engine<BLOCK, true, true>::choice_at(l1, a < (uint32_t)m ? (int)a : 0);
+  const uint32_t c2 = Engine<BLOCK, true, true>::choice_at(l2, b < (uint32_t)k ? (int)b : 0);
+  const uint32_t nr = rolls[i];
+  if (nr != 39u) {
+    const uint32_t r0 = (uint32_t)(e.rng >> 48) & 255u, r1 = (uint32_t)(e.rng >> 56);
+    const uint32_t step = nr > 1 ? 38u / (nr - 1) : 0u;
+    e.ovr[0] = nr == 1 ? 236u : 217u + step * (r0 % nr);
+    e.ovr[1] = nr == 1 ? 236u : 217u + step * (r1 % nr);
+  }
+  const uint32_t r = e.update(c1, c2);
+  e.end();
+  store_column<BLOCK>(col, battles + (size_t)i * 384);
+  *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
+  results[i] = (uint8_t)r;
+  uint4 act;
+  act.x = (uint32_t)e.act[0];
+  act.y = (uint32_t)(e.act[0] >> 32);
+  act.z = (uint32_t)e.act[1];
+  act.w = (uint32_t)(e.act[1] >> 32);
+  *reinterpret_cast<uint4*>(actions_out + (size_t)i * 16) = act;
+  int m2 = 0, k2 = 0;
+  if ((r & 15u) == 0) {
+    e.choices(0, (r >> 4) & 3, &m2);
+    e.choices(1, (r >> 6) & 3, &k2);
+  }
+  counts_out[(size_t)i * 2] = (uint8_t)m2;
+  counts_out[(size_t)i * 2 + 1] = (uint8_t)k2;
+}
+
+// ---------------------------------------------------------------------------------------------
 // MCTS::randomize_hidden_variables (reference cpp/include/search/durations.h:25-97). Touches a few
 // bytes per battle, so it works on the AoS records in place. Every draw uses the same battle.rng.
 __device__ __constant__ uint64_t HIDDEN_BINDING_CUM[4] = {

@@ -37,6 +37,13 @@ struct oakb200_ctx {
   std::string error;
 };
 
+// search.cu -> oakb200.cu
+cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_battles, const uint8_t* root_durations,
+                                        const uint8_t* root_results, const uint64_t* rng_values, uint32_t per_root,
+                                        uint8_t* battles, uint8_t* durations, uint8_t* results, uint32_t n);
+cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8_t* durations, uint8_t* results, const uint8_t* idx1,
+                                       const uint8_t* idx2, const uint8_t* rolls, uint8_t* actions, uint8_t* counts, uint32_t n);
+
 namespace {
 
 inline int fail(oakb200_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess) {

@@ -84,6 +84,26 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
 
 }  // namespace
 
+// kernel launches used by the tree-search driver (search.cu); battle_kernels.cuh is compiled in this unit only
+cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_battles, const uint8_t* root_durations,
+                                        const uint8_t* root_results, const uint64_t* rng_values, uint32_t per_root,
+                                        uint8_t* battles, uint8_t* durations, uint8_t* results, uint32_t n) {
+  search_spawn_kernel<<<(unsigned)(((size_t)n * 32 + 255) / 256), 256, 0, ctx->stream>>>(root_battles, root_durations, root_results,
+                                                                                        rng_values, per_root, battles, durations,
+                                                                                        results, n);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8_t* durations, uint8_t* results, const uint8_t* idx1,
+                                       const uint8_t* idx2, const uint8_t* rolls, uint8_t* actions, uint8_t* counts, uint32_t n) {
+  auto k = search_step_kernel<BLOCK>;
+  cudaError_t e = allow_smem(k);
+  if (e != cudaSuccess) return e;
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>(battles, durations, results, idx1, idx2, rolls, actions, counts, n);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
 extern "C" {
 
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {

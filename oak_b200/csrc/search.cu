@@ -1,0 +1,462 @@
+// Batched-leaf tree search: host trees, GPU transitions and leaves (BASELINE configs[3]).
+//
+// Reference algorithm: MCTS::Search::{run, run_root_iteration, run_iteration, init_stats_and_rollout}
+// (cpp/include/search/mcts.h:154-496) with the joint UCB bandit (cpp/include/search/bandit/ucb.h:15-71,
+// cpp/include/search/joint.h) on a Node heap keyed by (p1 index, p2 index, 16-byte chance observation)
+// (mcts.h:93-99,355-361), MonteCarlo evaluation, Search::battle_options_set's clamped damage rolls
+// (mcts.h:569-604; default_search = {root_rolls 3, other_rolls 1}, mcts.h:133).
+//
+// What stays on the host (as the north star says): the trees and the bandit arithmetic. What moves to the GPU: every
+// battle operation. R roots x P particles descend in lockstep; per tree level one search_step_kernel launch advances
+// all of them (choices, clamped update, observation, child sizes), then the hidden-variable draw and the playouts of
+// all leaves are one launch each. With P = 1 the search of each root is the reference's sequential algorithm
+// exactly (same selections, same statistics) for the documented random streams below; with P > 1 the particles of a
+// wave select with virtual visits (the visit of an in-flight descent is counted at selection time, its value at
+// back-propagation), which changes the order of selections, not the statistics kept.
+//
+// Random streams (the reference draws them from one std::mt19937 per thread, cpp/include/util/random.h): for root
+// seed s and that root's n-th iteration, battle rng = splitmix64(s ^ K * (2n + 1)), playout seed =
+// splitmix64(s ^ K * (2n + 2)), K = 0xD1B54A32D192ED03; the playout then picks as oakb200_rollout does.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+#include <condition_variable>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "context.h"
+
+namespace {
+
+uint64_t splitmix64(uint64_t x) {
+  uint64_t z = x + 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+const uint64_t STREAM_K = 0xD1B54A32D192ED03ull;
+
+// UCB::Bandit (ucb.h:15-66)
+struct Bandit {
+  float scores[9];
+  uint32_t visits[9];
+  uint8_t k = 0;
+  void init(int n) {
+    k = (uint8_t)n;
+    for (int i = 0; i < n; i++) {
+      scores[i] = 0.5f;
+      visits[i] = 1;
+    }
+  }
+  int select(float c) const {
+    if (k == 1) return 0;
+    uint64_t N = 0;
+    for (int i = 0; i < k; i++) N += visits[i];
+    const float sqrtN = (float)std::sqrt((double)N);
+    float max = 0;
+    int index = 0;
+    for (int i = 0; i < k; i++) {
+      const float e = c * sqrtN / k;
+      const float a = (e + scores[i]) / visits[i];
+      if (a > max) {
+        max = a;
+        index = i;
+      }
+    }
+    return index;
+  }
+};
+
+struct Child {
+  uint8_t i, j;
+  uint8_t obs[16];
+  int32_t node;
+};
+struct Node {
+  Bandit p1, p2;
+  std::vector<Child> children;
+  bool is_init() const { return p1.k != 0; }
+};
+struct PathEntry {
+  int32_t node;
+  uint8_t i, j;
+};
+
+struct Root {
+  std::vector<Node> nodes;  // nodes[0] = root
+  uint8_t k1 = 0, k2 = 0;
+  uint8_t choices[18] = {0};
+  uint32_t visit[81] = {0};
+  double value[81] = {0};
+  uint64_t iterations = 0;
+  uint64_t seed = 0;
+  uint64_t total_depth = 0;
+};
+
+struct Particle {
+  int32_t cur = 0;
+  bool active = false;
+  std::vector<PathEntry> path;
+};
+
+// persistent worker pool: parallel_for over roots
+class Pool {
+ public:
+  explicit Pool(int threads) {
+    if (threads < 1) threads = 1;
+    for (int t = 1; t < threads; t++) workers_.emplace_back([this] { loop(); });
+  }
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      stop_ = true;
+      gen_++;
+    }
+    cv_.notify_all();
+    for (auto& w : workers_) w.join();
+  }
+  void parallel_for(size_t n, const std::function<void(size_t)>& fn) {
+    if (workers_.empty() || n < 2) {
+      for (size_t i = 0; i < n; i++) fn(i);
+      return;
+    }
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      fn_ = &fn;
+      n_ = n;
+      next_.store(0);
+      pending_ = (int)workers_.size();
+      gen_++;
+    }
+    cv_.notify_all();
+    work();
+    std::unique_lock<std::mutex> l(mu_);
+    done_.wait(l, [this] { return pending_ == 0; });
+  }
+
+ private:
+  void work() {
+    for (;;) {
+      const size_t i = next_.fetch_add(1);
+      if (i >= n_) break;
+      (*fn_)(i);
+    }
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      {
+        std::unique_lock<std::mutex> l(mu_);
+        cv_.wait(l, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (stop_) return;
+      }
+      work();
+      {
+        std::lock_guard<std::mutex> l(mu_);
+        if (--pending_ == 0) done_.notify_one();
+      }
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex mu_;
+  std::condition_variable cv_, done_;
+  const std::function<void(size_t)>* fn_ = nullptr;
+  size_t n_ = 0;
+  std::atomic<size_t> next_{0};
+  int pending_ = 0;
+  uint64_t gen_ = 0;
+  bool stop_ = false;
+};
+
+}  // namespace
+
+struct oakb200_search {
+  oakb200_ctx* ctx = nullptr;
+  size_t roots_max = 0, n_roots = 0;
+  uint32_t P = 1;
+  std::vector<Root> roots;
+  std::vector<Particle> particles;
+  // device
+  uint8_t *d_root_b = nullptr, *d_root_d = nullptr, *d_root_r = nullptr;
+  uint8_t *d_b = nullptr, *d_d = nullptr, *d_r = nullptr, *d_idx1 = nullptr, *d_idx2 = nullptr, *d_rolls = nullptr, *d_act = nullptr,
+          *d_cnt = nullptr, *d_score = nullptr;
+  uint64_t *d_rng = nullptr, *d_pseed = nullptr;
+  // pinned host mirrors
+  uint8_t *h_idx1 = nullptr, *h_idx2 = nullptr, *h_rolls = nullptr, *h_res = nullptr, *h_act = nullptr, *h_cnt = nullptr, *h_score = nullptr;
+  uint64_t *h_rng = nullptr, *h_pseed = nullptr;
+  Pool* pool = nullptr;
+  int pool_threads = 0;
+  uint64_t levels = 0, waves = 0;
+};
+
+namespace {
+
+void search_free(oakb200_search* s) {
+  if (!s) return;
+  if (s->ctx) cudaSetDevice(s->ctx->device);
+  void* dev[] = {s->d_root_b, s->d_root_d, s->d_root_r, s->d_b, s->d_d, s->d_r, s->d_idx1, s->d_idx2, s->d_rolls, s->d_act, s->d_cnt,
+                 s->d_score, s->d_rng, s->d_pseed};
+  for (void* p : dev)
+    if (p) cudaFree(p);
+  void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed};
+  for (void* p : host)
+    if (p) cudaFreeHost(p);
+  delete s->pool;
+  delete s;
+}
+
+template <class T>
+cudaError_t dmalloc(T** p, size_t bytes) { return cudaMalloc(reinterpret_cast<void**>(p), bytes); }
+template <class T>
+cudaError_t hmalloc(T** p, size_t bytes) { return cudaMallocHost(reinterpret_cast<void**>(p), bytes); }
+
+}  // namespace
+
+extern "C" {
+
+int oakb200_search_create(oakb200_ctx* ctx, size_t roots, uint32_t particles, oakb200_search** out) {
+  if (!ctx || !out || roots == 0 || particles == 0 || particles > 4096 || roots * (size_t)particles > 0x7FFFFFFFull)
+    return fail(ctx, OAKB200_EINVAL, "search_create: roots >= 1, 1 <= particles <= 4096");
+  *out = nullptr;
+  CU(ctx, cudaSetDevice(ctx->device));
+  oakb200_search* s = new oakb200_search();
+  s->ctx = ctx;
+  s->roots_max = roots;
+  s->P = particles;
+  const size_t B = roots * (size_t)particles;
+  cudaError_t e = cudaSuccess;
+  auto ok = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+  ok(dmalloc(&s->d_root_b, roots * 384)); ok(dmalloc(&s->d_root_d, roots * 8)); ok(dmalloc(&s->d_root_r, roots));
+  ok(dmalloc(&s->d_b, B * 384)); ok(dmalloc(&s->d_d, B * 8)); ok(dmalloc(&s->d_r, B));
+  ok(dmalloc(&s->d_idx1, B)); ok(dmalloc(&s->d_idx2, B)); ok(dmalloc(&s->d_rolls, B));
+  ok(dmalloc(&s->d_act, B * 18)); ok(dmalloc(&s->d_cnt, B * 2)); ok(dmalloc(&s->d_score, B));
+  ok(dmalloc(&s->d_rng, B * 8)); ok(dmalloc(&s->d_pseed, B * 8));
+  ok(hmalloc(&s->h_idx1, B)); ok(hmalloc(&s->h_idx2, B)); ok(hmalloc(&s->h_rolls, B)); ok(hmalloc(&s->h_res, B));
+  ok(hmalloc(&s->h_act, B * 16)); ok(hmalloc(&s->h_cnt, B * 2)); ok(hmalloc(&s->h_score, B));
+  ok(hmalloc(&s->h_rng, B * 8)); ok(hmalloc(&s->h_pseed, B * 8));
+  if (e != cudaSuccess) {
+    search_free(s);
+    return fail(ctx, OAKB200_ECUDA, "search_create: allocation", e);
+  }
+  s->particles.resize(B);
+  *out = s;
+  return OAKB200_OK;
+}
+
+void oakb200_search_destroy(oakb200_search* s) { search_free(s); }
+
+int oakb200_search_set_roots(oakb200_search* s, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                             const uint64_t* seeds) {
+  if (!s) return OAKB200_EINVAL;
+  oakb200_ctx* ctx = s->ctx;
+  if (!battles || !durations || !results || !seeds || n == 0 || n > s->roots_max) return fail(ctx, OAKB200_EINVAL, "search_set_roots: bad argument");
+  CU(ctx, cudaSetDevice(ctx->device));
+  CU(ctx, cudaMemcpyAsync(s->d_root_b, battles, n * 384, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(s->d_root_d, durations, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(s->d_root_r, results, n, cudaMemcpyHostToDevice, ctx->stream));
+  // the roots' legal choices (mcts.h:161-166) come from the same kernel every caller uses
+  int rc = oakb200_choices_device(ctx, n, s->d_root_b, s->d_root_r, s->d_act, s->d_cnt);
+  if (rc) return rc;
+  std::vector<uint8_t> ch(n * 18), cnt(n * 2);
+  CU(ctx, cudaMemcpyAsync(ch.data(), s->d_act, n * 18, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(cnt.data(), s->d_cnt, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  s->n_roots = n;
+  s->roots.assign(n, Root());
+  for (size_t r = 0; r < n; r++) {
+    if ((results[r] & 15u) != 0) return fail(ctx, OAKB200_EINVAL, "search_set_roots: a root battle is already over");
+    Root& R = s->roots[r];
+    R.seed = seeds[r];
+    R.k1 = cnt[2 * r];
+    R.k2 = cnt[2 * r + 1];
+    memcpy(R.choices, ch.data() + 18 * r, 18);
+    R.nodes.reserve(1024);
+    R.nodes.emplace_back();
+    R.nodes[0].p1.init(R.k1);
+    R.nodes[0].p2.init(R.k2);
+  }
+  return OAKB200_OK;
+}
+
+int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint32_t root_rolls, uint32_t other_rolls, int host_threads) {
+  if (!s) return OAKB200_EINVAL;
+  oakb200_ctx* ctx = s->ctx;
+  auto rolls_ok = [](uint32_t r) { return r == 1 || r == 2 || r == 3 || r == 20 || r == 39; };
+  if (s->n_roots == 0 || !rolls_ok(root_rolls) || !rolls_ok(other_rolls))
+    return fail(ctx, OAKB200_EINVAL, "search_run: set roots first; rolls must be 1, 2, 3, 20 or 39");
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (host_threads < 1) host_threads = (int)std::thread::hardware_concurrency();
+  if (!s->pool || s->pool_threads != host_threads) {
+    delete s->pool;
+    s->pool = new Pool(host_threads);
+    s->pool_threads = host_threads;
+  }
+  const uint32_t P = s->P;
+  const size_t R = s->n_roots, B = R * P;
+  const uint32_t MAX_DEPTH = 100;  // mcts.h:309
+  const uint32_t waves = (iterations + P - 1) / P;
+  for (uint32_t w = 0; w < waves; w++) {
+    // ---- spawn: fresh rng per particle, hidden variables redrawn from the root's observed durations
+    s->pool->parallel_for(R, [&](size_t r) {
+      Root& root = s->roots[r];
+      for (uint32_t p = 0; p < P; p++) {
+        const size_t b = r * P + p;
+        const uint64_t nth = root.iterations + p;
+        s->h_rng[b] = splitmix64(root.seed ^ (STREAM_K * (2 * nth + 1)));
+        s->h_pseed[b] = splitmix64(root.seed ^ (STREAM_K * (2 * nth + 2)));
+        Particle& q = s->particles[b];
+        q.cur = 0;
+        q.active = true;
+        q.path.clear();
+      }
+    });
+    CU(ctx, cudaMemcpyAsync(s->d_rng, s->h_rng, B * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(s->d_pseed, s->h_pseed, B * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, oakb200_launch_search_spawn(ctx, s->d_root_b, s->d_root_d, s->d_root_r, s->d_rng, P, s->d_b, s->d_d, s->d_r, (uint32_t)B));
+    int rc = oakb200_randomize_hidden_device(ctx, B, s->d_b, s->d_d);
+    if (rc) return rc;
+    // ---- descend, one tree level per launch
+    for (uint32_t depth = 0;; depth++) {
+      std::atomic<size_t> n_active{0};
+      s->pool->parallel_for(R, [&](size_t r) {
+        Root& root = s->roots[r];
+        size_t cnt = 0;
+        for (uint32_t p = 0; p < P; p++) {
+          const size_t b = r * P + p;
+          Particle& q = s->particles[b];
+          if (!q.active || depth >= MAX_DEPTH) {
+            q.active = false;
+            s->h_idx1[b] = s->h_idx2[b] = 255;
+            continue;
+          }
+          Node& node = root.nodes[q.cur];
+          const int i = node.p1.select(ucb_c), j = node.p2.select(ucb_c);
+          node.p1.visits[i]++;  // the visit is counted now (virtual visit), the value at back-propagation
+          node.p2.visits[j]++;
+          q.path.push_back({q.cur, (uint8_t)i, (uint8_t)j});
+          s->h_idx1[b] = (uint8_t)i;
+          s->h_idx2[b] = (uint8_t)j;
+          s->h_rolls[b] = (uint8_t)(depth == 0 ? root_rolls : other_rolls);
+          cnt++;
+        }
+        n_active += cnt;
+      });
+      if (n_active.load() == 0) break;
+      s->levels++;
+      CU(ctx, cudaMemcpyAsync(s->d_idx1, s->h_idx1, B, cudaMemcpyHostToDevice, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(s->d_idx2, s->h_idx2, B, cudaMemcpyHostToDevice, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(s->d_rolls, s->h_rolls, B, cudaMemcpyHostToDevice, ctx->stream));
+      CU(ctx, oakb200_launch_search_step(ctx, s->d_b, s->d_d, s->d_r, s->d_idx1, s->d_idx2, s->d_rolls, s->d_act, s->d_cnt, (uint32_t)B));
+      CU(ctx, cudaMemcpyAsync(s->h_res, s->d_r, B, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(s->h_act, s->d_act, B * 16, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(ctx, cudaMemcpyAsync(s->h_cnt, s->d_cnt, B * 2, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(ctx, cudaStreamSynchronize(ctx->stream));
+      s->pool->parallel_for(R, [&](size_t r) {
+        Root& root = s->roots[r];
+        for (uint32_t p = 0; p < P; p++) {
+          const size_t b = r * P + p;
+          Particle& q = s->particles[b];
+          if (!q.active) continue;
+          const PathEntry& pe = q.path.back();
+          const uint8_t* obs = s->h_act + b * 16;
+          int32_t child = -1;
+          for (const Child& c : root.nodes[pe.node].children)
+            if (c.i == pe.i && c.j == pe.j && memcmp(c.obs, obs, 16) == 0) {
+              child = c.node;
+              break;
+            }
+          if (child < 0) {
+            child = (int32_t)root.nodes.size();
+            root.nodes.emplace_back();
+            Child c;
+            c.i = pe.i;
+            c.j = pe.j;
+            memcpy(c.obs, obs, 16);
+            c.node = child;
+            root.nodes[pe.node].children.push_back(c);
+          }
+          q.cur = child;
+          Node& cn = root.nodes[child];
+          const bool over = (s->h_res[b] & 15u) != 0;
+          if (cn.is_init() && !over) continue;  // keep descending (mcts.h:328)
+          if (!over) {                           // new leaf: init its bandits, then a playout (mcts.h:399, :463-465)
+            cn.p1.init(s->h_cnt[2 * b]);
+            cn.p2.init(s->h_cnt[2 * b + 1]);
+          }
+          root.total_depth += depth + 1;
+          q.active = false;
+        }
+      });
+    }
+    // ---- leaves: playouts of every particle (a finished battle returns its score at once)
+    rc = oakb200_rollout_device(ctx, B, s->d_b, s->d_d, s->d_r, s->d_pseed, 100000, 0, s->d_score, nullptr, nullptr);
+    if (rc) return rc;
+    CU(ctx, cudaMemcpyAsync(s->h_score, s->d_score, B, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    // ---- back-propagation (mcts.h:363-384)
+    s->pool->parallel_for(R, [&](size_t r) {
+      Root& root = s->roots[r];
+      for (uint32_t p = 0; p < P; p++) {
+        const size_t b = r * P + p;
+        const float v1 = (float)s->h_score[b] * 0.5f, v2 = 1.0f - v1;
+        const Particle& q = s->particles[b];
+        for (const PathEntry& pe : q.path) {
+          Node& node = root.nodes[pe.node];
+          node.p1.scores[pe.i] += v1;
+          node.p2.scores[pe.j] += v2;
+        }
+        if (!q.path.empty()) {
+          root.visit[q.path[0].i * 9 + q.path[0].j]++;
+          root.value[q.path[0].i * 9 + q.path[0].j] += v1;
+        }
+        root.iterations++;
+      }
+    });
+    s->waves++;
+  }
+  return OAKB200_OK;
+}
+
+int oakb200_search_output(oakb200_search* s, uint8_t* k, uint8_t* choices, uint32_t* visit_matrix, double* value_matrix,
+                          uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes) {
+  if (!s) return OAKB200_EINVAL;
+  for (size_t r = 0; r < s->n_roots; r++) {
+    const Root& R = s->roots[r];
+    if (k) { k[2 * r] = R.k1; k[2 * r + 1] = R.k2; }
+    if (choices) memcpy(choices + 18 * r, R.choices, 18);
+    if (visit_matrix) memcpy(visit_matrix + 81 * r, R.visit, sizeof(R.visit));
+    if (value_matrix) memcpy(value_matrix + 81 * r, R.value, sizeof(R.value));
+    if (iterations) iterations[r] = R.iterations;
+    if (nodes) nodes[r] = R.nodes.size();
+    // process_output (mcts.h:623-661) without the Nash solve, which stays with the caller (LRSNash)
+    double total = 0, e1[9] = {0}, e2[9] = {0};
+    for (int i = 0; i < R.k1; i++)
+      for (int j = 0; j < R.k2; j++) {
+        total += R.value[i * 9 + j];
+        e1[i] += R.visit[i * 9 + j];
+        e2[j] += R.visit[i * 9 + j];
+      }
+    const double it = R.iterations ? (double)R.iterations : 1.0;
+    if (empirical_value) empirical_value[r] = total / it;
+    if (empirical)
+      for (int i = 0; i < 9; i++) {
+        empirical[18 * r + i] = e1[i] / (float)it;
+        empirical[18 * r + 9 + i] = e2[i] / (float)it;
+      }
+  }
+  return OAKB200_OK;
+}
+
+int oakb200_search_stats(oakb200_search* s, uint64_t* waves, uint64_t* levels) {
+  if (!s) return OAKB200_EINVAL;
+  if (waves) *waves = s->waves;
+  if (levels) *levels = s->levels;
+  return OAKB200_OK;
+}
+
+}  // extern "C"

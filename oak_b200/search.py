@@ -1,0 +1,70 @@
+"""Batched-leaf tree search over the oakb200 C ABI (oakb200_search_*): host trees and UCB bandits in the library's C++
+host code, every battle operation on the GPU. Mirrors MCTS::Search::run -> MCTS::Output (reference
+cpp/include/search/mcts.h:68-89,154-246) for many roots at once."""
+import ctypes
+
+import numpy as np
+
+from .engine import OakB200Error, _np, _ptr
+
+
+class TreeSearch:
+    def __init__(self, engine, roots, particles=1):
+        self.eng, self.lib = engine, engine.lib
+        vp, sz, u32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32
+        lib = self.lib
+        lib.oakb200_search_create.restype = ctypes.c_int
+        lib.oakb200_search_create.argtypes = [vp, sz, u32, ctypes.POINTER(vp)]
+        lib.oakb200_search_destroy.restype = None
+        lib.oakb200_search_destroy.argtypes = [vp]
+        lib.oakb200_search_set_roots.restype = ctypes.c_int
+        lib.oakb200_search_set_roots.argtypes = [vp, sz, vp, vp, vp, vp]
+        lib.oakb200_search_run.restype = ctypes.c_int
+        lib.oakb200_search_run.argtypes = [vp, u32, ctypes.c_float, u32, u32, ctypes.c_int]
+        lib.oakb200_search_output.restype = ctypes.c_int
+        lib.oakb200_search_output.argtypes = [vp] * 9
+        lib.oakb200_search_stats.restype = ctypes.c_int
+        lib.oakb200_search_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
+        h = vp()
+        self._check(lib.oakb200_search_create(engine._h, int(roots), int(particles), ctypes.byref(h)))
+        self._h, self.roots_max, self.particles, self.n = h, int(roots), int(particles), 0
+
+    def _check(self, rc):
+        if rc != 0:
+            raise OakB200Error(f"oakb200 search error {rc}: {self.lib.oakb200_last_error(self.eng._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.oakb200_search_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_roots(self, battles, durations, results, seeds):
+        battles = _np(battles, np.uint8)
+        n = battles.shape[0]
+        battles, durations = _np(battles, np.uint8, (n, 384)), _np(durations, np.uint8, (n, 8))
+        results, seeds = _np(results, np.uint8, (n,)), _np(seeds, np.uint64, (n,))
+        self._check(self.lib.oakb200_search_set_roots(self._h, n, _ptr(battles), _ptr(durations), _ptr(results), _ptr(seeds)))
+        self.n = n
+
+    def run(self, iterations, c=1.0, root_rolls=3, other_rolls=1, host_threads=0):
+        self._check(self.lib.oakb200_search_run(self._h, int(iterations), float(c), int(root_rolls), int(other_rolls), int(host_threads)))
+
+    def output(self):
+        n = self.n
+        out = dict(k=np.zeros((n, 2), np.uint8), choices=np.zeros((n, 2, 9), np.uint8), visit_matrix=np.zeros((n, 9, 9), np.uint32),
+                   value_matrix=np.zeros((n, 9, 9), np.float64), iterations=np.zeros(n, np.uint64),
+                   empirical_value=np.zeros(n, np.float64), empirical=np.zeros((n, 2, 9), np.float64), nodes=np.zeros(n, np.uint64))
+        self._check(self.lib.oakb200_search_output(self._h, *[_ptr(out[k]) for k in ("k", "choices", "visit_matrix", "value_matrix",
+                                                                                  "iterations", "empirical_value", "empirical", "nodes")]))
+        return out
+
+    def stats(self):
+        w, lv = ctypes.c_uint64(), ctypes.c_uint64()
+        self._check(self.lib.oakb200_search_stats(self._h, ctypes.byref(w), ctypes.byref(lv)))
+        return w.value, lv.value

@@ -223,3 +223,20 @@ int oracle_policy_sample(const float* logits, int k, double temp, double floor_p
   return frames_oracle::policy_sample(logits, k, temp, floor_p, u, probs9);
 }
 }
+
+// ---- tree search (mcts_oracle.hpp) ----
+#include "mcts_oracle.hpp"
+extern "C" {
+void oracle_mcts_run(const uint8_t* battle384, const uint8_t* durations8, uint8_t result, uint64_t seed, uint32_t iterations, float c,
+                     uint32_t root_rolls, uint32_t other_rolls, uint32_t* visit81, double* value81, uint64_t* nodes) {
+  mcts_oracle::Search s;
+  s.c = c;
+  s.root_rolls = root_rolls;
+  s.other_rolls = other_rolls;
+  s.seed = seed;
+  s.run(battle384, durations8, result, iterations);
+  memcpy(visit81, s.visit, sizeof(s.visit));
+  memcpy(value81, s.value, sizeof(s.value));
+  if (nodes) *nodes = s.nodes;
+}
+}
