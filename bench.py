@@ -339,6 +339,47 @@ def main():
     sp_bytes = sum(len(x) for x in gathered) if gathered is not None else 0
     sp.close()
 
+    # ---- secondary: tree search with GPU leaves (BASELINE configs[3]): 4096 root positions sharded over the ranks,
+    # host trees + UCB bandits, 64 descents per root in flight, clamped rolls 3/1 as the reference's default_search
+    from oak_b200.search import TreeSearch
+    SR_ROOTS, SR_P, SR_ITERS = max(1, 4096 // world), 64, 256
+    sr_b, sr_d, sr_r = (x[:SR_ROOTS].cpu().numpy() for x in (lock_b, lock_d, lock_r))  # states after 19 playout steps
+    sr_live = (sr_r & 15) == 0
+    sr_b, sr_d, sr_r = sr_b[sr_live], sr_d[sr_live], sr_r[sr_live]
+    sr_seeds = seeds_np[:SR_ROOTS][sr_live]
+    ts = TreeSearch(eng, sr_b.shape[0], particles=SR_P)
+    ts.set_roots(sr_b, sr_d, sr_r, sr_seeds)
+    ts.run(SR_P)
+    barrier()
+    l0 = eng.launch_count
+    t0 = time.perf_counter()
+    ts.run(SR_ITERS)
+    barrier()
+    sr_s = time.perf_counter() - t0
+    launches += eng.launch_count - l0
+    sr_out = ts.output()
+    sr_done = float(sr_b.shape[0] * SR_ITERS)
+    ts.close()
+    sr_cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        import ctypes as _ct
+        from concurrent.futures import ThreadPoolExecutor
+        from oak_ref import Oracle as _O2
+        _f = _O2().lib.oracle_mcts_run
+        _f.restype = None
+        _f.argtypes = [_ct.c_void_p, _ct.c_void_p, _ct.c_uint8, _ct.c_uint64, _ct.c_uint32, _ct.c_float, _ct.c_uint32, _ct.c_uint32,
+                       _ct.c_void_p, _ct.c_void_p, _ct.c_void_p]
+        _thr = os.cpu_count() or 1
+        _nr, _it = 4 * _thr, 4096
+
+        def _one(i):
+            v, w = np.zeros(81, np.uint32), np.zeros(81, np.float64)
+            _f(sr_b[i].ctypes.data, sr_d[i].ctypes.data, int(sr_r[i]), int(sr_seeds[i]), _it, 1.0, 3, 1, v.ctypes.data, w.ctypes.data, None)
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(_thr) as ex:
+            list(ex.map(_one, range(min(_nr, sr_b.shape[0]))))
+        sr_cpu = min(_nr, sr_b.shape[0]) * _it / (time.perf_counter() - t0)
+
     eval_cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         from oak_ref import NetOracle, Oracle as _O
@@ -350,13 +391,13 @@ def main():
         eval_cpu = EV / (time.perf_counter() - t0)
 
     # ---- reduce over ranks: max time, sum of work
-    t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms], dtype=torch.float64, device=dev)
-    w = torch.tensor([steps_per_pass * args.steps, n * args.steps, e2e_steps * e2e_iters, launches, n], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms, sr_s * 1e3], dtype=torch.float64, device=dev)
+    w = torch.tensor([steps_per_pass * args.steps, n * args.steps, e2e_steps * e2e_iters, launches, n, sr_done], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(w, op=dist.ReduceOp.SUM)
-    ms_total_max, e2e_ms_max, lock_ms_max = t.tolist()
-    tot_steps, tot_rollouts, tot_e2e_steps, tot_launches, tot_battles = w.tolist()
+    ms_total_max, e2e_ms_max, lock_ms_max, sr_ms_max = t.tolist()
+    tot_steps, tot_rollouts, tot_e2e_steps, tot_launches, tot_battles, tot_sr = w.tolist()
 
     if rank == 0:
         pk, pk_src = peaks()
@@ -414,6 +455,12 @@ def main():
                                        "note": "executed = every tcgen05.mma issued (3 products per split-bf16 GEMM, K and N "
                                                "padding included); dense-equivalent = SURVEY 8d F_eval"},
                           "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (cache-free, sparse first layers), all host cores"},
+            "tree_search": {"iterations_per_s": tot_sr / (sr_ms_max * 1e-3), "roots_total": int(tot_sr / SR_ITERS),
+                            "descents_in_flight_per_root": SR_P, "iterations_per_root": SR_ITERS,
+                            "mean_root_value": float(sr_out["empirical_value"].mean()),
+                            "cpu_iterations_per_s": sr_cpu, "cpu_kind": "port (sequential MCTS restatement, all host cores)",
+                            "note": "MonteCarlo leaves, joint UCB c=1, clamped rolls 3/1 (mcts.h:133); host trees, one kernel "
+                                    "launch per tree level + hidden-variable draw + playouts per wave"},
             "selfplay": {"game_updates_per_s": world * SP_G * SP_STEPS / sp_s, "games_per_gpu": SP_G, "steps": SP_STEPS,
                          "stream_bytes_at_writer": int(sp_bytes),
                          "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
