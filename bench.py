@@ -233,8 +233,8 @@ def main():
     lib, h = eng.lib, eng._h
 
     def e2e_step():
-        rc = lib.oakb200_upload(h, n, phb.data_ptr(), phd.data_ptr(), phr.data_ptr())
-        rc |= lib.oakb200_rollout(h, phs.data_ptr(), 100000, 0, o_score.data_ptr(), o_turns.data_ptr(), o_steps.data_ptr())
+        rc = lib.oakb200_rollout_host(h, n, phb.data_ptr(), phd.data_ptr(), phr.data_ptr(), phs.data_ptr(), 100000,
+                                      o_score.data_ptr(), o_turns.data_ptr(), o_steps.data_ptr())
         if rc:
             raise RuntimeError(lib.oakb200_last_error(h).decode())
 
@@ -429,7 +429,7 @@ def main():
             "e2e": {"value": tot_e2e_steps / (e2e_ms_max * 1e-3), "unit": "battle-steps/s",
                     "rollouts_per_s": tot_battles * e2e_iters / (e2e_ms_max * 1e-3),
                     "h2d_bytes_per_step": int(tot_battles * (384 + 8 + 1 + 8)), "d2h_bytes_per_step": int(tot_battles * (1 + 2 + 4)),
-                    "iters": e2e_iters, "timing": "wall clock around upload+rollout+download, synchronised"},
+                    "iters": e2e_iters, "timing": "wall clock around oakb200_rollout_host (pinned host records in, score/turns/steps out; chunked upload pipelined behind the playouts), synchronised"},
             "roofline": {"bound": "hbm", "kernel": "rollout_kernel<128,false,false>", "achieved": achieved, "peak": pk["hbm_gbs"],
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_src,
                          "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": statistics.mean(kernel_ms),

@@ -98,6 +98,11 @@ int oakb200_rollout(oakb200_ctx* ctx, const uint64_t* seeds, uint32_t max_steps,
                     uint16_t* turns_out, uint32_t* steps_out);
 int oakb200_rollout_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
                            uint32_t max_steps, uint32_t flags, void* score2_out, void* turns_out, void* steps_out);
+/* oakb200_upload + oakb200_rollout in one call with the upload hidden behind the playouts (chunk copies on a copy stream,
+ * one persistent kernel that consumes records as they land): HOST pointers, PINNED memory required for the overlap. durations / results / any output may be NULL.
+ * The batch stays resident afterwards. No state write-back and no chance tracking (flags = 0). */
+int oakb200_rollout_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                         const uint64_t* seeds, uint32_t max_steps, uint8_t* score2_out, uint16_t* turns_out, uint32_t* steps_out);
 /* Sum of updates performed by all rollout launches on this context (device counter, synchronises). */
 int oakb200_total_steps(oakb200_ctx* ctx, uint64_t* out);
 

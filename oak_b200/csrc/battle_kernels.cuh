@@ -141,6 +141,15 @@ step_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint
   }
 }
 
+// Streaming input (oakb200_rollout_host): the batch is still arriving over PCIe while the kernel runs. The copy stream
+// raises *available (the number of leading records that have landed) after each chunk; a lane whose ticket is beyond it
+// waits. Tickets and chunks both advance in index order and every copy was queued before the launch, so the wait ends.
+__device__ __forceinline__ void wait_available(const uint32_t* available, uint32_t i) {
+  if (!available) return;
+  while (i >= *reinterpret_cast<const volatile uint32_t*>(available)) __nanosleep(500);
+  __threadfence();
+}
+
 // ---------------------------------------------------------------------------------------------
 // rollout_kernel: random playouts to a terminal result. Persistent CTAs; every lane pulls its next
 // battle from a global ticket counter the moment its current one ends (lane refill), so a warp
@@ -151,7 +160,7 @@ __global__ void __launch_bounds__(BLOCK, 3)
 rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
-               unsigned long long* __restrict__ total_steps) {
+               unsigned long long* __restrict__ total_steps, const uint32_t* __restrict__ available) {
   extern __shared__ uint32_t tile[];
   uint32_t* col = tile + threadIdx.x;
   Engine<BLOCK, false, CHANCE> e;
@@ -166,6 +175,7 @@ rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, u
     if (!have && !exhausted) {
       i = atomicAdd(ticket, 1u);
       if (i < n) {
+        wait_available(available, i);
         load_column<BLOCK>(col, battles + (size_t)i * 384);
         const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
         e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
@@ -238,7 +248,7 @@ __global__ void __launch_bounds__(BLOCK, 3)
 rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                        const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                        uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
-                       unsigned long long* __restrict__ total_steps) {
+                       unsigned long long* __restrict__ total_steps, const uint32_t* __restrict__ available) {
   static_assert(BLOCK == 128, "action_class and the sort assume 128 columns");
   extern __shared__ uint32_t tile[];
   uint32_t* s_meta = tile + BATTLE_WORDS * BLOCK;  // c1 | c2 << 8 | live << 16
@@ -260,6 +270,7 @@ rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ dura
     if (!have && !exhausted) {
       i = atomicAdd(ticket, 1u);
       if (i < n) {
+        wait_available(available, i);
         load_column<BLOCK>(col, battles + (size_t)i * 384);
         const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
         s_dur[2 * t] = d.x;

@@ -34,6 +34,11 @@ struct oakb200_ctx {
   float* eval_values = nullptr;
   float* eval_logits = nullptr;
   uint8_t* eval_counts = nullptr;
+  // transfer/compute pipeline of oakb200_rollout_host
+  bool pipe_ready = false;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t pipe_start = nullptr;
+  uint32_t* pipe_marks = nullptr;  // pinned: records available after each chunk
   std::string error;
 };
 

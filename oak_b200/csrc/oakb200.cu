@@ -50,7 +50,9 @@ cudaError_t launch_step(oakb200_ctx* ctx, size_t n, void* battles, void* duratio
 
 template <bool CHANCE, bool WRITE>
 cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
-                           uint32_t max_steps, void* score2, void* turns, void* steps) {
+                           uint32_t max_steps, void* score2, void* turns, void* steps, const uint32_t* available = nullptr) {
+  cudaStream_t stream = ctx->stream;
+  uint32_t* ticket = ctx->ticket;
   // OAKB200_ROLLOUT_GROUPED=1 selects the variant that regroups a CTA's battles by action class before every update.
   // Measured on B200 (profiles/r1h_rollout_grouping.txt): 16 % fewer warp instructions and 9.8 -> 12.8 active lanes, but
   // the CTA-wide barriers cost more issue slots than that saves (2.08 vs 2.35 G battle-steps/s), so it is not the default.
@@ -73,11 +75,11 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
   unsigned grid = (unsigned)(ctx->sm_count * per_sm);
   const unsigned need = grid_for(n);
   if (grid > need) grid = need;
-  e = cudaMemsetAsync(ctx->ticket, 0, sizeof(uint32_t), ctx->stream);
+  e = cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  k<<<grid, BLOCK, tile_bytes, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
-                                              (const uint64_t*)seeds, max_steps, (uint32_t)n, ctx->ticket,
-                                              (uint8_t*)score2, (uint16_t*)turns, (uint32_t*)steps, ctx->total_steps);
+  k<<<grid, BLOCK, tile_bytes, stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results,
+                                              (const uint64_t*)seeds, max_steps, (uint32_t)n, ticket,
+                                              (uint8_t*)score2, (uint16_t*)turns, (uint32_t*)steps, ctx->total_steps, available);
   ctx->launches++;
   return cudaGetLastError();
 }
@@ -140,7 +142,7 @@ int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
   CU(ctx, cudaMalloc(&ctx->eval_values, n_max * 4));
   CU(ctx, cudaMalloc(&ctx->eval_logits, n_max * 18 * 4));
   CU(ctx, cudaMalloc(&ctx->eval_counts, n_max * 2));
-  CU(ctx, cudaMalloc(&ctx->ticket, sizeof(uint32_t)));
+  CU(ctx, cudaMalloc(&ctx->ticket, 64 * sizeof(uint32_t)));  // [0] the context stream's, [1..] one per pipelined chunk
   CU(ctx, cudaMalloc(&ctx->total_steps, sizeof(unsigned long long)));
   CU(ctx, cudaMemset(ctx->total_steps, 0, sizeof(unsigned long long)));
   return OAKB200_OK;
@@ -156,6 +158,11 @@ void oakb200_destroy(oakb200_ctx* ctx) {
   oakb200_frames_release(ctx);
   for (void* b : bufs)
     if (b) cudaFree(b);
+  if (ctx->pipe_ready) {
+    cudaStreamDestroy(ctx->copy_stream);
+    cudaEventDestroy(ctx->pipe_start);
+    cudaFreeHost(ctx->pipe_marks);
+  }
   if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -314,6 +321,56 @@ int oakb200_rollout(oakb200_ctx* ctx, const uint64_t* seeds, uint32_t max_steps,
   if (turns_out) CU(ctx, cudaMemcpyAsync(turns_out, ctx->turns, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
   if (steps_out) CU(ctx, cudaMemcpyAsync(steps_out, ctx->steps, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
+// Host buffers in, host buffers out, with the upload hidden behind the playouts: every chunk copy is queued on a copy
+// stream, each followed by a 4-byte copy that raises the device-side "records available" counter; ONE persistent rollout
+// launch then consumes records as they land (wait_available in battle_kernels.cuh). Same results as
+// oakb200_upload + oakb200_rollout.
+int oakb200_rollout_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                         const uint64_t* seeds, uint32_t max_steps, uint8_t* score2_out, uint16_t* turns_out, uint32_t* steps_out) {
+  if (!ctx || !battles || !seeds) return fail(ctx, OAKB200_EINVAL, "rollout_host: null argument");
+  if (n > ctx->n_max) return fail(ctx, OAKB200_ECAPACITY, "rollout_host: n exceeds n_max");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  const int MAX_CHUNKS = 32;
+  if (!ctx->pipe_ready) {
+    CU(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    CU(ctx, cudaEventCreateWithFlags(&ctx->pipe_start, cudaEventDisableTiming));
+    CU(ctx, cudaMallocHost(&ctx->pipe_marks, MAX_CHUNKS * sizeof(uint32_t)));
+    ctx->pipe_ready = true;
+  }
+  size_t chunk = (size_t)1 << 16;
+  if (const char* c = getenv("OAKB200_PIPE_CHUNK")) chunk = (size_t)atol(c) > 0 ? (size_t)atol(c) : chunk;  // tuning knob
+  if ((n + chunk - 1) / chunk > (size_t)MAX_CHUNKS) chunk = (n + MAX_CHUNKS - 1) / MAX_CHUNKS;
+  const int chunks = (int)((n + chunk - 1) / chunk);
+  uint32_t* avail = ctx->ticket + 1;
+  // the counter is cleared in context-stream order; the copies start after that and after everything queued before
+  CU(ctx, cudaMemsetAsync(avail, 0, sizeof(uint32_t), ctx->stream));
+  // defaults are filled here, before the launch: the copy stream must carry DMA copies only, nothing that needs an SM
+  if (!durations) CU(ctx, cudaMemsetAsync(ctx->durations, 0, n * 8, ctx->stream));
+  if (!results) CU(ctx, cudaMemsetAsync(ctx->results, RESULT_DEFAULT, n, ctx->stream));
+  CU(ctx, cudaEventRecord(ctx->pipe_start, ctx->stream));
+  CU(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->pipe_start, 0));
+  cudaStream_t cs = ctx->copy_stream;
+  for (int k = 0; k < chunks; k++) {
+    const size_t at = (size_t)k * chunk, m = n - at < chunk ? n - at : chunk;
+    CU(ctx, cudaMemcpyAsync(ctx->battles + at * 384, battles + at * 384, m * 384, cudaMemcpyHostToDevice, cs));
+    if (durations) CU(ctx, cudaMemcpyAsync(ctx->durations + at * 8, durations + at * 8, m * 8, cudaMemcpyHostToDevice, cs));
+    if (results) CU(ctx, cudaMemcpyAsync(ctx->results + at, results + at, m, cudaMemcpyHostToDevice, cs));
+    CU(ctx, cudaMemcpyAsync(ctx->seeds + at, seeds + at, m * 8, cudaMemcpyHostToDevice, cs));
+    ctx->pipe_marks[k] = (uint32_t)(at + m);
+    CU(ctx, cudaMemcpyAsync(avail, ctx->pipe_marks + k, sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+  }
+  CU(ctx, (launch_rollout<false, false>(ctx, n, ctx->battles, ctx->durations, ctx->results, ctx->seeds, max_steps, ctx->score2,
+                                        ctx->turns, ctx->steps, avail)));
+  if (score2_out) CU(ctx, cudaMemcpyAsync(score2_out, ctx->score2, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (turns_out) CU(ctx, cudaMemcpyAsync(turns_out, ctx->turns, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  if (steps_out) CU(ctx, cudaMemcpyAsync(steps_out, ctx->steps, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  ctx->n = n;
   return OAKB200_OK;
 }
 

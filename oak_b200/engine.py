@@ -55,6 +55,7 @@ def load_library():
         "oakb200_step_random_device": (i32, [vp, sz, vp, vp, vp, vp, u32, vp, vp]),
         "oakb200_rollout": (i32, [vp, vp, u32, u32, vp, vp, vp]),
         "oakb200_rollout_device": (i32, [vp, sz, vp, vp, vp, vp, u32, u32, vp, vp, vp]),
+        "oakb200_rollout_host": (i32, [vp, sz, vp, vp, vp, vp, u32, vp, vp, vp]),
         "oakb200_total_steps": (i32, [vp, ctypes.POINTER(ctypes.c_uint64)]),
         "oakb200_randomize_hidden_device": (i32, [vp, sz, vp, vp]),
         "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
@@ -197,6 +198,20 @@ class BattleEngine:
         steps = np.empty((n,), np.uint32)
         flags = (ROLLOUT_WRITE_STATE if write_state else 0) | (ROLLOUT_TRACK_CHANCE if track_chance else 0)
         self._check(self.lib.oakb200_rollout(self._h, _ptr(seeds), int(max_steps), flags, _ptr(score), _ptr(turns), _ptr(steps)))
+        return score, turns, steps
+
+    def rollout_host(self, battles, durations, results, seeds, max_steps=100000):
+        """upload + rollout with the transfers pipelined behind the playouts -> (score2, turns, steps)."""
+        battles = _np(battles, np.uint8)
+        n = battles.shape[0]
+        battles = _np(battles, np.uint8, (n, 384))
+        durations = None if durations is None else _np(durations, np.uint8, (n, 8))
+        results = None if results is None else _np(results, np.uint8, (n,))
+        seeds = _np(seeds, np.uint64, (n,))
+        score, turns, steps = np.empty((n,), np.uint8), np.empty((n,), np.uint16), np.empty((n,), np.uint32)
+        self._check(self.lib.oakb200_rollout_host(self._h, n, _ptr(battles), _ptr(durations), _ptr(results), _ptr(seeds),
+                                                  int(max_steps), _ptr(score), _ptr(turns), _ptr(steps)))
+        self.n = n
         return score, turns, steps
 
     # ---------------------------------------------------------------- leaf evaluation

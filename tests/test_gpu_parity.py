@@ -226,3 +226,22 @@ def test_full_size_checksums_one_million_playouts(orc, eng):
     x_cpu = np.bitwise_xor.reduce(b[:, 376:384].copy().view(np.uint64).ravel())
     assert x_gpu == x_cpu
     assert np.array_equal(gb, b) and np.array_equal(gr, r)
+
+
+def test_pipelined_host_rollout_equals_resident_rollout(orc):
+    """oakb200_rollout_host (chunked upload overlapped with the playouts) returns exactly what upload + rollout returns,
+    including a batch that does not divide into chunks."""
+    import oak_b200
+    n = 300_001
+    b, d, r = oracle_sample_batch(orc, 0, n)
+    seeds = sample_seeds(0, n)
+    eng = oak_b200.BattleEngine(n)
+    eng.upload(b, d, r)
+    want = eng.rollout(seeds)
+    got = eng.rollout_host(b, d, r, seeds)
+    for a, w in zip(got, want):
+        assert np.array_equal(a, w)
+    got = eng.rollout_host(b[:1000], None, None, seeds[:1000])
+    for a, w in zip(got, want):
+        assert np.array_equal(a, w[:1000])
+    eng.close()
