@@ -240,3 +240,95 @@ void oracle_mcts_run(const uint8_t* battle384, const uint8_t* durations8, uint8_
   if (nodes) *nodes = s.nodes;
 }
 }
+
+// ---- training rows (train_rows_oracle.hpp) ----
+#include "train_rows_oracle.hpp"
+extern "C" {
+// Plays sample battle `index` (oak_oracle.hpp) to the end or `max_updates` with playout picks from `seed` and writes it
+// as one stored game with made-up search outputs (a counter-based stream), through frames_oracle::write_game.
+// Returns bytes written (0 if the game did not finish within max_updates: such games are not stored).
+uint32_t oracle_play_frame_game(uint64_t index, uint64_t seed, uint32_t max_updates, uint8_t* out) {
+  oracle::Battle b;
+  uint8_t dur[8], result;
+  oracle::oak_sample_battle(index, b, dur, &result);
+  uint8_t first[384];
+  memcpy(first, &b, 384);
+  std::vector<uint8_t> k, choice;
+  std::vector<uint32_t> iters;
+  std::vector<double> ev, nv, emp, nash;
+  uint64_t s = oracle::splitmix64(seed ^ 0xA5A5A5A5ull);
+  auto unit = [&]() {
+    s = oracle::splitmix64(s);
+    return (double)(s >> 11) * (1.0 / 9007199254740992.0);
+  };
+  uint32_t step = 0;
+  while ((result & 15) == 0 && step < max_updates) {
+    oracle::Options o{};
+    memcpy(o.durations, dur, 8);
+    oracle::OakEngine e(b, o);
+    uint8_t ch1[9], ch2[9];
+    const uint8_t m = e.choices(oracle::P1, (result >> 4) & 3, ch1), n = e.choices(oracle::P2, (result >> 6) & 3, ch2);
+    const uint64_t pick = oracle::oak_pick(seed, step);
+    const uint8_t c1 = ch1[pick % m], c2 = ch2[(pick >> 32) % n];
+    k.push_back(m);
+    k.push_back(n);
+    choice.push_back(c1);
+    choice.push_back(c2);
+    iters.push_back((uint32_t)(oracle::splitmix64(s + step) >> 40));
+    ev.push_back(unit());
+    nv.push_back(unit());
+    for (int side = 0; side < 2; side++) {
+      double pe[9] = {}, pn[9] = {}, se = 0, sn = 0;
+      const int cnt = side ? n : m;
+      for (int i = 0; i < cnt; i++) se += pe[i] = unit() + 1e-3, sn += pn[i] = unit() + 1e-3;
+      for (int i = 0; i < 9; i++) emp.push_back(pe[i] / se), nash.push_back(pn[i] / sn);
+    }
+    result = e.update(c1, c2);
+    memcpy(dur, o.durations, 8);
+    step++;
+  }
+  if ((result & 15) == 0) return 0;
+  return frames_oracle::write_game(first, result, step, k.data(), choice.data(), iters.data(), ev.data(), nv.data(), emp.data(),
+                                   nash.data(), out);
+}
+
+// Every game of a .battle.data stream -> rows (game g's rows start at the running sum of n_updates). `threads` host
+// threads over games. Returns the number of rows, or -(g + 1) for the first game whose replay fails.
+int64_t oracle_training_rows(const uint8_t* stream, uint64_t n_bytes, int threads, float* pokemon, float* active, float* hp,
+                             int64_t* choice_indices, uint8_t* k, uint8_t* choice, uint32_t* iterations, float* emp, float* nash, float* ev,
+                             float* nv, float* score) {
+  std::vector<uint64_t> off, first;
+  uint64_t at = 0, rows = 0;
+  while (at + 391 <= n_bytes) {
+    uint32_t nb;
+    uint16_t nu;
+    memcpy(&nb, stream + at, 4);
+    memcpy(&nu, stream + at + 4, 2);
+    if (nb < 391 || at + nb > n_bytes) break;
+    off.push_back(at);
+    first.push_back(rows);
+    rows += nu;
+    at += nb;
+  }
+  if (at != n_bytes) return INT64_MIN;
+  rows_oracle::Rows r{pokemon, active, hp, choice_indices, k, choice, iterations, emp, nash, ev, nv, score};
+  if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+  if (threads <= 0) threads = 1;
+  std::atomic<int64_t> bad{0};
+  std::atomic<size_t> next{0};
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++)
+    pool.emplace_back([&]() {
+      for (;;) {
+        const size_t g = next.fetch_add(1);
+        if (g >= off.size()) return;
+        if (rows_oracle::build_rows(stream + off[g], r, first[g]) < 0) {
+          int64_t expect = 0;
+          bad.compare_exchange_strong(expect, -(int64_t)(g + 1));
+        }
+      }
+    });
+  for (auto& t : pool) t.join();
+  return bad.load() ? bad.load() : (int64_t)rows;
+}
+}

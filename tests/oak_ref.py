@@ -298,3 +298,57 @@ def parse_battle_data(stream):
         games.append(g)
         at = end
     return games
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# training rows (oracle/train_rows_oracle.hpp; pinned to the reference's EncodedFrames::from_bytes by the golden file)
+ROW_FIELDS = ["pokemon", "active", "hp", "choice_indices", "k", "choice", "iterations", "empirical_policies", "nash_policies",
+              "empirical_value", "nash_value", "score"]
+ROW_SHAPES = dict(pokemon=((2, 6, 198), np.float32), active=((2, 1, 229), np.float32), hp=((2, 6, 1), np.float32),
+                  choice_indices=((2, 9), np.int64), k=((2, 1), np.uint8), choice=((2, 1), np.uint8), iterations=((1,), np.uint32),
+                  empirical_policies=((2, 9), np.float32), nash_policies=((2, 9), np.float32), empirical_value=((1,), np.float32),
+                  nash_value=((1,), np.float32), score=((1,), np.float32))
+
+
+def play_frame_games(orc, first, games, seed, max_updates=2000):
+    """`games` sample battles played to the end on the oracle with playout picks, stored as one .battle.data stream."""
+    f = orc.lib.oracle_play_frame_game
+    f.restype = ctypes.c_uint32
+    f.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
+    out = np.zeros(391 + 83 * max_updates + 16, np.uint8)
+    parts = []
+    for g in range(games):
+        nb = f(first + g, splitmix64(seed ^ (first + g)), max_updates, out.ctypes.data)
+        if nb:
+            parts.append(out[:nb].copy())
+    return np.concatenate(parts)
+
+
+def split_games(stream):
+    b, at, out = bytes(stream), 0, []
+    while at < len(b):
+        nb = int.from_bytes(b[at:at + 4], "little")
+        out.append(np.frombuffer(b[at:at + nb], np.uint8))
+        at += nb
+    return out
+
+
+def count_rows(stream):
+    return sum(int.from_bytes(bytes(g[4:6]), "little") for g in split_games(stream))
+
+
+def empty_rows(n):
+    return {name: np.zeros((n,) + shape, dtype) for name, (shape, dtype) in ROW_SHAPES.items()}
+
+
+def oracle_training_rows(orc, stream, threads=0):
+    """-> dict of the twelve arrays for every stored update of every game in the stream (oracle_training_rows)."""
+    f = orc.lib.oracle_training_rows
+    f.restype = ctypes.c_int64
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int] + [ctypes.c_void_p] * 12
+    stream = np.ascontiguousarray(stream, np.uint8)
+    n = count_rows(stream)
+    R = empty_rows(n)
+    got = f(stream.ctypes.data, stream.size, threads, *[R[x].ctypes.data for x in ROW_FIELDS])
+    assert got == n, f"oracle_training_rows -> {got}, expected {n}"
+    return R
