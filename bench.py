@@ -337,7 +337,65 @@ def main():
     sp_s = time.perf_counter() - t0
     launches += sp.eng.launch_count - l0
     sp_bytes = sum(len(x) for x in gathered) if gathered is not None else 0
+
+    # ---- secondary: training rows (pyoak EncodedBattleFrames.from_bytes / sample): the games this rank's
+    # self-play finishes are replayed on the device and encoded into the learner's dense tensors. Input: the self-play
+    # stream itself (more untimed steps until ~2^21 stored updates are there), so the whole chain is product kernels.
+    from oak_b200.engine import rows_index_host
+    from oak_b200.training_rows import EncodedBattleFrames
+    TR_ROWS = 1 << 21
+    tr_parts, tr_have = [local_stream], 0
+    for s_ in range(400):
+        if tr_have >= TR_ROWS:
+            break
+        sp.step()
+        if (s_ + 1) % 8 == 0:
+            st_, g_ = sp.collect()
+            tr_parts.append(np.array(st_, copy=True))
+            tr_have = rows_index_host(np.concatenate(tr_parts))[2] if g_ else tr_have
     sp.close()
+    tr_stream = np.concatenate(tr_parts)
+    tr_off, tr_base, tr_rows = rows_index_host(tr_stream)
+    if tr_rows > TR_ROWS:  # whole games only
+        cut = int(np.searchsorted(tr_base, TR_ROWS, side="right")) - 1
+        tr_stream, tr_off, tr_rows = tr_stream[:int(tr_off[cut])], tr_off[:cut], int(tr_base[cut])
+        tr_base = tr_base[:cut]
+    tr = EncodedBattleFrames(max(tr_rows, 1), device=local, engine=eng)
+    tr_out = tr._out()
+    d_ts = torch.from_numpy(tr_stream).to(dev)
+    d_to = torch.from_numpy(tr_off.view(np.int64)).to(dev)
+    d_tb = torch.from_numpy(tr_base.view(np.int32)).to(dev)
+    TR_IT = 5
+    eng.rows_build_device(d_ts, tr_stream.size, d_to, d_tb, len(tr_off), tr_rows, tr_out)
+    torch.cuda.synchronize(dev)
+    barrier()
+    tr_ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    tr_ev[0].record()
+    for _ in range(TR_IT):
+        eng.rows_build_device(d_ts, tr_stream.size, d_to, d_tb, len(tr_off), tr_rows, tr_out)
+    tr_ev[1].record()
+    torch.cuda.synchronize(dev)
+    tr_ms = tr_ev[0].elapsed_time(tr_ev[1]) / TR_IT
+    assert eng.rows_status() == -1, "a self-play game did not replay to its stored result"
+    tr_pin = torch.from_numpy(tr_stream).pin_memory()
+    eng.rows_build_host(tr_pin, tr_out, tr_rows)
+    t0 = time.perf_counter()
+    for _ in range(TR_IT):
+        eng.rows_build_host(tr_pin, tr_out, tr_rows)  # index walk + upload + replay + encode + status read-back
+    tr_e2e_s = (time.perf_counter() - t0) / TR_IT
+    launches += 2 * (2 * TR_IT + 2)
+    tr_cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oak_ref import Oracle as _O3, oracle_training_rows as _otr
+        _cut = int(np.searchsorted(tr_base, 1 << 17, side="right")) - 1  # ~131k rows: about a second of CPU work
+        _sub = tr_stream[:int(tr_off[_cut])] if _cut > 0 else tr_stream
+        _o3 = _O3()
+        t0 = time.perf_counter()
+        _r = _otr(_o3, _sub, threads=os.cpu_count() or 1)
+        tr_cpu = _r["k"].shape[0] / (time.perf_counter() - t0)
+        del _r
+    TR_ROW_BYTES = 4 * (2376 + 458 + 12 + 18 + 18 + 3) + 8 * 18 + 2 + 2 + 4  # every output array, per row
+    del tr, tr_out
 
     # ---- secondary: tree search with GPU leaves (BASELINE configs[3]): 4096 root positions sharded over the ranks,
     # host trees + UCB bandits, 64 descents per root in flight, clamped rolls 3/1 as the reference's default_search
@@ -391,13 +449,13 @@ def main():
         eval_cpu = EV / (time.perf_counter() - t0)
 
     # ---- reduce over ranks: max time, sum of work
-    t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms, sr_s * 1e3], dtype=torch.float64, device=dev)
-    w = torch.tensor([steps_per_pass * args.steps, n * args.steps, e2e_steps * e2e_iters, launches, n, sr_done], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms, sr_s * 1e3, tr_ms, tr_e2e_s * 1e3], dtype=torch.float64, device=dev)
+    w = torch.tensor([steps_per_pass * args.steps, n * args.steps, e2e_steps * e2e_iters, launches, n, sr_done, tr_rows], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(w, op=dist.ReduceOp.SUM)
-    ms_total_max, e2e_ms_max, lock_ms_max, sr_ms_max = t.tolist()
-    tot_steps, tot_rollouts, tot_e2e_steps, tot_launches, tot_battles, tot_sr = w.tolist()
+    ms_total_max, e2e_ms_max, lock_ms_max, sr_ms_max, tr_ms_max, tr_e2e_ms_max = t.tolist()
+    tot_steps, tot_rollouts, tot_e2e_steps, tot_launches, tot_battles, tot_sr, tot_tr_rows = w.tolist()
 
     if rank == 0:
         pk, pk_src = peaks()
@@ -466,6 +524,17 @@ def main():
                          "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
                                  "step: choices + tensor-core eval + policy sample + frame record + update + finish kernels; "
                                  "drain every 8 steps; frame streams gathered to rank 0"},
+            "training_rows": {"rows_per_s": tot_tr_rows / (tr_ms_max * 1e-3), "rows_per_gpu": int(tr_rows), "games_per_gpu": int(len(tr_off)),
+                              "ms_per_build": tr_ms_max, "e2e_rows_per_s": tot_tr_rows / (tr_e2e_ms_max * 1e-3),
+                              "e2e_note": "pinned host .battle.data stream in (header walk, H2D), rows left in device memory for the "
+                                          "learner, status word back; wall clock around oakb200_rows_build_host",
+                              "input": "the games this rank's GPU self-play finished (its own .battle.data stream)",
+                              "roofline": {"bound": "hbm", "kernel": "replay_kernel + rows_encode_kernel", "achieved": TR_ROW_BYTES * tr_rows / (tr_ms * 1e-3) / 1e9,
+                                           "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": TR_ROW_BYTES * tr_rows / (tr_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                                           "algorithmic_bytes_per_row": TR_ROW_BYTES, "peak_source": pk_src,
+                                           "note": "write-only stream: torch's fill of 40 GiB reaches 3.9 TB/s on this pool "
+                                                   "(tools/memset_bw.py), the copy peak counts read + write"},
+                              "cpu_rows_per_s": tr_cpu, "cpu_kind": "port (oracle_training_rows, all host cores)"},
             "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(tot_launches),
         }
         emit(line)

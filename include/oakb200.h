@@ -205,6 +205,52 @@ int oakb200_search_output(oakb200_search* search, uint8_t* k, uint8_t* choices, 
                           uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes);
 int oakb200_search_stats(oakb200_search* search, uint64_t* waves, uint64_t* levels);
 
+/* ---- training rows: stored games -> the dense tensors the learner trains on ------------------------------------------
+ * Replaces pyoak's EncodedBattleFrames.from_bytes / sample (reference cpp/include/py/battle/encoded-frames.h:24-133,
+ * cpp/include/py/battle/target.h:17-70, cpp/src/pyoak.cc:111-260,655-673): replay every stored game of a .battle.data
+ * stream (cpp/include/train/battle/compressed-frame.h:173-224) from its first battle with its stored choices and,
+ * before each update, write one row. Row-major arrays of n_rows rows, in DEVICE memory (they feed the learner there):
+ *   pokemon[n][2][6][198] f32, active[n][2][1][229] f32, hp[n][2][6][1] f32   dense encodings (encode/battle/battle.h),
+ *                                                                              zero for fainted / empty slots
+ *   choice_indices[n][2][9] i64   policy index of each legal choice (encode/battle/policy.h:29-58), 315 past the k-th
+ *   k[n][2] u8, choice[n][2] u8, iterations[n] u32, empirical_policies / nash_policies[n][2][9] f32 (u16 / 65535, zero
+ *   past k), empirical_value[n], nash_value[n] f32, score[n] f32 (1 win, 0 lose, 0.5 tie of the game's stored result)
+ * Any pointer may be NULL (that array is skipped). Rows of game g start at the running sum of the games' n_updates. */
+typedef struct oakb200_training_rows {
+  float* pokemon;
+  float* active;
+  float* hp;
+  int64_t* choice_indices;
+  uint8_t* k;
+  uint8_t* choice;
+  uint32_t* iterations;
+  float* empirical_policies;
+  float* nash_policies;
+  float* empirical_value;
+  float* nash_value;
+  float* score;
+} oakb200_training_rows;
+
+/* Host walk over the game headers of a stream (pyoak read_battle_data, pyoak.cc:43-71): byte offset and first row of
+ * every game. game_off / row_base may be NULL to count only; otherwise they hold `capacity` entries. OAKB200_EINVAL for a
+ * stream that does not split into whole games, OAKB200_ECAPACITY if there are more games than capacity. No GPU needed. */
+int oakb200_rows_index_host(const uint8_t* stream, uint64_t n_bytes, uint64_t* game_off, uint32_t* row_base, uint64_t capacity,
+                            uint64_t* n_games, uint64_t* n_rows);
+/* Stream and index already in device memory (n_bytes < 4 GiB). only_update NULL: every stored update becomes a row
+ * (from_bytes). only_update[g] >= 0: game g contributes the single row g, built before its update only_update[g]
+ * (`sample`: the caller draws the game and the update); row_base is then ignored. Asynchronous on the context's stream. */
+int oakb200_rows_build_device(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_bytes, const uint64_t* game_off,
+                              const uint32_t* row_base, const int32_t* only_update, uint64_t n_games, uint64_t n_rows,
+                              const oakb200_training_rows* out);
+/* Waits for the build and reports the lowest index of a game whose replay did not reproduce its stored final result or
+ * byte count (-1 if none; the reference asserts this, encoded-frames.h:132). Its rows are written but not trustworthy. */
+int oakb200_rows_status(oakb200_ctx* ctx, int64_t* first_bad_game);
+/* The whole path from a HOST stream: index, upload, build, status. out arrays (device) hold capacity_rows rows.
+ * only_update is a host array or NULL. */
+int oakb200_rows_build_host(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_bytes, const int32_t* only_update,
+                            const oakb200_training_rows* out, uint64_t capacity_rows, uint64_t* n_games, uint64_t* n_rows,
+                            int64_t* first_bad_game);
+
 #ifdef __cplusplus
 }
 #endif

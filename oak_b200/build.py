@@ -13,7 +13,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 def sources():
     return [os.path.join(CSRC, "oakb200.cu"), os.path.join(CSRC, "value_net.cu"), os.path.join(CSRC, "frame_log.cu"),
-            os.path.join(CSRC, "pkmn_compat.cu"), os.path.join(CSRC, "search.cu")]
+            os.path.join(CSRC, "pkmn_compat.cu"), os.path.join(CSRC, "search.cu"), os.path.join(CSRC, "train_rows.cu")]
 
 
 def _deps():

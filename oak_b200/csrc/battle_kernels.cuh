@@ -432,6 +432,97 @@ search_step_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ duration
 }
 
 // ---------------------------------------------------------------------------------------------
+// Training rows, step 1 of 2 (reference cpp/include/py/battle/encoded-frames.h:112-133, uncompress_from_bytes): replay
+// every stored game of a .battle.data stream from its first battle with its stored choices. Before each update the
+// state the learner's row is built from is staged as one ROW_STATE_BYTES record:
+//   [0,384) battle   [384,392) durations   392 result before the update   393 the game's stored final result
+//   394, 395 legal-choice counts   [396,400) byte offset of the stored update in the stream
+//   [400,409) P1's legal choices   [409,418) P2's   (pkmn_gen1_battle_choices order)
+// rows_encode_kernel (train_rows.cu) turns these into the dense tensors. Persistent CTAs with lane refill from a ticket
+// counter, as rollout_kernel: stored games differ in length by an order of magnitude.
+// only_update: null = every update of game g goes to rows row_base[g] + u (from_bytes); else game g stages only update
+// only_update[g] into row row_base[g] and stops there (pyoak `sample`, cpp/src/pyoak.cc:111-260).
+static const int ROW_STATE_BYTES = 432;
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 3)
+replay_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restrict__ game_off, const uint32_t* __restrict__ row_base,
+              const int32_t* __restrict__ only_update, uint32_t n_games, uint32_t* __restrict__ ticket, uint8_t* __restrict__ rows,
+              uint32_t* __restrict__ first_bad) {
+  extern __shared__ uint32_t tile[];
+  uint32_t* col = tile + threadIdx.x;
+  typedef Engine<BLOCK, false, true> E;
+  E e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+
+  uint32_t g = 0, u = 0, n_updates = 0, result = 0, stored = 0, base = 0;
+  int32_t only = -1;
+  uint64_t p = 0, end = 0;
+  bool have = false, exhausted = false;
+
+  for (;;) {
+    if (!have && !exhausted) {
+      g = atomicAdd(ticket, 1u);
+      if (g < n_games) {
+        const uint8_t* game = stream + game_off[g];  // games are packed back to back: no alignment to rely on
+        const uint32_t n_bytes = game[0] | (game[1] << 8) | (game[2] << 16) | ((uint32_t)game[3] << 24);
+        n_updates = game[4] | (game[5] << 8);
+#pragma unroll 4
+        for (int w = 0; w < BATTLE_WORDS; w++) {
+          const uint8_t* b = game + 6 + 4 * w;
+          col[w * BLOCK] = b[0] | (b[1] << 8) | (b[2] << 16) | ((uint32_t)b[3] << 24);
+        }
+        e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+        stored = game[390];
+        result = RESULT_DEFAULT;  // PKMN::result(): both players to move (cpp/include/libpkmn/pkmn.h:228-233)
+        p = game_off[g] + 391;
+        end = game_off[g] + n_bytes;
+        base = row_base[g];
+        only = only_update ? max(only_update[g], 0) : -1;
+        if (only >= 0 && n_updates != 0) {  // clamp to the game's last stored update
+          if ((uint32_t)only >= n_updates) only = (int32_t)n_updates - 1;
+          n_updates = (uint32_t)only + 1;
+        }
+        u = 0;
+        have = n_updates != 0;
+      } else {
+        exhausted = true;
+      }
+    }
+    if (__all_sync(0xFFFFFFFFu, !have)) break;
+    if (have) {
+      if (only < 0 || u == (uint32_t)only) {
+        e.end();
+        uint8_t* row = rows + (size_t)(only < 0 ? base + u : base) * ROW_STATE_BYTES;
+        store_column<BLOCK>(col, row);
+        int m, n;
+        const uint64_t l1 = e.choices(0, (result >> 4) & 3, &m);
+        const uint64_t l2 = e.choices(1, (result >> 6) & 3, &n);
+        uint32_t cw[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 9; i++) {
+          if (i < m) cw[i >> 2] |= E::choice_at(l1, i) << (8 * (i & 3));
+          if (i < n) cw[(9 + i) >> 2] |= E::choice_at(l2, i) << (8 * ((9 + i) & 3));
+        }
+        uint4* tail = reinterpret_cast<uint4*>(row + 384);
+        tail[0] = make_uint4(e.dur[0], e.dur[1], result | (stored << 8) | ((uint32_t)m << 16) | ((uint32_t)n << 24), (uint32_t)p);
+        tail[1] = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+        tail[2] = make_uint4(cw[4], 0, 0, 0);
+      }
+      const uint32_t hdr = stream[p], c1 = stream[p + 1], c2 = stream[p + 2];
+      e.act[0] = e.act[1] = 0;  // PKMN::update: options_set(null) before every update (pkmn.h:134-138)
+      result = e.update(c1, c2);
+      p += 11 + 4 * ((hdr & 15u) + (hdr >> 4) + 2);
+      u++;
+      if (u == n_updates) {
+        // a stored game must end on its stored result and fill its byte count (encoded-frames.h:132 asserts the first)
+        if (only < 0 && (result != stored || p != end)) atomicMin(first_bad, g);
+        have = false;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // MCTS::randomize_hidden_variables (reference cpp/include/search/durations.h:25-97). Touches a few
 // bytes per battle, so it works on the AoS records in place. Every draw uses the same battle.rng.
 __device__ __constant__ uint64_t HIDDEN_BINDING_CUM[4] = {

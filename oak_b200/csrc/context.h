@@ -10,6 +10,7 @@
 
 struct oakb200_net;     // device copy of a loaded network (value_net.cu)
 struct oakb200_frames;  // training-frame recorder (frame_log.cu)
+struct oakb200_rows;    // training-row builder scratch (train_rows.cu)
 
 struct oakb200_ctx {
   int device = -1;
@@ -30,6 +31,7 @@ struct oakb200_ctx {
   uint64_t launches = 0;
   oakb200_net* net = nullptr;
   oakb200_frames* frames = nullptr;
+  oakb200_rows* rows = nullptr;
   int eval_mode = 0;  // 0 auto (tensor cores when the shape fits), 1 fp32 CUDA-core kernel, 2 tensor cores or fail
   float* eval_values = nullptr;
   float* eval_logits = nullptr;
@@ -48,6 +50,11 @@ cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_ba
                                         uint8_t* battles, uint8_t* durations, uint8_t* results, uint32_t n);
 cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8_t* durations, uint8_t* results, const uint8_t* idx1,
                                        const uint8_t* idx2, const uint8_t* rolls, uint8_t* actions, uint8_t* counts, uint32_t n);
+
+// train_rows.cu -> oakb200.cu
+cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                  const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows);
+static const int OAKB200_ROW_STATE_BYTES = 432;  // = ROW_STATE_BYTES of battle_kernels.cuh
 
 namespace {
 

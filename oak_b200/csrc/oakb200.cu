@@ -23,6 +23,7 @@ const size_t TILE_BYTES = (size_t)BATTLE_WORDS * BLOCK * 4;  // 48 KB shared-mem
 
 void oakb200_net_release(oakb200_ctx* ctx);     // value_net.cu
 void oakb200_frames_release(oakb200_ctx* ctx);  // frame_log.cu
+void oakb200_rows_release(oakb200_ctx* ctx);    // train_rows.cu
 
 namespace {
 
@@ -106,6 +107,26 @@ cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8
   return cudaGetLastError();
 }
 
+// training rows (train_rows.cu): stage the pre-update state of every stored update. `words` = two zeroed uint32:
+// [0] the game ticket, [1] receives the lowest index of a game whose replay does not reproduce its stored result
+cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                  const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows) {
+  static_assert(ROW_STATE_BYTES == OAKB200_ROW_STATE_BYTES, "staged row layout");
+  auto k = replay_kernel<BLOCK>;
+  cudaError_t e = allow_smem(k);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, TILE_BYTES);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  unsigned grid = (unsigned)(ctx->sm_count * per_sm);
+  const unsigned need = grid_for(n_games);
+  if (grid > need) grid = need;
+  k<<<grid, BLOCK, TILE_BYTES, ctx->stream>>>(stream, game_off, row_base, only_update, n_games, words, rows, words + 1);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
 extern "C" {
 
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
@@ -156,6 +177,7 @@ void oakb200_destroy(oakb200_ctx* ctx) {
                   ctx->eval_values, ctx->eval_logits, ctx->eval_counts};
   oakb200_net_release(ctx);
   oakb200_frames_release(ctx);
+  oakb200_rows_release(ctx);
   for (void* b : bufs)
     if (b) cudaFree(b);
   if (ctx->pipe_ready) {

@@ -36,7 +36,7 @@ def load_library():
         raise OakB200Error(f"{path} is missing: run `python -m oak_b200.build` (needs nvcc). "
                            "oak_b200 has no CPU fallback.")
     lib = ctypes.CDLL(path)
-    vp, sz, u32, i32 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int
+    vp, sz, u32, i32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int, ctypes.c_uint64
     sig = {
         "oakb200_create": (i32, [i32, sz, ctypes.POINTER(vp)]),
         "oakb200_destroy": (None, [vp]),
@@ -69,6 +69,11 @@ def load_library():
         "oakb200_frames_finish_device": (i32, [vp, sz, vp]),
         "oakb200_frames_pending": (i32, [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]),
         "oakb200_frames_drain": (i32, [vp, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u32)]),
+        "oakb200_rows_index_host": (i32, [vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
+        "oakb200_rows_build_device": (i32, [vp, vp, u64, vp, vp, vp, u64, u64, vp]),
+        "oakb200_rows_status": (i32, [vp, ctypes.POINTER(ctypes.c_int64)]),
+        "oakb200_rows_build_host": (i32, [vp, vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64),
+                                         ctypes.POINTER(ctypes.c_int64)]),
         "oakb200_eval": (i32, [vp, vp, vp, vp]),
         "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
     }
@@ -308,3 +313,51 @@ class BattleEngine:
         out = np.empty(int(capacity), np.uint8)
         self._check(self.lib.oakb200_frames_drain(self._h, _ptr(out), out.size, ctypes.byref(need), ctypes.byref(games)))
         return out[:need.value], games.value
+
+    # ---------------------------------------------------------------- training rows (include/oakb200.h, train_rows.cu)
+    ROW_FIELDS = ("pokemon", "active", "hp", "choice_indices", "k", "choice", "iterations", "empirical_policies", "nash_policies",
+                  "empirical_value", "nash_value", "score")
+
+    def _rows_struct(self, out):
+        """dict name -> device tensor (or None) -> the oakb200_training_rows struct as an array of 12 pointers"""
+        arr = (ctypes.c_void_p * 12)()
+        for i, name in enumerate(self.ROW_FIELDS):
+            t = out.get(name)
+            arr[i] = _ptr(t) if t is not None else None
+        return arr
+
+    def rows_build_host(self, stream, out, capacity_rows, only_update=None):
+        """Host .battle.data bytes -> rows in the device tensors of `out`. -> (games, rows, first_bad_game or -1)."""
+        stream = np.ascontiguousarray(stream, np.uint8) if isinstance(stream, np.ndarray) else stream
+        nbytes = stream.size if isinstance(stream, np.ndarray) else stream.numel()
+        only = None if only_update is None else _np(only_update, np.int32)
+        g, r, bad = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_int64()
+        st = self._rows_struct(out)
+        self._check(self.lib.oakb200_rows_build_host(self._h, _ptr(stream), nbytes, _ptr(only), ctypes.addressof(st), int(capacity_rows),
+                                                     ctypes.byref(g), ctypes.byref(r), ctypes.byref(bad)))
+        return g.value, r.value, bad.value
+
+    def rows_build_device(self, stream, n_bytes, game_off, row_base, n_games, n_rows, out, only_update=None):
+        st = self._rows_struct(out)
+        self._check(self.lib.oakb200_rows_build_device(self._h, _ptr(stream), int(n_bytes), _ptr(game_off), _ptr(row_base),
+                                                       _ptr(only_update), int(n_games), int(n_rows), ctypes.addressof(st)))
+
+    def rows_status(self):
+        bad = ctypes.c_int64()
+        self._check(self.lib.oakb200_rows_status(self._h, ctypes.byref(bad)))
+        return bad.value
+
+
+def rows_index_host(stream):
+    """Header walk of a .battle.data stream -> (game_off u64[G], row_base u32[G], rows). No GPU needed."""
+    lib = load_library()
+    stream = np.ascontiguousarray(stream, np.uint8)
+    g, r = ctypes.c_uint64(), ctypes.c_uint64()
+    rc = lib.oakb200_rows_index_host(_ptr(stream), stream.size, None, None, 0, ctypes.byref(g), ctypes.byref(r))
+    if rc != 0:
+        raise OakB200Error(f"oakb200_rows_index_host: error {rc} (the stream does not split into whole games)")
+    off, base = np.zeros(g.value, np.uint64), np.zeros(g.value, np.uint32)
+    rc = lib.oakb200_rows_index_host(_ptr(stream), stream.size, _ptr(off), _ptr(base), g.value, None, None)
+    if rc != 0:
+        raise OakB200Error(f"oakb200_rows_index_host: error {rc}")
+    return off, base, r.value

@@ -53,3 +53,21 @@ def test_no_device_means_an_error_not_a_cpu_fallback():
     out = (ctypes.c_uint8 * 9)()
     lib.pkmn_gen1_battle_choices.restype = ctypes.c_uint8
     assert lib.pkmn_gen1_battle_choices(battle, 0, 1, out, ctypes.c_size_t(9)) == 0
+
+
+def test_rows_index_host_needs_no_gpu():
+    """oakb200_rows_index_host is plain host code: header walk of a .battle.data stream, and its error paths."""
+    import numpy as np
+    from oak_ref import ROOT as R
+    from oak_b200.engine import OakB200Error, rows_index_host
+    G = np.load(os.path.join(R, "tests", "golden", "training_rows_golden.npz"))
+    off, base, rows = rows_index_host(G["stream"])
+    assert rows == 1107 and len(off) == 8 and off[0] == 0 and base[0] == 0
+    assert int(off[1]) == int.from_bytes(G["stream"][0:4].tobytes(), "little")
+    for bad in (G["stream"][:-1], G["stream"][:200], np.concatenate([G["stream"], np.zeros(3, np.uint8)])):
+        try:
+            rows_index_host(bad)
+        except OakB200Error:
+            continue
+        raise AssertionError("a stream that does not split into whole games must be rejected")
+    assert rows_index_host(np.zeros(0, np.uint8))[2] == 0
