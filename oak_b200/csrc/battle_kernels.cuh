@@ -7,6 +7,7 @@
 #include <stdint.h>
 
 #include "gen1_engine.cuh"
+#include "train_rows_encode.cuh"
 
 namespace oakb200 {
 
@@ -518,6 +519,111 @@ replay_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restrict__ g
         if (only < 0 && (result != stored || p != end)) atomicMin(first_bad, g);
         have = false;
       }
+    }
+  }
+}
+
+// replay_encode_kernel: the two steps of the training-row build in ONE launch. replay_kernel is bound by instruction
+// issue under divergence, rows_encode_kernel by DRAM writes; back to back they add up (profiles/r1k_training_rows.txt).
+// Here every warp alternates: each lane advances its own game by one stored update and stages the state it had before
+// (as replay_kernel), then the whole warp encodes the <= 32 rows just staged (rows::encode_row, the body of
+// rows_encode_kernel). The staged state goes through global memory — written by its lane, read back by the warp out
+// of L2 with ld.global.cg — because a game's state is one bank-private COLUMN of the tile: no other lane can read it
+// from shared memory without a 32-way conflict. Warps of an SM are in different phases at any time, so the copy-out
+// of some overlaps the simulation of others.
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 3)
+replay_encode_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restrict__ game_off, const uint32_t* __restrict__ row_base,
+                     const int32_t* __restrict__ only_update, uint32_t n_games, uint32_t* __restrict__ ticket, uint8_t* rows,
+                     uint32_t* __restrict__ first_bad, oakb200_training_rows out) {
+  extern __shared__ uint32_t tile[];
+  uint32_t* col = tile + threadIdx.x;
+  uint8_t* st = reinterpret_cast<uint8_t*>(tile + BATTLE_WORDS * BLOCK) + (threadIdx.x >> 5) * ROW_STATE_BYTES;
+  const int lane = threadIdx.x & 31;
+  typedef Engine<BLOCK, false, true> E;
+  E e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+
+  uint32_t g = 0, u = 0, n_updates = 0, result = 0, stored = 0, base = 0;
+  int32_t only = -1;
+  uint64_t p = 0, end = 0;
+  bool have = false, exhausted = false;
+
+  for (;;) {
+    if (!have && !exhausted) {
+      g = atomicAdd(ticket, 1u);
+      if (g < n_games) {
+        const uint8_t* game = stream + game_off[g];
+        const uint32_t n_bytes = game[0] | (game[1] << 8) | (game[2] << 16) | ((uint32_t)game[3] << 24);
+        n_updates = game[4] | (game[5] << 8);
+#pragma unroll 4
+        for (int w = 0; w < BATTLE_WORDS; w++) {
+          const uint8_t* b = game + 6 + 4 * w;
+          col[w * BLOCK] = b[0] | (b[1] << 8) | (b[2] << 16) | ((uint32_t)b[3] << 24);
+        }
+        e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+        stored = game[390];
+        result = RESULT_DEFAULT;
+        p = game_off[g] + 391;
+        end = game_off[g] + n_bytes;
+        base = row_base[g];
+        only = only_update ? max(only_update[g], 0) : -1;
+        if (only >= 0 && n_updates != 0) {
+          if ((uint32_t)only >= n_updates) only = (int32_t)n_updates - 1;
+          n_updates = (uint32_t)only + 1;
+        }
+        u = 0;
+        have = n_updates != 0;
+      } else {
+        exhausted = true;
+      }
+    }
+    if (__all_sync(0xFFFFFFFFu, !have)) break;
+    bool emit = false;
+    uint32_t my_row = 0;
+    if (have) {
+      if (only < 0 || u == (uint32_t)only) {
+        e.end();
+        my_row = only < 0 ? base + u : base;
+        emit = true;
+        uint8_t* row = rows + (size_t)my_row * ROW_STATE_BYTES;
+        store_column<BLOCK>(col, row);
+        int m, n;
+        const uint64_t l1 = e.choices(0, (result >> 4) & 3, &m);
+        const uint64_t l2 = e.choices(1, (result >> 6) & 3, &n);
+        uint32_t cw[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 9; i++) {
+          if (i < m) cw[i >> 2] |= E::choice_at(l1, i) << (8 * (i & 3));
+          if (i < n) cw[(9 + i) >> 2] |= E::choice_at(l2, i) << (8 * ((9 + i) & 3));
+        }
+        uint4* tail = reinterpret_cast<uint4*>(row + 384);
+        tail[0] = make_uint4(e.dur[0], e.dur[1], result | (stored << 8) | ((uint32_t)m << 16) | ((uint32_t)n << 24), (uint32_t)p);
+        tail[1] = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+        tail[2] = make_uint4(cw[4], 0, 0, 0);
+      }
+      const uint32_t hdr = stream[p], c1 = stream[p + 1], c2 = stream[p + 2];
+      e.act[0] = e.act[1] = 0;
+      result = e.update(c1, c2);
+      p += 11 + 4 * ((hdr & 15u) + (hdr >> 4) + 2);
+      u++;
+      if (u == n_updates) {
+        if (only < 0 && (result != stored || p != end)) atomicMin(first_bad, g);
+        have = false;
+      }
+    }
+    // ---- the warp encodes what its lanes staged (the staged bytes are ordered before these reads by the barrier)
+    __threadfence_block();
+    __syncwarp();
+    uint32_t todo = __ballot_sync(0xFFFFFFFFu, emit);
+    while (todo) {
+      const int j = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint32_t r = __shfl_sync(0xFFFFFFFFu, my_row, j);
+      if (lane < ROW_STATE_BYTES / 16)
+        reinterpret_cast<uint4*>(st)[lane] = __ldcg(reinterpret_cast<const uint4*>(rows + (size_t)r * ROW_STATE_BYTES) + lane);
+      __syncwarp();
+      rows::encode_row(st, stream, out, r, lane);
+      __syncwarp();
     }
   }
 }

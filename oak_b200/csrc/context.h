@@ -54,6 +54,9 @@ cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8
 // train_rows.cu -> oakb200.cu
 cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
                                   const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows);
+cudaError_t oakb200_launch_replay_encode(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                         const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows,
+                                         const oakb200_training_rows* out);
 static const int OAKB200_ROW_STATE_BYTES = 432;  // = ROW_STATE_BYTES of battle_kernels.cuh
 
 namespace {

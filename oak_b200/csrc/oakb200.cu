@@ -127,6 +127,26 @@ cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const
   return cudaGetLastError();
 }
 
+// the same build in one launch (replay_encode_kernel): each warp stages and then encodes its own rows
+cudaError_t oakb200_launch_replay_encode(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                         const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows,
+                                         const oakb200_training_rows* out) {
+  auto k = replay_encode_kernel<BLOCK>;
+  const size_t smem = TILE_BYTES + (BLOCK / 32) * ROW_STATE_BYTES;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, smem);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  unsigned grid = (unsigned)(ctx->sm_count * per_sm);
+  const unsigned need = grid_for(n_games);
+  if (grid > need) grid = need;
+  k<<<grid, BLOCK, smem, ctx->stream>>>(stream, game_off, row_base, only_update, n_games, words, rows, words + 1, *out);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
 extern "C" {
 
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
