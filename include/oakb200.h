@@ -204,6 +204,14 @@ int oakb200_search_run(oakb200_search* search, uint32_t iterations, float ucb_c,
 int oakb200_search_output(oakb200_search* search, uint8_t* k, uint8_t* choices, uint32_t* visit_matrix, double* value_matrix,
                           uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes);
 int oakb200_search_stats(oakb200_search* search, uint64_t* waves, uint64_t* levels);
+/* Zero-sum matrix game, the job of LRSNash::solve_fast (mcts.h:643-649; pyoak solve_matrix, cpp/src/pyoak.cc:394-425):
+ * the row player receives payoff[i * cols + j] / denom, the column player 1 - that; rows, cols <= 9. -> both players'
+ * equilibrium strategies and the game value. An LP solved by simplex: the value is the game's, the strategies one of its
+ * equilibria (LRSNash may return another vertex of the same solution set). Pure host code, no GPU needed. */
+int oakb200_solve_matrix(int rows, int cols, const int* payoff, int denom, float* p1, float* p2, float* value);
+/* process_output's Nash half for every root (mcts.h:628-656: average values discretised to 1/256, then solved):
+ * nash[n][2][9] f32 (zero past k), nash_value[n] f32. Either may be NULL. */
+int oakb200_search_nash(oakb200_search* search, float* nash, float* nash_value);
 
 /* ---- training rows: stored games -> the dense tensors the learner trains on ------------------------------------------
  * Replaces pyoak's EncodedBattleFrames.from_bytes / sample (reference cpp/include/py/battle/encoded-frames.h:24-133,

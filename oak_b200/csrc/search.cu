@@ -452,6 +452,90 @@ int oakb200_search_output(oakb200_search* s, uint8_t* k, uint8_t* choices, uint3
   return OAKB200_OK;
 }
 
+// Matrix-game solve (the job of LRSNash::solve_fast, cpp/include/search/mcts.h:643-649, cpp/src/pyoak.cc:394-425).
+// LRSNash (github.com/lab-oak/lrsnash, an empty submodule in the reference tree) walks the vertices of the game's
+// polytopes in exact rational arithmetic; any equilibrium of the same game has the same value, the strategies are not
+// unique. Here: the classical LP — shift the payoffs positive, maximise sum(y) subject to A y <= 1 — by a dense-tableau
+// simplex in doubles with Bland's rule (no cycling); the row player's strategy is read from the duals. Data are
+// integers <= denom on at most 9 x 9, so doubles are far from their limits.
+int oakb200_solve_matrix(int rows, int cols, const int* payoff, int denom, float* p1, float* p2, float* value) {
+  if (rows < 1 || cols < 1 || rows > 9 || cols > 9 || !payoff || denom <= 0) return OAKB200_EINVAL;
+  const int m = rows, n = cols, W = n + m + 1;
+  double T[10][20];  // m constraint rows + the objective row; columns: y (n), slack (m), rhs
+  int lo = payoff[0];
+  for (int i = 0; i < m * n; i++) lo = payoff[i] < lo ? payoff[i] : lo;
+  const double shift = 1.0 - lo;  // every entry >= 1
+  for (int i = 0; i < m; i++) {
+    for (int j = 0; j < n; j++) T[i][j] = payoff[i * n + j] + shift;
+    for (int j = 0; j < m; j++) T[i][n + j] = i == j;
+    T[i][W - 1] = 1.0;
+  }
+  for (int j = 0; j < W; j++) T[m][j] = j < n ? -1.0 : 0.0;
+  int basis[9];
+  for (int i = 0; i < m; i++) basis[i] = n + i;
+  for (int iter = 0; iter < 10000; iter++) {
+    int enter = -1;
+    for (int j = 0; j < n + m; j++)
+      if (T[m][j] < -1e-12) { enter = j; break; }
+    if (enter < 0) break;
+    int leave = -1;
+    double best = 0;
+    for (int i = 0; i < m; i++) {
+      if (T[i][enter] <= 1e-12) continue;
+      const double ratio = T[i][W - 1] / T[i][enter];
+      if (leave < 0 || ratio < best - 1e-15 || (ratio <= best + 1e-15 && basis[i] < basis[leave])) { leave = i; best = ratio; }
+    }
+    if (leave < 0) return OAKB200_EINVAL;  // unbounded: impossible for positive A
+    const double piv = T[leave][enter];
+    for (int j = 0; j < W; j++) T[leave][j] /= piv;
+    for (int i = 0; i <= m; i++) {
+      if (i == leave) continue;
+      const double f = T[i][enter];
+      if (f == 0) continue;
+      for (int j = 0; j < W; j++) T[i][j] -= f * T[leave][j];
+    }
+    basis[leave] = enter;
+  }
+  const double total = T[m][W - 1];  // sum(y) = 1 / value of the shifted game
+  if (!(total > 0)) return OAKB200_EINVAL;
+  double y[9] = {0}, x[9];
+  for (int i = 0; i < m; i++)
+    if (basis[i] < n) y[basis[i]] = T[i][W - 1];
+  for (int i = 0; i < m; i++) x[i] = T[m][n + i];  // duals
+  double sx = 0, sy = 0;
+  for (int i = 0; i < m; i++) { x[i] = x[i] < 0 ? 0 : x[i]; sx += x[i]; }
+  for (int j = 0; j < n; j++) { y[j] = y[j] < 0 ? 0 : y[j]; sy += y[j]; }
+  if (p1) for (int i = 0; i < m; i++) p1[i] = (float)(x[i] / sx);
+  if (p2) for (int j = 0; j < n; j++) p2[j] = (float)(y[j] / sy);
+  if (value) *value = (float)((1.0 / total - shift) / denom);
+  return OAKB200_OK;
+}
+
+// process_output's Nash half (mcts.h:628-656): average values discretised to 1/256, solved, per root
+int oakb200_search_nash(oakb200_search* s, float* nash, float* nash_value) {
+  if (!s) return OAKB200_EINVAL;
+  for (size_t r = 0; r < s->n_roots; r++) {
+    const Root& R = s->roots[r];
+    int M[81];
+    for (int i = 0; i < R.k1; i++)
+      for (int j = 0; j < R.k2; j++) {
+        uint32_t n = R.visit[i * 9 + j];
+        n += !n;
+        M[R.k2 * i + j] = (int)(R.value[i * 9 + j] / n * 256);
+      }
+    float a[9] = {0}, b[9] = {0}, v = 0.5f;
+    if (R.k1 >= 1 && R.k2 >= 1 && oakb200_solve_matrix(R.k1, R.k2, M, 256, a, b, &v) != OAKB200_OK) return OAKB200_EINVAL;
+    if (nash) {
+      for (int i = 0; i < 9; i++) {
+        nash[18 * r + i] = i < R.k1 ? a[i] : 0.0f;
+        nash[18 * r + 9 + i] = i < R.k2 ? b[i] : 0.0f;
+      }
+    }
+    if (nash_value) nash_value[r] = v;
+  }
+  return OAKB200_OK;
+}
+
 int oakb200_search_stats(oakb200_search* s, uint64_t* waves, uint64_t* levels) {
   if (!s) return OAKB200_EINVAL;
   if (waves) *waves = s->waves;

@@ -64,7 +64,35 @@ class TreeSearch:
                                                                                   "iterations", "empirical_value", "empirical", "nodes")]))
         return out
 
+    def nash(self):
+        """process_output's Nash half (mcts.h:628-656): -> (nash[n,2,9] f32, nash_value[n] f32)."""
+        f = self.lib.oakb200_search_nash
+        f.restype = ctypes.c_int
+        f.argtypes = [ctypes.c_void_p] * 3
+        p, v = np.zeros((self.n, 2, 9), np.float32), np.zeros(self.n, np.float32)
+        self._check(f(self._h, _ptr(p), _ptr(v)))
+        return p, v
+
     def stats(self):
         w, lv = ctypes.c_uint64(), ctypes.c_uint64()
         self._check(self.lib.oakb200_search_stats(self._h, ctypes.byref(w), ctypes.byref(lv)))
         return w.value, lv.value
+
+
+def solve_matrix(row_payoff, discretize_factor=256):
+    """pyoak.solve_matrix (reference cpp/src/pyoak.cc:394-425): row player's payoffs in [0, 1] -> (p1, p2, value) of the
+    one-sum matrix game after discretising to 1/discretize_factor. Host code of liboakb200 (no GPU needed)."""
+    from .engine import load_library
+    lib = load_library()
+    lib.oakb200_solve_matrix.restype = ctypes.c_int
+    lib.oakb200_solve_matrix.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3
+    a = np.asarray(row_payoff, np.float32)
+    if a.ndim != 2:
+        raise ValueError("Expecting 2d array")
+    m, n = a.shape
+    disc = np.ascontiguousarray((a * np.float32(discretize_factor)).astype(np.int32))
+    p1, p2, v = np.zeros(m, np.float32), np.zeros(n, np.float32), np.zeros(1, np.float32)
+    rc = lib.oakb200_solve_matrix(m, n, _ptr(disc), int(discretize_factor), _ptr(p1), _ptr(p2), _ptr(v))
+    if rc != 0:
+        raise OakB200Error(f"oakb200_solve_matrix: error {rc}")
+    return p1, p2, float(v[0])

@@ -69,8 +69,9 @@ class SelfPlay:
         self.dev = torch.device("cuda", device)
         self.eng = BattleEngine(self.n, device=device)
         self.eng.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
-        self.eng.load_network(net_blob)
-        self.eng.set_eval_mode(eval_mode)
+        if net_blob is not None:
+            self.eng.load_network(net_blob)
+            self.eng.set_eval_mode(eval_mode)
         self.eng.frames_create(self.n, max_updates)
         self.pool = np.ascontiguousarray(team_pool, np.uint8)
         self.seed, self.temperature, self.min_prob = int(seed), float(temperature), float(min_prob)
@@ -150,3 +151,97 @@ class SelfPlay:
                 if writer is not None:
                     writer.add(stream, games)
         return done
+
+
+def runtime_policy(empirical, nash, mode="e", temp=1.0, min_prob=0.0):
+    """RuntimePolicy::get_policy (reference cpp/include/util/policy.h:22-98) for rows of 9 probabilities: `mode` is a
+    '-'-joined list of <letter>[weight] with e = empirical, n = nash, x = argmax of the empirical policy; then temperature,
+    floor and renormalisation in double. (p = the network prior and b = beta are not produced by this search.)"""
+    emp, nsh = np.asarray(empirical, np.float64), np.asarray(nash, np.float64)
+    pol = np.zeros_like(emp)
+    for word in mode.split("-"):
+        w = float(word[1:]) if len(word) > 1 else 1.0
+        if word[0] == "e":
+            pol += w * emp
+        elif word[0] == "n":
+            pol += w * nsh
+        elif word[0] == "x":
+            pol[np.arange(pol.shape[0]), emp.argmax(-1)] += w
+        else:
+            raise ValueError(f"RuntimePolicy: invalid mode char: {word[0]}")
+    if temp != 1:
+        pol = np.power(pol, temp)
+        pol /= pol.sum(-1, keepdims=True)
+    pol[pol < min_prob] = 0
+    s = pol.sum(-1, keepdims=True)
+    if (s == 0).any():
+        raise RuntimeError(f"RuntimePolicy: zero policy, mode: {mode}")
+    return pol / s
+
+
+class SearchSelfPlay(SelfPlay):
+    """The generate loop with its search (reference cpp/src/generate.cc:286-333): every turn of every running game gets
+    a tree search (oakb200_search_*: `iterations` MonteCarlo iterations, joint UCB, `particles` descents in flight per
+    root), the move is drawn from RuntimePolicy::get_policy of the search output, and the recorded update carries the
+    search's iteration count, empirical and Nash policies and values (CompressedFrames::Update(output, c1, c2),
+    compressed-frame.h:47-56). The network is not consulted (MonteCarlo leaves), so `net_blob` may be None."""
+
+    def __init__(self, games, team_pool, iterations, particles=16, policy_mode="e", ucb_c=1.0, rolls=(3, 1), net_blob=None, **kw):
+        from .search import TreeSearch
+        self._net = net_blob is not None
+        super().__init__(games, net_blob, team_pool, **kw)
+        self.iterations, self.policy_mode, self.ucb_c, self.rolls = int(iterations), policy_mode, float(ucb_c), rolls
+        self.search = TreeSearch(self.eng, self.n, particles=particles)
+        torch = self.torch
+        self.iters_t = torch.zeros(self.n, dtype=torch.int32, device=self.dev)
+        self.nash_value = torch.zeros(self.n, dtype=torch.float32, device=self.dev)
+        self.nash_probs = torch.zeros((self.n, 2, 9), dtype=torch.float32, device=self.dev)
+        self.searched = 0
+
+    def close(self):
+        self.search.close()
+        super().close()
+
+    def step(self):
+        torch, e, n = self.torch, self.eng, self.n
+        e.choices_device(self.battles, self.results, self.choices, self.counts)
+        b, d, r = (x.cpu().numpy() for x in (self.battles, self.durations, self.results))
+        seeds = self.seeds.cpu().numpy().view(np.uint64)
+        live = np.nonzero((r & 15) == 0)[0]
+        emp = np.zeros((n, 2, 9), np.float32)
+        nsh = np.zeros((n, 2, 9), np.float32)
+        ev, nv = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        it = np.zeros(n, np.int32)
+        c1, c2 = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        if live.size:
+            K = 0xD1B54A32D192ED03
+            sseeds = np.array([_splitmix64(int(s) ^ ((K * (2 * self.step_index + 1)) & MASK64)) for s in seeds[live]], np.uint64)
+            self.search.set_roots(b[live], d[live], r[live], sseeds)
+            self.search.run(self.iterations, c=self.ucb_c, root_rolls=self.rolls[0], other_rolls=self.rolls[1])
+            out = self.search.output()
+            np_, nv_ = self.search.nash()
+            emp[live], nsh[live] = out["empirical"].astype(np.float32), np_
+            ev[live], nv[live] = out["empirical_value"].astype(np.float32), nv_
+            it[live] = out["iterations"].astype(np.int32)
+            self.searched += int(out["iterations"].sum())
+            for p, dst in ((0, c1), (1, c2)):
+                pol = runtime_policy(out["empirical"][:, p], np_[:, p], self.policy_mode, self.temperature, self.min_prob)
+                u = np.array([(_splitmix64(int(s) ^ ((K * (2 * self.step_index + 2)) & MASK64) ^ p) >> 11) * 2.0 ** -53 for s in seeds[live]])
+                # mt19937::sample_pdf (util/random.h:41-50): first index whose cumulative probability reaches u
+                pick = np.minimum((np.cumsum(pol, -1) < u[:, None]).sum(-1), out["k"][:, p] - 1)
+                pick = np.where(pol[np.arange(live.size), pick] > 0, pick, pol.argmax(-1))
+                dst[live] = out["choices"][np.arange(live.size), p, pick]
+        dev = self.dev
+        self.c1.copy_(torch.from_numpy(c1).to(dev))
+        self.c2.copy_(torch.from_numpy(c2).to(dev))
+        self.probs.copy_(torch.from_numpy(emp).to(dev))
+        self.nash_probs.copy_(torch.from_numpy(nsh).to(dev))
+        self.value.copy_(torch.from_numpy(ev).to(dev))
+        self.nash_value.copy_(torch.from_numpy(nv).to(dev))
+        self.iters_t.copy_(torch.from_numpy(it).to(dev))
+        self.before.copy_(self.results)
+        e.frames_record_device(self.before, self.c1, self.c2, self.counts, self.value, self.nash_value, self.probs, self.nash_probs,
+                               iterations=self.iters_t)
+        e.step_device(self.battles, self.durations, self.results, self.c1, self.c2)
+        e.frames_finish_device(self.results)
+        self.step_index += 1
