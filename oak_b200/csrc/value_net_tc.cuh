@@ -289,6 +289,11 @@ __device__ __forceinline__ void put_hp(uint32_t hi, uint32_t lo, int r, int col,
   st16(elem(lo, r, col), l);
 }
 
+// CL = CTAs per cluster. CL = 2: the two CTAs of a cluster walk the chunk program in step on two different tiles, and
+// each weight chunk is read from L2 ONCE for both — each CTA's streamer fetches one half and multicasts it into both
+// rings — because the L2 -> SM weight stream (2.2 MB per tile, every SM asking for the same lines) is what bounds the
+// single-CTA form (profiles/r1f_eval_tc_ncu_summary.txt). A ring slot is reused when BOTH issuers have released it.
+template <int CL>
 __global__ void __launch_bounds__(THREADS, 1)
 eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __restrict__ durations, const uint8_t* __restrict__ results,
                float* __restrict__ values, float* __restrict__ logits, uint8_t* __restrict__ counts, uint32_t n) {
@@ -298,11 +303,17 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   const uint32_t bar = smem + OFF_BAR;
   const uint32_t bar_full = bar, bar_empty = bar + 32, bar_a = bar + 64, bar_d = bar + 72, bar_t = bar + 80;
   const uint32_t ntiles = (n + ROWS - 1) / ROWS;
+  // CTA `crank` of cluster `blockIdx.x / CL` takes tile base + crank of every group of CL tiles the cluster visits; a
+  // tile index >= ntiles is a dummy (rows clamp to the last evaluation, nothing is written) so that the CTAs of a
+  // cluster always run the same number of chunk programs
+  const uint32_t crank = CL > 1 ? umma::cluster_ctarank() : 0u;
+  const uint32_t tile0 = (blockIdx.x / CL) * CL, tile_step = gridDim.x;
+  const uint16_t cmask = (uint16_t)((1u << CL) - 1u);
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < (int)RING_SLOTS; i++) {
       umma::mbar_init(bar_full + 8 * i, 1);
-      umma::mbar_init(bar_empty + 8 * i, 1);
+      umma::mbar_init(bar_empty + 8 * i, CL);
     }
     umma::mbar_init(bar_a, WORKERS);
     umma::mbar_init(bar_d, 1);
@@ -319,6 +330,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   }
   umma::tc_fence_before();
   __syncthreads();
+  if (CL > 1) umma::cluster_sync();  // every CTA's barriers exist before any peer multicasts into them
   umma::tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(dsm + OFF_TMEM_SLOT);
   const Chunk* prog = reinterpret_cast<const Chunk*>(dsm + OFF_PROG);
@@ -327,13 +339,21 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // ===== weight streamer: packed chunks L2 -> ring =====
     if (lane == 0) {
       uint32_t g = 0;
-      for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (uint32_t t = tile0; t < ntiles; t += tile_step) {
         for (int c = 0; c < P.nchunks; c++, g++) {
           const uint32_t slot = g & (RING_SLOTS - 1);
           if (g >= RING_SLOTS) umma::mbar_wait(bar_empty + 8 * slot, ((g / RING_SLOTS) - 1) & 1);
           const uint32_t bytes = (uint32_t)prog[c].bytes16 << 4;
           umma::mbar_expect_tx(bar_full + 8 * slot, bytes);
-          umma::bulk_g2s(smem + OFF_RING + slot * RING_SLOT, P.wpack + ((size_t)prog[c].gofs16 << 4), bytes, bar_full + 8 * slot);
+          const uint8_t* src = P.wpack + ((size_t)prog[c].gofs16 << 4);
+          const uint32_t dst = smem + OFF_RING + slot * RING_SLOT;
+          if (CL > 1) {  // this CTA's half of the chunk, into both rings; the peer sends the other half
+            const uint32_t h0 = ((uint32_t)prog[c].bytes16 >> 1) << 4;
+            const uint32_t ofs = crank ? h0 : 0u, len = crank ? bytes - h0 : h0;
+            umma::bulk_g2s_multicast(dst + ofs, src + ofs, len, bar_full + 8 * slot, cmask);
+          } else {
+            umma::bulk_g2s(dst, src, bytes, bar_full + 8 * slot);
+          }
         }
       }
     }
@@ -341,7 +361,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // ===== MMA issuer =====
     if (lane == 0) {
       uint32_t g = 0, stage = 0;
-      for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (uint32_t t = tile0; t < ntiles; t += tile_step) {
         for (int c = 0; c < P.nchunks; c++, g++) {
           const Chunk ch = prog[c];
           if (ch.flags & F_STAGE_BEGIN) {
@@ -365,7 +385,8 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             umma::mma_bf16(d, da, dbl, idesc, 1u);
             if (i < ch.lo_steps) umma::mma_bf16(d, umma::smem_desc(a_lo + i * 2 * CORE, CORE, 128), dbh, idesc, 1u);
           }
-          umma::mma_commit(bar_empty + 8 * slot);
+          if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
+          else umma::mma_commit(bar_empty + 8 * slot);
           if (ch.flags & F_END_D) umma::mma_commit(bar_d);
           if (ch.flags & F_END_T) umma::mma_commit(bar_t);
         }
@@ -402,7 +423,8 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
         umma::tc_fence_after();
       }
     };
-    for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    for (uint32_t tb = tile0; tb < ntiles; tb += tile_step) {
+      const uint32_t t = tb + crank;
       const uint32_t e = t * ROWS + (uint32_t)r;
       const uint32_t ec = e < n ? e : n - 1;
       asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory");  // the other group has finished with the previous tile
@@ -527,6 +549,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   }
   umma::tc_fence_before();
   __syncthreads();
+  if (CL > 1) umma::cluster_sync();  // no CTA leaves while its peer's last commits are still on their way to its barriers
   if (warp == W_STREAM) {
     umma::tc_fence_after();
     umma::tmem_dealloc(tmem, TMEM_COLS);
