@@ -27,6 +27,7 @@ struct oakb200_ctx {
   uint32_t* steps = nullptr;
   uint8_t* teams = nullptr;
   uint32_t* ticket = nullptr;
+  int ticket_slot = 0;  // which of the 64 ticket words a rollout launch uses (search.cu runs rollouts on several streams)
   unsigned long long* total_steps = nullptr;
   uint64_t launches = 0;
   oakb200_net* net = nullptr;

@@ -53,7 +53,7 @@ template <bool CHANCE, bool WRITE>
 cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
                            uint32_t max_steps, void* score2, void* turns, void* steps, const uint32_t* available = nullptr) {
   cudaStream_t stream = ctx->stream;
-  uint32_t* ticket = ctx->ticket;
+  uint32_t* ticket = ctx->ticket + ctx->ticket_slot;
   // OAKB200_ROLLOUT_GROUPED=1 selects the variant that regroups a CTA's battles by action class before every update.
   // Measured on B200 (profiles/r1h_rollout_grouping.txt): 16 % fewer warp instructions and 9.8 -> 12.8 active lanes, but
   // the CTA-wide barriers cost more issue slots than that saves (2.08 vs 2.35 G battle-steps/s), so it is not the default.
