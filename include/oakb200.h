@@ -124,6 +124,12 @@ int oakb200_build_battles(oakb200_ctx* ctx, size_t n, const uint8_t* teams, cons
  * net_load: parse + upload a parameter file image (HOST pointer). Limits: hidden dims <= 128,
  * embedding dims <= 96, main hidden <= 64, head hidden <= 64; OAKB200_EINVAL otherwise. */
 int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* file_bytes, size_t len);
+/* The same parameter file loaded as the reference's "discrete" agent (cpp/src/search.cc:105-123): float embedding nets,
+ * embeddings and hp quantised to u8 (static_cast<uint8_t>(127 * f), nn/battle/cache.h:106,234, network.h:147,165), int8
+ * main net (nn/battle/quantized/{affine,clipped_relu,main-net}.h: int8 weights = w * 64, int32 biases = b * 64 * 127,
+ * ClippedReLU clamp(x >> 6, 0, 127), outputs / (127 * 64)). The integer part is exact. OAKB200_EINVAL unless the file's
+ * header says clamped activations and every main-net weight is inside (-2, 2), as the reference requires. */
+int oakb200_net_load_discrete(oakb200_ctx* ctx, const uint8_t* file_bytes, size_t len);
 /* Which kernel evaluates: 0 = auto (the tcgen05 tensor-core kernel whenever the layer shapes fit: hidden <= 128,
  * pokemon/active embedding <= 63/95, main hidden <= 64, value hidden <= 32, policy hidden <= 64 and a multiple
  * of 4 -- the reference's defaults do), 1 = the fp32 CUDA-core kernel, 2 = tensor cores or OAKB200_EINVAL.

@@ -101,18 +101,54 @@ void oakb200_net_release(oakb200_ctx* ctx) {
   }
 }
 
-extern "C" int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* bytes, size_t len) {
+static int net_load_impl(oakb200_ctx* ctx, const uint8_t* bytes, size_t len, bool discrete);
+
+extern "C" int oakb200_net_load(oakb200_ctx* ctx, const uint8_t* bytes, size_t len) { return net_load_impl(ctx, bytes, len, false); }
+
+// "discrete" agent (reference cpp/src/search.cc:105-123,133-141): the float embedding nets feed an int8 main net. The main
+// net's parameters are converted exactly as NN::Battle::Quantized::AffineTransform::try_copy_parameters does
+// (quantized/affine.h:74-96: int8 = float * 64, int32 bias = float * 64 * 127, both truncated) and kept as
+// integer-valued floats, so both evaluation kernels run them unchanged: every product and sum (< 2^24) is exact in fp32 /
+// in the bf16 x bf16 -> fp32 tensor-core path.
+extern "C" int oakb200_net_load_discrete(oakb200_ctx* ctx, const uint8_t* bytes, size_t len) {
+  if (!ctx || !bytes || len < 8) return fail(ctx, OAKB200_EINVAL, "net_load_discrete: null or short parameter image");
+  if (bytes[0] + 1 != 2)
+    return fail(ctx, OAKB200_EINVAL, "net_load_discrete: the parsed header does not encode clamped activations");  // search.cc:137-141
+  std::vector<uint8_t> q(bytes, bytes + len);
+  const uint8_t *p = q.data() + 8, *end = q.data() + len;
+  for (int i = 0; i < 12; i++) {
+    HostAffine a;
+    const uint8_t* next = read_affine(p, end, a);
+    if (!next) return fail(ctx, OAKB200_EINVAL, "net_load_discrete: truncated parameter image");
+    if (i >= 4) {
+      uint8_t* bw = q.data() + (reinterpret_cast<const uint8_t*>(a.bias) - q.data());
+      const size_t nb = a.out, nw = (size_t)a.out * a.in;
+      for (size_t k = 0; k < nb + nw; k++) {
+        float v;
+        memcpy(&v, bw + 4 * k, 4);
+        if (k >= nb && !(v < 2.0f && v > -2.0f))
+          return fail(ctx, OAKB200_EINVAL, "net_load_discrete: a main-net weight is outside (-2, 2)");  // affine.h:88-95
+        const float r = k < nb ? (float)static_cast<int32_t>(v * 64 * 127) : (float)static_cast<int8_t>(v * 64);
+        memcpy(bw + 4 * k, &r, 4);
+      }
+    }
+    p = next;
+  }
+  return net_load_impl(ctx, q.data(), len, true);
+}
+
+static int net_load_impl(oakb200_ctx* ctx, const uint8_t* bytes, size_t len, bool discrete) {
   if (!ctx || !bytes || len < 8) return fail(ctx, OAKB200_EINVAL, "net_load: null or short parameter image");
   HostAffine a[12];
   const uint8_t *p = bytes + 8, *end = bytes + len;
   for (int i = 0; i < 12; i++) p = read_affine(p, end, a[i]);
   if (p != end) return fail(ctx, OAKB200_EINVAL, "net_load: parameter image does not end at the last Affine block");
   NetDims d;
-  d.act = bytes[0] + 1;
+  d.act = discrete ? 3 : bytes[0] + 1;
   d.phd = a[0].out; d.pod = a[1].out; d.ahd = a[2].out; d.aod = a[3].out;
   d.side = (1 + d.aod) + 5 * (1 + d.pod);
   d.in = 2 * d.side; d.hd = a[4].out; d.vhd = a[6].out; d.pohd = a[8].out;
-  const bool ok = (d.act == 1 || d.act == 2) && a[0].in == 198 && a[1].in == (uint32_t)d.phd && a[2].in == 427 &&
+  const bool ok = (d.act >= 1 && d.act <= 3) && a[0].in == 198 && a[1].in == (uint32_t)d.phd && a[2].in == 427 &&
                   a[3].in == (uint32_t)d.ahd && a[4].in == (uint32_t)d.in && a[5].in == (uint32_t)d.hd && a[5].out == (uint32_t)d.hd &&
                   a[6].in == (uint32_t)d.hd && a[7].in == (uint32_t)d.vhd && a[7].out == 1 && a[8].in == (uint32_t)d.hd &&
                   a[9].in == (uint32_t)d.pohd && a[9].out == 315 && a[10].in == (uint32_t)d.hd && a[10].out == (uint32_t)d.pohd &&
@@ -167,9 +203,14 @@ struct NetView {
       *p1bW, *p1bb, *p2aT, *p2ab, *p2bW, *p2bb;
 };
 
+// act: 1 relu, 2 clamp to [0, 1]; discrete mode (NetDims::act == 3) uses 3 = clamp then floor(127 x) for the embedding
+// outputs (static_cast<uint8_t>(127 * f), nn/battle/cache.h:106,234) and 4 = the int8 net's ClippedReLU
+// clamp(x >> 6, 0, 127) (quantized/clipped_relu.h:53-98) on exact integer-valued floats
 __device__ __forceinline__ float activate(float x, int act) {
+  if (act == 4) return fminf(fmaxf(floorf(x * 0.015625f), 0.0f), 127.0f);
   x = fmaxf(x, 0.0f);
-  return act == 2 ? fminf(x, 1.0f) : x;
+  if (act >= 2) x = fminf(x, 1.0f);
+  return act == 3 ? floorf(127.0f * x) : x;
 }
 __device__ __forceinline__ int status_index(uint32_t status, uint32_t sleeps) {  // battle.h:106-123
   if ((status & 7u) == 0) return __ffs(status) - 1 - 3;
@@ -294,6 +335,10 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
             float* __restrict__ values, float* __restrict__ logits, uint8_t* __restrict__ counts, uint32_t n) {
   extern __shared__ __align__(16) float smem[];
   const NetDims d = nv.d;
+  // discrete mode: float embedding nets (clamp), embeddings and hp quantised to 0..127, integer main net (see activate)
+  const bool disc = d.act == 3;
+  const int act_h = disc ? 2 : d.act, act_e = d.act, act_m = disc ? 4 : d.act;
+  const float out_div = disc ? 8128.0f : 1.0f;  // 127 * 64 (quantized/main-net.h:127)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // CTA-shared second-layer weights
   float* s_pk1T = smem;
@@ -366,13 +411,13 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
         }
         __syncwarp();
         if (slot == 1) {
-          sparse_layer(nv.ac0T, nv.ac0b, d.ahd, fi, fv, cnt, d.act, h, lane);
-          dense_layer3(s_ac1T, nv.ac1b, d.ahd, d.aod, h, d.act, out + 1, lane);
+          sparse_layer(nv.ac0T, nv.ac0b, d.ahd, fi, fv, cnt, act_h, h, lane);
+          dense_layer3(s_ac1T, nv.ac1b, d.ahd, d.aod, h, act_e, out + 1, lane);
         } else {
-          sparse_layer(nv.pk0T, nv.pk0b, d.phd, fi, fv, cnt, d.act, h, lane);
-          dense_layer3(s_pk1T, nv.pk1b, d.phd, d.pod, h, d.act, out + 1, lane);
+          sparse_layer(nv.pk0T, nv.pk0b, d.phd, fi, fv, cnt, act_h, h, lane);
+          dense_layer3(s_pk1T, nv.pk1b, d.phd, d.pod, h, act_e, out + 1, lane);
         }
-        if (lane == 0) out[0] = (float)hpv / (float)maxhp;
+        if (lane == 0) out[0] = disc ? floorf(((float)hpv / (float)maxhp) * 127.0f) : (float)hpv / (float)maxhp;
         __syncwarp();
       }
     }
@@ -396,23 +441,23 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
           if (2 * lane + 1 < d.hd) a1 = fmaf(x, nv.fc0T[(size_t)k * d.hd + 2 * lane + 1], a1);
         }
       }
-      if (on) { b0[2 * lane] = activate(a0, d.act); if (2 * lane + 1 < d.hd) b0[2 * lane + 1] = activate(a1, d.act); }
+      if (on) { b0[2 * lane] = activate(a0, act_m); if (2 * lane + 1 < d.hd) b0[2 * lane + 1] = activate(a1, act_m); }
       __syncwarp();
     }
-    dense_layer3(nv.fc1T, nv.fc1b, d.hd, d.hd, b0, d.act, b1, lane);
-    dense_layer3(nv.v2T, nv.v2b, d.hd, d.vhd, b1, d.act, hv, lane);
+    dense_layer3(nv.fc1T, nv.fc1b, d.hd, d.hd, b0, act_m, b1, lane);
+    dense_layer3(nv.v2T, nv.v2b, d.hd, d.vhd, b1, act_m, hv, lane);
     {
       float part = 0.0f;
       for (int k = lane; k < d.vhd; k += 32) part = fmaf(hv[k], nv.v3w[k], part);
       for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
-      if (lane == 0) values[e] = 1.0f / (1.0f + expf(-(part + nv.v3b[0])));
+      if (lane == 0) values[e] = 1.0f / (1.0f + expf(-((part + nv.v3b[0]) / out_div)));
     }
     // ---- policy heads over the legal choices only
     Mem<1> m;
     m.set(const_cast<uint8_t*>(recb));
     const uint32_t res = results[e];
     for (int s = 0; s < 2; s++) {
-      dense_layer3(s == 0 ? nv.p1aT : nv.p2aT, s == 0 ? nv.p1ab : nv.p2ab, d.hd, d.pohd, b1, d.act, hp, lane);
+      dense_layer3(s == 0 ? nv.p1aT : nv.p2aT, s == 0 ? nv.p1ab : nv.p2ab, d.hd, d.pohd, b1, act_m, hp, lane);
       const uint64_t list = mem_choices(m, s, (res >> (4 + 2 * s)) & 3);
       const int cnt = choice_count(list);
       const float* W = s == 0 ? nv.p1bW : nv.p2bW;
@@ -433,7 +478,7 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
           float part = 0.0f;
           for (int j = lane; j < d.pohd; j += 32) part = fmaf(hp[j], W[(size_t)idx * d.pohd + j], part);
           for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
-          lg = part + B[idx];
+          lg = (part + B[idx]) / out_div;
         }
         if (lane == 0) logits[(size_t)e * 18 + s * 9 + k] = lg;
       }

@@ -111,7 +111,8 @@ __device__ __forceinline__ void stv4(uint32_t a, uint32_t x, uint32_t y, uint32_
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
 __device__ __forceinline__ uint32_t elem(uint32_t plane, int r, int k) { return plane + (uint32_t)((((k >> 3) * ROWS + r) << 4) + ((k & 7) << 1)); }
-__device__ __forceinline__ float actf(float x, int act) {
+__device__ __forceinline__ float actf(float x, int act) {  // 1 relu, 2 clamp, 4 the int8 net's ClippedReLU (value_net.cu: activate)
+  if (act == 4) return fminf(fmaxf(floorf(x * 0.015625f), 0.0f), 127.0f);
   x = fmaxf(x, 0.0f);
   return act == 2 ? fminf(x, 1.0f) : x;
 }
@@ -255,7 +256,16 @@ __device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_
 
 // One 32-column block of an accumulator: D[:, 32q .. 32q+31] -> min(max(D + bias, 0), bound) -> split planes, core
 // columns 4q .. 4q+3. bound = 1 for the clamp activation, +inf for ReLU, 0 for an empty slot's row.
-__device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
+// MODE (discrete networks): 1 = then floor(127 x), the u8 an embedding becomes (cache.h:106,234); 2 = the int8 net's
+// ClippedReLU clamp((D + bias) >> 6, 0, 127) instead. Both leave small integers: the hi plane is exact, the lo plane zero.
+template <int MODE>
+__device__ __forceinline__ float epi_act(float v, float b, float bound) {
+  if (MODE == 2) return fminf(fmaxf(floorf((v + b) * 0.015625f), 0.0f), 127.0f);
+  const float x = fminf(fmaxf(v + b, 0.0f), bound);
+  return MODE == 1 ? floorf(127.0f * x) : x;
+}
+template <int MODE>
+__device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
   uint32_t v[32];
   umma::tmem_ld32(taddr + 32u * q, v);
   umma::tmem_ld_wait();
@@ -263,14 +273,14 @@ __device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const floa
 #pragma unroll
   for (int g = 0; g < 4; g++) {
     const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
-    const float x0 = fminf(fmaxf(__uint_as_float(v[8 * g + 0]) + ba.x, 0.0f), bound);
-    const float x1 = fminf(fmaxf(__uint_as_float(v[8 * g + 1]) + ba.y, 0.0f), bound);
-    const float x2 = fminf(fmaxf(__uint_as_float(v[8 * g + 2]) + ba.z, 0.0f), bound);
-    const float x3 = fminf(fmaxf(__uint_as_float(v[8 * g + 3]) + ba.w, 0.0f), bound);
-    const float x4 = fminf(fmaxf(__uint_as_float(v[8 * g + 4]) + bb.x, 0.0f), bound);
-    const float x5 = fminf(fmaxf(__uint_as_float(v[8 * g + 5]) + bb.y, 0.0f), bound);
-    const float x6 = fminf(fmaxf(__uint_as_float(v[8 * g + 6]) + bb.z, 0.0f), bound);
-    const float x7 = fminf(fmaxf(__uint_as_float(v[8 * g + 7]) + bb.w, 0.0f), bound);
+    const float x0 = epi_act<MODE>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
+    const float x1 = epi_act<MODE>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
+    const float x2 = epi_act<MODE>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
+    const float x3 = epi_act<MODE>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
+    const float x4 = epi_act<MODE>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
+    const float x5 = epi_act<MODE>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
+    const float x6 = epi_act<MODE>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
+    const float x7 = epi_act<MODE>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
     uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
     split2(x0, x1, h0, l0);
     split2(x2, x3, h1, l1);
@@ -280,6 +290,13 @@ __device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const floa
     stv4(hi + o, h0, h1, h2, h3);
     stv4(lo + o, l0, l1, l2, l3);
   }
+}
+// mode is warp-uniform (a property of the loaded network)
+__device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
+                                               int mode = 0) {
+  if (mode == 0) epilogue_block_m<0>(taddr, q, bias, bound, hi, lo, r);
+  else if (mode == 1) epilogue_block_m<1>(taddr, q, bias, bound, hi, lo, r);
+  else epilogue_block_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
 // the hp / max-hp column of an embedding operand (written after the block stores of the same thread)
 __device__ __forceinline__ void put_hp(uint32_t hi, uint32_t lo, int r, int col, float hp) {
@@ -403,8 +420,13 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     uint32_t dphase = 0, tphase = 0;
     bool t_pending = false;
-    const int act = P.act;
-    const float act_bound = act == 2 ? 1.0f : __int_as_float(0x7F800000);
+    // discrete networks (P.act == 3): clamp in the embedding nets, embeddings / hp quantised to 0..127 (mode 1), the int8
+    // main net's ClippedReLU on exact integer accumulators (mode 2, act 4), outputs divided by 127 * 64
+    const bool disc = P.act == 3;
+    const int act = disc ? 4 : P.act;  // activation of the main net's head hidden layers
+    const int m_emb = disc ? 1 : 0, m_main = disc ? 2 : 0;
+    const float out_div = disc ? 8128.0f : 1.0f;
+    const float act_bound = (P.act == 2 || disc) ? 1.0f : __int_as_float(0x7F800000);
     auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
       umma::tc_fence_before();
       umma::fence_proxy_async();
@@ -439,7 +461,8 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           H pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
           const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
           const bool alive = hpv != 0;
-          const float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
           const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
           const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
           if (slot == 1) {
@@ -461,14 +484,14 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           wait_d();
           if (slot == 1) {  // 96 columns: group 0 takes 0..63, group 1 takes 64..95 (and the hp column aod >= 64 or not)
             if (grp == 0) {
-              epilogue_block(tl + D_WORK, 0, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
-              epilogue_block(tl + D_WORK, 1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
+              epilogue_block(tl + D_WORK, 0, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
+              epilogue_block(tl + D_WORK, 1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
             } else {
-              epilogue_block(tl + D_WORK, 2, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r);
+              epilogue_block(tl + D_WORK, 2, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
             }
             if ((P.aod >= 64) == (grp == 1)) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
           } else {
-            epilogue_block(tl + D_WORK, grp, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, r);
+            epilogue_block(tl + D_WORK, grp, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, r, m_emb);
             if ((P.pod >= 32) == (grp == 1)) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
           }
           publish();
@@ -478,10 +501,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       }
       // ---- trunk (main-net.h:66-107)
       wait_t();
-      epilogue_block(tl + D_TRUNK, grp, cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, r);
+      epilogue_block(tl + D_TRUNK, grp, cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, r, m_main);
       publish();
       wait_d();
-      epilogue_block(tl + D_WORK, grp, cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, r);
+      epilogue_block(tl + D_WORK, grp, cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, r, m_main);
       publish();
       wait_d();
       if (grp == 0) {
@@ -492,7 +515,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #pragma unroll
         for (int j = 0; j < 32; j++)
           if (j < P.vhd) acc = fmaf(actf(__uint_as_float(v[j]) + cst[C_HEADS + j], act), cst[C_V3W + j], acc);
-        if (e < n) values[e] = 1.0f / (1.0f + expf(-acc));
+        if (e < n) values[e] = 1.0f / (1.0f + expf(-(acc / out_div)));
       }
       {
         const int s = grp;  // group 0: player 1's policy head, group 1: player 2's
@@ -539,7 +562,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
                 a1 = fmaf(h[4 * j + 3], w.w, a1);
               }
             }
-            lg = a0 + a1 + __ldg(B + idx);
+            lg = (a0 + a1 + __ldg(B + idx)) / out_div;
           }
           if (e < n) logits[(size_t)e * 18 + s * 9 + k] = lg;
         }

@@ -60,6 +60,7 @@ def load_library():
         "oakb200_randomize_hidden_device": (i32, [vp, sz, vp, vp]),
         "oakb200_build_battles": (i32, [vp, sz, vp, vp]),
         "oakb200_net_load": (i32, [vp, vp, sz]),
+        "oakb200_net_load_discrete": (i32, [vp, vp, sz]),
         "oakb200_eval_set_mode": (i32, [vp, i32]),
         "oakb200_respawn_device": (i32, [vp, sz, vp, vp, vp, vp, vp]),
         "oakb200_policy_sample_device": (i32, [vp, sz, vp, vp, vp, vp, u32, ctypes.c_double, ctypes.c_double, vp, vp, vp]),
@@ -220,12 +221,14 @@ class BattleEngine:
         return score, turns, steps
 
     # ---------------------------------------------------------------- leaf evaluation
-    def load_network(self, blob):
-        """Parameter file image in the reference's format (bytes / uint8 array / path)."""
+    def load_network(self, blob, discrete=False):
+        """Parameter file image in the reference's format (bytes / uint8 array / path). discrete=True loads it as the
+        reference's `.discrete` agent: float embedding nets, u8 embeddings, int8 main net."""
         if isinstance(blob, (str, os.PathLike)):
             blob = np.fromfile(blob, np.uint8)
         blob = np.frombuffer(bytes(blob), np.uint8) if isinstance(blob, (bytes, bytearray)) else _np(blob, np.uint8)
-        self._check(self.lib.oakb200_net_load(self._h, _ptr(blob), blob.size))
+        fn = self.lib.oakb200_net_load_discrete if discrete else self.lib.oakb200_net_load
+        self._check(fn(self._h, _ptr(blob), blob.size))
 
     def set_eval_mode(self, mode):
         """0 auto (tensor cores when the layer shapes fit), 1 fp32 CUDA-core kernel, 2 tensor cores or error."""

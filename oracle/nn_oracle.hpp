@@ -241,6 +241,74 @@ struct BattleNet {
     }
     return 1.0f / (1.0f + std::exp(-value));
   }
+
+  // ---- "discrete" mode (cpp/src/search.cc:105-123): the float embedding nets feed an int8 main net.
+  //   embedding -> u8        static_cast<uint8_t>(127 * f), hp as percent * 127   nn/battle/cache.h:100-108,228-236, network.h:147,165
+  //   parameters             int8 = float * 64, int32 bias = float * 64 * 127     quantized/affine.h:74-96
+  //   layer                  int32 = bias + sum u8 * int8                          quantized/affine.h:99-186
+  //   activation             clamp(x >> 6, 0, 127)                                 quantized/clipped_relu.h:53-98
+  //   outputs                value_fc3 / (127 * 64) -> sigmoid; policy rows / (127 * 64)   quantized/main-net.h:104-147
+  // The network must carry clamped activations (search.cc:133-141).
+  static void quantize_embedding(const std::vector<float>& e, std::vector<uint8_t>& q) {
+    q.resize(e.size());
+    for (size_t i = 0; i < e.size(); i++) q[i] = (uint8_t)(127 * e[i]);
+  }
+  static int32_t qbias(float b) { return (int32_t)(b * 64 * 127); }
+  static int8_t qweight(float w) { return (int8_t)(w * 64); }
+  static void qdense(const AffineP& a, const uint8_t* x, int32_t* y) {
+    for (uint32_t o = 0; o < a.out; o++) {
+      int32_t acc = qbias(a.bias[o]);
+      for (uint32_t k = 0; k < a.in; k++) acc += (int32_t)x[k] * qweight(a.w[(size_t)o * a.in + k]);
+      y[o] = acc;
+    }
+  }
+  static void crelu(const int32_t* y, uint8_t* x, uint32_t n) {
+    for (uint32_t i = 0; i < n; i++) {
+      const int32_t v = y[i] >> 6;
+      x[i] = (uint8_t)(v < 0 ? 0 : v > 127 ? 127 : v);
+    }
+  }
+  // integer main net on a given u8 battle embedding; returns value_fc3 / 8128 (before the sigmoid)
+  float main_discrete(const uint8_t* q, int m, int n, const uint16_t* idx1, const uint16_t* idx2, float* l1, float* l2) const {
+    std::vector<int32_t> y(320);
+    std::vector<uint8_t> a0(fc0.out), a1(fc1.out), av(v2.out), ap(p1a.out > p2a.out ? p1a.out : p2a.out);
+    qdense(fc0, q, y.data());
+    crelu(y.data(), a0.data(), fc0.out);
+    qdense(fc1, a0.data(), y.data());
+    crelu(y.data(), a1.data(), fc1.out);
+    qdense(v2, a1.data(), y.data());
+    crelu(y.data(), av.data(), v2.out);
+    int32_t v;
+    qdense(v3, av.data(), &v);
+    const float conversion = 127 * (1 << 6);
+    for (int s = 0; s < 2; s++) {
+      const AffineP &a = s == 0 ? p1a : p2a, &o = s == 0 ? p1b : p2b;
+      qdense(a, a1.data(), y.data());
+      crelu(y.data(), ap.data(), a.out);
+      const int cnt = s == 0 ? m : n;
+      const uint16_t* idx = s == 0 ? idx1 : idx2;
+      float* lo = s == 0 ? l1 : l2;
+      for (int k = 0; k < cnt; k++) {
+        int32_t acc = qbias(o.bias[idx[k]]);
+        for (uint32_t j = 0; j < o.in; j++) acc += (int32_t)ap[j] * qweight(o.w[(size_t)idx[k] * o.in + j]);
+        lo[k] = acc / conversion;
+      }
+    }
+    return v / conversion;
+  }
+  float eval_discrete(const Battle& b, const uint8_t* durations, int m, int n, const uint8_t* c1, const uint8_t* c2, float* l1, float* l2,
+                      std::vector<uint8_t>* embedding_out = nullptr) const {
+    std::vector<float> e;
+    embed(b, durations, e);
+    std::vector<uint8_t> q;
+    quantize_embedding(e, q);
+    if (embedding_out) *embedding_out = q;
+    uint16_t i1[9], i2[9];
+    for (int k = 0; k < m; k++) i1[k] = policy_index(b.sides[0], c1[k]);
+    for (int k = 0; k < n; k++) i2[k] = policy_index(b.sides[1], c2[k]);
+    const float value = main_discrete(q.data(), m, n, i1, i2, l1, l2);
+    return 1.0f / (1.0f + std::exp(-value));
+  }
 };
 
 }  // namespace oracle

@@ -332,3 +332,43 @@ int64_t oracle_training_rows(const uint8_t* stream, uint64_t n_bytes, int thread
   return bad.load() ? bad.load() : (int64_t)rows;
 }
 }
+
+// ---- "discrete" evaluation (nn_oracle.hpp: eval_discrete) ----
+extern "C" {
+// the integer main net alone on a given u8 battle embedding (pins against oracle/_ref: ref_quantized_main)
+float oracle_net_main_discrete(void* h, const uint8_t* q, int m, int n, const uint16_t* idx1, const uint16_t* idx2, float* l1, float* l2) {
+  return static_cast<BattleNet*>(h)->main_discrete(q, m, n, idx1, idx2, l1, l2);
+}
+// batched, as oracle_net_eval_batch; embeddings_out nullable ([n][fc0.in] u8)
+void oracle_net_eval_discrete_batch(void* h, const uint8_t* battles, const uint8_t* durations, const uint8_t* results, size_t n, int threads,
+                                    float* values, float* logits, uint8_t* counts, uint8_t* embeddings_out) {
+  const BattleNet* net = static_cast<BattleNet*>(h);
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const size_t i0 = next.fetch_add(64);
+      if (i0 >= n) return;
+      const size_t i1 = i0 + 64 < n ? i0 + 64 : n;
+      for (size_t i = i0; i < i1; i++) {
+        Battle b;
+        memcpy(&b, battles + i * 384, 384);
+        Options o{};
+        OakEngine e(b, o);
+        uint8_t c1[9], c2[9];
+        const int m = e.choices(P1, (results[i] >> 4) & 3, c1);
+        const int k = e.choices(P2, (results[i] >> 6) & 3, c2);
+        float* lo = logits + i * 18;
+        for (int j = 0; j < 18; j++) lo[j] = 0.0f;
+        std::vector<uint8_t> q;
+        values[i] = net->eval_discrete(b, durations + i * 8, m, k, c1, c2, lo, lo + 9, embeddings_out ? &q : nullptr);
+        if (embeddings_out) memcpy(embeddings_out + i * net->fc0.in, q.data(), q.size());
+        counts[2 * i] = (uint8_t)m;
+        counts[2 * i + 1] = (uint8_t)k;
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < (threads < 1 ? 1 : threads); t++) pool.emplace_back(work);
+  for (auto& t : pool) t.join();
+}
+}

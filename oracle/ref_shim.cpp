@@ -128,3 +128,80 @@ uint32_t ref_frames_read_game(const char* bytes, uint8_t* battle384, uint8_t* re
   return (uint32_t)frames.updates.size();
 }
 }
+
+// ---- "discrete" main net: the reference's own int8 layers (nn/battle/quantized/{affine,clipped_relu}.h, AVX2) ----
+// quantized/main-net.h itself includes nn/affine.h (Eigen, an empty submodule here), so its propagate() glue — the fixed
+// order of layer calls, main-net.h:104-147 — is restated below around the reference's layer classes; parameters go in
+// through each layer's own try_copy_parameters (the float -> int8 / int32 conversion under test).
+#include <stdexcept>
+#include <string>
+
+#include <nn/battle/quantized/affine.h>
+#include <nn/battle/quantized/clipped_relu.h>
+
+namespace {
+struct FakeVec {
+  const float* p;
+  const float* data() const { return p; }
+};
+struct FakeAffine {  // the members AffineTransform::try_copy_parameters reads from NN::Affine
+  uint32_t in_dim, out_dim;
+  FakeVec weights, biases;
+};
+}  // namespace
+
+extern "C" {
+// Default shape 768 -> 64 -> 64, value 32, policy 64 -> 320 (315 rows zero-padded, main-net.h:56-63).
+// w[i] / b[i] for i = fc0, fc1, value_fc2, value_fc3, p1_fc2, p1_fc3 (320 x 64), p2_fc2, p2_fc3 (320 x 64), row-major [out][in].
+// Returns value_fc3 / (127 * 64) (before the sigmoid); p1[m], p2[n] = the chosen policy rows / (127 * 64). -1e9 on a
+// parameter outside (-2, 2).
+float ref_quantized_main(const float* const* w, const float* const* b, const uint8_t* input768, int m, int n, const uint16_t* idx1,
+                         const uint16_t* idx2, float* p1, float* p2) {
+  using namespace NN::Battle::Quantized;
+  static AffineTransform<768, 64> fc0;
+  static ClippedReLU<64> ac0;
+  static AffineTransform<64, 64> fc1;
+  static ClippedReLU<64> ac1;
+  static AffineTransform<64, 32> v2;
+  static ClippedReLU<32> vac2;
+  static AffineTransform<32, 1> v3;
+  static AffineTransform<64, 64> p1a, p2a;
+  static ClippedReLU<64> p1ac, p2ac;
+  static AffineTransform<64, 320> p1b, p2b;
+  // try_copy_parameters builds two std::strings per weight for its range message: convert once per parameter set
+  static const float* loaded = nullptr;
+  if (loaded != w[0]) try {
+    loaded = nullptr;
+    fc0.try_copy_parameters(FakeAffine{768, 64, {w[0]}, {b[0]}});
+    fc1.try_copy_parameters(FakeAffine{64, 64, {w[1]}, {b[1]}});
+    v2.try_copy_parameters(FakeAffine{64, 32, {w[2]}, {b[2]}});
+    v3.try_copy_parameters(FakeAffine{32, 1, {w[3]}, {b[3]}});
+    p1a.try_copy_parameters(FakeAffine{64, 64, {w[4]}, {b[4]}});
+    p1b.try_copy_parameters(FakeAffine{64, 320, {w[5]}, {b[5]}});
+    p2a.try_copy_parameters(FakeAffine{64, 64, {w[6]}, {b[6]}});
+    p2b.try_copy_parameters(FakeAffine{64, 320, {w[7]}, {b[7]}});
+    loaded = w[0];
+  } catch (const std::exception&) {
+    return -1e9f;
+  }
+  alignas(64) uint8_t in[768];
+  memcpy(in, input768, 768);
+  alignas(64) int32_t o0[64], o1[64], ov2[32], ov3[32], op1[64], op2[64];
+  alignas(64) uint8_t a0[64] = {}, a1[64] = {}, av2[32] = {}, ap1[64] = {}, ap2[64] = {};
+  fc0.propagate(in, o0);
+  ac0.propagate(o0, a0);
+  fc1.propagate(a0, o1);
+  ac1.propagate(o1, a1);
+  v2.propagate(a1, ov2);
+  vac2.propagate(ov2, av2);
+  v3.propagate(av2, ov3);
+  p1a.propagate(a1, op1);
+  p1ac.propagate(op1, ap1);
+  p2a.propagate(a1, op2);
+  p2ac.propagate(op2, ap2);
+  constexpr float conversion = 127 * (1 << 6);
+  for (int i = 0; i < m; i++) p1[i] = p1b.propagate_single(ap1, idx1[i]) / conversion;
+  for (int i = 0; i < n; i++) p2[i] = p2b.propagate_single(ap2, idx2[i]) / conversion;
+  return ov3[0] / conversion;
+}
+}

@@ -352,3 +352,99 @@ def oracle_training_rows(orc, stream, threads=0):
     got = f(stream.ctypes.data, stream.size, threads, *[R[x].ctypes.data for x in ROW_FIELDS])
     assert got == n, f"oracle_training_rows -> {got}, expected {n}"
     return R
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# "discrete" evaluation (oracle/nn_oracle.hpp: eval_discrete; integer main net pinned to the reference's quantized layers)
+def oracle_eval_discrete_batch(net, battles, durations, results, threads=None, want_embeddings=False):
+    """NetOracle -> (values, logits[n,2,9], counts[n,2][, u8 embeddings[n, 2*side_dim]])"""
+    n = battles.shape[0]
+    v, lg, cnt = np.zeros(n, np.float32), np.zeros((n, 2, 9), np.float32), np.zeros((n, 2), np.uint8)
+    emb = np.zeros((n, 2 * net.side_dim), np.uint8) if want_embeddings else None
+    f = net.lib.oracle_net_eval_discrete_batch
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_size_t, ctypes.c_int] + [ctypes.c_void_p] * 4
+    f(net.h, battles.ctypes.data, durations.ctypes.data, results.ctypes.data, n, threads or os.cpu_count() or 1, v.ctypes.data,
+      lg.ctypes.data, cnt.ctypes.data, emb.ctypes.data if want_embeddings else None)
+    return (v, lg, cnt, emb) if want_embeddings else (v, lg, cnt)
+
+
+def oracle_main_discrete(net, q, idx1, idx2):
+    """Integer main net alone on a u8 battle embedding -> (value before the sigmoid, l1[len(idx1)], l2[len(idx2)])."""
+    f = net.lib.oracle_net_main_discrete
+    f.restype = ctypes.c_float
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 4
+    q = np.ascontiguousarray(q, np.uint8)
+    i1, i2 = np.ascontiguousarray(idx1, np.uint16), np.ascontiguousarray(idx2, np.uint16)
+    l1, l2 = np.zeros(9, np.float32), np.zeros(9, np.float32)
+    v = f(net.h, q.ctypes.data, len(i1), len(i2), i1.ctypes.data, i2.ctypes.data, l1.ctypes.data, l2.ctypes.data)
+    return np.float32(v), l1[:len(i1)].copy(), l2[:len(i2)].copy()
+
+
+def blob_layers(blob):
+    """Parameter image -> 12 (w[out, in], b[out]) pairs in file order (pk0 pk1 ac0 ac1 fc0 fc1 v2 v3 p1a p1b p2a p2b)."""
+    blob = np.ascontiguousarray(blob, np.uint8)
+    p, layers = 8, []
+    for _ in range(12):
+        i, o = (int(x) for x in np.frombuffer(blob[p:p + 8].tobytes(), np.uint32))
+        p += 8
+        b = np.frombuffer(blob[p:p + 4 * o].tobytes(), np.float32).copy()
+        p += 4 * o
+        w = np.frombuffer(blob[p:p + 4 * o * i].tobytes(), np.float32).copy().reshape(o, i)
+        p += 4 * o * i
+        layers.append((w, b))
+    return layers
+
+
+class RefQuantizedMain:
+    """The reference's own int8 layers (oracle/_ref: ref_quantized_main), default shape only; parameters prepared once."""
+
+    def __init__(self, ref, blob):
+        main = blob_layers(blob)[4:]
+
+        def pad(w, b):
+            return (np.vstack([w, np.zeros((320 - w.shape[0], w.shape[1]), np.float32)]), np.r_[b, np.zeros(320 - b.size, np.float32)])
+        wb = [main[0], main[1], main[2], main[3], main[4], pad(*main[5]), main[6], pad(*main[7])]
+        self.ws = [np.ascontiguousarray(x[0], np.float32) for x in wb]
+        self.bs = [np.ascontiguousarray(x[1], np.float32) for x in wb]
+        self.PW = (ctypes.c_void_p * 8)(*[x.ctypes.data for x in self.ws])
+        self.PB = (ctypes.c_void_p * 8)(*[x.ctypes.data for x in self.bs])
+        self.f = ref.ref_quantized_main
+        self.f.restype = ctypes.c_float
+        self.f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 4
+
+    def __call__(self, q, idx1, idx2):
+        q = np.ascontiguousarray(q, np.uint8)
+        i1, i2 = np.ascontiguousarray(idx1, np.uint16), np.ascontiguousarray(idx2, np.uint16)
+        l1, l2 = np.zeros(9, np.float32), np.zeros(9, np.float32)
+        v = self.f(self.PW, self.PB, q.ctypes.data, len(i1), len(i2), i1.ctypes.data, i2.ctypes.data, l1.ctypes.data, l2.ctypes.data)
+        return np.float32(v), l1[:len(i1)].copy(), l2[:len(i2)].copy()
+
+
+def layers_to_blob(header8, layers):
+    """Inverse of blob_layers: 8 header bytes + 12 Affine blocks {u32 in, u32 out, f32 bias[out], f32 w[out][in]}."""
+    parts = [np.frombuffer(bytes(header8), np.uint8)]
+    for w, b in layers:
+        parts.append(np.array([w.shape[1], w.shape[0]], np.uint32).view(np.uint8))
+        parts.append(np.ascontiguousarray(b, np.float32).view(np.uint8))
+        parts.append(np.ascontiguousarray(w, np.float32).reshape(-1).view(np.uint8))
+    return np.concatenate(parts)
+
+
+def dyadic_clamp_blob(rng, scale=3.0):
+    """A clamp network whose EMBEDDING nets compute exactly in any summation order: weights and biases are multiples of
+    1/256 and the real-valued input columns (stats, boosts, volatile fields) have zero weight, so every float sum is a sum
+    of exactly representable dyadic numbers. Used to show that the discrete path is bit-exact once its u8 inputs are."""
+    blob = make_net_blob(rng, activation=2, scale=scale)
+    layers = blob_layers(blob)
+    out = []
+    for i, (w, b) in enumerate(layers):
+        if i < 4:
+            w, b = np.round(w * 256) / 256, np.round(b * 256) / 256
+            if i == 0:
+                w[:, 0:5] = 0
+            if i == 2:
+                for lo, hi in ((0, 5), (20, 26), (42, 45), (229, 234)):
+                    w[:, lo:hi] = 0
+        out.append((w.astype(np.float32), b.astype(np.float32)))
+    return layers_to_blob(blob[:8].tobytes(), out)
