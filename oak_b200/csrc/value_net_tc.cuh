@@ -361,6 +361,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           const uint32_t slot = g & (RING_SLOTS - 1);
           if (g >= RING_SLOTS) umma::mbar_wait(bar_empty + 8 * slot, ((g / RING_SLOTS) - 1) & 1);
           const uint32_t bytes = (uint32_t)prog[c].bytes16 << 4;
+#ifdef OAKB200_TC_NO_STREAM  // timing experiment only: the ring is never filled, results are garbage
+          umma::mbar_arrive(bar_full + 8 * slot);
+          continue;
+#endif
           umma::mbar_expect_tx(bar_full + 8 * slot, bytes);
           const uint8_t* src = P.wpack + ((size_t)prog[c].gofs16 << 4);
           const uint32_t dst = smem + OFF_RING + slot * RING_SLOT;
@@ -394,13 +398,23 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           const uint32_t b_hi = smem + OFF_RING + slot * RING_SLOT, b_lo = b_hi + ch.ksteps * kstep_b;
           const uint32_t a_hi = smem + ((uint32_t)ch.a_off16 << 4), a_lo = smem + ((uint32_t)ch.alo_off16 << 4);
           const uint32_t d = tmem + ch.dcol;
-          for (uint32_t i = 0; i < ch.ksteps; i++) {
-            const uint64_t da = umma::smem_desc(a_hi + i * 2 * CORE, CORE, 128);
-            const uint64_t dbh = umma::smem_desc(b_hi + i * kstep_b, N * 16, 128);
-            const uint64_t dbl = umma::smem_desc(b_lo + i * kstep_b, N * 16, 128);
-            umma::mma_bf16(d, da, dbh, idesc, ((ch.flags & F_OVERWRITE) && i == 0) ? 0u : 1u);
+          // One thread issues every MMA of the CTA, so its instruction stream is the tile's critical path: descriptors
+          // are built once per chunk and advanced by adding to their 14-bit address field (operands live below 256 KB,
+          // so the field never carries into its neighbours).
+          uint64_t da = umma::smem_desc(a_hi, CORE, 128), dal = umma::smem_desc(a_lo, CORE, 128);
+          uint64_t dbh = umma::smem_desc(b_hi, N * 16, 128), dbl = umma::smem_desc(b_lo, N * 16, 128);
+          const uint64_t a_step = (2 * CORE) >> 4, b_step = kstep_b >> 4;
+          uint32_t acc = (ch.flags & F_OVERWRITE) ? 0u : 1u;
+          const uint32_t lo_steps = ch.lo_steps, ksteps = ch.ksteps;
+          for (uint32_t i = 0; i < ksteps; i++) {
+            umma::mma_bf16(d, da, dbh, idesc, acc);
             umma::mma_bf16(d, da, dbl, idesc, 1u);
-            if (i < ch.lo_steps) umma::mma_bf16(d, umma::smem_desc(a_lo + i * 2 * CORE, CORE, 128), dbh, idesc, 1u);
+            if (i < lo_steps) umma::mma_bf16(d, dal, dbh, idesc, 1u);
+            acc = 1u;
+            da += a_step;
+            dal += a_step;
+            dbh += b_step;
+            dbl += b_step;
           }
           if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
           else umma::mma_commit(bar_empty + 8 * slot);
