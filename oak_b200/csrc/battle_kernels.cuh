@@ -491,6 +491,11 @@ replay_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restrict__ g
       }
     }
     if (__all_sync(0xFFFFFFFFu, !have)) break;
+    // a stored update must lie inside its game's bytes (a corrupt header must not walk the reads out of the stream)
+    if (have && (p + 11 > end || p + 11 + 4 * ((stream[p] & 15u) + (stream[p] >> 4) + 2) > end)) {
+      atomicMin(first_bad, g);
+      have = false;
+    }
     if (have) {
       if (only < 0 || u == (uint32_t)only) {
         e.end();
@@ -581,6 +586,10 @@ replay_encode_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restr
     if (__all_sync(0xFFFFFFFFu, !have)) break;
     bool emit = false;
     uint32_t my_row = 0;
+    if (have && (p + 11 > end || p + 11 + 4 * ((stream[p] & 15u) + (stream[p] >> 4) + 2) > end)) {
+      atomicMin(first_bad, g);
+      have = false;
+    }
     if (have) {
       if (only < 0 || u == (uint32_t)only) {
         e.end();

@@ -100,6 +100,16 @@ def test_partial_outputs_and_bad_games(orc):
     assert bad == 1
     with pytest.raises(ValueError):
         EncodedBattleFrames.from_bytes(stream.tobytes(), engine=eng)
+    # a corrupt update header that claims more bytes than its game has: reported, and nothing is read past the game
+    from oak_ref import parse_battle_data
+    stream = G["stream"].copy()
+    games = parse_battle_data(stream)
+    last = games[-1]["updates"][-1]
+    tail = 11 + 4 * (last["m"] + last["n"])
+    assert last["m"] + last["n"] < 18
+    stream[stream.size - tail] = 0x88  # m = n = 9
+    g, r, bad = eng.rows_build_host(stream, dict(hp=hp), n)
+    assert bad == len(games) - 1
     # truncated stream / empty stream
     with pytest.raises(OakB200Error):
         eng.rows_build_host(G["stream"][:-5], dict(hp=hp), n)
