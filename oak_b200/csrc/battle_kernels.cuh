@@ -637,6 +637,157 @@ replay_encode_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restr
   }
 }
 
+// replay_split_kernel: the training-row build as ONE launch of co-resident CTAs with two roles. CTAs [0, n_producers) run
+// the replay loop of replay_kernel and, after staging a row, append its index to a global work queue; every other CTA's
+// warps pop queue tickets and encode one row each (rows::encode_row) as soon as its entry appears. The two halves have
+// complementary limits — the replay is latency-bound on the longest game and leaves the SM's issue slots and all of
+// DRAM idle, the encode is a DRAM-write stream — so running them side by side costs about the larger of the two instead
+// of their sum. Producers never wait; consumers wait only on producers, and every CTA of the grid is resident
+// (cooperative launch), so the wait ends; a consumer that polls for ~a minute gives up and flags the build.
+//   queue[t] = 0 (not produced yet), row + 1, or 0xFFFFFFFF (a ticket without a row: a game with no updates in
+//   only_update mode); control[0] game ticket, [1] first bad game, [2] queue tail, [3] queue head, [4] consumer gave up
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 3)
+replay_split_kernel(const uint8_t* __restrict__ stream, const uint64_t* __restrict__ game_off, const uint32_t* __restrict__ row_base,
+                    const int32_t* __restrict__ only_update, uint32_t n_games, uint32_t n_rows, uint32_t n_producers,
+                    uint32_t* __restrict__ control, uint32_t* queue, uint8_t* rows, oakb200_training_rows out) {
+  extern __shared__ uint32_t tile[];
+  const int lane = threadIdx.x & 31;
+  uint32_t* ticket = control;
+  uint32_t* first_bad = control + 1;
+  uint32_t* q_tail = control + 2;
+  uint32_t* q_head = control + 3;
+
+  if (blockIdx.x >= n_producers) {
+    // ===== consumer warps =====
+    uint8_t* st = reinterpret_cast<uint8_t*>(tile) + (threadIdx.x >> 5) * ROW_STATE_BYTES;
+    for (;;) {
+      uint32_t t = 0, token = 0;
+      if (lane == 0) {
+        t = atomicAdd(q_head, 1u);
+        if (t < n_rows) {
+          const volatile uint32_t* slot = queue + t;
+          uint32_t polls = 0;
+          while ((token = *slot) == 0) {
+            __nanosleep(200);
+            if (++polls > (1u << 28)) {  // never in a correct build; do not hang the device if the producers failed
+              atomicExch(control + 4, 1u);
+              token = 0xFFFFFFFFu;
+              break;
+            }
+          }
+          __threadfence();  // the staged state was written before the queue entry
+        }
+      }
+      t = __shfl_sync(0xFFFFFFFFu, t, 0);
+      if (t >= n_rows) break;
+      token = __shfl_sync(0xFFFFFFFFu, token, 0);
+      if (token == 0xFFFFFFFFu) continue;
+      const uint32_t r = token - 1;
+      if (lane < ROW_STATE_BYTES / 16)
+        reinterpret_cast<uint4*>(st)[lane] = __ldcg(reinterpret_cast<const uint4*>(rows + (size_t)r * ROW_STATE_BYTES) + lane);
+      __syncwarp();
+      rows::encode_row(st, stream, out, r, lane);
+      __syncwarp();
+    }
+    return;
+  }
+
+  // ===== producer threads: replay_kernel's loop + publication =====
+  uint32_t* col = tile + threadIdx.x;
+  typedef Engine<BLOCK, false, true> E;
+  E e;
+  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+  uint32_t g = 0, u = 0, n_updates = 0, result = 0, stored = 0, base = 0;
+  int32_t only = -1;
+  uint64_t p = 0, end = 0;
+  bool have = false, exhausted = false;
+  for (;;) {
+    uint32_t publish = 0;  // 0 nothing, row + 1, or 0xFFFFFFFF
+    if (!have && !exhausted) {
+      g = atomicAdd(ticket, 1u);
+      if (g < n_games) {
+        const uint8_t* game = stream + game_off[g];
+        const uint32_t n_bytes = game[0] | (game[1] << 8) | (game[2] << 16) | ((uint32_t)game[3] << 24);
+        n_updates = game[4] | (game[5] << 8);
+#pragma unroll 4
+        for (int w = 0; w < BATTLE_WORDS; w++) {
+          const uint8_t* b = game + 6 + 4 * w;
+          col[w * BLOCK] = b[0] | (b[1] << 8) | (b[2] << 16) | ((uint32_t)b[3] << 24);
+        }
+        e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
+        stored = game[390];
+        result = RESULT_DEFAULT;
+        p = game_off[g] + 391;
+        end = game_off[g] + n_bytes;
+        base = row_base[g];
+        only = only_update ? max(only_update[g], 0) : -1;
+        if (only >= 0 && n_updates != 0) {
+          if ((uint32_t)only >= n_updates) only = (int32_t)n_updates - 1;
+          n_updates = (uint32_t)only + 1;
+        }
+        u = 0;
+        have = n_updates != 0;
+        if (!have && only_update) publish = 0xFFFFFFFFu;  // this game's ticket carries no row
+      } else {
+        exhausted = true;
+      }
+    }
+    if (__all_sync(0xFFFFFFFFu, !have && publish == 0)) break;
+    if (have && (p + 11 > end || p + 11 + 4 * ((stream[p] & 15u) + (stream[p] >> 4) + 2) > end)) {
+      atomicMin(first_bad, g);
+      // the rows this game still owes are published as empty tickets so that the consumers' count comes out
+      const uint32_t owed = only < 0 ? n_updates - u : 1u;
+      const uint32_t at = atomicAdd(q_tail, owed);
+      for (uint32_t k = 0; k < owed; k++) queue[at + k] = 0xFFFFFFFFu;
+      have = false;
+    }
+    if (have) {
+      if (only < 0 || u == (uint32_t)only) {
+        e.end();
+        const uint32_t my_row = only < 0 ? base + u : base;
+        publish = my_row + 1;
+        uint8_t* row = rows + (size_t)my_row * ROW_STATE_BYTES;
+        store_column<BLOCK>(col, row);
+        int m, n;
+        const uint64_t l1 = e.choices(0, (result >> 4) & 3, &m);
+        const uint64_t l2 = e.choices(1, (result >> 6) & 3, &n);
+        uint32_t cw[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 9; i++) {
+          if (i < m) cw[i >> 2] |= E::choice_at(l1, i) << (8 * (i & 3));
+          if (i < n) cw[(9 + i) >> 2] |= E::choice_at(l2, i) << (8 * ((9 + i) & 3));
+        }
+        uint4* tail = reinterpret_cast<uint4*>(row + 384);
+        tail[0] = make_uint4(e.dur[0], e.dur[1], result | (stored << 8) | ((uint32_t)m << 16) | ((uint32_t)n << 24), (uint32_t)p);
+        tail[1] = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+        tail[2] = make_uint4(cw[4], 0, 0, 0);
+      }
+    }
+    // ---- publish: one queue reservation per warp, entries written after the staged states are visible device-wide
+    {
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, publish != 0);
+      if (mask) {
+        __threadfence();
+        uint32_t at = 0;
+        if (lane == (__ffs(mask) - 1)) at = atomicAdd(q_tail, (uint32_t)__popc(mask));
+        at = __shfl_sync(0xFFFFFFFFu, at, __ffs(mask) - 1);
+        if (publish != 0) queue[at + __popc(mask & ((1u << lane) - 1u))] = publish;
+      }
+    }
+    if (have) {
+      const uint32_t hdr = stream[p], c1 = stream[p + 1], c2 = stream[p + 2];
+      e.act[0] = e.act[1] = 0;
+      result = e.update(c1, c2);
+      p += 11 + 4 * ((hdr & 15u) + (hdr >> 4) + 2);
+      u++;
+      if (u == n_updates) {
+        if (only < 0 && (result != stored || p != end)) atomicMin(first_bad, g);
+        have = false;
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // MCTS::randomize_hidden_variables (reference cpp/include/search/durations.h:25-97). Touches a few
 // bytes per battle, so it works on the AoS records in place. Every draw uses the same battle.rng.

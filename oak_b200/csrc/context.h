@@ -58,6 +58,9 @@ cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const
 cudaError_t oakb200_launch_replay_encode(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
                                          const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows,
                                          const oakb200_training_rows* out);
+cudaError_t oakb200_launch_replay_split(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                        const int32_t* only_update, uint32_t n_games, uint32_t n_rows, uint32_t* control, uint32_t* queue,
+                                        uint8_t* rows, const oakb200_training_rows* out);
 static const int OAKB200_ROW_STATE_BYTES = 432;  // = ROW_STATE_BYTES of battle_kernels.cuh
 
 namespace {

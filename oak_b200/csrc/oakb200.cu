@@ -147,6 +147,35 @@ cudaError_t oakb200_launch_replay_encode(oakb200_ctx* ctx, const uint8_t* stream
   return cudaGetLastError();
 }
 
+// one cooperative launch, two roles (replay_split_kernel): `control` = 5 zeroed words except [1] = 0xFFFFFFFF, `queue` =
+// n_rows zeroed words
+cudaError_t oakb200_launch_replay_split(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
+                                        const int32_t* only_update, uint32_t n_games, uint32_t n_rows, uint32_t* control, uint32_t* queue,
+                                        uint8_t* rows, const oakb200_training_rows* out) {
+  auto k = replay_split_kernel<BLOCK>;
+  cudaError_t e = allow_smem(k);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, TILE_BYTES);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 2) return cudaErrorLaunchOutOfResources;  // needs a producer and a consumer CTA per SM
+  const unsigned grid = (unsigned)(ctx->sm_count * per_sm);  // every CTA resident: consumers may wait on producers
+  unsigned producers = grid_for(n_games);
+  int prod_per_sm = 1;  // producer CTAs per SM (the first CTAs placed); OAKB200_ROWS_PRODUCERS overrides, < per_sm
+  if (const char* pp = getenv("OAKB200_ROWS_PRODUCERS")) prod_per_sm = atoi(pp);
+  if (prod_per_sm < 1) prod_per_sm = 1;
+  if (prod_per_sm > per_sm - 1) prod_per_sm = per_sm - 1;
+  if (producers > (unsigned)(ctx->sm_count * prod_per_sm)) producers = (unsigned)(ctx->sm_count * prod_per_sm);
+  uint32_t n_prod = producers;
+  oakb200_training_rows o = *out;
+  void* args[] = {(void*)&stream, (void*)&game_off, (void*)&row_base, (void*)&only_update, (void*)&n_games, (void*)&n_rows,
+                  (void*)&n_prod, (void*)&control, (void*)&queue, (void*)&rows, (void*)&o};
+  e = cudaLaunchCooperativeKernel((const void*)k, dim3(grid), dim3(BLOCK), args, TILE_BYTES, ctx->stream);
+  if (e != cudaSuccess) return e;
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
 extern "C" {
 
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {

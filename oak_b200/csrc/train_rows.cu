@@ -31,6 +31,7 @@ using namespace oakb200::rows;
 
 namespace {
 
+const int OAKB200_ROWS_DEFAULT_MODE = 0;
 const int ENC_WARPS = 8;
 static_assert(STATE_BYTES == OAKB200_ROW_STATE_BYTES, "staged row layout");
 
@@ -60,7 +61,8 @@ rows_encode_kernel(const uint8_t* __restrict__ states, const uint8_t* __restrict
 struct oakb200_rows {
   uint8_t* states = nullptr;  // [rows_cap][432]
   size_t rows_cap = 0;
-  uint32_t* words = nullptr;  // [0] ticket, [1] first bad game
+  uint32_t* words = nullptr;  // [0] ticket, [1] first bad game, [2] queue tail, [3] queue head, [4] a consumer gave up
+  uint32_t* queue = nullptr;  // [rows_cap] work queue of the one-launch form
   // host entry point only
   uint8_t* stream = nullptr;
   size_t stream_cap = 0;
@@ -77,6 +79,7 @@ void oakb200_rows_release(oakb200_ctx* ctx) {
   if (!r) return;
   cudaFree(r->states);
   cudaFree(r->words);
+  cudaFree(r->queue);
   cudaFree(r->stream);
   cudaFree(r->game_off);
   cudaFree(r->row_base);
@@ -93,14 +96,17 @@ int rows_scratch(oakb200_ctx* ctx, size_t n_rows) {
     if (!ctx->rows) return fail(ctx, OAKB200_ECAPACITY, "rows: out of host memory");
   }
   oakb200_rows* r = ctx->rows;
-  if (!r->words) CU(ctx, cudaMalloc(&r->words, 2 * sizeof(uint32_t)));
+  if (!r->words) CU(ctx, cudaMalloc(&r->words, 8 * sizeof(uint32_t)));
   if (n_rows > r->rows_cap) {
     // the previous build may still be reading the old buffer
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     cudaFree(r->states);
+    cudaFree(r->queue);
     r->states = nullptr;
+    r->queue = nullptr;
     r->rows_cap = 0;
     CU(ctx, cudaMalloc(&r->states, n_rows * (size_t)OAKB200_ROW_STATE_BYTES));
+    CU(ctx, cudaMalloc(&r->queue, n_rows * sizeof(uint32_t)));
     r->rows_cap = n_rows;
   }
   return OAKB200_OK;
@@ -147,18 +153,24 @@ int oakb200_rows_build_device(oakb200_ctx* ctx, const uint8_t* stream, uint64_t 
   CU(ctx, cudaSetDevice(ctx->device));
   if (int rc = rows_scratch(ctx, n_rows ? n_rows : 1)) return rc;
   oakb200_rows* r = ctx->rows;
-  const uint32_t init[2] = {0u, 0xFFFFFFFFu};
+  const uint32_t init[8] = {0u, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u, 0u};
   CU(ctx, cudaMemcpyAsync(r->words, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
   if (n_games == 0 || n_rows == 0) return OAKB200_OK;
-  // OAKB200_ROWS_FUSED=1 selects the one-launch form (replay_encode_kernel: each warp encodes the rows its lanes just
-  // staged). Measured on B200 it is slower — 33.1 ms against 17.0 ms for 3.98 M rows (profiles/r1k_training_rows.txt): a
-  // warp's 32 rows are encoded one after the other, ~3 us of dependent latency each, with only 12 warps per SM to hide it
-  // — so the two-kernel form stays the default.
-  static const bool fused = [] {
-    const char* f = getenv("OAKB200_ROWS_FUSED");
-    return f && f[0] == '1';
+  // Three forms of the same build, all bit-exact (OAKB200_ROWS_MODE): 0 = replay_kernel then rows_encode_kernel; 1 = one
+  // launch in which every warp alternates replaying and encoding its own rows (replay_encode_kernel: measured slower,
+  // 33.1 ms against 17.0 ms for 3.98 M rows); 2 = one cooperative launch of producer CTAs (replay) and consumer CTAs
+  // (encode) joined by a work queue (replay_split_kernel). Numbers in profiles/r1k_training_rows.txt.
+  static const int mode = [] {
+    const char* f = getenv("OAKB200_ROWS_MODE");
+    return f ? atoi(f) : OAKB200_ROWS_DEFAULT_MODE;
   }();
-  if (fused) {
+  if (mode == 2) {
+    CU(ctx, cudaMemsetAsync(r->queue, 0, n_rows * sizeof(uint32_t), ctx->stream));
+    CU(ctx, oakb200_launch_replay_split(ctx, stream, game_off, row_base, only_update, (uint32_t)n_games, (uint32_t)n_rows, r->words, r->queue,
+                                        r->states, out));
+    return OAKB200_OK;
+  }
+  if (mode == 1) {
     CU(ctx, oakb200_launch_replay_encode(ctx, stream, game_off, row_base, only_update, (uint32_t)n_games, r->words, r->states, out));
     return OAKB200_OK;
   }
@@ -183,9 +195,10 @@ int oakb200_rows_status(oakb200_ctx* ctx, int64_t* first_bad_game) {
   if (!ctx) return OAKB200_EINVAL;
   if (!ctx->rows || !ctx->rows->words) return fail(ctx, OAKB200_EINVAL, "rows_status: nothing was built");
   CU(ctx, cudaSetDevice(ctx->device));
-  uint32_t w[2];
+  uint32_t w[8];
   CU(ctx, cudaMemcpyAsync(w, ctx->rows->words, sizeof(w), cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
+  if (w[4]) return fail(ctx, OAKB200_ECUDA, "rows: an encode warp gave up waiting for its row (internal error)");
   if (first_bad_game) *first_bad_game = w[1] == 0xFFFFFFFFu ? -1 : (int64_t)w[1];
   return OAKB200_OK;
 }
