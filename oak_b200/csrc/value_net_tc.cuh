@@ -406,7 +406,19 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           const uint64_t a_step = (2 * CORE) >> 4, b_step = kstep_b >> 4;
           uint32_t acc = (ch.flags & F_OVERWRITE) ? 0u : 1u;
           const uint32_t lo_steps = ch.lo_steps, ksteps = ch.ksteps;
+#ifdef OAKB200_TC_NO_MMA  // timing experiment only: no tensor-core work is issued, results are garbage
+          if (ksteps) { da = dal = dbh = dbl = 0; }
+          for (uint32_t i = 0; i < 0; i++) {
+#elif defined(OAKB200_TC_HALF_MMA)  // timing experiment only: the hi x hi product alone
           for (uint32_t i = 0; i < ksteps; i++) {
+            umma::mma_bf16(d, da, dbh, idesc, acc);
+            acc = 1u;
+            da += a_step;
+            dbh += b_step;
+            continue;
+#else
+          for (uint32_t i = 0; i < ksteps; i++) {
+#endif
             umma::mma_bf16(d, da, dbh, idesc, acc);
             umma::mma_bf16(d, da, dbl, idesc, 1u);
             if (i < lo_steps) umma::mma_bf16(d, dal, dbh, idesc, 1u);
@@ -485,7 +497,9 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             publish();
             wait_d();
           }
+#ifndef OAKB200_TC_NO_BUILD  // timing experiment only
           if (grp == 0) build_pokemon(smem, r, m, pk, sleep, alive);
+#endif
           wait_t();
           publish();
           wait_d();
