@@ -303,8 +303,7 @@ def main():
     pec = torch.empty((EV, 2), dtype=torch.uint8).pin_memory()
 
     def eval_e2e():
-        rc = lib.oakb200_upload(h, EV, peb.data_ptr(), ped.data_ptr(), per_.data_ptr())
-        rc |= lib.oakb200_eval(h, pev.data_ptr(), pel.data_ptr(), pec.data_ptr())
+        rc = lib.oakb200_eval_host(h, EV, peb.data_ptr(), ped.data_ptr(), per_.data_ptr(), pev.data_ptr(), pel.data_ptr(), pec.data_ptr())
         if rc:
             raise RuntimeError(lib.oakb200_last_error(h).decode())
     eval_e2e()
@@ -503,7 +502,7 @@ def main():
                           "kernel": "eval_tc_kernel (tcgen05.mma kind::f16 on split-bf16 operand pairs, fp32 accumulate in TMEM; "
                                     "one-hot first layers as dense tiles)",
                           "e2e_evals_per_s": world * EV / eval_e2e_s,
-                          "e2e_note": "pinned host records in (393 B/eval H2D), value + logits + counts out (78 B/eval D2H), wall clock around oakb200_upload + oakb200_eval",
+                          "e2e_note": "pinned host records in (393 B/eval H2D), value + logits + counts out (78 B/eval D2H), wall clock around oakb200_eval_host (chunked upload / kernel / download on three streams)",
                           "fp32_cuda_core_kernel_evals_per_s": world * EV / (eval_ms_mode[1] * 1e-3),
                           "roofline": {"bound": "tensor", "achieved": F_EVAL_TC * EV / (eval_ms * 1e-3) / 1e12,
                                        "peak": pk["bf16_tflops"], "unit": "TFLOP/s",

@@ -141,6 +141,11 @@ int oakb200_eval_set_mode(oakb200_ctx* ctx, int mode);
 int oakb200_eval(oakb200_ctx* ctx, float* value_out, float* logits_out, uint8_t* counts_out);
 int oakb200_eval_device(oakb200_ctx* ctx, size_t n, const void* battles, const void* durations, const void* results,
                         void* value_out, void* logits_out, void* counts_out);
+/* Evaluation of a HOST batch with the PCIe transfers hidden behind the kernels: chunked upload, evaluation and download
+ * on three streams. Same outputs as oakb200_upload + oakb200_eval; durations / results may be NULL as in oakb200_upload.
+ * Returns when the outputs are in the host arrays. */
+int oakb200_eval_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                      float* value_out, float* logits_out, uint8_t* counts_out);
 
 /* Rebuild, in place, every battle of the batch whose result byte says it has ended (PKMN::battle + update(0,0) as
  * oakb200_build_battles; teams[n][2][6][5] and seeds[n] are DEVICE arrays, only the entries of ended slots are read).

@@ -42,6 +42,10 @@ struct oakb200_ctx {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t pipe_start = nullptr;
   uint32_t* pipe_marks = nullptr;  // pinned: records available after each chunk
+  // transfer/compute pipeline of oakb200_eval_host
+  bool eval_pipe_ready = false;
+  cudaStream_t eval_h2d = nullptr, eval_d2h = nullptr;
+  cudaEvent_t eval_ev[130] = {};  // [0] start, then {uploaded, evaluated} per chunk
   std::string error;
 };
 

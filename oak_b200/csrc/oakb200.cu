@@ -229,6 +229,12 @@ void oakb200_destroy(oakb200_ctx* ctx) {
   oakb200_rows_release(ctx);
   for (void* b : bufs)
     if (b) cudaFree(b);
+  if (ctx->eval_pipe_ready) {
+    cudaStreamDestroy(ctx->eval_h2d);
+    cudaStreamDestroy(ctx->eval_d2h);
+    for (cudaEvent_t ev : ctx->eval_ev)
+      if (ev) cudaEventDestroy(ev);
+  }
   if (ctx->pipe_ready) {
     cudaStreamDestroy(ctx->copy_stream);
     cudaEventDestroy(ctx->pipe_start);

@@ -758,3 +758,57 @@ extern "C" int oakb200_eval(oakb200_ctx* ctx, float* value_out, float* logits_ou
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return OAKB200_OK;
 }
+
+
+// Leaf evaluation of a HOST batch with the transfers hidden: the batch is cut into chunks, every chunk's upload is queued
+// on one copy stream, its evaluation on the context's stream behind that upload, and its download on a second copy
+// stream behind the evaluation, so the two copy engines and the SMs work on three different chunks at a time. Same
+// results as oakb200_upload + oakb200_eval (the kernels see the same records); the resident batch of the context is
+// replaced by this one.
+extern "C" int oakb200_eval_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                                 float* value_out, float* logits_out, uint8_t* counts_out) {
+  if (!ctx || !battles || !value_out || !logits_out || !counts_out) return fail(ctx, OAKB200_EINVAL, "eval_host: null argument");
+  if (n > ctx->n_max) return fail(ctx, OAKB200_ECAPACITY, "eval_host: n exceeds n_max");
+  if (!ctx->net) return fail(ctx, OAKB200_EINVAL, "eval: no network loaded (oakb200_net_load)");
+  ctx->n = n;
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  const int MAX_CHUNKS = 64;
+  if (!ctx->eval_pipe_ready) {
+    CU(ctx, cudaStreamCreateWithFlags(&ctx->eval_h2d, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&ctx->eval_d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < 2 * MAX_CHUNKS + 1; i++) CU(ctx, cudaEventCreateWithFlags(&ctx->eval_ev[i], cudaEventDisableTiming));
+    ctx->eval_pipe_ready = true;
+  }
+  size_t chunk = 148 * 128;  // one tile per SM of the tensor-core kernel
+  if (const char* c = getenv("OAKB200_EVAL_CHUNK")) chunk = (size_t)atol(c) > 0 ? (size_t)atol(c) : chunk;  // tuning knob
+  if ((n + chunk - 1) / chunk > (size_t)MAX_CHUNKS) chunk = (n + MAX_CHUNKS - 1) / MAX_CHUNKS;
+  const int chunks = (int)((n + chunk - 1) / chunk);
+  if (!durations) CU(ctx, cudaMemsetAsync(ctx->durations, 0, n * 8, ctx->stream));
+  if (!results) CU(ctx, cudaMemsetAsync(ctx->results, 0x50, n, ctx->stream));
+  CU(ctx, cudaEventRecord(ctx->eval_ev[0], ctx->stream));  // everything queued so far on the context's stream comes first
+  CU(ctx, cudaStreamWaitEvent(ctx->eval_h2d, ctx->eval_ev[0], 0));
+  CU(ctx, cudaStreamWaitEvent(ctx->eval_d2h, ctx->eval_ev[0], 0));
+  for (int k = 0; k < chunks; k++) {
+    const size_t at = (size_t)k * chunk, m = n - at < chunk ? n - at : chunk;
+    CU(ctx, cudaMemcpyAsync(ctx->battles + at * 384, battles + at * 384, m * 384, cudaMemcpyHostToDevice, ctx->eval_h2d));
+    if (durations) CU(ctx, cudaMemcpyAsync(ctx->durations + at * 8, durations + at * 8, m * 8, cudaMemcpyHostToDevice, ctx->eval_h2d));
+    if (results) CU(ctx, cudaMemcpyAsync(ctx->results + at, results + at, m, cudaMemcpyHostToDevice, ctx->eval_h2d));
+    CU(ctx, cudaEventRecord(ctx->eval_ev[1 + 2 * k], ctx->eval_h2d));
+  }
+  for (int k = 0; k < chunks; k++) {
+    const size_t at = (size_t)k * chunk, m = n - at < chunk ? n - at : chunk;
+    CU(ctx, cudaStreamWaitEvent(ctx->stream, ctx->eval_ev[1 + 2 * k], 0));
+    const int rc = oakb200_eval_device(ctx, m, ctx->battles + at * 384, ctx->durations + at * 8, ctx->results + at, ctx->eval_values + at,
+                                       ctx->eval_logits + at * 18, ctx->eval_counts + at * 2);
+    if (rc) return rc;
+    CU(ctx, cudaEventRecord(ctx->eval_ev[2 + 2 * k], ctx->stream));
+    CU(ctx, cudaStreamWaitEvent(ctx->eval_d2h, ctx->eval_ev[2 + 2 * k], 0));
+    CU(ctx, cudaMemcpyAsync(value_out + at, ctx->eval_values + at, m * 4, cudaMemcpyDeviceToHost, ctx->eval_d2h));
+    CU(ctx, cudaMemcpyAsync(logits_out + at * 18, ctx->eval_logits + at * 18, m * 18 * 4, cudaMemcpyDeviceToHost, ctx->eval_d2h));
+    CU(ctx, cudaMemcpyAsync(counts_out + at * 2, ctx->eval_counts + at * 2, m * 2, cudaMemcpyDeviceToHost, ctx->eval_d2h));
+  }
+  CU(ctx, cudaStreamSynchronize(ctx->eval_d2h));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}

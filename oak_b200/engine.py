@@ -77,6 +77,7 @@ def load_library():
                                          ctypes.POINTER(ctypes.c_int64)]),
         "oakb200_eval": (i32, [vp, vp, vp, vp]),
         "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
+        "oakb200_eval_host": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -242,6 +243,17 @@ class BattleEngine:
         cnt = np.empty((n, 2), np.uint8)
         self._check(self.lib.oakb200_eval(self._h, _ptr(v), _ptr(lg), _ptr(cnt)))
         return v, lg, cnt
+
+    def evaluate_host(self, battles, durations, results, value_out=None, logits_out=None, counts_out=None):
+        """Host records in, value / logits / counts out, transfers pipelined behind the kernels (pinned arrays are fastest)."""
+        n = battles.shape[0]
+        value_out = np.empty(n, np.float32) if value_out is None else value_out
+        logits_out = np.empty((n, 2, 9), np.float32) if logits_out is None else logits_out
+        counts_out = np.empty((n, 2), np.uint8) if counts_out is None else counts_out
+        self._check(self.lib.oakb200_eval_host(self._h, n, _ptr(battles), _ptr(durations), _ptr(results), _ptr(value_out),
+                                               _ptr(logits_out), _ptr(counts_out)))
+        self.n = n
+        return value_out, logits_out, counts_out
 
     def evaluate_device(self, battles, durations, results, value_out, logits_out, counts_out):
         self._check(self.lib.oakb200_eval_device(self._h, battles.shape[0], _ptr(battles), _ptr(durations), _ptr(results),

@@ -136,3 +136,22 @@ def test_eval_rejects_bad_parameter_files(eng):
         eng.load_network(np.concatenate([blob, np.zeros(3, np.uint8)]))
     with pytest.raises(oak_b200.OakB200Error):
         eng.load_network(blob[:1000])
+
+
+def test_pipelined_host_evaluation_matches_upload_then_eval(orc, eng):
+    """oakb200_eval_host (chunked upload / kernel / download on three streams) returns what oakb200_upload + oakb200_eval do,
+    for a batch that is not a multiple of the chunk, with and without explicit durations / results."""
+    import torch
+    n = 50_000
+    b, d, r = oracle_sample_batch(orc, 300_000, n)
+    eng.load_network(make_net_blob(np.random.default_rng(21)))
+    for mode in (2, 1):
+        eng.set_eval_mode(mode)
+        eng.upload(b, d, r)
+        v0, l0, c0 = eng.evaluate()
+        pb, pd, pr = (torch.from_numpy(x).pin_memory() for x in (b, d, r))
+        v1, l1, c1 = eng.evaluate_host(pb, pd, pr)
+        assert np.array_equal(v0, v1) and np.array_equal(l0, l1) and np.array_equal(c0, c1)
+        v2, l2, c2 = eng.evaluate_host(b[:777], None, None)  # pageable memory, defaults
+        assert np.array_equal(v2, v0[:777]) and np.array_equal(l2, l0[:777]) and np.array_equal(c2, c0[:777])
+    eng.set_eval_mode(0)
