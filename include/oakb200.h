@@ -214,6 +214,10 @@ int oakb200_search_run(oakb200_search* search, uint32_t iterations, float ucb_c,
  * iterations[n], empirical_value[n] f64, empirical[n][2][9] f64 (process_output, mcts.h:623-661), nodes[n]. Any may be NULL. */
 int oakb200_search_output(oakb200_search* search, uint8_t* k, uint8_t* choices, uint32_t* visit_matrix, double* value_matrix,
                           uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes);
+/* Leaf evaluation of the search: 0 = MonteCarlo playout (default), 1 = the loaded network's value (value_inference at a new
+ * leaf, mcts.h:409-424, with the chance durations tracked down the path; a battle that ended on the way scores 1 / 0 /
+ * 0.5). Mode 1 needs oakb200_net_load[_discrete] first; all leaves of a wave are one batched evaluation. */
+int oakb200_search_set_leaf(oakb200_search* search, int mode);
 int oakb200_search_stats(oakb200_search* search, uint64_t* waves, uint64_t* levels);
 /* Zero-sum matrix game, the job of LRSNash::solve_fast (mcts.h:643-649; pyoak solve_matrix, cpp/src/pyoak.cc:394-425):
  * the row player receives payoff[i * cols + j] / denom, the column player 1 - that; rows, cols <= 9. -> both players'

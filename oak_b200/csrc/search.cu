@@ -189,6 +189,10 @@ struct oakb200_search {
   uint8_t *d_b = nullptr, *d_d = nullptr, *d_r = nullptr, *d_idx1 = nullptr, *d_idx2 = nullptr, *d_rolls = nullptr, *d_act = nullptr,
           *d_cnt = nullptr, *d_score = nullptr;
   uint64_t *d_rng = nullptr, *d_pseed = nullptr;
+  // network leaves
+  int leaf_mode = 0;  // 0 MonteCarlo playout, 1 network value
+  float *d_value = nullptr, *d_logits = nullptr, *h_value = nullptr;
+  uint8_t* d_ecnt = nullptr;
   // pinned host mirrors
   uint8_t *h_idx1 = nullptr, *h_idx2 = nullptr, *h_rolls = nullptr, *h_res = nullptr, *h_act = nullptr, *h_cnt = nullptr, *h_score = nullptr;
   uint64_t *h_rng = nullptr, *h_pseed = nullptr;
@@ -203,10 +207,10 @@ void search_free(oakb200_search* s) {
   if (!s) return;
   if (s->ctx) cudaSetDevice(s->ctx->device);
   void* dev[] = {s->d_root_b, s->d_root_d, s->d_root_r, s->d_b, s->d_d, s->d_r, s->d_idx1, s->d_idx2, s->d_rolls, s->d_act, s->d_cnt,
-                 s->d_score, s->d_rng, s->d_pseed};
+                 s->d_score, s->d_rng, s->d_pseed, s->d_value, s->d_logits, s->d_ecnt};
   for (void* p : dev)
     if (p) cudaFree(p);
-  void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed};
+  void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed, s->h_value};
   for (void* p : host)
     if (p) cudaFreeHost(p);
   delete s->pool;
@@ -467,7 +471,19 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
         G.phase = 2;
         return;
       }
-      // ---- every descent of the group has reached a leaf: playouts (a finished battle returns its score at once)
+      // ---- every descent of the group has reached a leaf
+      if (s->leaf_mode == 1) {
+        // the network's value of every leaf (mcts.h:409-424: UCB is not a contextual bandit, so value_inference) with
+        // the durations tracked down the path; a finished battle's score replaces it at back-propagation
+        const int rc = oakb200_eval_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_value + b0, s->d_logits + b0 * 18,
+                                           s->d_ecnt + b0 * 2);
+        if (rc) { rc_out = rc; return; }
+        if (fail_cuda(cudaMemcpyAsync(s->h_value + b0, s->d_value + b0, nb * 4, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
+        if (fail_cuda(cudaMemcpyAsync(s->h_res + b0, s->d_r + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
+        G.phase = 3;
+        return;
+      }
+      // playouts (a finished battle returns its score at once)
       const int rc = oakb200_rollout_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_pseed + b0, 100000, 0,
                                             s->d_score + b0, nullptr, nullptr);
       if (rc) { rc_out = rc; return; }
@@ -482,7 +498,14 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
         Root& root = s->roots[r];
         for (uint32_t p = 0; p < P; p++) {
           const size_t b = r * P + p;
-          const float v1 = (float)s->h_score[b] * 0.5f, v2 = 1.0f - v1;
+          float v1;
+          if (s->leaf_mode == 1) {
+            const uint32_t t = s->h_res[b] & 15u;
+            v1 = t == 0 ? s->h_value[b] : (t == 1 ? 1.0f : (t == 2 ? 0.0f : 0.5f));
+          } else {
+            v1 = (float)s->h_score[b] * 0.5f;
+          }
+          const float v2 = 1.0f - v1;
           const Particle& q = s->particles[b];
           for (const PathEntry& pe : q.path) {
             Node& node = root.nodes[pe.node];
@@ -635,6 +658,25 @@ int oakb200_search_nash(oakb200_search* s, float* nash, float* nash_value) {
     }
     if (nash_value) nash_value[r] = v;
   }
+  return OAKB200_OK;
+}
+
+int oakb200_search_set_leaf(oakb200_search* s, int mode) {
+  if (!s) return OAKB200_EINVAL;
+  oakb200_ctx* ctx = s->ctx;
+  if (mode != 0 && mode != 1) return fail(ctx, OAKB200_EINVAL, "search_set_leaf: 0 = MonteCarlo playouts, 1 = network value");
+  if (mode == 1) {
+    if (!ctx->net) return fail(ctx, OAKB200_EINVAL, "search_set_leaf: no network loaded (oakb200_net_load)");
+    if (!s->d_value) {
+      const size_t B = s->roots_max * (size_t)s->P;
+      CU(ctx, cudaSetDevice(ctx->device));
+      CU(ctx, cudaMalloc(&s->d_value, B * 4));
+      CU(ctx, cudaMalloc(&s->d_logits, B * 18 * 4));
+      CU(ctx, cudaMalloc(&s->d_ecnt, B * 2));
+      CU(ctx, cudaMallocHost(&s->h_value, B * 4));
+    }
+  }
+  s->leaf_mode = mode;
   return OAKB200_OK;
 }
 

@@ -64,6 +64,13 @@ class TreeSearch:
                                                                                   "iterations", "empirical_value", "empirical", "nodes")]))
         return out
 
+    def set_leaf(self, mode):
+        """0 = MonteCarlo playouts, 1 = the loaded network's value at every new leaf."""
+        f = self.lib.oakb200_search_set_leaf
+        f.restype = ctypes.c_int
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        self._check(f(self._h, int(mode)))
+
     def nash(self):
         """process_output's Nash half (mcts.h:628-656): -> (nash[n,2,9] f32, nash_value[n] f32)."""
         f = self.lib.oakb200_search_nash

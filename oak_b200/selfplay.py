@@ -184,14 +184,18 @@ class SearchSelfPlay(SelfPlay):
     a tree search (oakb200_search_*: `iterations` MonteCarlo iterations, joint UCB, `particles` descents in flight per
     root), the move is drawn from RuntimePolicy::get_policy of the search output, and the recorded update carries the
     search's iteration count, empirical and Nash policies and values (CompressedFrames::Update(output, c1, c2),
-    compressed-frame.h:47-56). The network is not consulted (MonteCarlo leaves), so `net_blob` may be None."""
+    compressed-frame.h:47-56). Leaves are MonteCarlo playouts without a network (`net_blob` None) and the network's value
+    with one."""
 
-    def __init__(self, games, team_pool, iterations, particles=16, policy_mode="e", ucb_c=1.0, rolls=(3, 1), net_blob=None, **kw):
+    def __init__(self, games, team_pool, iterations, particles=16, policy_mode="e", ucb_c=1.0, rolls=(3, 1), net_blob=None,
+                 net_leaves=None, **kw):
         from .search import TreeSearch
         self._net = net_blob is not None
         super().__init__(games, net_blob, team_pool, **kw)
         self.iterations, self.policy_mode, self.ucb_c, self.rolls = int(iterations), policy_mode, float(ucb_c), rolls
         self.search = TreeSearch(self.eng, self.n, particles=particles)
+        if net_leaves if net_leaves is not None else self._net:  # a network, when given, evaluates the leaves (mcts.h:409-424)
+            self.search.set_leaf(1)
         torch = self.torch
         self.iters_t = torch.zeros(self.n, dtype=torch.int32, device=self.dev)
         self.nash_value = torch.zeros(self.n, dtype=torch.float32, device=self.dev)

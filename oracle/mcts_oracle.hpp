@@ -20,6 +20,7 @@
 
 #include "gen1_oracle.hpp"
 #include "oak_oracle.hpp"
+#include "nn_oracle.hpp"
 
 namespace mcts_oracle {
 
@@ -75,6 +76,10 @@ struct Search {
   // per-iteration
   Options options{};
   uint64_t playout_seed = 0;
+  // leaf evaluation: null = MonteCarlo playout, else the network's value (mcts.h:409-424, UCB is not a contextual bandit:
+  // value_inference only) with the durations the search has tracked down to the leaf
+  const BattleNet* net = nullptr;
+  bool net_discrete = false;
 
   static uint8_t roll_byte(uint32_t n_rolls, uint8_t s) {
     if (n_rolls == 1) return 236;
@@ -130,6 +135,11 @@ struct Search {
         heap.p2.init(n);
         uint8_t dur[8];
         memcpy(dur, options.durations, 8);
+        if (net) {
+          float l1[9], l2[9];
+          const float v = net_discrete ? net->eval_discrete(battle, dur, 0, 0, nullptr, nullptr, l1, l2) : net->eval(battle, dur, 0, 0, nullptr, nullptr, l1, l2);
+          return {v, 1 - v};
+        }
         oak_rollout(battle, dur, &result, playout_seed, 100000);
         const float v = (result & 15) == RES_WIN ? 1.0f : ((result & 15) == RES_LOSE ? 0.0f : 0.5f);
         return {v, 1 - v};

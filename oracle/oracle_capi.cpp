@@ -372,3 +372,20 @@ void oracle_net_eval_discrete_batch(void* h, const uint8_t* battles, const uint8
   for (auto& t : pool) t.join();
 }
 }
+
+// tree search with network-value leaves (mcts_oracle.hpp: Search::net)
+extern "C" void oracle_mcts_run_net(void* net, int discrete, const uint8_t* battle384, const uint8_t* durations8, uint8_t result, uint64_t seed,
+                                    uint32_t iterations, float c, uint32_t root_rolls, uint32_t other_rolls, uint32_t* visit81, double* value81,
+                                    uint64_t* nodes) {
+  mcts_oracle::Search s;
+  s.c = c;
+  s.root_rolls = root_rolls;
+  s.other_rolls = other_rolls;
+  s.seed = seed;
+  s.net = static_cast<BattleNet*>(net);
+  s.net_discrete = discrete != 0;
+  s.run(battle384, durations8, result, iterations);
+  memcpy(visit81, s.visit, sizeof(s.visit));
+  memcpy(value81, s.value, sizeof(s.value));
+  if (nodes) *nodes = s.nodes;
+}

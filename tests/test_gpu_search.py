@@ -127,3 +127,72 @@ def test_reference_sleep_known_answers(slept, expected):
     ts.close()
     eng.close()
     assert abs(out["empirical_value"][0] - expected) <= (0 if expected == 1.0 else 0.03)
+
+
+def oracle_search_net(orc, net, discrete, b, d, r, seed, iters, c, rr, orl):
+    f = orc.lib.oracle_mcts_run_net
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint64, ctypes.c_uint32,
+                  ctypes.c_float, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    visit, value, nodes = np.zeros(81, np.uint32), np.zeros(81, np.float64), np.zeros(1, np.uint64)
+    f(net.h, int(discrete), b.ctypes.data, d.ctypes.data, int(r), int(seed), iters, c, rr, orl, visit.ctypes.data, value.ctypes.data,
+      nodes.ctypes.data)
+    return visit.reshape(9, 9), value.reshape(9, 9), int(nodes[0])
+
+
+@pytest.mark.parametrize("discrete", [False, True])
+def test_network_leaves_follow_the_sequential_oracle(discrete):
+    """Leaf = the network's value (mcts.h:409-424) instead of a playout, one descent in flight. The leaf values are floats
+    computed in a different order on the GPU (tensor cores, ~1e-6 apart from the oracle's), and UCB by design drives the
+    arms' indices together, so near-ties — where such a difference decides the selection — are common: some roots follow
+    the oracle selection for selection for all 300 iterations, the others part ways at a near-tie and stay statistically
+    the same search. Required: at least half identical (value matrices then equal to 1e-4), every root's value within
+    0.02 and root policies within 0.2 (L1) of the oracle's."""
+    import oak_b200
+    from oak_b200.search import TreeSearch
+    from oak_ref import NetOracle, dyadic_clamp_blob, make_net_blob
+    orc = Oracle()
+    n, iters = 8, 300
+    b, d, r = midgame(orc, n, first=900)
+    seeds = np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x7654321)
+    blob = dyadic_clamp_blob(np.random.default_rng(4)) if discrete else make_net_blob(np.random.default_rng(4), scale=3.0)
+    net = NetOracle(orc, blob)
+    eng = oak_b200.BattleEngine(64)
+    eng.load_network(blob, discrete=discrete)
+    ts = TreeSearch(eng, n, particles=1)
+    ts.set_leaf(1)
+    ts.set_roots(b, d, r, seeds)
+    ts.run(iters, c=1.0, root_rolls=3, other_rolls=1)
+    out = ts.output()
+    same = 0
+    for i in range(n):
+        visit, value, nodes = oracle_search_net(orc, net, discrete, b[i], d[i], r[i], seeds[i], iters, 1.0, 3, 1)
+        assert out["iterations"][i] == iters and out["visit_matrix"][i].sum() == iters
+        assert abs(out["empirical_value"][i] - value.sum() / iters) < 0.02
+        for axis in (0, 1):
+            assert np.abs(out["visit_matrix"][i].sum(axis) - visit.sum(axis)).sum() / iters < 0.2
+        if np.array_equal(out["visit_matrix"][i], visit) and out["nodes"][i] == nodes:
+            same += 1
+            assert np.abs(out["value_matrix"][i] - value).max() < 1e-4 * iters
+    assert same >= n // 2, same
+    # the values really are the network's: a search of playouts on the same roots gives different statistics
+    ts.set_leaf(0)
+    ts.set_roots(b, d, r, seeds)
+    ts.run(iters)
+    assert not np.array_equal(ts.output()["value_matrix"], out["value_matrix"])
+    ts.close()
+    eng.close()
+
+
+def test_network_leaves_need_a_network():
+    import oak_b200
+    from oak_b200.engine import OakB200Error
+    from oak_b200.search import TreeSearch
+    eng = oak_b200.BattleEngine(8)
+    ts = TreeSearch(eng, 4, particles=2)
+    with pytest.raises(OakB200Error):
+        ts.set_leaf(1)
+    with pytest.raises(OakB200Error):
+        ts.set_leaf(7)
+    ts.close()
+    eng.close()

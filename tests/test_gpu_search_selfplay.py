@@ -60,3 +60,32 @@ def test_search_selfplay_stream():
     for name in ("pokemon", "active", "hp", "choice_indices", "empirical_policies", "nash_policies", "nash_value", "score"):
         assert np.array_equal(getattr(f, name).cpu().numpy(), want[name]), name
     f.close()
+
+
+def test_search_selfplay_with_network_leaves():
+    """The same loop with the network evaluating the leaves (the reference's usual generate configuration)."""
+    from oak_ref import make_net_blob
+    from oak_b200.selfplay import SearchSelfPlay
+    orc = Oracle()
+    pool = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    blob = make_net_blob(np.random.default_rng(3), scale=3.0)
+    sp = SearchSelfPlay(32, pool, iterations=32, particles=8, net_blob=blob, seed=9, max_updates=700)
+    assert sp.search.lib is not None
+    chunks, games = [], 0
+    for s_ in range(900):
+        sp.step()
+        if (s_ + 1) % 20 == 0:
+            st, g = sp.collect()
+            if g:
+                chunks.append(np.array(st, copy=True))
+                games += g
+        if games >= 8:
+            break
+    sp.close()
+    assert games >= 8
+    for g in parse_battle_data(np.concatenate(chunks)):
+        b, d, r = g["battle"].copy(), np.zeros(8, np.uint8), 0x50
+        for u in g["updates"]:
+            assert u["iterations"] == 32
+            r, _ = orc.update(b, u["c1"], u["c2"], d)
+        assert r == g["result"] and (r & 15) != 0
