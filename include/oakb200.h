@@ -184,6 +184,14 @@ int oakb200_frames_record_device(oakb200_ctx* ctx, size_t n, const void* results
                                  const void* empirical, const void* nash);
 /* Close every recording slot whose battle has ended (result byte AFTER the update): header + result. */
 int oakb200_frames_finish_device(oakb200_ctx* ctx, size_t n, const void* results);
+/* One turn of network-policy self-play for n games in one call (the battle loop of cpp/src/generate.cc:271-333 with a
+ * budget-0 agent): choices, evaluation, RuntimePolicy temperature / floor / sample (counter-based stream from seeds and
+ * step_index), frame record (empirical = nash = the network's policy and value, iterations 0), update, finish. All
+ * arrays DEVICE; choices[n][2][9], counts[n][2], value[n], logits[n][2][9], eval_counts[n][2], probs[n][2][9], c1[n], c2[n],
+ * before[n] are outputs / scratch the caller owns. Needs oakb200_net_load and oakb200_frames_create + _begin_device. */
+int oakb200_selfplay_step_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                                 uint32_t step_index, double temperature, double min_prob, void* choices, void* counts, void* value,
+                                 void* logits, void* eval_counts, void* probs, void* c1, void* c2, void* before);
 /* Finished games waiting to be drained / games dropped for length so far (synchronises). */
 int oakb200_frames_pending(oakb200_ctx* ctx, uint32_t* finished, uint32_t* dropped);
 /* Pack the finished games in slot order into out[cap] (HOST), free their slots. *bytes = stream length (also set when

@@ -355,3 +355,27 @@ int oakb200_policy_sample_device(oakb200_ctx* ctx, size_t n, const void* choices
 }
 
 }  // extern "C"
+
+// One turn of the network-policy self-play loop as ONE call (generate.cc:271-333 for every running game at once):
+// legal choices, leaf evaluation, RuntimePolicy + sample, frame record, update, finish. The same six launches
+// oak_b200/selfplay.py used to make one by one; issuing them from here removes the per-launch host round trips that
+// dominated a step at 16 Ki games. `before` is scratch for the results as they were before the update.
+extern "C" int oakb200_selfplay_step_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
+                                            uint32_t step_index, double temperature, double min_prob, void* choices, void* counts,
+                                            void* value, void* logits, void* eval_counts, void* probs, void* c1, void* c2, void* before) {
+  if (!ctx || !battles || !durations || !results || !seeds || !choices || !counts || !value || !logits || !eval_counts || !probs || !c1 ||
+      !c2 || !before)
+    return fail(ctx, OAKB200_EINVAL, "selfplay_step: null argument");
+  int rc = oakb200_choices_device(ctx, n, battles, results, choices, counts);
+  if (rc) return rc;
+  rc = oakb200_eval_device(ctx, n, battles, durations, results, value, logits, eval_counts);
+  if (rc) return rc;
+  rc = oakb200_policy_sample_device(ctx, n, choices, counts, logits, seeds, step_index, temperature, min_prob, probs, c1, c2);
+  if (rc) return rc;
+  CU(ctx, cudaMemcpyAsync(before, results, n, cudaMemcpyDeviceToDevice, ctx->stream));
+  rc = oakb200_frames_record_device(ctx, n, before, c1, c2, counts, nullptr, value, value, probs, probs);
+  if (rc) return rc;
+  rc = oakb200_step_device(ctx, n, battles, durations, results, c1, c2, nullptr, nullptr);
+  if (rc) return rc;
+  return oakb200_frames_finish_device(ctx, n, results);
+}

@@ -68,6 +68,7 @@ def load_library():
         "oakb200_frames_begin_device": (i32, [vp, sz, vp, vp]),
         "oakb200_frames_record_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "oakb200_frames_finish_device": (i32, [vp, sz, vp]),
+        "oakb200_selfplay_step_device": (i32, [vp, sz, vp, vp, vp, vp, u32, ctypes.c_double, ctypes.c_double] + [vp] * 9),
         "oakb200_frames_pending": (i32, [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]),
         "oakb200_frames_drain": (i32, [vp, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u32)]),
         "oakb200_rows_index_host": (i32, [vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
@@ -310,6 +311,13 @@ class BattleEngine:
 
     def frames_finish_device(self, results):
         self._check(self.lib.oakb200_frames_finish_device(self._h, results.shape[0], _ptr(results)))
+
+    def selfplay_step_device(self, battles, durations, results, seeds, step_index, temperature, min_prob, choices, counts, value,
+                             logits, eval_counts, probs, c1, c2, before):
+        self._check(self.lib.oakb200_selfplay_step_device(self._h, results.shape[0], _ptr(battles), _ptr(durations), _ptr(results),
+                                                          _ptr(seeds), int(step_index), float(temperature), float(min_prob),
+                                                          _ptr(choices), _ptr(counts), _ptr(value), _ptr(logits), _ptr(eval_counts),
+                                                          _ptr(probs), _ptr(c1), _ptr(c2), _ptr(before)))
 
     def frames_pending(self):
         a, b = ctypes.c_uint32(), ctypes.c_uint32()

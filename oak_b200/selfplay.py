@@ -28,6 +28,15 @@ def _splitmix64(x):
     return z ^ (z >> 31)
 
 
+def _splitmix64_np(x):
+    """_splitmix64 on a uint64 array (wrapping arithmetic)."""
+    with np.errstate(over="ignore"):
+        z = x + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
 class FrameWriter:
     """N.battle.data files of at least `buffer_mb` MiB each (generate.cc:169-188), plain concatenations of game records."""
 
@@ -112,7 +121,7 @@ class SelfPlay:
         self.started += idx.size
         pick = self.rng.integers(0, self.pool.shape[0], (idx.size, 2))
         teams = self.pool[pick]  # [k,2,6,5]
-        seeds = np.array([_splitmix64(self.seed ^ int(g)) for g in ids], np.uint64)
+        seeds = _splitmix64_np(np.uint64(self.seed) ^ ids.astype(np.uint64))
         di = torch.from_numpy(idx).to(self.dev)
         self.teams[di] = torch.from_numpy(teams).to(self.dev)
         self.seeds[di] = torch.from_numpy(seeds.view(np.int64)).to(self.dev)
@@ -120,16 +129,11 @@ class SelfPlay:
         self.eng.frames_begin_device(self.battles, self.results)
 
     def step(self):
-        """One lockstep turn of every running game."""
-        e = self.eng
-        e.choices_device(self.battles, self.results, self.choices, self.counts)
-        e.evaluate_device(self.battles, self.durations, self.results, self.value, self.logits, self.ecounts)
-        e.policy_sample_device(self.choices, self.counts, self.logits, self.seeds, self.step_index, self.probs, self.c1, self.c2,
-                               self.temperature, self.min_prob)
-        self.before.copy_(self.results)
-        e.frames_record_device(self.before, self.c1, self.c2, self.counts, self.value, self.value, self.probs, self.probs)
-        e.step_device(self.battles, self.durations, self.results, self.c1, self.c2)
-        e.frames_finish_device(self.results)
+        """One lockstep turn of every running game: one library call (oakb200_selfplay_step_device = choices, evaluation,
+        policy sample, frame record, update, finish)."""
+        self.eng.selfplay_step_device(self.battles, self.durations, self.results, self.seeds, self.step_index, self.temperature,
+                                      self.min_prob, self.choices, self.counts, self.value, self.logits, self.ecounts, self.probs,
+                                      self.c1, self.c2, self.before)
         self.step_index += 1
 
     def collect(self):
