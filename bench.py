@@ -488,7 +488,10 @@ def main():
                     "h2d_bytes_per_step": int(tot_battles * (384 + 8 + 1 + 8)), "d2h_bytes_per_step": int(tot_battles * (1 + 2 + 4)),
                     "iters": e2e_iters, "timing": "wall clock around oakb200_rollout_host (pinned host records in, score/turns/steps out; chunked upload pipelined behind the playouts), synchronised"},
             "roofline": {"bound": "hbm", "kernel": "rollout_kernel<128,false,false>", "achieved": achieved, "peak": pk["hbm_gbs"],
-                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_src,
+                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                         "traffic": int(424_100_608 * n / (1 << 20)), "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum = 414.9 + 9.2 MB "
+                         "for one launch of 2^20 playouts (ncu --set full, profiles/r1m_rollout_kernel_ncu_summary.txt), scaled to this n",
+                         "peak_source": pk_src,
                          "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": statistics.mean(kernel_ms),
                          "note": "fused playouts read each 393-byte record once per ~120 updates: the kernel is bound by SM "
                                  "instruction issue under divergence, not HBM (see profiles/)"},
