@@ -494,7 +494,11 @@ def main():
                          "peak_source": pk_src,
                          "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": statistics.mean(kernel_ms),
                          "note": "fused playouts read each 393-byte record once per ~120 updates: the kernel is bound by SM "
-                                 "instruction issue under divergence, not HBM (see profiles/)"},
+                                 "instruction issue under divergence, not HBM (see profiles/)",
+                         "issue": {"issue_slots_busy": 0.262, "threads_per_warp_inst": 11.1, "stall_no_instruction_share": 0.52,
+                                   "registers": 63, "warps_per_sm": 15.6, "code_bytes": 65024,
+                                   "source": "ncu --set full of this command, profiles/r1m_rollout_kernel_ncu_summary.txt (SURVEY 8d asks "
+                                             "for issue-slot utilisation and lane efficiency beside the HBM figure); static, not re-measured per run"}},
             "lockstep_step_kernel": {"ms_per_launch": lock_ms_max, "battles": int(tot_battles),
                                      "battle_steps_per_s": tot_battles / (lock_ms_max * 1e-3),
                                      "achieved_gbs": B_STEP * n / (lock_ms * 1e-3) / 1e9,

@@ -260,6 +260,13 @@ typedef struct oakb200_training_rows {
   float* empirical_value;
   float* nash_value;
   float* score;
+  /* the uncompressed frame of the same row (pyoak BattleFrames, py/battle/frames.h:17-51): the battle, durations and
+   * result the row was built from; legal_choices[n][2][9] u8 = the legal choices of both players, zero past their count
+   * (the reference allocates `choices` and leaves it zero, frames.h:47-49 — this array is what it was meant to hold) */
+  uint8_t* battle;
+  uint8_t* durations;
+  uint8_t* result;
+  uint8_t* legal_choices;
 } oakb200_training_rows;
 
 /* Host walk over the game headers of a stream (pyoak read_battle_data, pyoak.cc:43-71): byte offset and first row of

@@ -183,6 +183,21 @@ __device__ __forceinline__ void encode_row(const uint8_t* st, const uint8_t* __r
     const uint32_t t = st[393] & 15u;
     if (out.score) out.score[row] = t == RES_WIN ? 1.0f : (t == RES_LOSE ? 0.0f : 0.5f);
   }
+  // ---- the uncompressed frame (Py::Battle::Frames::write, py/battle/frames.h:39-51): the state the row was built from
+  if (out.battle) {
+    uint8_t* dst = out.battle + (size_t)row * 384;
+    if ((reinterpret_cast<uintptr_t>(out.battle) & 15u) == 0) {
+      if (lane < 24) reinterpret_cast<uint4*>(dst)[lane] = reinterpret_cast<const uint4*>(st)[lane];
+    } else {
+      for (int i = lane; i < 384; i += 32) dst[i] = st[i];
+    }
+  }
+  if (out.durations && lane < 8) out.durations[(size_t)row * 8 + lane] = st[384 + lane];
+  if (out.result && lane == 8) out.result[row] = st[392];
+  if (out.legal_choices && lane >= 9 && lane < 27) {
+    const int j = lane - 9, s = j / 9, i = j % 9;
+    out.legal_choices[(size_t)row * 18 + j] = (uint32_t)i < st[394 + s] ? st[400 + j] : (uint8_t)0;
+  }
 }
 
 }  // namespace rows

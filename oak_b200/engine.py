@@ -339,11 +339,11 @@ class BattleEngine:
 
     # ---------------------------------------------------------------- training rows (include/oakb200.h, train_rows.cu)
     ROW_FIELDS = ("pokemon", "active", "hp", "choice_indices", "k", "choice", "iterations", "empirical_policies", "nash_policies",
-                  "empirical_value", "nash_value", "score")
+                  "empirical_value", "nash_value", "score", "battle", "durations", "result", "legal_choices")
 
     def _rows_struct(self, out):
-        """dict name -> device tensor (or None) -> the oakb200_training_rows struct as an array of 12 pointers"""
-        arr = (ctypes.c_void_p * 12)()
+        """dict name -> device tensor (or None) -> the oakb200_training_rows struct as an array of 16 pointers"""
+        arr = (ctypes.c_void_p * 16)()
         for i, name in enumerate(self.ROW_FIELDS):
             t = out.get(name)
             arr[i] = _ptr(t) if t is not None else None

@@ -21,6 +21,15 @@ def _shapes(torch):
                 empirical_value=((1,), torch.float32), nash_value=((1,), torch.float32), score=((1,), torch.float32))
 
 
+def _frame_shapes(torch):
+    t = _shapes(torch)
+    for name in ("pokemon", "active", "hp", "choice_indices"):
+        del t[name]
+    t.update(battle=((384,), torch.uint8), durations=((8,), torch.uint8), result=((1,), torch.uint8), choices=((2, 9), torch.uint8),
+             legal_choices=((2, 9), torch.uint8))
+    return t
+
+
 class EncodedBattleFrames:
     """`size` rows of training data in device memory. `iterations` holds the u32 of the reference bit-for-bit (torch has no
     uint32 arithmetic; view it with .view(torch.uint32) where needed)."""
@@ -33,20 +42,22 @@ class EncodedBattleFrames:
         self.engine = engine or BattleEngine(1, device=device)
         self._own_engine = engine is None
         self.engine.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
-        for name, (shape, dtype) in _shapes(torch).items():
+        for name, (shape, dtype) in self._fields(torch).items():
             setattr(self, name, torch.zeros((self.size,) + shape, dtype=dtype, device=self.device))
         self.rows = 0
         self.games = 0
+
+    _fields = staticmethod(_shapes)
 
     def close(self):
         if self._own_engine:
             self.engine.close()
 
     def _out(self):
-        return {name: getattr(self, name) for name in BattleEngine.ROW_FIELDS}
+        return {name: getattr(self, name, None) for name in BattleEngine.ROW_FIELDS}
 
     def clear(self):
-        for name in BattleEngine.ROW_FIELDS:
+        for name in self._fields(self.torch):
             getattr(self, name).zero_()
 
     def fill(self, data, only_update=None):
@@ -60,14 +71,14 @@ class EncodedBattleFrames:
             raise ValueError(f"game {bad} of the stream does not replay to its stored result")
         return rows
 
-    @staticmethod
-    def from_bytes(data, size=None, device=0, engine=None):
-        """EncodedBattleFrames.from_bytes(data, size): every stored update of every game in `data` becomes a row."""
+    @classmethod
+    def from_bytes(cls, data, size=None, device=0, engine=None):
+        """from_bytes(data, size): every stored update of every game in `data` becomes a row."""
         if isinstance(data, (bytes, bytearray, memoryview)):
             data = np.frombuffer(data, np.uint8)
         if size is None:
             size = rows_index_host(data if isinstance(data, np.ndarray) else data.numpy())[2]
-        f = EncodedBattleFrames(size, device=device, engine=engine)
+        f = cls(size, device=device, engine=engine)
         f.fill(data)
         return f
 
@@ -98,3 +109,11 @@ class EncodedBattleFrames:
             return 0
         sub = np.concatenate([data[o:o + nb] for o, nb in keep])
         return self.fill(sub, only_update=np.asarray(picks, np.int32))
+
+
+class BattleFrames(EncodedBattleFrames):
+    """pyoak's `BattleFrames` (reference cpp/include/py/battle/frames.h:17-80, pyoak.cc:638-653): the same replay, but each
+    row keeps the raw state — battle[size,384], durations[size,8], result[size,1] u8 — next to the targets instead of the
+    dense encodings. `choices` stays zero as in the reference (frames.h:47-49 computes the legal choices and does not store
+    them); `legal_choices` is this library's extra: the list `choices` was meant to hold, zero past k."""
+    _fields = staticmethod(_frame_shapes)

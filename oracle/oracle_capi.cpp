@@ -333,6 +333,23 @@ int64_t oracle_training_rows(const uint8_t* stream, uint64_t n_bytes, int thread
 }
 }
 
+// Uncompressed frames of every game of a stream (rows_oracle::build_frames). Returns rows or -(g + 1).
+extern "C" int64_t oracle_battle_frames(const uint8_t* stream, uint64_t n_bytes, uint8_t* battle, uint8_t* durations, uint8_t* result,
+                                        uint8_t* legal) {
+  uint64_t at = 0, rows = 0, g = 0;
+  while (at + 391 <= n_bytes) {
+    uint32_t nb;
+    memcpy(&nb, stream + at, 4);
+    if (nb < 391 || at + nb > n_bytes) break;
+    const int got = rows_oracle::build_frames(stream + at, rows, battle, durations, result, legal);
+    if (got < 0) return -(int64_t)(g + 1);
+    rows += (uint64_t)got;
+    at += nb;
+    g++;
+  }
+  return at == n_bytes ? (int64_t)rows : INT64_MIN;
+}
+
 // ---- "discrete" evaluation (nn_oracle.hpp: eval_discrete) ----
 extern "C" {
 // the integer main net alone on a given u8 battle embedding (pins against oracle/_ref: ref_quantized_main)

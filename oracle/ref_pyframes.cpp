@@ -68,6 +68,7 @@ uint8_t pkmn_gen1_battle_choices(const pkmn_gen1_battle* battle, pkmn_player pla
 }
 
 #include <py/battle/encoded-frames.h>
+#include <py/battle/frames.h>
 
 namespace py = pybind11;
 
@@ -89,6 +90,24 @@ PYBIND11_MODULE(ref_pyframes, m) {
     d["active"] = f.active;
     d["hp"] = f.hp;
     d["choice_indices"] = f.choice_indices;
+    return d;
+  });
+  // the uncompressed form (pyoak BattleFrames, pyoak.cc:638-653)
+  m.def("frames_from_bytes", [](const py::bytes& data, size_t sz) {
+    auto f = Py::Battle::Frames::from_bytes(data, sz);
+    py::dict d;
+    d["k"] = f.k;
+    d["choice"] = f.choice;
+    d["iterations"] = f.iterations;
+    d["empirical_policies"] = f.empirical_policies;
+    d["nash_policies"] = f.nash_policies;
+    d["empirical_value"] = f.empirical_value;
+    d["nash_value"] = f.nash_value;
+    d["score"] = f.score;
+    d["battle"] = f.battle;
+    d["durations"] = f.durations;
+    d["result"] = f.result;
+    d["choices"] = f.choices;
     return d;
   });
 }

@@ -203,4 +203,38 @@ inline int build_rows(const uint8_t* game, Rows& r, size_t first) {
   return result == stored_result ? (int)n_updates : -1;
 }
 
+// One stored game -> the uncompressed frames of pyoak's BattleFrames (Frames::write / uncompress_from_bytes,
+// cpp/include/py/battle/frames.h:39-69): the battle, durations and result each update was applied to, and the legal
+// choices of both players (which the reference computes at frames.h:47 and leaves unstored). Rows [first, first + n).
+inline int build_frames(const uint8_t* game, size_t first, uint8_t* battle, uint8_t* durations, uint8_t* result, uint8_t* legal) {
+  uint16_t n_updates;
+  memcpy(&n_updates, game + 4, 2);
+  Battle b;
+  memcpy(&b, game + 6, 384);
+  Options o{};
+  uint8_t res = RESULT_DEFAULT;
+  const uint8_t* p = game + 391;
+  for (uint32_t u = 0; u < n_updates; u++) {
+    const size_t f = first + u;
+    memcpy(battle + f * 384, &b, 384);
+    memcpy(durations + f * 8, o.durations, 8);
+    result[f] = res;
+    Battle copy = b;
+    Options oc{};
+    OakEngine ec(copy, oc);
+    for (int s = 0; s < 2; s++) {
+      uint8_t ch[9] = {0};
+      const uint8_t k = ec.choices(s, (res >> (4 + 2 * s)) & 3, ch);
+      for (int i = 0; i < 9; i++) legal[f * 18 + s * 9 + i] = i < k ? ch[i] : 0;
+    }
+    const uint32_t m = (p[0] & 15) + 1, n = (p[0] >> 4) + 1;
+    memset(o.actions, 0, 16);
+    memset(o.overrides, 0, 16);
+    OakEngine e(b, o);
+    res = e.update(p[1], p[2]);
+    p += 11 + 4 * (m + n);
+  }
+  return res == game[390] ? (int)n_updates : -1;
+}
+
 }  // namespace rows_oracle

@@ -354,6 +354,20 @@ def oracle_training_rows(orc, stream, threads=0):
     return R
 
 
+def oracle_battle_frames(orc, stream):
+    """-> dict battle[n,384], durations[n,8], result[n,1], legal_choices[n,2,9] for every stored update (oracle_battle_frames)."""
+    f = orc.lib.oracle_battle_frames
+    f.restype = ctypes.c_int64
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64] + [ctypes.c_void_p] * 4
+    stream = np.ascontiguousarray(stream, np.uint8)
+    n = count_rows(stream)
+    R = dict(battle=np.zeros((n, 384), np.uint8), durations=np.zeros((n, 8), np.uint8), result=np.zeros((n, 1), np.uint8),
+             legal_choices=np.zeros((n, 2, 9), np.uint8))
+    got = f(stream.ctypes.data, stream.size, *[R[x].ctypes.data for x in ("battle", "durations", "result", "legal_choices")])
+    assert got == n, f"oracle_battle_frames -> {got}, expected {n}"
+    return R
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # "discrete" evaluation (oracle/nn_oracle.hpp: eval_discrete; integer main net pinned to the reference's quantized layers)
 def oracle_eval_discrete_batch(net, battles, durations, results, threads=None, want_embeddings=False):

@@ -67,3 +67,21 @@ def test_bad_replay_is_reported(orc):
     stream[390] ^= 3  # the first game's stored result no longer matches its replay
     with pytest.raises(AssertionError):
         oracle_training_rows(orc, stream, threads=1)
+
+
+def test_uncompressed_frames_match_reference_golden(orc):
+    """pyoak BattleFrames (py/battle/frames.h): battle / durations / result before every stored update."""
+    from oak_ref import oracle_battle_frames
+    S = np.load(os.path.join(ROOT, "tests", "golden", "training_rows_golden.npz"))["stream"]
+    G = np.load(os.path.join(ROOT, "tests", "golden", "battle_frames_golden.npz"))
+    R = oracle_battle_frames(orc, S)
+    for name in ("battle", "durations", "result"):
+        assert R[name].shape == G[name].shape and np.array_equal(R[name], G[name]), name
+    assert not G["choices"].any()  # the reference leaves `choices` zero (frames.h:47-49)
+    # the legal choices are those of the engine for that frame: counts agree with the stored policy lengths wherever the
+    # stored k is the legal count (it always is for games this library records)
+    k = np.load(os.path.join(ROOT, "tests", "golden", "training_rows_golden.npz"))["k"]
+    legal = R["legal_choices"]
+    cnt = np.maximum((legal != 0).sum(-1), 1)  # a lone pass (choice 0) counts as one
+    assert np.array_equal(cnt, k[..., 0])
+    assert (R["durations"] != 0).any() and len(np.unique(R["result"])) > 1
