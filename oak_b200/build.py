@@ -36,7 +36,8 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     srcs = [s for s in sources() if os.path.exists(s)]
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + srcs
+    extra = os.environ.get("OAKB200_NVCC_EXTRA", "").split()  # diagnostic builds only (e.g. -DOAKB200_TC_TIMING)
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + srcs
     print("[oak_b200.build]", " ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)
     return LIB

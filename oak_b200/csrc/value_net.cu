@@ -615,7 +615,7 @@ cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
     }
   }
   P.stage(fc1, tc::AT_HI, tc::AT_LO, 4, tc::D_WORK, true, tc::F_END_D);
-  P.stage(heads, tc::AEP_HI, tc::AEP_LO, 4, tc::D_WORK, true, tc::F_END_D);
+  P.stage(heads, tc::AEP_HI, tc::AEP_LO, 4, tc::D_HEADS, true, tc::F_END_D);
   if (P.prog.size() > tc::PROG_MAX) {
     n->tc_ok = false;
     return cudaSuccess;

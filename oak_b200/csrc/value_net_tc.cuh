@@ -18,8 +18,11 @@
 // One-hot feature columns are exact in bf16, so the first layer needs its A_lo plane only for the 14 real-valued
 // columns, which the host-side packing permutes to the front of K.
 //
-// Roles: warps 0-3 workers (encode, epilogues), warps 4-7 a second thread per row (the two split every epilogue by columns), warp 8 lane 0 streams weight chunks L2 -> shared memory with
-// cp.async.bulk through a 4-slot mbarrier ring (and owns the TMEM allocation), warp 9 lane 0 issues tcgen05.mma.
+// Roles: warps 0-15 workers, FOUR threads per row (thread r of group g = warps 4g..4g+3 serves evaluation r; the groups
+// split every epilogue by accumulator columns and the zero-fill of the feature tile by core columns, group 0 writes the
+// features), warp 16 lane 0 streams weight chunks L2 -> shared memory with cp.async.bulk through a 4-slot mbarrier ring
+// (and owns the TMEM allocation), warp 17 lane 0 issues tcgen05.mma. The worker side of the per-slot chain is bound by
+// instruction latency, not issue slots, so four warps per scheduler instead of two shorten it (profiles/r1o_*).
 // The per-tile schedule is a static chunk program built on the host at oakb200_net_load.
 #pragma once
 
@@ -44,9 +47,15 @@ struct Chunk {        // 16 bytes; one weight chunk = `ksteps` K=16 steps of a [
 enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8 };
 
 const int ROWS = 128;
-const int WORKERS = 256;  // two threads per row: they split the epilogue columns
-const int THREADS = WORKERS + 64;
-const int W_STREAM = WORKERS / 32, W_MMA = WORKERS / 32 + 1;
+#ifndef OAKB200_TC_GROUPS
+#define OAKB200_TC_GROUPS 2
+#endif
+const int GROUPS = OAKB200_TC_GROUPS;  // threads per row (2 or 4): they split the epilogue columns and the zero-fill
+static_assert(GROUPS == 2 || GROUPS == 4, "two or four worker threads per row");
+const int WORKERS = GROUPS * ROWS;
+const int THREADS = WORKERS + 64 + ROWS;
+const int W_STREAM = WORKERS / 32, W_MMA = WORKERS / 32 + 1, W_HEADS = WORKERS / 32 + 2;  // W_HEADS .. +3: the head warps
+static_assert(W_HEADS % 4 == 2, "head warp w serves TMEM lane quarter w % 4");
 const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden) / active embedding / trunk input
 const uint32_t OFF_EMB = 65536;      // benched-Pokemon embedding / second trunk operand
 const uint32_t OFF_TILE = 98304;     // 128 battle records as word-transposed columns (gen1_state.cuh)
@@ -56,9 +65,11 @@ const uint32_t OFF_PROG = OFF_RING + RING_SLOTS * RING_SLOT;
 const uint32_t PROG_MAX = 192;
 const uint32_t OFF_CONST = OFF_PROG + PROG_MAX * 16;
 const uint32_t CONST_FLOATS = 740;
-const uint32_t OFF_BAR = OFF_CONST + CONST_FLOATS * 4;  // full[4], empty[4], a_ready, d_ready, t_done
-const uint32_t OFF_TMEM_SLOT = OFF_BAR + 11 * 8;
-const uint32_t SMEM_BYTES = OFF_TMEM_SLOT + 8;
+const uint32_t OFF_BAR = OFF_CONST + CONST_FLOATS * 4;  // full[4], empty[4], a_ready, d_ready, t_done, heads_ready, heads_free
+const uint32_t OFF_TMEM_SLOT = OFF_BAR + 13 * 8;
+const uint32_t OFF_ROWIDX = OFF_TMEM_SLOT + 8;          // [2 players][128 rows][12] u16: last-layer rows of the legal choices
+const uint32_t SMEM_BYTES = OFF_ROWIDX + 2 * ROWS * 24;
+static_assert(OFF_ROWIDX % 8 == 0, "row index records are written as 32-bit words");
 static_assert(OFF_BAR % 8 == 0, "mbarriers are 8-byte aligned");
 static_assert(SMEM_BYTES <= 232448, "fits the 227 KB of one CTA");
 
@@ -70,7 +81,7 @@ const uint32_t AEA_HI = OFF_UNION, AEA_LO = OFF_UNION + 12 * CORE; // active emb
 const uint32_t AT_HI = OFF_UNION, AT_LO = OFF_UNION + 8 * CORE;    // trunk hidden, K = 64
 const uint32_t AEP_HI = OFF_EMB, AEP_LO = OFF_EMB + 8 * CORE;      // benched embedding / second trunk operand, K = 64
 // TMEM columns
-const uint32_t TMEM_COLS = 256, D_WORK = 0, D_TRUNK = 192;
+const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // one CTA per SM: all of Tensor Memory
 // constants block (floats)
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
 const int K_POK = 208, K_ACT = 240;
@@ -93,11 +104,12 @@ struct Params {
   int nchunks, act, pod, aod, vhd, pohd;
 };
 
-// AoS record (384 B, 16-byte aligned) -> column of the word-transposed tile; the two threads of a row take half each
-__device__ __forceinline__ void load_record_half(uint32_t* col, const uint8_t* record, int half) {
+// AoS record (384 B, 16-byte aligned) -> column of the word-transposed tile; the four threads of a row take a quarter each
+__device__ __forceinline__ void load_record_part(uint32_t* col, const uint8_t* record, int part) {
   const uint4* src = reinterpret_cast<const uint4*>(record);
-#pragma unroll 6
-  for (int k = 12 * half; k < 12 * half + 12; k++) {
+  const int per = 24 / GROUPS;
+#pragma unroll
+  for (int k = per * part; k < per * part + per; k++) {
     const uint4 v = __ldg(src + k);
     col[(4 * k + 0) * ROWS] = v.x;
     col[(4 * k + 1) * ROWS] = v.y;
@@ -157,10 +169,13 @@ __device__ __forceinline__ void put_moves(uint32_t plane, int r, int col0, const
 }
 
 // Pokemon block (battle.h:208-214): K = 208, columns as in the reference (stats 0-4 are the real-valued ones)
+// zero-fill of a feature tile, split by core columns over the groups (c0 = first core column not written by q.store)
+__device__ __forceinline__ void zero_features(uint32_t smem, int r, int grp, int c0, int cores) {
+  const uint32_t hi = smem + A1_HI;
+  for (int c = c0 + grp; c < cores; c += GROUPS) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
+}
 __device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<ROWS>& m, H pk, uint32_t sleep, bool alive) {
   const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
-#pragma unroll 5
-  for (int c = 1; c < K_POK / 8; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
   stv4(lo + (uint32_t)((ROWS + r) << 4), 0, 0, 0, 0);
   Row8 q;
   q.h[2] = q.h[3] = q.l[2] = q.l[3] = 0;
@@ -189,8 +204,6 @@ __device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<RO
 // Active block (battle.h:480-489) with the act_col() column order: K = 240, real-valued columns 0-13
 __device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROWS>& m, int s, uint32_t dur, bool alive) {
   const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
-#pragma unroll 4
-  for (int c = 2; c < K_ACT / 8; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
   Row8 q0, q1;
   if (!alive) {
 #pragma unroll
@@ -291,6 +304,40 @@ __device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const fl
     stv4(lo + o, l0, l1, l2, l3);
   }
 }
+// the same for a 16-column block: D[:, 16q .. 16q+15] -> core columns 2q, 2q+1
+template <int MODE>
+__device__ __forceinline__ void epilogue_half_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
+  uint32_t v[16];
+  umma::tmem_ld16(taddr + 16u * q, v);
+  umma::tmem_ld_wait();
+  const float4* b4 = reinterpret_cast<const float4*>(bias + 16 * q);
+#pragma unroll
+  for (int g = 0; g < 2; g++) {
+    const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
+    const float x0 = epi_act<MODE>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
+    const float x1 = epi_act<MODE>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
+    const float x2 = epi_act<MODE>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
+    const float x3 = epi_act<MODE>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
+    const float x4 = epi_act<MODE>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
+    const float x5 = epi_act<MODE>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
+    const float x6 = epi_act<MODE>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
+    const float x7 = epi_act<MODE>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
+    uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
+    split2(x0, x1, h0, l0);
+    split2(x2, x3, h1, l1);
+    split2(x4, x5, h2, l2);
+    split2(x6, x7, h3, l3);
+    const uint32_t o = (uint32_t)(((2 * q + g) * ROWS + r) << 4);
+    stv4(hi + o, h0, h1, h2, h3);
+    stv4(lo + o, l0, l1, l2, l3);
+  }
+}
+__device__ __forceinline__ void epilogue_half(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
+                                              int mode = 0) {
+  if (mode == 0) epilogue_half_m<0>(taddr, q, bias, bound, hi, lo, r);
+  else if (mode == 1) epilogue_half_m<1>(taddr, q, bias, bound, hi, lo, r);
+  else epilogue_half_m<2>(taddr, q, bias, bound, hi, lo, r);
+}
 // mode is warp-uniform (a property of the loaded network)
 __device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
                                                int mode = 0) {
@@ -319,6 +366,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bar = smem + OFF_BAR;
   const uint32_t bar_full = bar, bar_empty = bar + 32, bar_a = bar + 64, bar_d = bar + 72, bar_t = bar + 80;
+  const uint32_t bar_h = bar + 88, bar_hfree = bar + 96;
   const uint32_t ntiles = (n + ROWS - 1) / ROWS;
   // CTA `crank` of cluster `blockIdx.x / CL` takes tile base + crank of every group of CL tiles the cluster visits; a
   // tile index >= ntiles is a dummy (rows clamp to the last evaluation, nothing is written) so that the CTAs of a
@@ -332,9 +380,11 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       umma::mbar_init(bar_full + 8 * i, 1);
       umma::mbar_init(bar_empty + 8 * i, CL);
     }
-    umma::mbar_init(bar_a, WORKERS);
+    umma::mbar_init(bar_a, WORKERS / 32);
     umma::mbar_init(bar_d, 1);
     umma::mbar_init(bar_t, 1);
+    umma::mbar_init(bar_h, 2 * ROWS / 32);  // one arrival per warp of worker groups 0 and 1
+    umma::mbar_init(bar_hfree, ROWS / 32);  // one per head warp
     umma::mbar_fence_init();
   }
   if (warp == W_STREAM) umma::tmem_alloc(smem + OFF_TMEM_SLOT, TMEM_COLS);
@@ -382,16 +432,32 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // ===== MMA issuer =====
     if (lane == 0) {
       uint32_t g = 0, stage = 0;
+#ifdef OAKB200_TC_TIMING  // diagnostic build only: where the issuer's time goes, by N of the stage (printed by CTA 0)
+      long long tm[4][5] = {};  // [N bin][wait workers, wait weights, issue, drain, commit]
+      uint32_t tm_d = 0, tm_t = 0;
+      long long tm_c = clock64();
+      auto tm_lap = [&](int bin, int what) { const long long now = clock64(); tm[bin][what] += now - tm_c; tm_c = now; };
+#endif
       for (uint32_t t = tile0; t < ntiles; t += tile_step) {
         for (int c = 0; c < P.nchunks; c++, g++) {
           const Chunk ch = prog[c];
+#ifdef OAKB200_TC_TIMING
+          const int tm_bin = ch.n8 == 16 ? 0 : ch.n8 == 8 ? 1 : ch.n8 == 12 ? 2 : 3;
+          tm_lap(tm_bin, 2);
+#endif
           if (ch.flags & F_STAGE_BEGIN) {
             umma::mbar_wait(bar_a, stage & 1);
             stage++;
           }
+#ifdef OAKB200_TC_TIMING
+          tm_lap(tm_bin, 0);
+#endif
           const uint32_t slot = g & (RING_SLOTS - 1);
           umma::mbar_wait(bar_full + 8 * slot, (g / RING_SLOTS) & 1);
           umma::tc_fence_after();
+#ifdef OAKB200_TC_TIMING
+          tm_lap(tm_bin, 1);
+#endif
           const uint32_t N = (uint32_t)ch.n8 << 3;
           const uint32_t idesc = umma::idesc_bf16_f32(N);
           const uint32_t kstep_b = N * 32;  // bytes of one K = 16 step of B (two core columns of N rows)
@@ -403,7 +469,13 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           // so the field never carries into its neighbours).
           uint64_t da = umma::smem_desc(a_hi, CORE, 128), dal = umma::smem_desc(a_lo, CORE, 128);
           uint64_t dbh = umma::smem_desc(b_hi, N * 16, 128), dbl = umma::smem_desc(b_lo, N * 16, 128);
+#ifdef OAKB200_TC_SWZ_TIMING  // timing experiment only: 128-byte-swizzled descriptors over the un-swizzled data, results are garbage
+          da = umma::smem_desc(a_hi, 16, 1024) | (2ull << 61); dal = umma::smem_desc(a_lo, 16, 1024) | (2ull << 61);
+          dbh = dbl = umma::smem_desc(smem + OFF_RING, 16, 1024) | (2ull << 61);  // stays inside the ring whatever N
+          const uint64_t a_step = 2, b_step = 2;
+#else
           const uint64_t a_step = (2 * CORE) >> 4, b_step = kstep_b >> 4;
+#endif
           uint32_t acc = (ch.flags & F_OVERWRITE) ? 0u : 1u;
           const uint32_t lo_steps = ch.lo_steps, ksteps = ch.ksteps;
 #ifdef OAKB200_TC_NO_MMA  // timing experiment only: no tensor-core work is issued, results are garbage
@@ -419,8 +491,13 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #else
           for (uint32_t i = 0; i < ksteps; i++) {
 #endif
+#ifdef OAKB200_TC_WIDE_TIMING  // timing experiment only: A_hi x [B_hi | B_lo] as ONE instruction of twice the N, results are garbage
+            if (N <= 128) umma::mma_bf16(d, da, dbh, umma::idesc_bf16_f32(2 * N), acc);
+            else { umma::mma_bf16(d, da, dbh, idesc, acc); umma::mma_bf16(d, da, dbl, idesc, 1u); }
+#else
             umma::mma_bf16(d, da, dbh, idesc, acc);
             umma::mma_bf16(d, da, dbl, idesc, 1u);
+#endif
             if (i < lo_steps) umma::mma_bf16(d, dal, dbh, idesc, 1u);
             acc = 1u;
             da += a_step;
@@ -428,116 +505,45 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             dbh += b_step;
             dbl += b_step;
           }
+#ifdef OAKB200_TC_TIMING
+          tm_lap(tm_bin, 2);
+#endif
           if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
           else umma::mma_commit(bar_empty + 8 * slot);
           if (ch.flags & F_END_D) umma::mma_commit(bar_d);
           if (ch.flags & F_END_T) umma::mma_commit(bar_t);
+#ifdef OAKB200_TC_TIMING
+          tm_lap(tm_bin, 4);
+          if (ch.flags & F_END_D) { umma::mbar_wait(bar_d, tm_d & 1); tm_d++; tm_lap(tm_bin, 3); }
+          if (ch.flags & F_END_T) { umma::mbar_wait(bar_t, tm_t & 1); tm_t++; tm_lap(tm_bin, 3); }
+#endif
         }
       }
+#ifdef OAKB200_TC_TIMING
+      if (blockIdx.x == 0)
+        for (int b = 0; b < 4; b++)
+          printf("[eval_tc timing] N bin %d: wait workers %lld, wait weights %lld, issue %lld, drain %lld, commit %lld cycles\n", b, tm[b][0],
+                 tm[b][1], tm[b][2], tm[b][3], tm[b][4]);
+#endif
     }
-  } else {
-    // ===== workers: threads r and r + 128 share evaluation r of the tile = TMEM lane r; group 0 encodes, and the
-    // two groups split every epilogue by accumulator columns (a warp may touch TMEM lanes 32 * (warp % 4) .. + 31)
-    const int r = threadIdx.x & (ROWS - 1), grp = threadIdx.x >> 7;
-    uint32_t* col = reinterpret_cast<uint32_t*>(dsm + OFF_TILE) + r;
-    Mem<ROWS> m;
-    m.set(reinterpret_cast<uint8_t*>(col));
+  } else if (warp >= W_HEADS) {
+    // ===== head warps: thread r serves row r = TMEM lane r of the tile the workers have just finished: value head
+    // (32 -> 1) and the <= 9 legal rows of each policy head (64 -> 315), per-thread fp32 dot products, while the workers
+    // and the tensor pipe are already on the next tile.
+    const int r = 32 * (warp & 3) + lane;
     const float* cst = reinterpret_cast<const float*>(dsm + OFF_CONST);
     const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-    uint32_t dphase = 0, tphase = 0;
-    bool t_pending = false;
-    // discrete networks (P.act == 3): clamp in the embedding nets, embeddings / hp quantised to 0..127 (mode 1), the int8
-    // main net's ClippedReLU on exact integer accumulators (mode 2, act 4), outputs divided by 127 * 64
     const bool disc = P.act == 3;
-    const int act = disc ? 4 : P.act;  // activation of the main net's head hidden layers
-    const int m_emb = disc ? 1 : 0, m_main = disc ? 2 : 0;
+    const int act = disc ? 4 : P.act;
     const float out_div = disc ? 8128.0f : 1.0f;
-    const float act_bound = (P.act == 2 || disc) ? 1.0f : __int_as_float(0x7F800000);
-    auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
-      umma::tc_fence_before();
-      umma::fence_proxy_async();
-      umma::mbar_arrive(bar_a);
-    };
-    auto wait_d = [&]() {
-      umma::mbar_wait(bar_d, dphase & 1);
-      dphase++;
+    uint32_t iter = 0;
+    for (uint32_t tb = tile0; tb < ntiles; tb += tile_step, iter++) {
+      const uint32_t e = (tb + crank) * ROWS + (uint32_t)r;
+      umma::mbar_wait(bar_h, iter & 1);
       umma::tc_fence_after();
-    };
-    auto wait_t = [&]() {
-      if (t_pending) {
-        umma::mbar_wait(bar_t, tphase & 1);
-        tphase++;
-        t_pending = false;
-        umma::tc_fence_after();
-      }
-    };
-    for (uint32_t tb = tile0; tb < ntiles; tb += tile_step) {
-      const uint32_t t = tb + crank;
-      const uint32_t e = t * ROWS + (uint32_t)r;
-      const uint32_t ec = e < n ? e : n - 1;
-      asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory");  // the other group has finished with the previous tile
-      load_record_half(col, battles + (size_t)ec * 384, grp);
-      const uint2 durw = *reinterpret_cast<const uint2*>(durations + (size_t)ec * 8);
-      asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory");
-      for (int s = 0; s < 2; s++) {
-        const H sb = Mem<ROWS>::sb(s);
-        const uint32_t dur = s ? durw.y : durw.x;
-        for (int slot = 1; slot <= 6; slot++) {
-          const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
-          H pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
-          const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
-          const bool alive = hpv != 0;
-          float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
-          if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
-          const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
-          const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
-          if (slot == 1) {
-            if (grp == 0) build_active(smem, r, m, s, dur, alive);
-            wait_t();
-            publish();
-            wait_d();
-          }
-#ifndef OAKB200_TC_NO_BUILD  // timing experiment only
-          if (grp == 0) build_pokemon(smem, r, m, pk, sleep, alive);
-#endif
-          wait_t();
-          publish();
-          wait_d();
-          {
-            const float* b0 = cst + (slot == 1 ? C_AC0 : C_PK0);
-            epilogue_block(tl + D_WORK, 2 * grp, b0, act_bound, smem + A2_HI, smem + A2_LO, r);
-            epilogue_block(tl + D_WORK, 2 * grp + 1, b0, act_bound, smem + A2_HI, smem + A2_LO, r);
-          }
-          publish();
-          wait_d();
-          if (slot == 1) {  // 96 columns: group 0 takes 0..63, group 1 takes 64..95 (and the hp column aod >= 64 or not)
-            if (grp == 0) {
-              epilogue_block(tl + D_WORK, 0, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
-              epilogue_block(tl + D_WORK, 1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
-            } else {
-              epilogue_block(tl + D_WORK, 2, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, r, m_emb);
-            }
-            if ((P.aod >= 64) == (grp == 1)) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
-          } else {
-            epilogue_block(tl + D_WORK, grp, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, r, m_emb);
-            if ((P.pod >= 32) == (grp == 1)) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
-          }
-          publish();
-          t_pending = true;
-          if (slot == 1) wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
-        }
-      }
-      // ---- trunk (main-net.h:66-107)
-      wait_t();
-      epilogue_block(tl + D_TRUNK, grp, cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, r, m_main);
-      publish();
-      wait_d();
-      epilogue_block(tl + D_WORK, grp, cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, r, m_main);
-      publish();
-      wait_d();
-      if (grp == 0) {
+      {
         uint32_t v[32];
-        umma::tmem_ld32(tl + D_WORK, v);
+        umma::tmem_ld32(tl + D_HEADS, v);
         umma::tmem_ld_wait();
         float acc = cst[C_V3B];
 #pragma unroll
@@ -545,39 +551,28 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           if (j < P.vhd) acc = fmaf(actf(__uint_as_float(v[j]) + cst[C_HEADS + j], act), cst[C_V3W + j], acc);
         if (e < n) values[e] = 1.0f / (1.0f + expf(-(acc / out_div)));
       }
-      {
-        const int s = grp;  // group 0: player 1's policy head, group 1: player 2's
-        const uint32_t res = results[ec];
+#pragma unroll 1
+      for (int s = 0; s < 2; s++) {
         float h[64];
         {
           uint32_t v[32];
-          umma::tmem_ld32(tl + D_WORK + 32 + 64 * s, v);
+          umma::tmem_ld32(tl + D_HEADS + 32 + 64 * s, v);
           umma::tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; j++) h[j] = actf(__uint_as_float(v[j]) + cst[C_HEADS + 32 + 64 * s + j], act);
-          umma::tmem_ld32(tl + D_WORK + 64 + 64 * s, v);
+          umma::tmem_ld32(tl + D_HEADS + 64 + 64 * s, v);
           umma::tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; j++) h[32 + j] = actf(__uint_as_float(v[j]) + cst[C_HEADS + 64 + 64 * s + j], act);
         }
-        const uint64_t list = mem_choices(m, s, (res >> (4 + 2 * s)) & 3);
-        const int cnt = choice_count(list);
         const float* W = s == 0 ? P.p1bW : P.p2bW;
         const float* B = s == 0 ? P.p1bb : P.p2bb;
-        const H sb = Mem<ROWS>::sb(s);
+        const uint32_t ia = smem + OFF_ROWIDX + (uint32_t)((s * ROWS + r) * 24);
         for (int k = 0; k < 9; k++) {
+          uint32_t idx;
+          asm volatile("ld.shared.u16 %0, [%1];" : "=r"(idx) : "r"(ia + 2 * k) : "memory");
           float lg = 0.0f;
-          if (k < cnt) {
-            const uint32_t c = choice_at(list, k);
-            const uint32_t type = c & 3, data = c >> 2;
-            uint32_t idx = 0;  // policy.h:29-58
-            if (type == CH_MOVE) {
-              const uint32_t mid = data >= 1 ? m.ld8(m.stored(s), PK_MOVES + 2 * ((int)data - 1)) : 0;
-              idx = mid == 0 ? 0 : mid - 1;
-            } else if (type == CH_SWITCH) {
-              const uint32_t pid = m.ld8(sb, S_ORDER + (int)data - 1);
-              idx = 164 + m.ld8(Mem<ROWS>::pokemon(s, (int)pid - 1), PK_SPECIES) - 1;
-            }
+          if (idx != 0xFFFFu) {
             const float4* row = reinterpret_cast<const float4*>(W + (size_t)idx * P.pohd);
             float a0 = 0.0f, a1 = 0.0f;
 #pragma unroll
@@ -594,9 +589,178 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           }
           if (e < n) logits[(size_t)e * 18 + s * 9 + k] = lg;
         }
-        if (e < n) counts[(size_t)e * 2 + s] = (uint8_t)cnt;
       }
+      umma::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(bar_hfree);
     }
+  } else {
+    // ===== workers: threads r, r + 128, r + 256, r + 384 share evaluation r of the tile = TMEM lane r; group 0 writes the
+    // features, and the groups split every epilogue by accumulator columns (a warp may touch TMEM lanes
+    // 32 * (warp % 4) .. + 31)
+    const int r = threadIdx.x & (ROWS - 1), grp = threadIdx.x >> 7;
+    uint32_t* col = reinterpret_cast<uint32_t*>(dsm + OFF_TILE) + r;
+    Mem<ROWS> m;
+    m.set(reinterpret_cast<uint8_t*>(col));
+    const float* cst = reinterpret_cast<const float*>(dsm + OFF_CONST);
+    const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    uint32_t dphase = 0, tphase = 0, iter = 0;
+    bool t_pending = false;
+    // discrete networks (P.act == 3): clamp in the embedding nets, embeddings / hp quantised to 0..127 (mode 1), the int8
+    // main net's ClippedReLU on exact integer accumulators (mode 2, act 4), outputs divided by 127 * 64
+    const bool disc = P.act == 3;
+    const int act = disc ? 4 : P.act;  // activation of the main net's head hidden layers
+    const int m_emb = disc ? 1 : 0, m_main = disc ? 2 : 0;
+    const float out_div = disc ? 8128.0f : 1.0f;
+    const float act_bound = (P.act == 2 || disc) ? 1.0f : __int_as_float(0x7F800000);
+#ifdef OAKB200_TC_TIMING  // diagnostic build only: where a worker's time goes (thread 0 of CTA 0 prints)
+    long long wt[7] = {};  // waiting on MMAs, epilogues, publish, feature build, tile load, heads
+    long long wt_c = clock64();
+#define WT_LAP(k) do { const long long now_ = clock64(); wt[k] += now_ - wt_c; wt_c = now_; } while (0)
+#else
+#define WT_LAP(k) do { } while (0)
+#endif
+    auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
+      umma::tc_fence_before();
+      umma::fence_proxy_async();
+      __syncwarp();  // one arrival per warp
+      if (lane == 0) umma::mbar_arrive(bar_a);
+      WT_LAP(2);
+    };
+    auto wait_d = [&]() {
+      umma::mbar_wait(bar_d, dphase & 1);
+      dphase++;
+      umma::tc_fence_after();
+      WT_LAP(0);
+    };
+    auto wait_t = [&]() {
+      if (t_pending) {
+        umma::mbar_wait(bar_t, tphase & 1);
+        tphase++;
+        t_pending = false;
+        umma::tc_fence_after();
+        WT_LAP(0);
+      }
+    };
+    auto workers_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory"); };
+    // accumulator columns [c0, c1) of D (multiples of 16; 32-column blocks where aligned) -> activation -> operand planes
+    auto epi = [&](uint32_t dcol, int c0, int c1, const float* bias, float bound, uint32_t hi, uint32_t lo, int mode) {
+      int c = c0;
+      for (; c + 32 <= c1; c += 32) epilogue_block(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
+      if (c < c1) epilogue_half(tl + dcol, c >> 4, bias, bound, hi, lo, r, mode);
+      WT_LAP(1);
+    };
+    for (uint32_t tb = tile0; tb < ntiles; tb += tile_step) {
+      const uint32_t t = tb + crank;
+      const uint32_t e = t * ROWS + (uint32_t)r;
+      const uint32_t ec = e < n ? e : n - 1;
+      workers_sync();  // the other groups have finished with the previous tile
+      load_record_part(col, battles + (size_t)ec * 384, grp);
+      const uint2 durw = *reinterpret_cast<const uint2*>(durations + (size_t)ec * 8);
+      workers_sync();
+      WT_LAP(4);
+      for (int s = 0; s < 2; s++) {
+        const H sb = Mem<ROWS>::sb(s);
+        const uint32_t dur = s ? durw.y : durw.x;
+        for (int slot = 1; slot <= 6; slot++) {
+          const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
+          H pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
+          const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
+          const bool alive = hpv != 0;
+          float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
+          const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
+          const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
+          if (slot == 1) {
+            zero_features(smem, r, grp, 2, K_ACT / 8);
+            workers_sync();  // group 0's one-hot entries land on zeroed columns
+            if (grp == 0) build_active(smem, r, m, s, dur, alive);
+            WT_LAP(3);
+            wait_t();
+            publish();
+            wait_d();
+          }
+#ifndef OAKB200_TC_NO_BUILD  // timing experiment only
+          zero_features(smem, r, grp, 1, K_POK / 8);
+          workers_sync();
+          if (grp == 0) build_pokemon(smem, r, m, pk, sleep, alive);
+#endif
+          WT_LAP(3);
+          wait_t();
+          publish();
+          wait_d();
+          epi(D_WORK, (128 / GROUPS) * grp, (128 / GROUPS) * (grp + 1), cst + (slot == 1 ? C_AC0 : C_PK0), act_bound, smem + A2_HI,
+              smem + A2_LO, 0);
+          publish();
+          wait_d();
+          if (slot == 1) {  // 96 columns: 64 + 32 (two groups) or 32 + 32 + 32 + none; the hp column goes with its block's thread
+            const int c0 = GROUPS == 2 ? 64 * grp : 32 * grp, c1 = GROUPS == 2 ? (grp ? 96 : 64) : (grp < 3 ? c0 + 32 : c0);
+            epi(D_WORK, c0, c1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, m_emb);
+            if (P.aod >= c0 && P.aod < c1) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
+          } else {          // 64 columns
+            const int c0 = (64 / GROUPS) * grp, c1 = c0 + 64 / GROUPS;
+            epi(D_WORK, c0, c1, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, m_emb);
+            if (P.pod >= c0 && P.pod < c1) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
+          }
+          publish();
+          t_pending = true;
+          if (slot == 1) wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
+        }
+      }
+      // ---- trunk (main-net.h:66-107)
+      wait_t();
+      epi(D_TRUNK, (64 / GROUPS) * grp, (64 / GROUPS) * (grp + 1), cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, m_main);
+      publish();
+      wait_d();
+      epi(D_WORK, (64 / GROUPS) * grp, (64 / GROUPS) * (grp + 1), cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, m_main);
+      // The head warps read the previous tile's head accumulators and row indices while this tile runs; both are rewritten
+      // from here on (a fresh barrier passes the parity-1 wait of the first tile).
+      umma::mbar_wait(bar_hfree, (iter + 1) & 1);
+      WT_LAP(6);
+      publish();
+      wait_d();
+      // Policy heads (policy.h:29-58), worker part: legal choices -> row indices of the last layer. The dot products
+      // themselves (one 256-byte weight row per legal choice, gathered from L2) are latency-bound, 15 % of the tile time
+      // when the workers did them (profiles/r1o_eval_tc_timing.txt): the head warps run them off the critical path.
+      if (grp < 2) {
+        const int s = grp;
+        const uint32_t res = results[ec];
+        const uint64_t list = mem_choices(m, s, (res >> (4 + 2 * s)) & 3);
+        const int cnt = choice_count(list);
+        const H sb = Mem<ROWS>::sb(s);
+        uint32_t idx[12];
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+          idx[k] = 0xFFFFu;
+          if (k < 9 && k < cnt) {
+            const uint32_t c = choice_at(list, k);
+            const uint32_t type = c & 3, data = c >> 2;
+            idx[k] = 0;
+            if (type == CH_MOVE) {
+              const uint32_t mid = data >= 1 ? m.ld8(m.stored(s), PK_MOVES + 2 * ((int)data - 1)) : 0;
+              idx[k] = mid == 0 ? 0 : mid - 1;
+            } else if (type == CH_SWITCH) {
+              const uint32_t pid = m.ld8(sb, S_ORDER + (int)data - 1);
+              idx[k] = 164 + m.ld8(Mem<ROWS>::pokemon(s, (int)pid - 1), PK_SPECIES) - 1;
+            }
+          }
+        }
+        const uint32_t ia = smem + OFF_ROWIDX + (uint32_t)((s * ROWS + r) * 24);
+#pragma unroll
+        for (int k = 0; k < 6; k++) asm volatile("st.shared.u32 [%0], %1;" ::"r"(ia + 4 * k), "r"(idx[2 * k] | (idx[2 * k + 1] << 16)) : "memory");
+        if (e < n) counts[(size_t)e * 2 + s] = (uint8_t)cnt;
+        umma::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bar_h);
+      }
+      iter++;
+      WT_LAP(5);
+    }
+#ifdef OAKB200_TC_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+      printf("[eval_tc timing] worker 0: waiting on MMAs %lld, epilogues %lld, publish %lld, feature build %lld, tile load %lld, wait for the head warps %lld, row indices %lld cycles\n",
+             wt[0], wt[1], wt[2], wt[3], wt[4], wt[6], wt[5]);
+#endif
   }
   umma::tc_fence_before();
   __syncthreads();
