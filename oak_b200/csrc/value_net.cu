@@ -580,8 +580,11 @@ cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
   for (int idx = 0; idx < 229; idx++) inv_act[tc::act_col(idx)] = idx;
   const int phd = d.phd, pod = d.pod, ahd = d.ahd, aod = d.aod, hd = d.hd, in = d.in;
   const PackedMatrix ac0a = P.matrix(128, tc::K_ACT, [&](int o, int k) { return o < ahd && inv_act[k] >= 0 ? rdf(a[2].w, (size_t)o * 427 + inv_act[k]) : 0.0f; });
-  const PackedMatrix ac0p = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < ahd && k < 198 ? rdf(a[2].w, (size_t)o * 427 + 229 + k) : 0.0f; });
-  const PackedMatrix pk0 = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < phd && k < 198 ? rdf(a[0].w, (size_t)o * 198 + k) : 0.0f; });
+  int inv_pok[tc::K_POK];
+  for (int k = 0; k < tc::K_POK; k++) inv_pok[k] = -1;
+  for (int idx = 0; idx < 198; idx++) inv_pok[tc::pok_col(idx)] = idx;
+  const PackedMatrix ac0p = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < ahd && inv_pok[k] >= 0 ? rdf(a[2].w, (size_t)o * 427 + 229 + inv_pok[k]) : 0.0f; });
+  const PackedMatrix pk0 = P.matrix(128, tc::K_POK, [&](int o, int k) { return o < phd && inv_pok[k] >= 0 ? rdf(a[0].w, (size_t)o * 198 + inv_pok[k]) : 0.0f; });
   const PackedMatrix pk1 = P.matrix(64, 128, [&](int o, int k) { return o < pod && k < phd ? rdf(a[1].w, (size_t)o * phd + k) : 0.0f; });
   const PackedMatrix ac1 = P.matrix(96, 128, [&](int o, int k) { return o < aod && k < ahd ? rdf(a[3].w, (size_t)o * ahd + k) : 0.0f; });
   // fc0 column slices: operand column k < od is embedding output k, column od is the hp fraction (network.h:131-175)

@@ -60,7 +60,10 @@ const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden) 
 const uint32_t OFF_EMB = 65536;      // benched-Pokemon embedding / second trunk operand
 const uint32_t OFF_TILE = 98304;     // 128 battle records as word-transposed columns (gen1_state.cuh)
 const uint32_t OFF_RING = 147456;    // weight chunk ring
-const uint32_t RING_SLOT = 16384, RING_SLOTS = 4;
+#ifndef OAKB200_TC_RING_SLOTS
+#define OAKB200_TC_RING_SLOTS 2
+#endif
+const uint32_t RING_SLOTS = OAKB200_TC_RING_SLOTS, RING_SLOT = 65536 / RING_SLOTS;  // 4 x 16 KB or 2 x 32 KB
 const uint32_t OFF_PROG = OFF_RING + RING_SLOTS * RING_SLOT;
 const uint32_t PROG_MAX = 192;
 const uint32_t OFF_CONST = OFF_PROG + PROG_MAX * 16;
@@ -86,15 +89,26 @@ const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // on
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
 const int K_POK = 208, K_ACT = 240;
 
-// feature column of the Active block after the host-side permutation (real-valued columns first)
-__host__ __device__ inline int act_col(int idx) {
-  if (idx < 5) return idx;         // stats
-  if (idx < 20) return idx + 11;   // types      5..19  -> 16..30
-  if (idx < 26) return idx - 15;   // boosts    20..25  ->  5..10
-  if (idx < 42) return idx + 5;    // flags     26..41  -> 31..46
-  if (idx < 45) return idx - 31;   // state/substitute/toxic 42..44 -> 11..13
-  return idx + 2;                  // moves, durations  45..228 -> 47..230
+// Feature columns after the host-side permutation. Every block of columns starts on a core column (8 columns), the
+// real-valued columns come first (they alone need an A lo plane) and the move block comes last, so that two worker
+// groups can each zero-fill and write their own core columns without meeting: group 0 everything but the moves, group 1
+// the moves.
+__host__ __device__ inline int act_col(int idx) {   // Active block (battle.h:480-489), 229 -> K_ACT = 240
+  if (idx < 5) return idx;           // stats                          0..4   ->   0..4
+  if (idx < 20) return idx + 11;     // types                          5..19  ->  16..30
+  if (idx < 26) return idx - 15;     // boosts                        20..25  ->   5..10
+  if (idx < 42) return idx + 6;      // flags                         26..41  ->  32..47
+  if (idx < 45) return idx - 31;     // state / substitute / toxic    42..44  ->  11..13
+  if (idx < 209) return idx + 27;    // moves                         45..208 ->  72..235
+  return idx - 161;                  // durations                    209..228 ->  48..67
 }
+__host__ __device__ inline int pok_col(int idx) {   // Pokemon block (battle.h:208-214), 198 -> K_POK = 208
+  if (idx < 5) return idx;           // stats                          0..4   ->   0..4
+  if (idx < 169) return idx + 3;     // moves                          5..168 ->   8..171
+  if (idx < 183) return idx + 7;     // status                       169..182 -> 176..189
+  return idx + 9;                    // types                        183..197 -> 192..206
+}
+const int POK_MOVE_CORE0 = 1, POK_MOVE_CORE1 = 22, ACT_MOVE_CORE0 = 9, ACT_MOVE_CORE1 = 30;  // core columns of the move blocks
 
 struct Params {
   const uint8_t* wpack;
@@ -168,14 +182,26 @@ __device__ __forceinline__ void put_moves(uint32_t plane, int r, int col0, const
   }
 }
 
-// Pokemon block (battle.h:208-214): K = 208, columns as in the reference (stats 0-4 are the real-valued ones)
-// zero-fill of a feature tile, split by core columns over the groups (c0 = first core column not written by q.store)
-__device__ __forceinline__ void zero_features(uint32_t smem, int r, int grp, int c0, int cores) {
-  const uint32_t hi = smem + A1_HI;
-  for (int c = c0 + grp; c < cores; c += GROUPS) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
+__device__ __forceinline__ void zero_cores(uint32_t hi, int r, int c0, int c1) {
+  for (int c = c0; c < c1; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
 }
-__device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<ROWS>& m, H pk, uint32_t sleep, bool alive) {
+// Pokemon block, pok_col() column order: group 0 writes stats / status / types, group 1 the moves
+__device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<ROWS>& m, H pk, uint32_t sleep, bool alive, int grp) {
   const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+  if (grp == 1) {
+    zero_cores(hi, r, POK_MOVE_CORE0, POK_MOVE_CORE1);
+    if (!alive) return;
+    uint32_t id[4], pp[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      id[k] = m.ld8(pk, PK_MOVES + 2 * k);
+      pp[k] = m.ld8(pk, PK_MOVES + 2 * k + 1);
+    }
+    put_moves(hi, r, 8, id, pp);
+    return;
+  }
+  if (grp != 0) return;
+  zero_cores(hi, r, POK_MOVE_CORE1, K_POK / 8);
   stv4(lo + (uint32_t)((ROWS + r) << 4), 0, 0, 0, 0);
   Row8 q;
   q.h[2] = q.h[3] = q.l[2] = q.l[3] = 0;
@@ -187,23 +213,31 @@ __device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<RO
 #pragma unroll
   for (int c = 0; c < 5; c++) q.set(c, (float)m.ld16(pk, PK_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
   q.store(hi, lo, 0, r);
-  uint32_t id[4], pp[4];
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    id[k] = m.ld8(pk, PK_MOVES + 2 * k);
-    pp[k] = m.ld8(pk, PK_MOVES + 2 * k + 1);
-  }
-  put_moves(hi, r, 5, id, pp);
   const uint32_t st = m.ld8(pk, PK_STATUS);
-  if (st) st16(elem(hi, r, 169 + status_index(st, sleep)), 0x3F80u);
+  if (st) st16(elem(hi, r, 176 + status_index(st, sleep)), 0x3F80u);
   const uint32_t ty = m.ld8(pk, PK_TYPES), t1 = ty & 15u, t2 = ty >> 4;
-  st16(elem(hi, r, 183 + (int)t1), 0x3F80u);
-  if (t2 != t1) st16(elem(hi, r, 183 + (int)t2), 0x3F80u);
+  st16(elem(hi, r, 192 + (int)t1), 0x3F80u);
+  if (t2 != t1) st16(elem(hi, r, 192 + (int)t2), 0x3F80u);
 }
 
-// Active block (battle.h:480-489) with the act_col() column order: K = 240, real-valued columns 0-13
-__device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROWS>& m, int s, uint32_t dur, bool alive) {
+// Active block, act_col() column order: group 0 writes everything but the moves, group 1 the moves
+__device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROWS>& m, int s, uint32_t dur, bool alive, int grp) {
   const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+  const H sb = Mem<ROWS>::sb(s);
+  if (grp == 1) {
+    zero_cores(hi, r, ACT_MOVE_CORE0, ACT_MOVE_CORE1);
+    if (!alive) return;
+    uint32_t id[4], pp[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      id[k] = m.ld8(sb, A_MOVES + 2 * k);
+      pp[k] = m.ld8(sb, A_MOVES + 2 * k + 1);
+    }
+    put_moves(hi, r, 72, id, pp);
+    return;
+  }
+  if (grp != 0) return;
+  zero_cores(hi, r, 2, ACT_MOVE_CORE0);
   Row8 q0, q1;
   if (!alive) {
 #pragma unroll
@@ -212,7 +246,6 @@ __device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROW
     q1.store(hi, lo, 1, r);
     return;
   }
-  const H sb = Mem<ROWS>::sb(s);
 #pragma unroll
   for (int c = 0; c < 5; c++) q0.set(c, (float)m.ld16(sb, A_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
   const uint32_t b = m.ld32(sb, A_BOOSTS) & 0xFFFFFFu;
@@ -244,20 +277,13 @@ __device__ __forceinline__ void build_active(uint32_t smem, int r, const Mem<ROW
   while (fl) {
     const int j = __ffs(fl) - 1;
     fl &= fl - 1;
-    st16(elem(hi, r, 31 + j), 0x3F80u);
+    st16(elem(hi, r, 32 + j), 0x3F80u);
   }
-  uint32_t id[4], pp[4];
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    id[k] = m.ld8(sb, A_MOVES + 2 * k);
-    pp[k] = m.ld8(sb, A_MOVES + 2 * k + 1);
-  }
-  put_moves(hi, r, 47, id, pp);
   uint32_t n;
-  if ((n = bf_get(dur, DF_CONFUSION)) != 0) st16(elem(hi, r, 211 + (int)n - 1), 0x3F80u);
-  if ((n = bf_get(dur, DF_DISABLE)) != 0) st16(elem(hi, r, 216 + (int)n - 1), 0x3F80u);
-  if ((n = bf_get(dur, DF_ATTACKING)) != 0) st16(elem(hi, r, 224 + (int)n - 1), 0x3F80u);
-  if ((n = bf_get(dur, DF_BINDING)) != 0) st16(elem(hi, r, 227 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_CONFUSION)) != 0) st16(elem(hi, r, 48 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_DISABLE)) != 0) st16(elem(hi, r, 53 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_ATTACKING)) != 0) st16(elem(hi, r, 61 + (int)n - 1), 0x3F80u);
+  if ((n = bf_get(dur, DF_BINDING)) != 0) st16(elem(hi, r, 64 + (int)n - 1), 0x3F80u);
 }
 
 // two fp32 -> packed split-bf16: hi = {bf16(x1), bf16(x0)}, lo = the rounded residuals (x0 in the low half)
@@ -609,9 +635,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // discrete networks (P.act == 3): clamp in the embedding nets, embeddings / hp quantised to 0..127 (mode 1), the int8
     // main net's ClippedReLU on exact integer accumulators (mode 2, act 4), outputs divided by 127 * 64
     const bool disc = P.act == 3;
-    const int act = disc ? 4 : P.act;  // activation of the main net's head hidden layers
     const int m_emb = disc ? 1 : 0, m_main = disc ? 2 : 0;
-    const float out_div = disc ? 8128.0f : 1.0f;
     const float act_bound = (P.act == 2 || disc) ? 1.0f : __int_as_float(0x7F800000);
 #ifdef OAKB200_TC_TIMING  // diagnostic build only: where a worker's time goes (thread 0 of CTA 0 prints)
     long long wt[7] = {};  // waiting on MMAs, epilogues, publish, feature build, tile load, heads
@@ -672,18 +696,14 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
           const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
           if (slot == 1) {
-            zero_features(smem, r, grp, 2, K_ACT / 8);
-            workers_sync();  // group 0's one-hot entries land on zeroed columns
-            if (grp == 0) build_active(smem, r, m, s, dur, alive);
+            build_active(smem, r, m, s, dur, alive, grp);
             WT_LAP(3);
             wait_t();
             publish();
             wait_d();
           }
 #ifndef OAKB200_TC_NO_BUILD  // timing experiment only
-          zero_features(smem, r, grp, 1, K_POK / 8);
-          workers_sync();
-          if (grp == 0) build_pokemon(smem, r, m, pk, sleep, alive);
+          build_pokemon(smem, r, m, pk, sleep, alive, grp);
 #endif
           WT_LAP(3);
           wait_t();
