@@ -456,7 +456,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     }
   } else if (warp == W_MMA) {
     // ===== MMA issuer =====
-    if (lane == 0) {
+    if (umma::elect_one()) {
       uint32_t g = 0, stage = 0;
 #ifdef OAKB200_TC_TIMING  // diagnostic build only: where the issuer's time goes, by N of the stage (printed by CTA 0)
       long long tm[4][5] = {};  // [N bin][wait workers, wait weights, issue, drain, commit]
