@@ -185,39 +185,74 @@ __device__ __forceinline__ void put_moves(uint32_t plane, int r, int col0, const
 __device__ __forceinline__ void zero_cores(uint32_t hi, int r, int c0, int c1) {
   for (int c = c0; c < c1; c++) stv4(hi + (uint32_t)((c * ROWS + r) << 4), 0, 0, 0, 0);
 }
-// Pokemon block, pok_col() column order: group 0 writes stats / status / types, group 1 the moves
-__device__ __forceinline__ void build_pokemon(uint32_t smem, int r, const Mem<ROWS>& m, H pk, uint32_t sleep, bool alive, int grp) {
-  const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+// Pokemon block, pok_col() column order: group 0 writes stats / status / types, group 1 the moves. Two steps so that the
+// loads, divisions and conversions of the NEXT slot run while this slot's first-layer MMAs do (the workers only wait
+// then); what is left on the critical path is the stores.
+struct PokemonFeatures {
+  Row8 q;            // group 0: core column 0 (the five stats)
+  uint32_t at[4];    // shared-memory addresses of up to four one-hot entries (0 = none) ...
+  uint32_t val[4];   // ... and their bf16 values (1.0, or the count of a duplicated move)
+};
+__device__ __forceinline__ void prepare_pokemon(PokemonFeatures& f, uint32_t smem, int r, const Mem<ROWS>& m, int s, int slot,
+                                                uint32_t dur, int grp) {
+  const uint32_t hi = smem + A1_HI;
+  const uint32_t id0 = m.ld8(Mem<ROWS>::sb(s), S_ORDER + slot - 1);
+  const H pk = Mem<ROWS>::pokemon(s, id0 ? (int)id0 - 1 : 0);
+  const bool alive = id0 != 0 && m.ld16(pk, PK_HP) != 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) { f.at[k] = 0; f.val[k] = 0x3F80u; }
+#pragma unroll
+  for (int k = 0; k < 4; k++) f.q.h[k] = f.q.l[k] = 0;
+  if (!alive) return;
   if (grp == 1) {
-    zero_cores(hi, r, POK_MOVE_CORE0, POK_MOVE_CORE1);
-    if (!alive) return;
     uint32_t id[4], pp[4];
+    bool ok[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       id[k] = m.ld8(pk, PK_MOVES + 2 * k);
       pp[k] = m.ld8(pk, PK_MOVES + 2 * k + 1);
+      ok[k] = id[k] != MOVE_None && id[k] != MOVE_Struggle && pp[k] != 0;
     }
-    put_moves(hi, r, 8, id, pp);
-    return;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {  // as put_moves: duplicates add up on their first occurrence
+      int cnt = 0;
+      bool first = ok[k];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const bool same = ok[j] && id[j] == id[k];
+        cnt += same ? 1 : 0;
+        if (j < k && same) first = false;
+      }
+      if (first) {
+        f.at[k] = elem(hi, r, 8 + (int)id[k] - 1);
+        f.val[k] = bf16_count(cnt);
+      }
+    }
+  } else if (grp == 0) {
+#pragma unroll
+    for (int c = 0; c < 5; c++) f.q.set(c, (float)m.ld16(pk, PK_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
+    const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
+    const uint32_t st = m.ld8(pk, PK_STATUS);
+    if (st) f.at[0] = elem(hi, r, 176 + status_index(st, sleep));
+    const uint32_t ty = m.ld8(pk, PK_TYPES), t1 = ty & 15u, t2 = ty >> 4;
+    f.at[1] = elem(hi, r, 192 + (int)t1);
+    if (t2 != t1) f.at[2] = elem(hi, r, 192 + (int)t2);
   }
-  if (grp != 0) return;
-  zero_cores(hi, r, POK_MOVE_CORE1, K_POK / 8);
-  stv4(lo + (uint32_t)((ROWS + r) << 4), 0, 0, 0, 0);
-  Row8 q;
-  q.h[2] = q.h[3] = q.l[2] = q.l[3] = 0;
-  if (!alive) {
-    q.h[0] = q.h[1] = q.l[0] = q.l[1] = 0;
-    q.store(hi, lo, 0, r);
+}
+__device__ __forceinline__ void emit_pokemon(const PokemonFeatures& f, uint32_t smem, int r, int grp) {
+  const uint32_t hi = smem + A1_HI, lo = smem + A1_LO;
+  if (grp == 1) {
+    zero_cores(hi, r, POK_MOVE_CORE0, POK_MOVE_CORE1);
+  } else if (grp == 0) {
+    zero_cores(hi, r, POK_MOVE_CORE1, K_POK / 8);
+    stv4(lo + (uint32_t)((ROWS + r) << 4), 0, 0, 0, 0);
+    f.q.store(hi, lo, 0, r);
+  } else {
     return;
   }
 #pragma unroll
-  for (int c = 0; c < 5; c++) q.set(c, (float)m.ld16(pk, PK_STATS + 2 * c) / (c == 0 ? 703.0f : 999.0f));
-  q.store(hi, lo, 0, r);
-  const uint32_t st = m.ld8(pk, PK_STATUS);
-  if (st) st16(elem(hi, r, 176 + status_index(st, sleep)), 0x3F80u);
-  const uint32_t ty = m.ld8(pk, PK_TYPES), t1 = ty & 15u, t2 = ty >> 4;
-  st16(elem(hi, r, 192 + (int)t1), 0x3F80u);
-  if (t2 != t1) st16(elem(hi, r, 192 + (int)t2), 0x3F80u);
+  for (int k = 0; k < 4; k++)
+    if (f.at[k]) st16(f.at[k], f.val[k]);
 }
 
 // Active block, act_col() column order: group 0 writes everything but the moves, group 1 the moves
@@ -683,6 +718,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       const uint2 durw = *reinterpret_cast<const uint2*>(durations + (size_t)ec * 8);
       workers_sync();
       WT_LAP(4);
+      PokemonFeatures feat;
       for (int s = 0; s < 2; s++) {
         const H sb = Mem<ROWS>::sb(s);
         const uint32_t dur = s ? durw.y : durw.x;
@@ -694,20 +730,23 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
           if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
           const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
-          const uint32_t sleep = (dur >> (3 * (slot - 1))) & 7u;
           if (slot == 1) {
             build_active(smem, r, m, s, dur, alive, grp);
             WT_LAP(3);
             wait_t();
             publish();
+            prepare_pokemon(feat, smem, r, m, s, 1, dur, grp);  // under the Active block's MMAs
+            WT_LAP(3);
             wait_d();
           }
 #ifndef OAKB200_TC_NO_BUILD  // timing experiment only
-          build_pokemon(smem, r, m, pk, sleep, alive, grp);
+          emit_pokemon(feat, smem, r, grp);  // slots 2..6 were prepared under the previous slot's first-layer MMAs
 #endif
           WT_LAP(3);
           wait_t();
           publish();
+          if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);
+          WT_LAP(3);
           wait_d();
           epi(D_WORK, (128 / GROUPS) * grp, (128 / GROUPS) * (grp + 1), cst + (slot == 1 ? C_AC0 : C_PK0), act_bound, smem + A2_HI,
               smem + A2_LO, 0);
