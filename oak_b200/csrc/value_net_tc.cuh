@@ -494,30 +494,29 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     if (umma::elect_one()) {
       uint32_t g = 0, stage = 0;
 #ifdef OAKB200_TC_TIMING  // diagnostic build only: where the issuer's time goes, by N of the stage (printed by CTA 0)
-      long long tm[4][5] = {};  // [N bin][wait workers, wait weights, issue, drain, commit]
+      long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0, tm4 = 0;  // wait workers, wait weights, issue, drain, commit
       uint32_t tm_d = 0, tm_t = 0;
       long long tm_c = clock64();
-      auto tm_lap = [&](int bin, int what) { const long long now = clock64(); tm[bin][what] += now - tm_c; tm_c = now; };
+#define TM_LAP(acc) do { const long long now_ = clock64(); acc += now_ - tm_c; tm_c = now_; } while (0)
 #endif
       for (uint32_t t = tile0; t < ntiles; t += tile_step) {
         for (int c = 0; c < P.nchunks; c++, g++) {
           const Chunk ch = prog[c];
 #ifdef OAKB200_TC_TIMING
-          const int tm_bin = ch.n8 == 16 ? 0 : ch.n8 == 8 ? 1 : ch.n8 == 12 ? 2 : 3;
-          tm_lap(tm_bin, 2);
+          TM_LAP(tm2);
 #endif
           if (ch.flags & F_STAGE_BEGIN) {
             umma::mbar_wait(bar_a, stage & 1);
             stage++;
           }
 #ifdef OAKB200_TC_TIMING
-          tm_lap(tm_bin, 0);
+          TM_LAP(tm0);
 #endif
           const uint32_t slot = g & (RING_SLOTS - 1);
           umma::mbar_wait(bar_full + 8 * slot, (g / RING_SLOTS) & 1);
           umma::tc_fence_after();
 #ifdef OAKB200_TC_TIMING
-          tm_lap(tm_bin, 1);
+          TM_LAP(tm1);
 #endif
           const uint32_t N = (uint32_t)ch.n8 << 3;
           const uint32_t idesc = umma::idesc_bf16_f32(N);
@@ -567,24 +566,23 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             dbl += b_step;
           }
 #ifdef OAKB200_TC_TIMING
-          tm_lap(tm_bin, 2);
+          TM_LAP(tm2);
 #endif
           if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
           else umma::mma_commit(bar_empty + 8 * slot);
           if (ch.flags & F_END_D) umma::mma_commit(bar_d);
           if (ch.flags & F_END_T) umma::mma_commit(bar_t);
 #ifdef OAKB200_TC_TIMING
-          tm_lap(tm_bin, 4);
-          if (ch.flags & F_END_D) { umma::mbar_wait(bar_d, tm_d & 1); tm_d++; tm_lap(tm_bin, 3); }
-          if (ch.flags & F_END_T) { umma::mbar_wait(bar_t, tm_t & 1); tm_t++; tm_lap(tm_bin, 3); }
+          TM_LAP(tm4);
+          if (ch.flags & F_END_D) { umma::mbar_wait(bar_d, tm_d & 1); tm_d++; TM_LAP(tm3); }
+          if (ch.flags & F_END_T) { umma::mbar_wait(bar_t, tm_t & 1); tm_t++; TM_LAP(tm3); }
 #endif
         }
       }
 #ifdef OAKB200_TC_TIMING
       if (blockIdx.x == 0)
-        for (int b = 0; b < 4; b++)
-          printf("[eval_tc timing] N bin %d: wait workers %lld, wait weights %lld, issue %lld, drain %lld, commit %lld cycles\n", b, tm[b][0],
-                 tm[b][1], tm[b][2], tm[b][3], tm[b][4]);
+        printf("[eval_tc timing] issuer: wait workers %lld, wait weights %lld, issue %lld, drain %lld, commit %lld cycles\n", tm0, tm1, tm2,
+               tm3, tm4);
 #endif
     }
   } else if (warp >= W_HEADS) {
