@@ -319,19 +319,29 @@ def main():
     pool = np.array(_json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
     SP_G, SP_STEPS = 16384, 96
     sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
-    sp.run(16)  # warm-up
+
+    def sp_pass():
+        t_pass = time.perf_counter()
+        streams, games = [], 0
+        for s_ in range(SP_STEPS):
+            sp.step()
+            if (s_ + 1) % 8 == 0:
+                st_, g_ = sp.collect()
+                streams.append(st_)
+                games += g_
+        t_gen = time.perf_counter()
+        local = np.concatenate(streams) if streams else np.empty(0, np.uint8)
+        out = gather_streams(local, dst=0, device=dev)
+        if os.environ.get("OAKB200_BENCH_DEBUG"):
+            print(f"[bench] rank {rank} self-play pass: generate + drain {t_gen - t_pass:.3f} s, gather {time.perf_counter() - t_gen:.3f} s, "
+                  f"{local.size} stream bytes", file=sys.stderr, flush=True)
+        return local, games, out
+
+    sp_pass()  # warm-up: the same pass (the writer rank's page-locked gather buffer is allocated here, once)
     barrier()
     l0 = sp.eng.launch_count
     t0 = time.perf_counter()
-    sp_streams, sp_games = [], 0
-    for s_ in range(SP_STEPS):
-        sp.step()
-        if (s_ + 1) % 8 == 0:
-            st_, g_ = sp.collect()
-            sp_streams.append(st_)
-            sp_games += g_
-    local_stream = np.concatenate(sp_streams) if sp_streams else np.empty(0, np.uint8)
-    gathered = gather_streams(local_stream, dst=0, device=dev)
+    local_stream, sp_games, gathered = sp_pass()
     barrier()
     sp_s = time.perf_counter() - t0
     launches += sp.eng.launch_count - l0
