@@ -317,35 +317,31 @@ def main():
     import json as _json
     from oak_b200.selfplay import SelfPlay
     pool = np.array(_json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
-    SP_G, SP_STEPS = 16384, 96
+    SP_G, SP_STEPS = 65536, 96
     sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
 
     def sp_pass():
-        t_pass = time.perf_counter()
-        streams, games = [], 0
+        # every drain goes to the writer rank as it is produced (one gather per drain), as a running generator would
+        streams, games, at_writer = [], 0, 0
         for s_ in range(SP_STEPS):
             sp.step()
             if (s_ + 1) % 8 == 0:
-                st_, g_ = sp.collect()
-                streams.append(st_)
+                st_, g_ = sp.collect(device=True)  # the drained stream stays on the device until the writer rank has it
+                streams.append(st_.clone())
                 games += g_
-        t_gen = time.perf_counter()
-        local = np.concatenate(streams) if streams else np.empty(0, np.uint8)
-        out = gather_streams(local, dst=0, device=dev)
-        if os.environ.get("OAKB200_BENCH_DEBUG"):
-            print(f"[bench] rank {rank} self-play pass: generate + drain {t_gen - t_pass:.3f} s, gather {time.perf_counter() - t_gen:.3f} s, "
-                  f"{local.size} stream bytes", file=sys.stderr, flush=True)
-        return local, games, out
+                got = gather_streams(st_, dst=0, device=dev)
+                at_writer += sum(len(x) for x in got) if got is not None else 0
+        return streams, games, at_writer
 
     sp_pass()  # warm-up: the same pass (the writer rank's page-locked gather buffer is allocated here, once)
     barrier()
     l0 = sp.eng.launch_count
     t0 = time.perf_counter()
-    local_stream, sp_games, gathered = sp_pass()
+    sp_streams, sp_games, sp_bytes = sp_pass()
     barrier()
     sp_s = time.perf_counter() - t0
+    local_stream = torch.cat(sp_streams).cpu().numpy() if sp_streams else np.empty(0, np.uint8)
     launches += sp.eng.launch_count - l0
-    sp_bytes = sum(len(x) for x in gathered) if gathered is not None else 0
 
     # ---- secondary: training rows (pyoak EncodedBattleFrames.from_bytes / sample): the games this rank's
     # self-play finishes are replayed on the device and encoded into the learner's dense tensors. Input: the self-play

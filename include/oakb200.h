@@ -194,8 +194,9 @@ int oakb200_selfplay_step_device(oakb200_ctx* ctx, size_t n, void* battles, void
                                  void* logits, void* eval_counts, void* probs, void* c1, void* c2, void* before);
 /* Finished games waiting to be drained / games dropped for length so far (synchronises). */
 int oakb200_frames_pending(oakb200_ctx* ctx, uint32_t* finished, uint32_t* dropped);
-/* Pack the finished games in slot order into out[cap] (HOST), free their slots. *bytes = stream length (also set when
- * the call fails with OAKB200_ECAPACITY), *games = how many games it holds. */
+/* Pack the finished games in slot order into out[cap] (HOST or DEVICE memory: a device buffer keeps the stream on the GPU
+ * for a gather over NCCL), free their slots. *bytes = stream length (also set when the call fails with
+ * OAKB200_ECAPACITY, which consumes nothing), *games = how many games it holds. */
 int oakb200_frames_drain(oakb200_ctx* ctx, uint8_t* out, size_t cap, size_t* bytes, uint32_t* games);
 
 /* ---- batched-leaf tree search: host trees + bandits, GPU battle operations -----------------------------------------

@@ -334,7 +334,7 @@ int oakb200_frames_drain(oakb200_ctx* ctx, uint8_t* out, size_t cap, size_t* byt
   ctx->launches++;
   CU(ctx, cudaGetLastError());
   CU(ctx, cudaMemsetAsync(f->counters, 0, 4, ctx->stream));
-  CU(ctx, cudaMemcpyAsync(out, f->pack, total, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(out, f->pack, total, cudaMemcpyDefault, ctx->stream));  // `out` may be host or device memory
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   return OAKB200_OK;
 }

@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-from .engine import BattleEngine
+from .engine import BattleEngine, OakB200Error
 
 MASK64 = (1 << 64) - 1
 
@@ -136,9 +136,21 @@ class SelfPlay:
                                       self.c1, self.c2, self.before)
         self.step_index += 1
 
-    def collect(self):
-        """Drain finished games -> (stream, games) and restart their slots."""
-        stream, games = self.eng.frames_drain()
+    def collect(self, device=False):
+        """Drain finished games -> (stream, games) and restart their slots. device=True leaves the stream in device memory
+        (a torch uint8 tensor, valid until the next collect) for sharding.gather_streams."""
+        if device:
+            buf = getattr(self, "_drain_dev", None)
+            if buf is None:
+                buf = self._drain_dev = self.torch.empty(64 << 20, dtype=self.torch.uint8, device=self.dev)
+            try:
+                stream, games = self.eng.frames_drain(out=buf)
+            except OakB200Error:
+                # too small (a failed drain consumes nothing): grow and retry
+                buf = self._drain_dev = self.torch.empty(4 * buf.numel(), dtype=self.torch.uint8, device=self.dev)
+                stream, games = self.eng.frames_drain(out=buf)
+        else:
+            stream, games = self.eng.frames_drain()
         ended = (self.results.cpu().numpy() & 15) != 0
         self.updates += int((~ended).sum())
         self._refill(ended)

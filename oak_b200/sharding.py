@@ -54,65 +54,50 @@ def broadcast_bytes(data, src=0, device=None):
 
 
 _pinned = {}
-_STAGE_BYTES = 32 << 20
 
-
-def _device_to_numpy(torch, src, out):
-    """Device uint8 tensor -> the numpy array `out`, through one cached page-locked staging buffer of fixed size (a
-    pageable .cpu() of a few hundred MB costs more than the self-play pass that produced it)."""
-    stage = _pinned.get("stage")
-    if stage is None:
-        stage = _pinned["stage"] = torch.empty(_STAGE_BYTES, dtype=torch.uint8).pin_memory()
-    flat, host = src.reshape(-1), stage.numpy()
-    stream = torch.cuda.current_stream(src.device)
-    for o in range(0, flat.numel(), _STAGE_BYTES):
-        k = min(_STAGE_BYTES, flat.numel() - o)
-        stage[:k].copy_(flat[o:o + k], non_blocking=True)
-        stream.synchronize()
-        out[o:o + k] = host[:k]
+def _to_pinned(rows):
+    """Device uint8 tensor [world, cap] -> numpy view of one cached page-locked buffer (grown geometrically, so re-pinning
+    happens a few times early on and never in steady state); valid until the next call."""
+    big = _pinned.get("rows")
+    if big is None or big.numel() < rows.numel():
+        big = _pinned["rows"] = torch.empty(4 * rows.numel(), dtype=torch.uint8).pin_memory()
+    host = big[:rows.numel()].view(rows.shape)
+    host.copy_(rows, non_blocking=True)
+    torch.cuda.current_stream(rows.device).synchronize()
+    return host.numpy()
 
 
 def gather_streams(stream, dst=0, device=None):
-    """Gather every rank's frame stream (uint8 array, possibly empty, ragged across ranks) to rank `dst`. Returns the
-    list of per-rank arrays on `dst` (rank order) and None elsewhere. Sizes travel first, payloads are padded to the
-    largest. This is the only collective of the self-play path: the game records themselves are
-    independent, so the writer just concatenates them. Only `dst` receives (dist.gather); with NCCL its copy comes back
-    through page-locked memory (see below: the arrays may be views of a cached buffer, valid until the next call)."""
+    """Gather every rank's frame stream (ragged across ranks, possibly empty) to rank `dst`. `stream` is a uint8 numpy array
+    or a torch uint8 CUDA tensor (SelfPlay.collect(device=True): the drained stream never visits this rank's host).
+    Returns the list of per-rank numpy arrays on `dst` (rank order) and None elsewhere. Sizes travel first, payloads are
+    padded to the largest. This is the only collective of the self-play path: the game records themselves
+    are independent, so the writer just concatenates them. Only `dst` receives (dist.gather); with NCCL its copy comes
+    back through a cached page-locked buffer and the returned arrays are views of it, valid until the next call."""
     import numpy as np
     dev = _group_device(device)
-    stream = np.ascontiguousarray(stream, np.uint8)
+    on_device = torch.is_tensor(stream)
+    if not on_device:
+        stream = np.ascontiguousarray(stream, np.uint8)
+    size = int(stream.numel()) if on_device else int(stream.size)
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return [stream]
+        if not on_device:
+            return [stream]
+        return [_to_pinned(stream.reshape(1, -1))[0]] if size else [np.empty(0, np.uint8)]
     world, rank = dist.get_world_size(), dist.get_rank()
     sizes = torch.zeros(world, dtype=torch.int64, device=dev)
-    sizes[rank] = stream.size
+    sizes[rank] = size
     dist.all_reduce(sizes, op=dist.ReduceOp.SUM)
     sizes = sizes.cpu()
     cap = int(sizes.max().item())
     if cap == 0:
         return [np.empty(0, np.uint8) for _ in range(world)] if rank == dst else None
     mine = torch.empty(cap, dtype=torch.uint8, device=dev)
-    mine[:stream.size] = torch.from_numpy(stream).to(dev)
+    mine[:size] = stream.to(dev) if on_device else torch.from_numpy(stream).to(dev)
     if rank != dst:
         dist.gather(mine, None, dst=dst)
         return None
     rows = torch.empty((world, cap), dtype=torch.uint8, device=dev)
     dist.gather(mine, list(rows.unbind(0)), dst=dst)
-    if rows.is_cuda:
-        # the writer's copy lands in one cached page-locked buffer (allocated with 4x head-room the first time: streams
-        # grow until games end at a steady rate) and the returned arrays are views of it, valid until the next call; a
-        # gather that has outgrown it goes through the fixed staging buffer into fresh memory instead of re-pinning
-        big = _pinned.get("rows")
-        if big is None:
-            big = _pinned["rows"] = torch.empty(4 * world * cap, dtype=torch.uint8).pin_memory()
-        if big.numel() >= world * cap:
-            host = big[:world * cap].view(world, cap)
-            host.copy_(rows, non_blocking=True)
-            torch.cuda.current_stream(rows.device).synchronize()
-            out = host.numpy()
-        else:
-            out = np.empty((world, cap), np.uint8)
-            _device_to_numpy(torch, rows, out.reshape(-1))
-    else:
-        out = rows.numpy()
+    out = _to_pinned(rows) if rows.is_cuda else rows.numpy()
     return [out[r, :int(sizes[r].item())] for r in range(world)]
