@@ -53,3 +53,30 @@ def test_selfplay_frames_replay_on_oracle(tmp_path):
             assert (r & 15) == 0 or ui + 1 == len(g["updates"])
         assert r == g["result"] and (r & 15) != 0
     assert checked > 50
+
+
+def test_device_drain_and_gather_equal_the_host_drain():
+    """SelfPlay.collect(device=True) + sharding.gather_streams (the path the 8-GPU generator takes: the drained stream stays
+    in device memory until the writer rank has it) delivers the bytes the host drain delivers: two generators with the
+    same seed, one drained each way."""
+    import torch
+    from oak_b200.selfplay import SelfPlay
+    from oak_b200.sharding import gather_streams
+    pool = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    blob = make_net_blob(np.random.default_rng(5), scale=3.0)
+    a = SelfPlay(512, blob, pool, seed=42, max_updates=400)
+    b = SelfPlay(512, blob, pool, seed=42, max_updates=400)
+    total = 0
+    for s in range(160):
+        a.step()
+        b.step()
+        if (s + 1) % 8 == 0:
+            sa, ga = a.collect()
+            sb, gb = b.collect(device=True)
+            assert torch.is_tensor(sb) and sb.is_cuda and ga == gb
+            got = gather_streams(sb)  # one rank: the writer's own copy
+            assert len(got) == 1 and np.array_equal(got[0], sa)
+            total += ga
+    assert total > 100
+    a.close()
+    b.close()
