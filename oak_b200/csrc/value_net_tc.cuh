@@ -29,6 +29,13 @@
 #include "gen1_mem_ops.cuh"
 #include "umma.cuh"
 
+// hand-overs between the workers and the MMA issuer: OAKB200_TC_SPIN polls instead of the suspending try_wait (A/B switch)
+#ifdef OAKB200_TC_SPIN
+#define OAKB200_TC_WAIT(bar, parity) umma::mbar_wait_spin(bar, parity)
+#else
+#define OAKB200_TC_WAIT(bar, parity) umma::mbar_wait(bar, parity)
+#endif
+
 namespace tc {
 
 using namespace oakb200;
@@ -506,7 +513,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           TM_LAP(tm2);
 #endif
           if (ch.flags & F_STAGE_BEGIN) {
-            umma::mbar_wait(bar_a, stage & 1);
+            OAKB200_TC_WAIT(bar_a, stage & 1);
             stage++;
           }
 #ifdef OAKB200_TC_TIMING
@@ -685,14 +692,14 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       WT_LAP(2);
     };
     auto wait_d = [&]() {
-      umma::mbar_wait(bar_d, dphase & 1);
+      OAKB200_TC_WAIT(bar_d, dphase & 1);
       dphase++;
       umma::tc_fence_after();
       WT_LAP(0);
     };
     auto wait_t = [&]() {
       if (t_pending) {
-        umma::mbar_wait(bar_t, tphase & 1);
+        OAKB200_TC_WAIT(bar_t, tphase & 1);
         tphase++;
         t_pending = false;
         umma::tc_fence_after();
