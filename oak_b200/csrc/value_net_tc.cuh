@@ -710,6 +710,9 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // accumulator columns [c0, c1) of D (multiples of 16; 32-column blocks where aligned) -> activation -> operand planes
     auto epi = [&](uint32_t dcol, int c0, int c1, const float* bias, float bound, uint32_t hi, uint32_t lo, int mode) {
       int c = c0;
+#ifdef OAKB200_TC_NO_EPI  // timing experiment only: hand-overs without the epilogue work, results are garbage
+      c = c1;
+#endif
       for (; c + 32 <= c1; c += 32) epilogue_block(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
       if (c < c1) epilogue_half(tl + dcol, c >> 4, bias, bound, hi, lo, r, mode);
       WT_LAP(1);
