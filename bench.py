@@ -320,8 +320,11 @@ def main():
     SP_G, SP_STEPS = 65536, 96
     sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
 
+    from oak_b200.sharding import StreamGatherer
+    gatherer = StreamGatherer(dst=0, device=dev)
+
     def sp_pass():
-        # every drain goes to the writer rank as it is produced (one gather per drain), as a running generator would
+        # every drain goes to the writer rank as it is produced (one gather per drain, one drain behind the generator)
         streams, games, at_writer = [], 0, 0
         for s_ in range(SP_STEPS):
             sp.step()
@@ -329,8 +332,10 @@ def main():
                 st_, g_ = sp.collect(device=True)  # the drained stream stays on the device until the writer rank has it
                 streams.append(st_.clone())
                 games += g_
-                got = gather_streams(st_, dst=0, device=dev)
+                got = gatherer.submit(st_)  # the previous drain's bytes, gathered while these 8 steps ran
                 at_writer += sum(len(x) for x in got) if got is not None else 0
+        got = gatherer.flush()
+        at_writer += sum(len(x) for x in got) if got is not None else 0
         return streams, games, at_writer
 
     sp_pass()  # warm-up: the same pass (the writer rank's page-locked gather buffer is allocated here, once)

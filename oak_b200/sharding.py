@@ -101,3 +101,87 @@ def gather_streams(stream, dst=0, device=None):
     dist.gather(mine, list(rows.unbind(0)), dst=dst)
     out = _to_pinned(rows) if rows.is_cuda else rows.numpy()
     return [out[r, :int(sizes[r].item())] for r in range(world)]
+
+
+class StreamGatherer:
+    """gather_streams one drain behind the generator (CUDA/NCCL groups): submit() exchanges the sizes (a few bytes, the only
+    point where the host waits for the other ranks), copies the drained stream aside and queues the payload gather and the
+    writer's device -> page-locked-host copy on a side stream; the generator's next steps run meanwhile. The result of a
+    submit is returned by the NEXT submit() or by flush(): on the writer rank a list of per-rank numpy arrays (views of one
+    of two page-locked buffers, valid until the submit after next), elsewhere None."""
+
+    def __init__(self, dst=0, device=None):
+        self.dst, self.dev = dst, _group_device(device)
+        self.multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        self.world = dist.get_world_size() if self.multi else 1
+        self.rank = dist.get_rank() if self.multi else 0
+        self.side = torch.cuda.Stream(self.dev)
+        self.pinned = [None, None]
+        self.turn = 0
+        self.pending = None
+
+    def _pinned(self, nbytes):
+        buf = self.pinned[self.turn]
+        if buf is None or buf.numel() < nbytes:
+            buf = self.pinned[self.turn] = torch.empty(4 * nbytes, dtype=torch.uint8).pin_memory()
+        return buf[:nbytes]
+
+    def _finish(self):
+        p, self.pending = self.pending, None
+        if p is None:
+            return None
+        done, host, sizes, keep = p
+        done.synchronize()
+        del keep
+        if self.multi and self.rank != self.dst:
+            return None
+        import numpy as np
+        if host is None:  # every rank's drain was empty
+            return [np.empty(0, np.uint8) for _ in range(self.world)]
+        out = host.numpy()
+        return [out[r, :sizes[r]] if sizes[r] else np.empty(0, np.uint8) for r in range(self.world)]
+
+    def submit(self, stream):
+        """stream: torch uint8 CUDA tensor (SelfPlay.collect(device=True)). -> the previous submit's result."""
+        prev = self._finish()
+        main = torch.cuda.current_stream(self.dev)
+        size = int(stream.numel())
+        if self.multi:
+            sizes_t = torch.zeros(self.world, dtype=torch.int64, device=self.dev)
+            sizes_t[self.rank] = size
+            dist.all_reduce(sizes_t, op=dist.ReduceOp.SUM)
+            sizes = [int(x) for x in sizes_t.cpu().tolist()]
+        else:
+            sizes = [size]
+        cap = max(sizes)
+        done = torch.cuda.Event()
+        if cap == 0:
+            done.record(main)
+            self.pending = (done, None, sizes, None)
+            return prev
+        mine = torch.empty(cap, dtype=torch.uint8, device=self.dev)
+        mine[:size] = stream  # on the generator's stream: the drain buffer is free again when submit returns
+        ready = torch.cuda.Event()
+        ready.record(main)
+        host = None
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(ready)
+            mine.record_stream(self.side)
+            rows = None
+            if not self.multi:
+                rows = mine.view(1, cap)
+            elif self.rank == self.dst:
+                rows = torch.empty((self.world, cap), dtype=torch.uint8, device=self.dev)
+                dist.gather(mine, list(rows.unbind(0)), dst=self.dst)
+            else:
+                dist.gather(mine, None, dst=self.dst)
+            if rows is not None:
+                host = self._pinned(rows.numel()).view(rows.shape)
+                host.copy_(rows, non_blocking=True)
+            done.record(self.side)
+        self.turn ^= 1
+        self.pending = (done, host, sizes, (mine, rows))
+        return prev
+
+    def flush(self):
+        return self._finish()

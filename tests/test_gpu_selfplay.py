@@ -66,6 +66,8 @@ def test_device_drain_and_gather_equal_the_host_drain():
     blob = make_net_blob(np.random.default_rng(5), scale=3.0)
     a = SelfPlay(512, blob, pool, seed=42, max_updates=400)
     b = SelfPlay(512, blob, pool, seed=42, max_updates=400)
+    from oak_b200.sharding import StreamGatherer
+    gatherer, previous = StreamGatherer(device=torch.device("cuda:0")), None
     total = 0
     for s in range(160):
         a.step()
@@ -76,7 +78,13 @@ def test_device_drain_and_gather_equal_the_host_drain():
             assert torch.is_tensor(sb) and sb.is_cuda and ga == gb
             got = gather_streams(sb)  # one rank: the writer's own copy
             assert len(got) == 1 and np.array_equal(got[0], sa)
+            late = gatherer.submit(sb)  # the asynchronous form hands back the PREVIOUS drain
+            if previous is not None:
+                assert late is not None and len(late) == 1 and np.array_equal(late[0], previous)
+            previous = sa
             total += ga
+    last = gatherer.flush()
+    assert np.array_equal(last[0], previous) and gatherer.flush() is None
     assert total > 100
     a.close()
     b.close()
