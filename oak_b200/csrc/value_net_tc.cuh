@@ -346,10 +346,8 @@ __device__ __forceinline__ float epi_act(float v, float b, float bound) {
   return MODE == 1 ? floorf(127.0f * x) : x;
 }
 template <int MODE>
-__device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
-  uint32_t v[32];
-  umma::tmem_ld32(taddr + 32u * q, v);
-  umma::tmem_ld_wait();
+__device__ __forceinline__ void epilogue_values_m(const uint32_t (&v)[32], int q, const float* bias, float bound, uint32_t hi, uint32_t lo,
+                                                  int r) {
   const float4* b4 = reinterpret_cast<const float4*>(bias + 32 * q);
 #pragma unroll
   for (int g = 0; g < 4; g++) {
@@ -371,6 +369,29 @@ __device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const fl
     stv4(hi + o, h0, h1, h2, h3);
     stv4(lo + o, l0, l1, l2, l3);
   }
+}
+template <int MODE>
+__device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
+  uint32_t v[32];
+  umma::tmem_ld32(taddr + 32u * q, v);
+  umma::tmem_ld_wait();
+  epilogue_values_m<MODE>(v, q, bias, bound, hi, lo, r);
+}
+// two neighbouring blocks q, q + 1 with both Tensor Memory loads in flight before the one wait
+template <int MODE>
+__device__ __forceinline__ void epilogue_pair_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
+  uint32_t v0[32], v1[32];
+  umma::tmem_ld32(taddr + 32u * q, v0);
+  umma::tmem_ld32(taddr + 32u * q + 32u, v1);
+  umma::tmem_ld_wait();
+  epilogue_values_m<MODE>(v0, q, bias, bound, hi, lo, r);
+  epilogue_values_m<MODE>(v1, q + 1, bias, bound, hi, lo, r);
+}
+__device__ __forceinline__ void epilogue_pair(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
+                                              int mode = 0) {
+  if (mode == 0) epilogue_pair_m<0>(taddr, q, bias, bound, hi, lo, r);
+  else if (mode == 1) epilogue_pair_m<1>(taddr, q, bias, bound, hi, lo, r);
+  else epilogue_pair_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
 // the same for a 16-column block: D[:, 16q .. 16q+15] -> core columns 2q, 2q+1
 template <int MODE>
@@ -713,6 +734,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #ifdef OAKB200_TC_NO_EPI  // timing experiment only: hand-overs without the epilogue work, results are garbage
       c = c1;
 #endif
+      for (; c + 64 <= c1; c += 64) epilogue_pair(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
       for (; c + 32 <= c1; c += 32) epilogue_block(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
       if (c < c1) epilogue_half(tl + dcol, c >> 4, bias, bound, hi, lo, r, mode);
       WT_LAP(1);
