@@ -297,7 +297,16 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
   if (s->n_roots == 0 || !rolls_ok(root_rolls) || !rolls_ok(other_rolls))
     return fail(ctx, OAKB200_EINVAL, "search_run: set roots first; rolls must be 1, 2, 3, 20 or 39");
   CU(ctx, cudaSetDevice(ctx->device));
-  if (host_threads < 1) host_threads = (int)std::thread::hardware_concurrency();
+  if (host_threads < 1) {
+    // one process per GPU: the ranks of a node share its cores (torchrun exports LOCAL_WORLD_SIZE); 8 ranks x every core
+    // each would oversubscribe the host 8 times over
+    host_threads = (int)std::thread::hardware_concurrency();
+    if (const char* lw = getenv("LOCAL_WORLD_SIZE")) {
+      const int ranks = atoi(lw);
+      if (ranks > 1) host_threads /= ranks;
+    }
+    if (host_threads < 1) host_threads = 1;
+  }
   if (!s->pool || s->pool_threads != host_threads) {
     delete s->pool;
     s->pool = new Pool(host_threads);
