@@ -195,13 +195,158 @@ static const int NULLR = -1;  // "no result yet" (Zig `null` of ?Result)
 #define ORACLE_ASSERT(x) ((void)0)
 #endif
 
-template <bool MISS, bool ADVANCE, bool EBC, bool KEY, bool FIXED>
+// Protocol log sink (common/protocol.zig:831-863 `Writer`): fixed caller buffer; a write that does not fit
+// aborts the update (Zig `try` -> error.NoSpaceLeft -> result byte 0b1100, bindings/c.zig:6,181).
+struct LogBuf {
+  uint8_t* buf;
+  size_t cap, pos;
+};
+struct LogOverflow {};
+static const uint8_t RESULT_LOG_OVERFLOW = 0x0C;
+
+// ArgType / reason ordinals (common/protocol.zig:16-311), Generation I subset
+enum : uint8_t {
+  LG_None = 0, LG_LastStill, LG_LastMiss, LG_Move, LG_Switch, LG_Cant, LG_Faint, LG_Turn, LG_Win, LG_Tie, LG_Damage,
+  LG_Heal, LG_Status, LG_CureStatus, LG_Boost, LG_ClearAllBoost, LG_Fail, LG_Miss, LG_HitCount, LG_Prepare,
+  LG_MustRecharge, LG_Activate, LG_FieldActivate, LG_Start, LG_End, LG_OHKO, LG_Crit, LG_SuperEffective, LG_Resisted,
+  LG_Immune, LG_Transform,
+};
+enum : uint8_t { CANT_Sleep = 0, CANT_Freeze, CANT_Paralysis, CANT_Bound, CANT_Flinch, CANT_Disable, CANT_Recharge };
+enum : uint8_t { HEAL_None = 0, HEAL_Silent, HEAL_Drain };
+enum : uint8_t { DMG_None = 0, DMG_Poison, DMG_Burn, DMG_Confusion, DMG_LeechSeed, DMG_RecoilOf };
+enum : uint8_t { STS_None = 0, STS_Silent, STS_From };
+enum : uint8_t { CURE_Message = 0, CURE_Silent };
+enum : uint8_t { BST_Rage = 0, BST_Attack, BST_Defense, BST_Speed, BST_SpecialAttack, BST_SpecialDefense, BST_Accuracy, BST_Evasion };
+enum : uint8_t { FAIL_None = 0, FAIL_Sleep, FAIL_Poison, FAIL_Burn, FAIL_Freeze, FAIL_Paralysis, FAIL_Toxic, FAIL_Substitute, FAIL_Weak };
+enum : uint8_t { ACT_Bide = 0, ACT_Confusion, ACT_Haze, ACT_Mist, ACT_Struggle, ACT_Substitute, ACT_Splash };
+enum : uint8_t {
+  START_Bide = 0, START_Confusion, START_ConfusionSilent, START_FocusEnergy, START_LeechSeed, START_LightScreen, START_Mist,
+  START_Reflect, START_Substitute, START_TypeChange, START_Disable, START_Mimic,
+};
+enum : uint8_t {
+  END_Disable = 0, END_Confusion, END_Bide, END_Substitute, END_DisableSilent = 15, END_ConfusionSilent, END_MistSilent,
+  END_FocusEnergySilent, END_LeechSeedSilent, END_ToxicSilent, END_LightScreenSilent, END_ReflectSilent,
+};
+enum : uint8_t { IMM_None = 0, IMM_OHKO };
+
+template <bool MISS, bool ADVANCE, bool EBC, bool KEY, bool FIXED, bool LOG = false>
 struct Engine {
   Battle& b;
   Options& o;
   Rolls32* fx;
+  LogBuf* lg;
 
-  Engine(Battle& battle, Options& options, Rolls32* fixed = nullptr) : b(battle), o(options), fx(fixed) {}
+  Engine(Battle& battle, Options& options, Rolls32* fixed = nullptr, LogBuf* log = nullptr)
+      : b(battle), o(options), fx(fixed), lg(log) {}
+
+  // ------------------------------------------------------------------ protocol log (common/protocol.zig:313-824)
+  // Every writer below is one `Log.*` method; the grouping of bytes into `lw` calls is the reference's grouping into
+  // writeAll / writeInt / writeByte calls, so that an overflowing buffer is left with exactly the same prefix.
+  void lw(const uint8_t* bytes, size_t n) {
+    if (lg->pos + n > lg->cap) throw LogOverflow{};
+    memcpy(lg->buf + lg->pos, bytes, n);
+    lg->pos += n;
+  }
+  template <class... A>
+  void lwb(A... a) {
+    const uint8_t t[] = {(uint8_t)a...};
+    lw(t, sizeof...(A));
+  }
+  void lw16(uint16_t v) { lwb(v & 255, v >> 8); }
+  void log_move(uint8_t src, uint8_t move, uint8_t target, uint8_t from = 0) {  // :337-352
+    if (!LOG) return;
+    lwb(LG_Move, src, move, target);
+    if (from == 0) lwb(0); else lwb(1, from);
+  }
+  void log_switched(uint8_t id, const Pokemon& pk) {  // :355-378
+    if (!LOG) return;
+    lwb(LG_Switch, id);
+    lwb(pk.species, pk.level);
+    lw16(pk.hp);
+    lw16(pk.stats.hp);
+    lwb(pk.status);
+  }
+  void log_cant(uint8_t id, uint8_t reason) {  // :382-393
+    if (!LOG) return;
+    lwb(LG_Cant, id, reason);
+  }
+  void log_cant_disable(uint8_t id, uint8_t move) {
+    if (!LOG) return;
+    lwb(LG_Cant, id, CANT_Disable);
+    lwb(move);
+  }
+  void log_faint(uint8_t id, bool done) {  // :396-401
+    if (!LOG) return;
+    lwb(LG_Faint, id);
+    if (done) lwb(LG_None);
+  }
+  void log_turn(uint16_t n) {  // :404-410
+    if (!LOG) return;
+    lwb(LG_Turn);
+    lw16(n);
+    lwb(LG_None);
+  }
+  void log_win(int player) {  // :413-421
+    if (!LOG) return;
+    lwb(LG_Win, player, LG_None);
+  }
+  void log_tie() {  // :424-428
+    if (!LOG) return;
+    lwb(LG_Tie, LG_None);
+  }
+  void log_hp(uint8_t op, uint8_t id, const Pokemon& pk, uint8_t reason, int of) {  // damage :432-444, heal :448-458
+    if (!LOG) return;
+    lwb(op, id);
+    lw16(pk.hp);
+    lw16(pk.stats.hp);
+    lwb(pk.status, reason);
+    if (of >= 0) lwb(of);
+  }
+  void log_damage(uint8_t id, const Pokemon& pk, uint8_t reason, int of = -1) { log_hp(LG_Damage, id, pk, reason, of); }
+  void log_heal(uint8_t id, const Pokemon& pk, uint8_t reason, int of = -1) { log_hp(LG_Heal, id, pk, reason, of); }
+  void log_status(uint8_t id, uint8_t value, uint8_t reason, int from = -1) {  // :462-473
+    if (!LOG) return;
+    lwb(LG_Status, id, value, reason);
+    if (from >= 0) lwb(from);
+  }
+  void log_curestatus(uint8_t id, uint8_t value, uint8_t reason) {  // :476-485
+    if (!LOG) return;
+    lwb(LG_CureStatus, id, value, reason);
+  }
+  void log_boost(uint8_t id, uint8_t reason, int num) {  // :488-498
+    if (!LOG) return;
+    lwb(LG_Boost, id, reason, num + 6);
+  }
+  void log_op(uint8_t op) {  // clearallboost :501, fieldactivate :599, ohko :644, laststill :810, lastmiss :817
+    if (!LOG) return;
+    lwb(op);
+  }
+  void log_id(uint8_t op, uint8_t id) {  // miss :519, mustrecharge :549, crit :651, supereffective :658, resisted :668
+    if (!LOG) return;
+    lwb(op, id);
+  }
+  void log_id_arg(uint8_t op, uint8_t id, uint8_t arg) {  // fail :508, hitcount :526, prepare :537, activate :563, start :606, end :633, immune :678, transform :689
+    if (!LOG) return;
+    lwb(op, id, arg);
+  }
+  void log_fail(uint8_t id, uint8_t reason) { log_id_arg(LG_Fail, id, reason); }
+  void log_lastmiss_miss(int p) {
+    log_op(LG_LastMiss);
+    log_id(LG_Miss, ident(p));
+  }
+  void log_activate(uint8_t id, uint8_t reason) { log_id_arg(LG_Activate, id, reason); }
+  void log_start(uint8_t id, uint8_t reason) { log_id_arg(LG_Start, id, reason); }
+  void log_start_move(uint8_t id, uint8_t reason, uint8_t move) {  // .Disable / .Mimic
+    if (!LOG) return;
+    lwb(LG_Start, id, reason);
+    lwb(move);
+  }
+  void log_start_typechange(uint8_t id, uint8_t types, uint8_t target) {
+    if (!LOG) return;
+    lwb(LG_Start, id, START_TypeChange);
+    lwb(types, target);
+  }
+  void log_end(uint8_t id, uint8_t reason) { log_id_arg(LG_End, id, reason); }
 
   // ------------------------------------------------------------------ accessors
   Side& side(int p) { return b.sides[p]; }
@@ -558,7 +703,11 @@ struct Engine {
     statusModify(incoming.status, a.stats);
     ch_switched(p, slot);
     vset(f.active, V_Binding, false);
-    if (incoming.status == STATUS_TOX) incoming.status = status_init(ST_PSN);
+    log_switched(ident(p), incoming);
+    if (incoming.status == STATUS_TOX) {
+      incoming.status = status_init(ST_PSN);
+      log_status(ident(p), incoming.status, STS_Silent);
+    }
   }
 
   int turnOrder(uint8_t c1, uint8_t c2) {  // :265-316
@@ -670,7 +819,10 @@ struct Engine {
     Active& a = s.active;
     Pokemon& st = stored(s);
 
+    const uint8_t id = ident(p);
+
     if (status_is(st.status, ST_SLP)) {
+      const uint8_t before = st.status;
       const bool slf = status_is(st.status, ST_EXT);
       const uint32_t ov = overridden(p, A_sleep);
       if (ov) {
@@ -684,26 +836,42 @@ struct Engine {
       }
       const uint32_t duration = st.status & 7;
       ch_sleep(p, slf ? OBS_NONE : (duration == 0 ? OBS_ENDED : OBS_CONTINUING));
-      if (duration == 0) st.status = 0;
+      if (duration == 0) {
+        log_curestatus(id, before, CURE_Message);
+        st.status = 0;
+      } else {
+        log_cant(id, CANT_Sleep);
+      }
       s.last_used_move = MOVE_None;
       return BM_done;
     }
     if (status_is(st.status, ST_FRZ)) {
+      log_cant(id, CANT_Freeze);
       s.last_used_move = MOVE_None;
       return BM_done;
     }
-    if (skip || vget(f.active, V_Binding)) return BM_done;
-    if (vget(a, V_Flinch)) return BM_done;
+    if (skip || vget(f.active, V_Binding)) {
+      log_cant(id, CANT_Bound);
+      return BM_done;
+    }
+    if (vget(a, V_Flinch)) {
+      log_cant(id, CANT_Flinch);
+      return BM_done;
+    }
     if (vget(a, V_Recharging)) {
       vset(a, V_Recharging, false);
+      log_cant(id, CANT_Recharge);
       return BM_done;
     }
     if (vfget(a, VF_disable_duration) > 0) {
       vfset(a, VF_disable_duration, decrement<uint32_t>(A_disable, p, vfget(a, VF_disable_duration)));
       ch_disable(p, vfget(a, VF_disable_duration) == 0 ? OBS_ENDED : OBS_CONTINUING);
-      if (vfget(a, VF_disable_duration) == 0) vfset(a, VF_disable_move, 0);
+      if (vfget(a, VF_disable_duration) == 0) {
+        vfset(a, VF_disable_move, 0);
+        log_end(id, END_Disable);
+      }
     }
-    if (disabled(s)) return BM_done;
+    if (disabled(s, id)) return BM_done;
     if (s.last_selected_move == MOVE_None) return BM_err;  // unreachable with mod=true (assert :572)
 
     if (vget(a, V_Confusion)) {
@@ -721,7 +889,8 @@ struct Engine {
       ch_confusion(p, vfget(a, VF_confusion) == 0 ? OBS_ENDED : OBS_CONTINUING);
       if (vfget(a, VF_confusion) == 0) {
         vset(a, V_Confusion, false);
-      } else if (roll_confused(p)) {
+        log_end(id, END_Confusion);
+      } else if (log_activate(id, ACT_Confusion), roll_confused(p)) {
         if (!vget(a, V_Rage)) vfset(a, VF_state, 0);
         vset(a, V_Bide, false);
         vset(a, V_Thrashing, false);
@@ -740,7 +909,7 @@ struct Engine {
           if (!ok) return BM_err;
         }
         const uint16_t uncapped = b.last_damage;
-        applyDamage(p, p ^ 1);
+        applyDamage(p, p ^ 1, DMG_Confusion);
         b.last_damage = uncapped;
         return BM_done;
       }
@@ -754,6 +923,7 @@ struct Engine {
       vset(a, V_Binding, false);
       ch_observe(F_attacking, p, OBS_NONE);
       ch_observe(F_binding, p, OBS_NONE);
+      log_cant(id, CANT_Paralysis);
       return BM_done;
     }
 
@@ -763,12 +933,19 @@ struct Engine {
       vfset(a, VF_state, state);
       vfset(a, VF_attacks, decrement<uint32_t>(A_attacking, p, vfget(a, VF_attacks)));
       ch_attacking(p, vfget(a, VF_attacks) == 0 ? OBS_ENDED : OBS_CONTINUING);
-      if (vfget(a, VF_attacks) != 0) return BM_done;
+      if (vfget(a, VF_attacks) != 0) {
+        log_activate(id, ACT_Bide);
+        return BM_done;
+      }
 
       vset(a, V_Bide, false);
+      log_end(id, END_Bide);
       b.last_damage = (uint16_t)(vfget(a, VF_state) * 2);  // *% 2 wraps to u16
       vfset(a, VF_state, 0);
-      if (b.last_damage == 0) return BM_done;
+      if (b.last_damage == 0) {
+        log_fail(id, FAIL_None);
+        return BM_done;
+      }
 
       const bool sub = vget(f.active, V_Substitute);
       applyDamage(p ^ 1, p ^ 1);
@@ -779,6 +956,7 @@ struct Engine {
     }
 
     if (vget(a, V_Thrashing)) {
+      log_move(id, s.last_selected_move, ident(p ^ 1));
       vfset(a, VF_attacks, decrement<uint32_t>(A_attacking, p, vfget(a, VF_attacks)));
       ch_attacking(p, vfget(a, VF_attacks) == 0 ? OBS_ENDED : OBS_CONTINUING);
       if (vfget(a, VF_attacks) == 0) {
@@ -786,6 +964,7 @@ struct Engine {
         vset(a, V_Thrashing, false);
         vset(a, V_Confusion, true);
         vfset(a, VF_confusion, roll_duration(p, 2, 6));
+        log_start(id, START_ConfusionSilent);
         ch_observe(F_confusion, p, overwritten ? OBS_OVERWRITTEN : OBS_STARTED);
         if (!overwritten) calc_confusion(p);
       }
@@ -796,6 +975,7 @@ struct Engine {
     if (vget(a, V_Binding)) {
       vfset(a, VF_attacks, decrement<uint32_t>(A_binding, p, vfget(a, VF_attacks)));
       ch_binding(p, vfget(a, VF_attacks) == 0 ? OBS_ENDED : OBS_CONTINUING);
+      log_move(id, s.last_selected_move, ident(p ^ 1));
       const bool sub = vget(f.active, V_Substitute);
       applyDamage(p ^ 1, p ^ 1);
       if (stored(f).hp > 0 && !sub) buildRage(p ^ 1);
@@ -805,21 +985,25 @@ struct Engine {
     return vget(a, V_Rage) ? BM_skip_pp : BM_ok;
   }
 
-  bool canMove(int p, int mslot, bool autosel, bool skip_pp, bool& residual) {  // :746-795
+  bool canMove(int p, int mslot, bool autosel, bool skip_pp, bool& residual, uint8_t from = MOVE_None) {  // :746-795
     Side& s = side(p);
     const MoveData move = move_get(s.last_selected_move);
     if (vget(s.active, V_Charging)) {
       vset(s.active, V_Charging, false);
       vset(s.active, V_Invulnerable, false);
     } else if (move.effect == EFF_Charge) {
+      log_move(ident(p), s.last_selected_move, 0, from);
       setCounterable(p, move);
       // Effects.charge :1867-1876
       vset(s.active, V_Charging, true);
       if (s.last_selected_move == MOVE_Fly || s.last_selected_move == MOVE_Dig) vset(s.active, V_Invulnerable, true);
+      log_op(LG_LastStill);
+      log_id_arg(LG_Prepare, ident(p), s.last_selected_move);
       return false;
     }
     s.last_used_move = s.last_selected_move;
     if (!skip_pp) decrementPP(s, mslot, autosel);
+    log_move(ident(p), s.last_selected_move, ident(move.target_self ? p : p ^ 1), from);
     setCounterable(p, move);
 
     if (eff_onBegin(move.effect)) {
@@ -875,6 +1059,7 @@ struct Engine {
 
       bool crit = false, ohko = false, immune = false, mist = false;
       uint32_t hits = 1;
+      uint32_t effectiveness = 100;  // Effectiveness.neutral (data.zig:546-557)
 
       if (!counter) b.last_damage = 0;
       if (move.effect == EFF_SuperFang || move.effect == EFF_SpecialDamage) return specialDamage(p, move);
@@ -914,8 +1099,10 @@ struct Engine {
             if (!calcDamage(p, p ^ 1, &move, crit)) return RES_ERROR;
             if (b.last_damage == 0) {
               immune = true;
+              effectiveness = 0;
             } else {
-              immune = adjustDamage(p) == 0;
+              effectiveness = adjustDamage(p);
+              immune = effectiveness == 0;
             }
             randomizeDamage(p);
           }
@@ -926,15 +1113,18 @@ struct Engine {
         if (move.effect == EFF_MirrorMove) {
           // mirrorMove :1351-1376
           s.last_selected_move = f.last_used_move;
-          if (f.last_used_move == MOVE_None || f.last_used_move == MOVE_MirrorMove) return NULLR;
+          if (f.last_used_move == MOVE_None || f.last_used_move == MOVE_MirrorMove) {
+            log_fail(ident(p), FAIL_None);
+            return NULLR;
+          }
           if (f.last_used_move != MOVE_Struggle) incrementPP(s, p, mslot);
-          if (!canMove(p, mslot, autosel, false, residual)) return NULLR;
+          if (!canMove(p, mslot, autosel, false, residual, MOVE_MirrorMove)) return NULLR;
           continue;
         } else if (move.effect == EFF_Metronome) {
           // metronome :1378-1396
           s.last_selected_move = roll_metronome(p);
           incrementPP(s, p, mslot);
-          if (!canMove(p, mslot, autosel, false, residual)) return NULLR;
+          if (!canMove(p, mslot, autosel, false, residual, MOVE_Metronome)) return NULLR;
           continue;
         } else if (eff_onEnd(move.effect)) {
           onEnd(p, move);
@@ -943,6 +1133,21 @@ struct Engine {
       }
 
       if (miss) {
+        if (LOG) {  // :951-992
+          const uint8_t foe_ident = ident(p ^ 1);
+          const bool invulnerable = vget(f.active, V_Invulnerable) && move.effect != EFF_Swift;
+          ohko = !immune && !invulnerable && move.effect == EFF_OHKO && s.active.stats.spe < f.active.stats.spe;
+          if (ohko) {
+            log_id_arg(LG_Immune, foe_ident, IMM_OHKO);
+          } else if (immune && !invulnerable && move.effect != EFF_Binding) {
+            log_id_arg(LG_Immune, foe_ident, IMM_None);
+          } else if (mist) {
+            if (!vget(f.active, V_Substitute)) log_activate(foe_ident, ACT_Mist);
+            log_fail(foe_ident, FAIL_None);
+          } else {
+            log_lastmiss_miss(p);
+          }
+        }
         if (move.effect == EFF_JumpKick) {
           b.last_damage = 1;
           applyDamage(p, p ^ 1);
@@ -960,7 +1165,16 @@ struct Engine {
       bool nullified = false;
       uint32_t hit = 0;
       while (hit < hits) {
+        if (LOG && hit == 0) {
+          if (crit) log_id(LG_Crit, ident(p ^ 1));
+          if (effectiveness > 100) {
+            log_id(LG_SuperEffective, ident(p ^ 1));
+          } else if (effectiveness < 100) {
+            log_id(LG_Resisted, ident(p ^ 1));
+          }
+        }
         if (!skip) nullified = applyDamage(p ^ 1, p ^ 1);
+        if (hit == 0 && ohko) log_op(LG_OHKO);
         hit++;
         if (stored(f).hp == 0) break;
         if (!late && (!sub || move.effect == EFF_Explode)) buildRage(p ^ 1);
@@ -973,11 +1187,17 @@ struct Engine {
         if (move.effect == EFF_Twineedle && !nullified && stored(f).hp > 0) {
           effect_poison(p, move_get(MOVE_PoisonSting));
         }
+        log_id_arg(LG_HitCount, ident(p ^ 1), (uint8_t)hit);
       } else if (move.effect == EFF_Binding) {
         effect_binding(p, rewrap);
         if (immune) {
           b.last_damage = 0;
-          if (!sub) buildRage(p ^ 1);
+          if (sub) {
+            log_activate(ident(p ^ 1), ACT_Substitute);
+          } else {
+            log_damage(ident(p ^ 1), stored(f), DMG_None);
+            buildRage(p ^ 1);
+          }
           return NULLR;
         }
       }
@@ -1091,15 +1311,20 @@ struct Engine {
 
   int counterDamage(int p) {  // :1266-1312
     Side& f = foe(p);
-    if (b.last_damage == 0) return NULLR;
+    if (b.last_damage == 0) {
+      log_fail(ident(p), FAIL_None);
+      return NULLR;
+    }
     const uint8_t fm = (f.last_selected_move == MOVE_None || f.last_selected_move == MOVE_SKIP_TURN)
                            ? (uint8_t)MOVE_Splash : f.last_selected_move;
     const MoveData fmd = move_get(fm);
     const bool used = b.last_moves[p ^ 1].counterable != 0;
     const bool selected = fmd.bp > 0 && f.last_selected_move != MOVE_Counter &&
                           (fmd.type == TYPE_Normal || fmd.type == TYPE_Fighting);
-    if (!used && !selected) return NULLR;
-    if (!used || !selected) return NULLR;  // Desync Clause Mod
+    if (!used || !selected) {  // both :1283-1286 and the Desync Clause Mod case :1288-1295
+      log_fail(ident(p), FAIL_None);
+      return NULLR;
+    }
     b.last_damage = b.last_damage > 32767 ? 65535 : (uint16_t)(b.last_damage * 2);
     const bool sub = vget(f.active, V_Substitute);
     applyDamage(p ^ 1, p ^ 1);
@@ -1107,7 +1332,7 @@ struct Engine {
     return NULLR;
   }
 
-  bool applyDamage(int tp, int sp) {  // :1314-1349
+  bool applyDamage(int tp, int sp, uint8_t reason = DMG_None) {  // :1314-1349
     Side& t = side(tp);
     if (vget(t.active, V_Substitute)) {
       Side& sb = side(sp);
@@ -1115,20 +1340,26 @@ struct Engine {
       if (b.last_damage >= vfget(sb.active, VF_substitute)) {
         vfset(sb.active, VF_substitute, 0);
         vset(sb.active, V_Substitute, false);
+        log_end(ident(sp), END_Substitute);
         return true;
       }
       vfset(sb.active, VF_substitute, vfget(sb.active, VF_substitute) - b.last_damage);
+      log_activate(ident(sp), ACT_Substitute);
       return false;
     }
     Pokemon& st = stored(t);
     if (b.last_damage > st.hp) b.last_damage = st.hp;
     st.hp -= b.last_damage;
+    log_damage(ident(tp), st, reason);
     return false;
   }
 
   bool checkHit(int p, const MoveData& move) {  // :1398-1420
     bool immune = false, mist = false;
-    return moveHit(p, move, immune, mist);
+    if (moveHit(p, move, immune, mist)) return true;
+    // `mist` is only ever raised for stat-down moves, which do not come through checkHit in showdown mode (:1408-1412)
+    log_lastmiss_miss(p);
+    return false;
   }
 
   bool moveHit(int p, const MoveData& move, bool& immune, bool& mist) {  // :1422-1505
@@ -1180,17 +1411,27 @@ struct Engine {
     const bool foe_fainted = stored(f).hp == 0;
     const bool player_out = findFirstAlive(s) == 0;
     const bool foe_out = foe_fainted && findFirstAlive(f) == 0;
-    faint(p);
-    if (foe_fainted) faint(p ^ 1);
-    if (player_out && foe_out) return RES_TIE;
-    if (player_out) return p == P1 ? RES_LOSE : RES_WIN;
-    if (foe_out) return p == P1 ? RES_WIN : RES_LOSE;
+    const bool more = player_out || foe_out;
+    faint(p, !(more || foe_fainted));
+    if (foe_fainted) faint(p ^ 1, !more);
+    if (player_out && foe_out) {
+      log_tie();
+      return RES_TIE;
+    }
+    if (player_out) {
+      log_win(p ^ 1);
+      return p == P1 ? RES_LOSE : RES_WIN;
+    }
+    if (foe_out) {
+      log_win(p);
+      return p == P1 ? RES_WIN : RES_LOSE;
+    }
     const int foe_choice = foe_fainted ? CH_SWITCH : CH_PASS;
     if (p == P1) return (CH_SWITCH << 4) | (foe_choice << 6);
     return (foe_choice << 4) | (CH_SWITCH << 6);
   }
 
-  void faint(int p) {  // :1545-1583
+  void faint(int p, bool done) {  // :1545-1583
     Side& s = side(p);
     Side& f = foe(p);
     if (vget(f.active, V_Bide)) vfset(f.active, VF_state, 0);
@@ -1201,6 +1442,7 @@ struct Engine {
     const uint8_t status = st.status;
     st.status = 0;
     s.active.stats.spe = status_is(status, ST_PAR) ? (uint16_t)(st.stats.spe / 4 > 1 ? st.stats.spe / 4 : 1) : st.stats.spe;
+    log_faint(ident(p), done);
   }
 
   void handleResidual(int p) {  // :1585-1637
@@ -1215,7 +1457,10 @@ struct Engine {
         damage *= vfget(a, VF_toxic);
       }
       if (damage > st.hp) damage = st.hp;
-      if (damage > 0) st.hp -= (uint16_t)damage;
+      if (damage > 0) {
+        st.hp -= (uint16_t)damage;
+        log_damage(ident(p), st, brn ? DMG_Burn : DMG_Poison);
+      }
     }
     if (vget(a, V_LeechSeed)) {
       Pokemon& fs = stored(foe(p));
@@ -1227,15 +1472,21 @@ struct Engine {
       }
       const uint32_t amount = damage < st.hp ? damage : st.hp;
       st.hp -= (uint16_t)amount;
+      if (amount > 0) log_damage(ident(p), st, DMG_LeechSeed);
+      const uint16_t before = fs.hp;
       const uint32_t h = fs.hp + damage;
       fs.hp = (uint16_t)(h < fs.stats.hp ? h : fs.stats.hp);
+      if (fs.hp > before) log_heal(ident(p ^ 1), fs, HEAL_Silent);
     }
   }
 
   uint8_t endTurn() {  // :1639-1660
     b.turn += 1;
-    if (EBC && checkEBC()) return RES_TIE;
-    if (b.turn >= 1000) return RES_TIE;
+    if ((EBC && checkEBC()) || b.turn >= 1000) {
+      log_tie();
+      return RES_TIE;
+    }
+    log_turn(b.turn);
     return RESULT_DEFAULT;
   }
 
@@ -1286,13 +1537,14 @@ struct Engine {
     return false;
   }
 
-  bool disabled(Side& s) {  // :1716-1732
+  bool disabled(Side& s, uint8_t id) {  // :1716-1732
     const uint32_t dm = vfget(s.active, VF_disable_move);
     if (dm != 0) {
       const uint8_t m = s.active.moves[dm - 1].id;
       const uint8_t last = (m == MOVE_Bide && vget(s.active, V_Bide)) ? m : s.last_selected_move;
       if (m != MOVE_None && m == last) {
         vset(s.active, V_Charging, false);
+        log_cant_disable(id, last);
         return true;
       }
     }
@@ -1309,17 +1561,41 @@ struct Engine {
     switch (move.effect) {
       case EFF_Confusion: effect_confusion(p, move); break;
       case EFF_Conversion: effect_conversion(p); break;
-      case EFF_FocusEnergy: vset(side(p).active, V_FocusEnergy, true); break;
+      case EFF_FocusEnergy:  // :2004-2011
+        if (!vget(side(p).active, V_FocusEnergy)) {
+          vset(side(p).active, V_FocusEnergy, true);
+          log_start(ident(p), START_FocusEnergy);
+        }
+        break;
       case EFF_Haze: effect_haze(p); break;
       case EFF_Heal: effect_heal(p); break;
       case EFF_LeechSeed: effect_leechSeed(p, move); break;
-      case EFF_LightScreen: vset(side(p).active, V_LightScreen, true); break;
+      case EFF_LightScreen:  // :2136-2144
+        if (vget(side(p).active, V_LightScreen)) {
+          log_fail(ident(p), FAIL_None);
+        } else {
+          vset(side(p).active, V_LightScreen, true);
+          log_start(ident(p), START_LightScreen);
+        }
+        break;
       case EFF_Mimic: effect_mimic(p, move, mslot); break;
-      case EFF_Mist: vset(side(p).active, V_Mist, true); break;
+      case EFF_Mist:  // :2182-2189
+        if (!vget(side(p).active, V_Mist)) {
+          vset(side(p).active, V_Mist, true);
+          log_start(ident(p), START_Mist);
+        }
+        break;
       case EFF_Paralyze: effect_paralyze(p, move); break;
       case EFF_Poison: effect_poison(p, move); break;
-      case EFF_Reflect: vset(side(p).active, V_Reflect, true); break;
-      case EFF_Splash: break;
+      case EFF_Reflect:  // :2337-2345
+        if (vget(side(p).active, V_Reflect)) {
+          log_fail(ident(p), FAIL_None);
+        } else {
+          vset(side(p).active, V_Reflect, true);
+          log_start(ident(p), START_Reflect);
+        }
+        break;
+      case EFF_Splash: log_activate(ident(p), ACT_Splash); break;
       case EFF_Substitute: effect_substitute(p, residual); break;
       case EFF_SwitchAndTeleport: effect_switchAndTeleport(p, move); break;
       case EFF_Transform: effect_transform(p); break;
@@ -1334,6 +1610,7 @@ struct Engine {
         vfset(a, VF_state, 0);
         vfset(a, VF_attacks, roll_duration(p, 2, 4));
         ch_observe(F_attacking, p, OBS_STARTED);
+        log_start(ident(p), START_Bide);
         break;
       }
       case EFF_AttackUp1: case EFF_AttackUp2: case EFF_DefenseUp1: case EFF_DefenseUp2:
@@ -1352,7 +1629,9 @@ struct Engine {
     switch (move.effect) {
       case EFF_DrainHP: case EFF_DreamEater: effect_drainHP(p); break;
       case EFF_Explode: effect_explode(p); break;
-      case EFF_PayDay: break;
+      case EFF_PayDay:  // :2257-2261
+        if (!vget(foe(p).active, V_Substitute)) log_op(LG_FieldActivate);
+        break;
       case EFF_Rage: vset(side(p).active, V_Rage, true); break;
       case EFF_Recoil: effect_recoil(p, residual); break;
       default: break;  // JumpKick, Binding
@@ -1364,7 +1643,10 @@ struct Engine {
       case EFF_ConfusionChance: effect_confusion(p, move); break;
       case EFF_FlinchChance1: case EFF_FlinchChance2: effect_flinchChance(p, move); break;
       case EFF_FreezeChance: effect_freezeChance(p, move); break;
-      case EFF_HyperBeam: vset(side(p).active, V_Recharging, true); break;
+      case EFF_HyperBeam:  // :2108-2111
+        vset(side(p).active, V_Recharging, true);
+        log_id(LG_MustRecharge, ident(p));
+        break;
       case EFF_ParalyzeChance1: case EFF_ParalyzeChance2: effect_paralyzeChance(p, move); break;
       case EFF_PoisonChance1: case EFF_PoisonChance2: effect_poison(p, move); break;
       case EFF_AttackDownChance: case EFF_DefenseDownChance: case EFF_SpecialDownChance: case EFF_SpeedDownChance:
@@ -1381,13 +1663,17 @@ struct Engine {
     if (vget(f.active, V_Substitute)) return;
     if (fs.status != 0) {
       if (!types_includes(f.active.types, move.type)) advance(1);
-      if (status_is(fs.status, ST_FRZ)) fs.status = 0;
+      if (status_is(fs.status, ST_FRZ)) {
+        log_curestatus(ident(p ^ 1), fs.status, CURE_Message);
+        fs.status = 0;
+      }
       return;
     }
     if (types_includes(f.active.types, move.type)) return;
     if (!roll_secondary(p, move.effect == EFF_BurnChance1 ? 26 : 77)) return;
     fs.status = status_init(ST_BRN);
     f.active.stats.atk = (uint16_t)(f.active.stats.atk / 2 > 1 ? f.active.stats.atk / 2 : 1);
+    log_status(ident(p ^ 1), fs.status, STS_None);
   }
   void effect_confusion(int p, const MoveData& move) {  // :1878-1902
     Side& f = foe(p);
@@ -1396,23 +1682,34 @@ struct Engine {
       if (!roll_secondary(p, 25)) return;
     } else {
       if (!checkHit(p, move)) return;
-      if (sub) return;
+      if (sub) {
+        log_fail(ident(p ^ 1), FAIL_None);
+        return;
+      }
     }
     if (vget(f.active, V_Confusion)) return;
     vset(f.active, V_Confusion, true);
     vfset(f.active, VF_confusion, roll_duration(p, 2, 6));
     ch_observe(F_confusion, p ^ 1, OBS_STARTED);
     calc_confusion(p ^ 1);
+    log_start(ident(p ^ 1), START_Confusion);
   }
   void effect_conversion(int p) {  // :1904-1919
     Side& f = foe(p);
-    if (vget(f.active, V_Invulnerable)) return;
+    if (vget(f.active, V_Invulnerable)) {
+      log_lastmiss_miss(p);
+      return;
+    }
     side(p).active.types = f.active.types;
+    log_start_typechange(ident(p), f.active.types, ident(p ^ 1));
   }
   void effect_disable(int p) {  // :1921-1961
     Side& f = foe(p);
     Active& fa = f.active;
-    if (vfget(fa, VF_disable_move) != 0) return;
+    if (vfget(fa, VF_disable_move) != 0) {
+      log_fail(ident(p ^ 1), FAIL_None);
+      return;
+    }
     uint32_t n = 0;
     bool err = true;
     for (int i = 0; i < 4; i++) {
@@ -1421,10 +1718,14 @@ struct Engine {
         if (fa.moves[i].id != MOVE_None) err = false;
       }
     }
-    if (n == 0 || err) return;
+    if (n == 0 || err) {
+      log_fail(ident(p ^ 1), FAIL_None);
+      return;
+    }
     vfset(fa, VF_disable_move, roll_moveSlot(p, fa.moves, n));
     vfset(fa, VF_disable_duration, roll_duration(p, 1, 9));
     ch_observe(F_disable, p ^ 1, OBS_STARTED);
+    log_start_move(ident(p ^ 1), START_Disable, fa.moves[vfget(fa, VF_disable_move) - 1].id);
   }
   void effect_drainHP(int p) {  // :1963-1979
     Pokemon& st = stored(side(p));
@@ -1436,6 +1737,7 @@ struct Engine {
     if (st.hp == st.stats.hp) return;
     const uint32_t h = (uint32_t)st.hp + drain;
     st.hp = (uint16_t)(h < st.stats.hp ? h : st.stats.hp);
+    log_heal(ident(p), st, HEAL_Drain, ident(p ^ 1));
   }
   void effect_explode(int p) {  // :1981-1990
     Side& s = side(p);
@@ -1462,6 +1764,7 @@ struct Engine {
     for (int i = 0; i < 6; i++)
       if (status_is(f.pokemon[i].status, ST_FRZ)) return;  // Freeze Clause Mod
     fs.status = status_init(ST_FRZ);
+    log_status(ident(p ^ 1), fs.status, STS_None);
   }
   void effect_haze(int p) {  // :2035-2082
     Side& s = side(p);
@@ -1470,13 +1773,17 @@ struct Engine {
     f.active.boosts = 0;
     s.active.stats = stored(s).stats;
     f.active.stats = stored(f).stats;
+    log_activate(ident(p), ACT_Haze);
+    log_op(LG_ClearAllBoost);
     for (int i = 0; i < 2; i++) {
       Pokemon& st = stored(b.sides[i]);
       if (i != p && st.status != 0) {
+        log_curestatus(ident(p ^ 1), st.status, CURE_Silent);
         st.status = 0;
         ch_observe(F_sleep, i, OBS_NONE);
       } else if (st.status == STATUS_TOX) {
         st.status = status_init(ST_PSN);
+        log_status(ident(i), st.status, STS_None);
       }
       clearVolatiles(i);
     }
@@ -1485,22 +1792,32 @@ struct Engine {
     Side& s = side(p);
     Pokemon& st = stored(s);
     const uint16_t delta = (uint16_t)(st.stats.hp - st.hp);
-    if (delta == 0 || ((delta & 255) == 255 && st.hp % 256 != 0)) return;
-    if (s.last_selected_move == MOVE_Rest) {
+    if (delta == 0 || ((delta & 255) == 255 && st.hp % 256 != 0)) {
+      log_fail(ident(p), FAIL_None);
+      return;
+    }
+    const bool rest = s.last_selected_move == MOVE_Rest;
+    if (rest) {
       advance(1);
       st.status = 0x80 | 2;
+      log_status(ident(p), st.status, STS_From, MOVE_Rest);
       st.hp = st.stats.hp;
     } else {
       const uint32_t h = (uint32_t)st.hp + st.stats.hp / 2;
       st.hp = (uint16_t)(h < st.stats.hp ? h : st.stats.hp);
     }
+    log_heal(ident(p), st, rest ? HEAL_Silent : HEAL_None);
   }
   void effect_leechSeed(int p, const MoveData& move) {  // :2113-2134
     Side& f = foe(p);
-    if (!vget(f.active, V_Invulnerable) && types_includes(f.active.types, TYPE_Grass)) return;
+    if (!vget(f.active, V_Invulnerable) && types_includes(f.active.types, TYPE_Grass)) {
+      log_id_arg(LG_Immune, ident(p ^ 1), IMM_None);
+      return;
+    }
     if (!checkHit(p, move)) return;
     if (vget(f.active, V_LeechSeed)) return;
     vset(f.active, V_LeechSeed, true);
+    log_start(ident(p ^ 1), START_LeechSeed);
   }
   void effect_mimic(int p, const MoveData& move, int mslot) {  // :2146-2180
     Side& s = side(p);
@@ -1515,12 +1832,14 @@ struct Engine {
       }
     }
     if (!has_mimic) {
-      (void)checkHit(p, move);
+      if (!checkHit(p, move)) return;
+      log_fail(ident(p ^ 1), FAIL_None);
       return;
     }
     if (!checkHit(p, move)) return;
     const uint32_t rslot = roll_moveSlot(p, f.active.moves, 0);
     s.active.moves[oslot - 1].id = f.active.moves[rslot - 1].id;
+    log_start_move(ident(p), START_Mimic, s.active.moves[oslot - 1].id);
   }
   void effect_multiHit(int p, const MoveData& move) {  // :2191-2201
     Active& a = side(p).active;
@@ -1532,11 +1851,18 @@ struct Engine {
     Pokemon& fs = stored(f);
     const bool immune = move.type == TYPE_Electric &&
                         (type_eff(move.type, f.active.types & 15) == 0 || type_eff(move.type, f.active.types >> 4) == 0);
-    if (immune && !vget(f.active, V_Invulnerable)) return;
+    if (immune && !vget(f.active, V_Invulnerable)) {
+      log_id_arg(LG_Immune, ident(p ^ 1), IMM_None);
+      return;
+    }
     if (!checkHit(p, move)) return;
-    if (fs.status != 0) return;
+    if (fs.status != 0) {
+      log_fail(ident(p ^ 1), status_is(fs.status, ST_PAR) ? FAIL_Paralysis : FAIL_None);
+      return;
+    }
     fs.status = status_init(ST_PAR);
     f.active.stats.spe = (uint16_t)(f.active.stats.spe / 4 > 1 ? f.active.stats.spe / 4 : 1);
+    log_status(ident(p ^ 1), fs.status, STS_None);
   }
   void effect_paralyzeChance(int p, const MoveData& move) {  // :2235-2255
     Side& f = foe(p);
@@ -1550,6 +1876,7 @@ struct Engine {
     if (!roll_secondary(p, move.effect == EFF_ParalyzeChance1 ? 26 : 77)) return;
     fs.status = status_init(ST_PAR);
     f.active.stats.spe = (uint16_t)(f.active.stats.spe / 4 > 1 ? f.active.stats.spe / 4 : 1);
+    log_status(ident(p ^ 1), fs.status, STS_None);
   }
   void effect_poison(int p, const MoveData& move) {  // :2263-2309
     Side& f = foe(p);
@@ -1558,12 +1885,23 @@ struct Engine {
     if (move.effect == EFF_Poison && !checkHit(p, move)) {
       return;
     } else if (vget(f.active, V_Substitute)) {
+      if (move.effect == EFF_Poison) log_fail(ident(p ^ 1), FAIL_None);
       return;
     } else if (fs.status != 0) {
-      if (move.effect != EFF_Poison) advance(1);
+      if (move.effect != EFF_Poison) {
+        advance(1);
+        return;
+      }
+      uint8_t why = FAIL_None;  // :2276-2286
+      if (status_is(fs.status, ST_PSN) && toxic == (fs.status == STATUS_TOX)) why = toxic ? FAIL_Toxic : FAIL_Poison;
+      log_fail(ident(p ^ 1), why);
       return;
     } else if (types_includes(f.active.types, TYPE_Poison)) {
-      if (move.effect != EFF_Poison) advance(1);
+      if (move.effect != EFF_Poison) {
+        advance(1);
+        return;
+      }
+      log_id_arg(LG_Immune, ident(p ^ 1), IMM_None);
       return;
     }
     if (move.effect != EFF_Poison) {
@@ -1575,6 +1913,7 @@ struct Engine {
       vset(f.active, V_Toxic, true);
       vfset(f.active, VF_toxic, 0);
     }
+    log_status(ident(p ^ 1), fs.status, STS_None);
   }
   void effect_recoil(int p, bool& residual) {  // :2317-2335
     Side& s = side(p);
@@ -1584,13 +1923,17 @@ struct Engine {
     const int damage = b.last_damage / div > 1 ? b.last_damage / div : 1;
     const int hp = (int)st.hp - damage;
     st.hp = (uint16_t)(hp > 0 ? hp : 0);
+    log_damage(ident(p), st, DMG_RecoilOf, ident(p ^ 1));
     if (st.hp == 0) residual = false;
   }
   void effect_sleep(int p) {  // :2347-2380
     Side& f = foe(p);
     Pokemon& fs = stored(f);
     if (!vget(f.active, V_Recharging)) {
-      if (fs.status != 0) return;
+      if (fs.status != 0) {
+        log_fail(ident(p ^ 1), status_is(fs.status, ST_SLP) ? FAIL_Sleep : FAIL_None);
+        return;
+      }
     }
     for (int i = 0; i < 6; i++) {
       const uint8_t st = f.pokemon[i].status;
@@ -1599,17 +1942,26 @@ struct Engine {
     vset(f.active, V_Recharging, false);
     fs.status = (uint8_t)roll_duration(p, 1, 8);
     ch_observe(F_sleep, p ^ 1, OBS_STARTED);
+    log_status(ident(p ^ 1), fs.status, STS_From, side(p).last_selected_move);
   }
   void effect_substitute(int p, bool& residual) {  // :2386-2413
     Side& s = side(p);
     Pokemon& st = stored(s);
-    if (vget(s.active, V_Substitute)) return;
+    if (vget(s.active, V_Substitute)) {
+      log_fail(ident(p), FAIL_Substitute);
+      return;
+    }
     const uint8_t hp = (uint8_t)(st.stats.hp / 4);
     const uint16_t required = (uint16_t)((st.stats.hp - 1) / 4 + 1);
-    if (st.hp < required) return;
+    if (st.hp < required) {
+      log_fail(ident(p), FAIL_Weak);
+      return;
+    }
     st.hp -= hp;
     vfset(s.active, VF_substitute, (uint32_t)hp + 1);
     vset(s.active, V_Substitute, true);
+    log_start(ident(p), START_Substitute);
+    if (hp > 0) log_damage(ident(p), st, DMG_None);
     if (hp > 0 && st.hp == 0) residual = false;
   }
   void effect_switchAndTeleport(int p, const MoveData& move) {  // :2415-2425
@@ -1634,6 +1986,7 @@ struct Engine {
       s.active.moves[i].id = f.active.moves[i].id;
       s.active.moves[i].pp = f.active.moves[i].id != MOVE_None ? 5 : 0;
     }
+    log_id_arg(LG_Transform, ident(p), ident(p ^ 1));
   }
   void effect_binding(int p, bool rewrap) {  // :2467-2482
     Side& s = side(p);
@@ -1677,20 +2030,38 @@ struct Engine {
       case EFF_SpecialUp2: which = B_spc; n = 2; break;
       default: which = B_evasion; n = 1; break;  // EvasionUp1
     }
-    if (bget(a, which) == 6) return;
+    const uint8_t id = ident(p);
+    if (bget(a, which) == 6) {
+      log_fail(id, FAIL_None);
+      return;
+    }
     const int nb = bget(a, which) + n;
     bset(a, which, nb > 6 ? 6 : nb);
+    // log reason(s): Special raises SpecialAttack and SpecialDefense, Rage has its own (:2499,2558-2569)
+    static const uint8_t REASON[6] = {BST_Attack, BST_Defense, BST_Speed, BST_SpecialAttack, BST_Accuracy, BST_Evasion};
+    const uint8_t reason = move.effect == EFF_Rage ? (uint8_t)BST_Rage : REASON[which];
     if (which != B_evasion) {
       uint16_t* stat = stat_ptr(a.stats, which);
       if (*stat == 999) {
         bset(a, which, bget(a, which) - 1);
+        log_boost(id, reason, n);
+        log_boost(id, REASON[which], -1);
+        if (which == B_spc) {
+          log_boost(id, BST_SpecialDefense, n);
+          log_boost(id, BST_SpecialDefense, -1);
+        }
+        if (move.effect != EFF_Rage) log_fail(id, FAIL_None);
         return;
       }
       const uint8_t* mod = BOOSTS[bget(a, which) + 6];
       const uint32_t base = *stat_ptr(unmodifiedStats(s), which);
       const uint32_t v = base * mod[0] / mod[1];
       *stat = (uint16_t)(v < 999 ? v : 999);
+      log_boost(id, reason, n);
+      if (which == B_spc) log_boost(id, BST_SpecialDefense, n);
       if (move.effect == EFF_Rage) return;
+    } else {
+      log_boost(id, BST_Evasion, 1);
     }
     Side& f = foe(p);
     statusModify(stored(f).status, f.active.stats);
@@ -1700,7 +2071,11 @@ struct Engine {
     Side& f = foe(p);
     Active& fa = f.active;
     const bool secondary = eff_isStatDownChance(move.effect);
-    if (vget(fa, V_Substitute)) return;
+    const uint8_t id = ident(p ^ 1);
+    if (vget(fa, V_Substitute)) {
+      if (!secondary) log_fail(id, FAIL_None);
+      return;
+    }
     if (secondary) {
       const bool proc = roll_secondary(p, 85);
       if (!proc || vget(fa, V_Invulnerable)) return;
@@ -1714,42 +2089,64 @@ struct Engine {
       case EFF_SpecialDownChance: which = B_spc; break;
       default: which = B_accuracy; break;  // AccuracyDown1
     }
-    if (bget(fa, which) == -6) return;
+    if (bget(fa, which) == -6) {
+      log_fail(id, FAIL_None);  // `fail` = showdown or !secondary (:2603)
+      return;
+    }
     const int nb = bget(fa, which) - n;
     bset(fa, which, nb < -6 ? -6 : nb);
+    static const uint8_t REASON[6] = {BST_Attack, BST_Defense, BST_Speed, BST_SpecialAttack, BST_Accuracy, BST_Evasion};
     if (which != B_accuracy) {
       uint16_t* stat = stat_ptr(fa.stats, which);
       if (*stat == 1) {
         bset(fa, which, bget(fa, which) + 1);
+        log_boost(id, REASON[which], -n);
+        log_boost(id, REASON[which], 1);
+        if (which == B_spc) {
+          log_boost(id, BST_SpecialDefense, -1);
+          log_boost(id, BST_SpecialDefense, 1);
+        }
+        log_fail(id, FAIL_None);
         return;
       }
       const uint8_t* mod = BOOSTS[bget(fa, which) + 6];
       const uint32_t base = *stat_ptr(unmodifiedStats(f), which);
       const uint32_t v = base * mod[0] / mod[1];
       *stat = (uint16_t)(v > 1 ? v : 1);
+      log_boost(id, REASON[which], -n);
+      if (which == B_spc) log_boost(id, BST_SpecialDefense, -1);
+    } else {
+      log_boost(id, BST_Accuracy, -1);
     }
     statusModify(stored(f).status, fa.stats);
   }
 
   void clearVolatiles(int who) {  // :2711-2759
     Active& a = side(who).active;
+    const uint8_t id = ident(who);
     if (vfget(a, VF_disable_move) != 0) {
       vfset(a, VF_disable_move, 0);
       vfset(a, VF_disable_duration, 0);
       ch_observe(F_disable, who, OBS_NONE);
+      log_end(id, END_DisableSilent);
     }
     if (vget(a, V_Confusion)) {
       vset(a, V_Confusion, false);
       ch_observe(F_confusion, who, OBS_NONE);
+      log_end(id, END_ConfusionSilent);
     }
-    vset(a, V_Mist, false);
-    vset(a, V_FocusEnergy, false);
-    vset(a, V_LeechSeed, false);
-    vset(a, V_LightScreen, false);
-    vset(a, V_Reflect, false);
+    static const struct { int bit; uint8_t end; } FLAGS[5] = {{V_Mist, END_MistSilent}, {V_FocusEnergy, END_FocusEnergySilent},
+        {V_LeechSeed, END_LeechSeedSilent}, {V_LightScreen, END_LightScreenSilent}, {V_Reflect, END_ReflectSilent}};
+    for (const auto& fl : FLAGS) {
+      if (vget(a, fl.bit)) {
+        vset(a, fl.bit, false);
+        log_end(id, fl.end);
+      }
+    }
     if (vget(a, V_Toxic)) {
       vset(a, V_Toxic, false);
       vfset(a, VF_toxic, 0);
+      log_end(id, END_ToxicSilent);
     }
   }
 
@@ -1807,8 +2204,10 @@ struct Engine {
 
 // Oak's build of libpkmn (reference dev/libpkmn:9): -Dshowdown miss=false advance=false ebc=false key=true
 using OakEngine = Engine<false, false, false, true, false>;
+using OakLogEngine = Engine<false, false, false, true, false, true>;
 // libpkmn's default -Dshowdown options with a scripted roll list: what gen1/test.zig is written for
 using KatEngine = Engine<true, true, true, false, true>;
+using KatLogEngine = Engine<true, true, true, false, true, true>;
 // libpkmn default -Dshowdown options with the live PRNG
 using DefaultEngine = Engine<true, true, true, false, false>;
 

@@ -37,6 +37,37 @@ uint8_t oracle_gen1_update_kat(uint8_t* battle, uint8_t c1, uint8_t c2, Options*
   return r;
 }
 
+// The same two with the binary protocol log (common/protocol.zig:313-863) appended to buf[*pos..cap); a log that does
+// not fit returns 0b1100 (bindings/c.zig:6,181) with the battle left wherever the update was when the write failed.
+uint8_t oracle_gen1_update_log(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o, uint8_t* buf, size_t cap, size_t* pos) {
+  LogBuf lg{buf, cap, *pos};
+  OakLogEngine e(*reinterpret_cast<Battle*>(battle), *o, nullptr, &lg);
+  uint8_t r;
+  try {
+    r = e.update(c1, c2);
+  } catch (const LogOverflow&) {
+    r = RESULT_LOG_OVERFLOW;
+  }
+  *pos = lg.pos;
+  return r;
+}
+uint8_t oracle_gen1_update_kat_log(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o, const uint32_t* rolls, size_t len,
+                                   size_t* index, int* overrun, uint8_t* buf, size_t cap, size_t* pos) {
+  Rolls32 fx{rolls, len, *index, false};
+  LogBuf lg{buf, cap, *pos};
+  KatLogEngine e(*reinterpret_cast<Battle*>(battle), *o, &fx, &lg);
+  uint8_t r;
+  try {
+    r = e.update(c1, c2);
+  } catch (const LogOverflow&) {
+    r = RESULT_LOG_OVERFLOW;
+  }
+  *index = fx.index;
+  *overrun = fx.overrun;
+  *pos = lg.pos;
+  return r;
+}
+
 // libpkmn-default-flag update with the live PRNG (used to diff flag sets on roll-free scenarios).
 uint8_t oracle_gen1_update_default(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o) {
   DefaultEngine e(*reinterpret_cast<Battle*>(battle), *o);

@@ -4,9 +4,11 @@ driving the CPU oracle through ctypes.
 The known-answer cases in tests/golden/gen1_kat_cases.py are machine-transcribed from the reference's
 gen1/test.zig by tools/transcribe_kat.py; they are written against the API below, which keeps the
 reference's names (Test(rolls).init(p1, p2), t.update(move(1), move(1)), t.expected.p1.get(1).hp,
-t.verify(), ...). Protocol-log expectations are dropped (the oracle has no log writer yet); HP of all
-twelve Pokémon after every update, explicit state expectations, results, legal-choice lists and
-"scripted roll list fully consumed" are checked.
+t.verify(), ...). Checked after every update, as test.zig:10535-10553 does: the protocol-log bytes the
+update wrote against the bytes the case's `t.log.expected.*` calls wrote (the expected writer below is a
+separate Python statement of common/protocol.zig:337-824 over the ordinals tools/gen_tables.py read from
+that file), HP of all twelve Pokémon, explicit state expectations, results, legal-choice lists and
+"scripted roll list fully consumed".
 """
 import ctypes
 import json
@@ -20,6 +22,10 @@ SPECIES_ID = {n: i for i, n in enumerate(NAMES["species"])}
 TYPE_ID = {n: i for i, n in enumerate(NAMES["types"])}
 MOVE_ID["SKIP_TURN"] = 255
 
+PROTOCOL = {k: {n: i for i, n in enumerate(v)} for k, v in NAMES["protocol"].items()}
+ARG = PROTOCOL["ArgType"]
+LOG_CAP = 1 << 16
+
 _lib = None
 
 
@@ -32,6 +38,7 @@ def oracle_lib():
             subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
         _lib = ctypes.CDLL(path)
         _lib.oracle_gen1_update_kat.restype = ctypes.c_uint8
+        _lib.oracle_gen1_update_kat_log.restype = ctypes.c_uint8
         _lib.oracle_gen1_update.restype = ctypes.c_uint8
         _lib.oracle_gen1_choices.restype = ctypes.c_uint8
     return _lib
@@ -578,6 +585,159 @@ class _Pair:
     pass
 
 
+def ID():
+    """Zig `ID{}`: no target."""
+    return 0
+
+
+def Types(type1, type2):
+    return dict(type1=type1, type2=type2)
+
+
+class LogExpected:
+    """`t.log.expected` of the Zig harness: each method appends what common/protocol.zig's `Log` method of the same
+    name writes (:337-824). Enum literals resolve against the argument's own reason enum, as Zig's result-location typing
+    does."""
+
+    def __init__(self):
+        self.buf = bytearray()
+
+    @staticmethod
+    def _r(v, enum):
+        if isinstance(v, Lit):
+            return PROTOCOL[enum][v.name]
+        return int(v)
+
+    @staticmethod
+    def _mv(v):
+        return lit_int(v, MOVE_ID)
+
+    def _pk(self, pk):
+        self.buf += struct.pack("<HH", pk.hp, pk.stats.hp)
+
+    def move(self, a):
+        self.buf += bytes([ARG["Move"], int(a[0]), self._mv(a[1]), int(a[2])])
+        if len(a) < 4 or self._mv(a[3]) == 0:
+            self.buf.append(0)
+        else:
+            self.buf += bytes([1, self._mv(a[3])])
+
+    def switched(self, a):
+        pk = a[1]
+        self.buf += bytes([ARG["Switch"], int(a[0]), pk.species, pk.level])
+        self._pk(pk)
+        self.buf.append(pk.status)
+
+    def cant(self, a):
+        self.buf += bytes([ARG["Cant"], int(a[0]), self._r(a[1], "Cant")])
+        if len(a) == 3:
+            self.buf.append(self._mv(a[2]))
+
+    def faint(self, a):
+        self.buf += bytes([ARG["Faint"], int(a[0])])
+        if a[1]:
+            self.buf.append(0)
+
+    def turn(self, a):
+        self.buf += bytes([ARG["Turn"]]) + struct.pack("<H", int(a[0])) + b"\0"
+
+    def win(self, a):
+        self.buf += bytes([ARG["Win"], lit_int(a[0], MISC), 0])
+
+    def tie(self, a):
+        self.buf += bytes([ARG["Tie"], 0])
+
+    def _hp(self, op, a, enum):
+        self.buf += bytes([ARG[op], int(a[0])])
+        self._pk(a[1])
+        self.buf += bytes([a[1].status, self._r(a[2], enum)])
+        if len(a) == 4:
+            self.buf.append(int(a[3]))
+
+    def damage(self, a):
+        self._hp("Damage", a, "Damage")
+
+    def heal(self, a):
+        self._hp("Heal", a, "Heal")
+
+    def status(self, a):
+        self.buf += bytes([ARG["Status"], int(a[0]), int(a[1]), self._r(a[2], "Status")])
+        if len(a) == 4:
+            self.buf.append(self._mv(a[3]))
+
+    def curestatus(self, a):
+        self.buf += bytes([ARG["CureStatus"], int(a[0]), int(a[1]), self._r(a[2], "CureStatus")])
+
+    def boost(self, a):
+        self.buf += bytes([ARG["Boost"], int(a[0]), self._r(a[1], "Boost"), int(a[2]) + 6])
+
+    def clearallboost(self, a):
+        self.buf.append(ARG["ClearAllBoost"])
+
+    def fail(self, a):
+        self.buf += bytes([ARG["Fail"], int(a[0]), self._r(a[1], "Fail")])
+
+    def miss(self, a):
+        self.buf += bytes([ARG["Miss"], int(a[0])])
+
+    def hitcount(self, a):
+        self.buf += bytes([ARG["HitCount"], int(a[0]), int(a[1])])
+
+    def prepare(self, a):
+        self.buf += bytes([ARG["Prepare"], int(a[0]), self._mv(a[1])])
+
+    def mustrecharge(self, a):
+        self.buf += bytes([ARG["MustRecharge"], int(a[0])])
+
+    def activate(self, a):
+        self.buf += bytes([ARG["Activate"], int(a[0]), self._r(a[1], "Activate")])
+
+    def fieldactivate(self, a):
+        self.buf.append(ARG["FieldActivate"])
+
+    def start(self, a):
+        self.buf += bytes([ARG["Start"], int(a[0]), self._r(a[1], "Start")])
+        if len(a) == 3:
+            self.buf.append(self._mv(a[2]))
+        elif len(a) == 4:
+            t = a[2]
+            types = t._b[t._o] if isinstance(t, TypesV) else (lit_int(t["type1"], TYPE_ID) | lit_int(t["type2"], TYPE_ID) << 4)
+            self.buf += bytes([types, int(a[3])])
+
+    def end(self, a):
+        self.buf += bytes([ARG["End"], int(a[0]), self._r(a[1], "End")])
+
+    def ohko(self, a):
+        self.buf.append(ARG["OHKO"])
+
+    def crit(self, a):
+        self.buf += bytes([ARG["Crit"], int(a[0])])
+
+    def supereffective(self, a):
+        self.buf += bytes([ARG["SuperEffective"], int(a[0])])
+
+    def resisted(self, a):
+        self.buf += bytes([ARG["Resisted"], int(a[0])])
+
+    def immune(self, a):
+        self.buf += bytes([ARG["Immune"], int(a[0]), self._r(a[1], "Immune")])
+
+    def transform(self, a):
+        self.buf += bytes([ARG["Transform"], int(a[0]), int(a[1])])
+
+    def laststill(self, a):
+        self.buf.append(ARG["LastStill"])
+
+    def lastmiss(self, a):
+        self.buf.append(ARG["LastMiss"])
+
+
+def format_log(b):
+    """Best-effort split of a log stream into messages, for failure output."""
+    inv = {v: k for k, v in ARG.items()}
+    return " ".join(f"{inv.get(x, '')}:{x}" if x in inv and 0 < x < 31 else str(x) for x in b)
+
+
 class OptionsV:
     """options.chance / options.calc as seen by the few tests that poke them."""
 
@@ -606,6 +766,11 @@ class TestCase:
         self.opt = (ctypes.c_uint8 * 40)()
         self.options = OptionsV(self)
         self.updates = 0
+        self.log = _Pair()
+        self.log.expected = LogExpected()
+        self.log_actual = (ctypes.c_uint8 * LOG_CAP)()
+        self.log_pos = ctypes.c_size_t(0)
+        self.log_offset = 0
 
     def deinit(self):
         pass
@@ -618,8 +783,20 @@ class TestCase:
             # calc.update: options.chance.reset() keeps durations (calc.zig:425-426)
             for i in range(16):
                 opt[i] = 0
-        r = lib.oracle_gen1_update_kat(raw, c1, c2, opt, self._rolls_c, len(self.rolls),
-                                       ctypes.byref(self.index), ctypes.byref(self.overrun))
+        if fresh_options:  # Test.start() logs into its own scratch buffer (test.zig:10474-10492)
+            scratch = (ctypes.c_uint8 * 64)()
+            pos = ctypes.c_size_t(0)
+            r = lib.oracle_gen1_update_kat_log(raw, c1, c2, opt, self._rolls_c, len(self.rolls), ctypes.byref(self.index),
+                                               ctypes.byref(self.overrun), scratch, 64, ctypes.byref(pos))
+            exp = LogExpected()
+            exp.switched([P1.ident(1), self.actual.p1.get(1)])
+            exp.switched([P2.ident(1), self.actual.p2.get(1)])
+            exp.turn([1])
+            if bytes(scratch[:pos.value]) != bytes(exp.buf):
+                raise KatFailure(f"start log: expected {format_log(exp.buf)} actual {format_log(scratch[:pos.value])}")
+        else:
+            r = lib.oracle_gen1_update_kat_log(raw, c1, c2, opt, self._rolls_c, len(self.rolls), ctypes.byref(self.index),
+                                               ctypes.byref(self.overrun), self.log_actual, LOG_CAP, ctypes.byref(self.log_pos))
         if self.overrun.value:
             raise KatFailure("Insufficient number of rolls provided")
         self.updates += 1
@@ -638,6 +815,12 @@ class TestCase:
         return r
 
     def validate(self):
+        exp = bytes(self.log.expected.buf)
+        act = bytes(self.log_actual[:self.log_pos.value])
+        if exp != act:
+            o = self.log_offset
+            raise KatFailure(f"protocol log after update #{self.updates}:\n  expected {format_log(exp[o:])}\n  actual   {format_log(act[o:])}")
+        self.log_offset = len(exp)
         for s, (e, a) in enumerate(((self.expected.p1, self.actual.p1), (self.expected.p2, self.actual.p2))):
             for i in range(6):
                 if e.pokemon[i].hp != a.pokemon[i].hp:
@@ -693,7 +876,7 @@ def expectEqualSlices(_ty, a, b):
 def namespace():
     g = dict(Test=Test, move=move, swtch=swtch, forced=forced, Result=Result, Status=Status, Move=Move,
              Species=Species, ranged=ranged, metronome=metronome, MIN=MIN, MAX=MAX, NOP=NOP, HIT=HIT, CRIT=CRIT,
-             MIN_DMG=MIN_DMG, MAX_DMG=MAX_DMG, P1=P1, P2=P2, L=L, EMPTY=EMPTY, expectEqual=expectEqual, expect=expect,
+             MIN_DMG=MIN_DMG, MAX_DMG=MAX_DMG, P1=P1, P2=P2, L=L, ID=ID, Types=Types, EMPTY=EMPTY, expectEqual=expectEqual, expect=expect,
              expectEqualSlices=expectEqualSlices, showdown=True, SkipCase=SkipCase, Choice=None,
              choices=[0] * 16)
     return g

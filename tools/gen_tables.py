@@ -155,18 +155,37 @@ def main():
     ty_enum = ["enum Gen1Type {"] + [f"    TYPE_{n} = {i}," for i, n in enumerate(types)] + ["};"]
     enum_txt = "\n".join(enums) + "\n\n" + "\n".join(mv_enum) + "\n\n" + "\n".join(ty_enum) + "\n"
 
+    # protocol-log ordinals (common/protocol.zig:16-311): ArgType and the reason enums of the Generation I messages
+    proto_src = open(f"{REF}/lib/common/protocol.zig").read()
+    protocol = {}
+    for name in ("ArgType", "Move", "Cant", "Heal", "Damage", "Status", "CureStatus", "Boost", "Fail", "Activate", "Start", "End",
+                 "Immune"):
+        m = re.search(r"pub const " + name + r" = enum\(u8\) \{(.*?)\n\};", proto_src, re.S)
+        body_ = re.sub(r"//[^\n]*", "", m.group(1))
+        protocol[name] = [w.strip() for w in body_.split(",") if w.strip()]
+    assert protocol["ArgType"][30] == "Transform" and protocol["End"][22] == "ReflectSilent"
+    GEN1_ARGS = protocol["ArgType"][:31]
+    KEEP = {"Cant": 7, "Heal": 3, "Damage": 6, "Status": 3, "CureStatus": 2, "Boost": 8, "Fail": 9, "Activate": 7, "Start": 12,
+            "End": 24, "Immune": 2}
+    PREFIX = {"Cant": "CANT", "Heal": "HEAL", "Damage": "DMG", "Status": "STS", "CureStatus": "CURE", "Boost": "BST", "Fail": "FAIL",
+              "Activate": "ACT", "Start": "START", "End": "END", "Immune": "IMM"}
+    lg = ["enum LogArg {"] + [f"    LG_{n} = {i}," for i, n in enumerate(GEN1_ARGS)] + ["};"]
+    for k, n_keep in KEEP.items():
+        lg += [f"enum Log{k} {{"] + [f"    {PREFIX[k]}_{n} = {i}," for i, n in enumerate(protocol[k][:n_keep])] + ["};"]
+    log_txt = "\n// protocol-log ordinals (reference engine/src/lib/common/protocol.zig:16-311)\n" + "\n".join(lg) + "\n"
+
     os.makedirs(f"{ROOT}/oracle", exist_ok=True)
     os.makedirs(f"{ROOT}/oak_b200/csrc", exist_ok=True)
     os.makedirs(f"{ROOT}/tests/golden", exist_ok=True)
     with open(f"{ROOT}/oracle/gen1_tables.h", "w") as f:
         f.write(hdr + "#pragma once\n\n" + enum_txt + "\n" + body("static const"))
     with open(f"{ROOT}/oak_b200/csrc/gen1_tables.cuh", "w") as f:
-        f.write(hdr + "#pragma once\n\n" + enum_txt.replace("Gen1Effect", "Effect").replace("Gen1Move", "Move").replace("Gen1Type", "Type")
+        f.write(hdr + "#pragma once\n\n" + enum_txt.replace("Gen1Effect", "Effect").replace("Gen1Move", "Move").replace("Gen1Type", "Type") + log_txt
                 + "\n#ifdef __CUDACC__\n#define OAK_TABLE static __device__ const\n#else\n#define OAK_TABLE static const\n#endif\n\n"
                 + body("OAK_TABLE"))
     with open(f"{ROOT}/tests/golden/gen1_names.json", "w") as f:
         json.dump(dict(moves=moves, species=species, types=types, effects=effects,
-                       move_data=move_data, pp=pp, species_data=species_data, chart=chart), f)
+                       move_data=move_data, pp=pp, species_data=species_data, chart=chart, protocol=protocol), f)
     print(f"moves={len(moves)} effects={len(effects)} species={len(species)} types={len(types)}")
 
 

@@ -6,8 +6,8 @@ Input : /root/reference/cpp/extern/engine/src/lib/gen1/test.zig (126 `test "..."
 Output: tests/golden/gen1_kat_cases.py — one `def case_NNN(h)` per test, written against the API of
         tests/kat_harness.py (which mirrors the Zig harness, test.zig:10415-10554).
 
-Only the Pokémon Showdown compatibility branch of every `if (showdown) A else B` is kept, protocol-log
-expectations (`t.log.expected.*`) and probability expectations are dropped. Tests using constructs the
+Only the Pokémon Showdown compatibility branch of every `if (showdown) A else B` is kept; protocol-log
+expectations (`t.log.expected.*`) become calls on the harness's expected-log writer; probability expectations are dropped. Tests using constructs the
 translator does not understand are emitted as skipped with the reason, never silently altered.
 
 Run in the build container only (the reference tree is not on the GPU box); the output is committed.
@@ -348,7 +348,7 @@ def translate_expr(s):
 
 # ----------------------------------------------------------------------------- statements
 SKIP_STMT = re.compile(
-    r"^(try\s+)?(t\.log\.expected\.|expected\.\w+\(|defer\b|try\s+expectLog\b|expectLog\b|"
+    r"^(try\s+)?(expected\.\w+\(|defer\b|try\s+expectLog\b|expectLog\b|"
     r"(var|const)\s+(expected_buf|actual_buf|expected_writer|actual_writer)\b|"
     r"(var|const)\s+(expected|actual)(:\s*FixedLog)?\s*=\s*(FixedLog|\.\{\s*\.writer)|"
     r"(var|const)\s+options\s*=\s*pkmn\.battle\.options|(var|const)\s+size\s*=|"
