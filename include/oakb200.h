@@ -82,6 +82,19 @@ int oakb200_step(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const u
                  uint8_t* results_out, uint8_t* actions_out);
 int oakb200_step_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
                         const void* c2, const void* overrides, void* actions_out);
+/* The same update with libpkmn's binary protocol log, i.e. what a -Dlog build of libpkmn writes through
+ * pkmn_gen1_log_options (pkmn.h:184-193; messages engine/src/lib/common/protocol.zig:313-824, docs/PROTOCOL.md; consumer
+ * in Oak: cpp/include/util/debug-log.h:13-68, cpp/src/log.cc). logs_out[n][log_stride] receives battle i's messages for
+ * this update at row i, log_lens_out[n] (u32) their byte count. log_stride >= OAKB200_MAX_LOGS always suffices
+ * (PKMN_GEN1_MAX_LOGS, engine/src/lib/gen1/data.zig:22). A battle whose log does not fit keeps the message parts that did,
+ * gets the result byte 0x0C (pkmn_error(), bindings/c.zig:6,181) and is not stepped again; unlike the reference, which
+ * abandons the update half-way at that point, its state is that of the completed update. */
+#define OAKB200_MAX_LOGS 180
+int oakb200_step_log(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const uint8_t* overrides, uint8_t* results_out,
+                     uint8_t* actions_out, uint8_t* logs_out, uint32_t log_stride, uint32_t* log_lens_out);
+int oakb200_step_log_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
+                            const void* c2, const void* overrides, void* actions_out, void* logs, uint32_t log_stride,
+                            void* log_lens);
 /* One random-playout step (body of the loop at mcts.h:467-479): choices for both players, then
  * c1 = choices1[pick % m], c2 = choices2[(pick >> 32) % n], options_set(null), update.
  * pick for battle i = splitmix64(seeds[i] ^ (0xD1B54A32D192ED03 * step_index)). */

@@ -43,6 +43,21 @@ __device__ __forceinline__ void load_column(uint32_t* col, const uint8_t* record
     col[(4 * k + 3) * STRIDE] = v.w;
   }
 }
+// The same through L2 only (ld.global.cg): for records that a copy engine may have written while this kernel was already
+// running (oakb200_rollout_host). The read-only path (ld.global.nc) is defined only for data that does not change during
+// the kernel; L2 is the point of coherence with the copy engines.
+template <int STRIDE>
+__device__ __forceinline__ void load_column_cg(uint32_t* col, const uint8_t* record) {
+  const uint4* src = reinterpret_cast<const uint4*>(record);
+#pragma unroll 6
+  for (int k = 0; k < BATTLE_WORDS / 4; k++) {
+    const uint4 v = __ldcg(src + k);
+    col[(4 * k + 0) * STRIDE] = v.x;
+    col[(4 * k + 1) * STRIDE] = v.y;
+    col[(4 * k + 2) * STRIDE] = v.z;
+    col[(4 * k + 3) * STRIDE] = v.w;
+  }
+}
 template <int STRIDE>
 __device__ __forceinline__ void store_column(const uint32_t* col, uint8_t* record) {
   uint4* dst = reinterpret_cast<uint4*>(record);
@@ -142,13 +157,71 @@ step_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint
   }
 }
 
+// step_log_kernel: step_kernel with libpkmn's binary protocol log (the -Dlog build; common/protocol.zig:313-863,
+// call sites = every `options.log.*` of mechanics.zig). Battle i's messages for this update go to logs[i * log_stride ..],
+// their byte count to log_lens[i]; a log that does not fit in log_stride bytes ends at the last message part that did and
+// the battle's result byte becomes 0b1100 (bindings/c.zig:6,181). A separate instantiation of the engine: the kernels
+// above carry no trace of it.
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK)
+step_log_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+                const uint8_t* __restrict__ c1s, const uint8_t* __restrict__ c2s, const uint8_t* __restrict__ overrides,
+                uint8_t* __restrict__ actions_out, uint8_t* __restrict__ logs, uint32_t log_stride, uint32_t* __restrict__ log_lens,
+                uint32_t n) {
+  extern __shared__ uint32_t tile[];
+  const uint32_t i = blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  uint32_t* col = tile + threadIdx.x;
+  load_column<BLOCK>(col, battles + (size_t)i * 384);
+  const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+  Engine<BLOCK, true, true, true> e;
+  e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
+  e.sink.buf = logs + (size_t)i * log_stride;
+  e.sink.cap = log_stride;
+  e.sink.pos = 0;
+  e.sink.overflow = 0;
+  if (overrides) {
+    const uint4 o = *reinterpret_cast<const uint4*>(overrides + (size_t)i * 16);
+    e.ovr[0] = (uint64_t)o.x | ((uint64_t)o.y << 32);
+    e.ovr[1] = (uint64_t)o.z | ((uint64_t)o.w << 32);
+  }
+  const uint32_t prev = results[i];
+  if ((prev & 15u) == 0) {  // a finished battle is frozen
+    uint32_t r = e.update(c1s[i], c2s[i]);
+    if (e.sink.overflow) r = RESULT_LOG_OVERFLOW;
+    e.end();
+    store_column<BLOCK>(col, battles + (size_t)i * 384);
+    *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
+    results[i] = (uint8_t)r;
+  }
+  log_lens[i] = e.sink.pos;
+  if (actions_out) {
+    uint4 a;
+    a.x = (uint32_t)e.act[0];
+    a.y = (uint32_t)(e.act[0] >> 32);
+    a.z = (uint32_t)e.act[1];
+    a.w = (uint32_t)(e.act[1] >> 32);
+    *reinterpret_cast<uint4*>(actions_out + (size_t)i * 16) = a;
+  }
+}
+
 // Streaming input (oakb200_rollout_host): the batch is still arriving over PCIe while the kernel runs. The copy stream
 // raises *available (the number of leading records that have landed) after each chunk; a lane whose ticket is beyond it
 // waits. Tickets and chunks both advance in index order and every copy was queued before the launch, so the wait ends.
-__device__ __forceinline__ void wait_available(const uint32_t* available, uint32_t i) {
-  if (!available) return;
-  while (i >= *reinterpret_cast<const volatile uint32_t*>(available)) __nanosleep(500);
+// available[1] is an error word: a lane that has polled for about a minute (a failed or blocked copy) raises it and gives
+// up instead of holding the SMs forever; the host turns it into OAKB200_ECUDA.
+__device__ __forceinline__ bool wait_available(uint32_t* available, uint32_t i) {
+  if (!available) return true;
+  uint32_t polls = 0;
+  while (i >= *reinterpret_cast<const volatile uint32_t*>(available)) {
+    __nanosleep(500);
+    if (++polls > (1u << 27)) {
+      atomicExch(available + 1, 1u);
+      return false;
+    }
+  }
   __threadfence();
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -161,7 +234,7 @@ __global__ void __launch_bounds__(BLOCK, 3)
 rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
-               unsigned long long* __restrict__ total_steps, const uint32_t* __restrict__ available) {
+               unsigned long long* __restrict__ total_steps, uint32_t* available) {
   extern __shared__ uint32_t tile[];
   uint32_t* col = tile + threadIdx.x;
   Engine<BLOCK, false, CHANCE> e;
@@ -175,13 +248,12 @@ rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, u
   for (;;) {
     if (!have && !exhausted) {
       i = atomicAdd(ticket, 1u);
-      if (i < n) {
-        wait_available(available, i);
-        load_column<BLOCK>(col, battles + (size_t)i * 384);
-        const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+      if (i < n && wait_available(available, i)) {
+        load_column_cg<BLOCK>(col, battles + (size_t)i * 384);
+        const uint2 d = __ldcg(reinterpret_cast<const uint2*>(durations + (size_t)i * 8));
         e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
-        result = results[i];
-        seed = seeds[i];
+        result = __ldcg(results + i);
+        seed = __ldcg(seeds + i);
         step = 0;
         have = true;
       } else {
@@ -249,7 +321,7 @@ __global__ void __launch_bounds__(BLOCK, 3)
 rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                        const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                        uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
-                       unsigned long long* __restrict__ total_steps, const uint32_t* __restrict__ available) {
+                       unsigned long long* __restrict__ total_steps, uint32_t* available) {
   static_assert(BLOCK == 128, "action_class and the sort assume 128 columns");
   extern __shared__ uint32_t tile[];
   uint32_t* s_meta = tile + BATTLE_WORDS * BLOCK;  // c1 | c2 << 8 | live << 16
@@ -270,14 +342,13 @@ rollout_grouped_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ dura
     // ---- owner: refill, legal choices, playout pick, sort key
     if (!have && !exhausted) {
       i = atomicAdd(ticket, 1u);
-      if (i < n) {
-        wait_available(available, i);
-        load_column<BLOCK>(col, battles + (size_t)i * 384);
-        const uint2 d = *reinterpret_cast<const uint2*>(durations + (size_t)i * 8);
+      if (i < n && wait_available(available, i)) {
+        load_column_cg<BLOCK>(col, battles + (size_t)i * 384);
+        const uint2 d = __ldcg(reinterpret_cast<const uint2*>(durations + (size_t)i * 8));
         s_dur[2 * t] = d.x;
         s_dur[2 * t + 1] = d.y;
-        result = results[i];
-        seed = seeds[i];
+        result = __ldcg(results + i);
+        seed = __ldcg(seeds + i);
         step = 0;
         have = true;
       } else {

@@ -21,6 +21,9 @@ struct oakb200_ctx {
   uint8_t *battles = nullptr, *durations = nullptr, *results = nullptr;
   // scratch for the host-pointer entry points
   uint8_t *c1 = nullptr, *c2 = nullptr, *overrides = nullptr, *actions = nullptr, *choices = nullptr, *counts = nullptr;
+  uint8_t* scalar_pin = nullptr;  // pinned staging of the scalar pkmn_* symbols (1 KiB)
+  uint8_t* logs = nullptr;  // scratch of oakb200_step_log: [n] u32 lengths, then [n][log_stride] bytes
+  size_t log_bytes = 0;
   uint64_t* seeds = nullptr;
   uint8_t* score2 = nullptr;
   uint16_t* turns = nullptr;
@@ -48,6 +51,12 @@ struct oakb200_ctx {
   cudaEvent_t eval_ev[130] = {};  // [0] start, then {uploaded, evaluated} per chunk
   std::string error;
 };
+
+// pkmn_compat.cu -> oakb200.cu: a batch of one through pinned staging, every copy and the kernel queued on the context
+// stream, ONE synchronisation. `log` non-null selects the LOG kernel (log_cap bytes at most, *log_len written).
+int oakb200_scalar_update(oakb200_ctx* ctx, uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, const uint8_t* overrides,
+                          uint8_t* actions, uint8_t* result, uint8_t* log, uint32_t log_cap, uint32_t* log_len);
+int oakb200_scalar_choices(oakb200_ctx* ctx, const uint8_t* battle, uint8_t result, uint8_t* choices18, uint8_t* counts2);
 
 // search.cu -> oakb200.cu
 cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_battles, const uint8_t* root_durations,

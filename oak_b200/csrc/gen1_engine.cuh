@@ -23,9 +23,13 @@ enum { OBSF_SLEEP = 0, OBSF_CONFUSION, OBSF_DISABLE, OBSF_ATTACKING, OBSF_BINDIN
 enum { BM_DONE = 0, BM_SKIP_CAN, BM_SKIP_PP, BM_OK, BM_ERR };
 static const int NO_RESULT = -1;
 
-template <int STRIDE, bool CALC, bool CHANCE>
+// LOG: write the binary protocol log of every update into `sink` (set sink.buf / cap / pos before update()); a separate
+// instantiation, so the kernels built without it carry none of it.
+template <int STRIDE, bool CALC, bool CHANCE, bool LOG = false>
 struct Engine {
-  Mem<STRIDE> m;
+  typedef typename MemFor<STRIDE, LOG>::type M;
+  M m;
+  LogSink sink;
   uint64_t rng;
   uint32_t last_damage;
   uint64_t act[2];  // chance actions (per-update observation)
@@ -33,8 +37,11 @@ struct Engine {
   uint64_t ovr[2];  // calc overrides (CALC only)
 
   // ---------------------------------------------------------------- load / store of register copies
+  OAK_HD void attach_sink(Mem<STRIDE>&) {}
+  OAK_HD void attach_sink(MemL<STRIDE>& w) { w.sink = &sink; }
   OAK_HD void begin(uint8_t* column_base, uint32_t d0, uint32_t d1) {
     m.set(column_base);
+    attach_sink(m);
     rng = m.ld64(B_RNG);
     last_damage = m.ld16(B_LAST_DAMAGE);
     act[0] = act[1] = 0;
@@ -48,8 +55,14 @@ struct Engine {
   }
 
   // ---------------------------------------------------------------- field helpers (forward to Mem)
-  static OAK_HD H sb(int p) { return Mem<STRIDE>::sb(p); }
-  static OAK_HD H pokemon(int p, int idx) { return Mem<STRIDE>::pokemon(p, idx); }
+  static OAK_HD H sb(int p) { return M::sb(p); }
+  static OAK_HD H pokemon(int p, int idx) { return M::pokemon(p, idx); }
+  OAK_HD uint32_t ident(int p) const { return m.ident(p); }
+  OAK_HD void log_lastmiss_miss(int p) const {  // checkHit's miss report (:1413-1415)
+    if (!LOG) return;
+    m.lg1(LG_LastMiss);
+    m.lg2(LG_Miss, ident(p));
+  }
   OAK_HD H stored(int p) const { return m.stored(p); }
   OAK_HD uint32_t vlo(int p) const { return m.vlo(p); }
   OAK_HD void set_vlo(int p, uint32_t v) const { m.set_vlo(p, v); }
@@ -71,8 +84,8 @@ struct Engine {
   OAK_HD uint32_t active_stat(int p, int st) const { return m.active_stat(p, st); }
   OAK_HD void set_active_stat(int p, int st, uint32_t v) const { m.set_active_stat(p, st, v); }
   // applyDamage through the shared routine; returns true when a Substitute broke
-  OAK_HD bool applyDamage(int t, int subp) {
-    const uint32_t r = mem_apply_damage(m, t, subp, last_damage);
+  OAK_HD bool applyDamage(int t, int subp, uint32_t reason = DMG_None) {
+    const uint32_t r = LOG ? mem_apply_damage_reason(m, t, subp, last_damage, reason) : mem_apply_damage(m, t, subp, last_damage);
     last_damage = r & 0x7FFFFFFFu;
     return (r >> 31) != 0;
   }

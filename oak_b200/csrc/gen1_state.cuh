@@ -267,6 +267,100 @@ struct Mem {
   OAK_HD uint32_t active_stat(int p, int st) const { return ld16(sb(p), A_STATS + st); }
   OAK_HD void set_active_stat(int p, int st, uint32_t v) const { st16(sb(p), A_STATS + st, v); }
   OAK_HD uint32_t ident(int p) const { return ((uint32_t)p << 3) | ld8(sb(p), S_ORDER); }
+
+  // ---- protocol log: nothing in this window type (MemL below writes); calls compile away
+  static const bool LOGGING = false;
+  OAK_HD void lg1(uint32_t) const {}
+  OAK_HD void lg2(uint32_t, uint32_t) const {}
+  OAK_HD void lg3(uint32_t, uint32_t, uint32_t) const {}
+  OAK_HD void lg4(uint32_t, uint32_t, uint32_t, uint32_t) const {}
+  OAK_HD void lg_hp(uint32_t, uint32_t, H, uint32_t) const {}
+  OAK_HD void lg_hp_of(uint32_t, uint32_t, H, uint32_t, uint32_t) const {}
+  OAK_HD void lg_switched(uint32_t, H) const {}
+  OAK_HD void lg_boost(uint32_t, uint32_t, int) const {}
+};
+
+// Binary protocol log of one update (reference engine/src/lib/common/protocol.zig:313-863). The sink is the caller's
+// buffer (`Writer`, :831-863): a write that does not fit is refused whole and raises `overflow`, after which nothing more
+// is written, so an undersized buffer ends with the same bytes as the reference's; the update then returns 0b1100
+// (bindings/c.zig:6,181). The byte groups passed to lgN are the reference's writeAll / writeInt / writeByte groups.
+struct LogSink {
+  uint8_t* buf;
+  uint32_t cap, pos, overflow;
+  OAK_HD bool room(uint32_t n) {
+    if (overflow || pos + n > cap) {
+      overflow = 1;
+      return false;
+    }
+    return true;
+  }
+};
+static const uint32_t RESULT_LOG_OVERFLOW = 0x0C;
+
+// The memory window of a LOG build: Mem plus the sink, so that the non-inlined state routines (gen1_mem_ops.cuh), which
+// receive the window by value, can log. The non-LOG kernels never see this type: their code is unchanged.
+template <int STRIDE>
+struct MemL : Mem<STRIDE> {
+  LogSink* sink;
+  static const bool LOGGING = true;
+  OAK_HD void lg1(uint32_t a) const {
+    if (!sink->room(1)) return;
+    sink->buf[sink->pos++] = (uint8_t)a;
+  }
+  OAK_HD void lg2(uint32_t a, uint32_t b) const {
+    if (!sink->room(2)) return;
+    uint8_t* o = sink->buf + sink->pos;
+    o[0] = (uint8_t)a;
+    o[1] = (uint8_t)b;
+    sink->pos += 2;
+  }
+  OAK_HD void lg3(uint32_t a, uint32_t b, uint32_t c) const {
+    if (!sink->room(3)) return;
+    uint8_t* o = sink->buf + sink->pos;
+    o[0] = (uint8_t)a;
+    o[1] = (uint8_t)b;
+    o[2] = (uint8_t)c;
+    sink->pos += 3;
+  }
+  OAK_HD void lg4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) const {
+    if (!sink->room(4)) return;
+    uint8_t* o = sink->buf + sink->pos;
+    o[0] = (uint8_t)a;
+    o[1] = (uint8_t)b;
+    o[2] = (uint8_t)c;
+    o[3] = (uint8_t)d;
+    sink->pos += 4;
+  }
+  OAK_HD void lg16(uint32_t v) const { lg2(v & 255u, v >> 8); }
+  // damage / heal (protocol.zig:432-458): op, ident | hp | max hp | status, reason [| of]
+  OAK_HD void lg_hp(uint32_t op, uint32_t id, H pk, uint32_t reason) const {
+    lg2(op, id);
+    lg16(this->ld16(pk, PK_HP));
+    lg16(this->ld16(pk, PK_STATS + ST_HP));
+    lg2(this->ld8(pk, PK_STATUS), reason);
+  }
+  OAK_HD void lg_hp_of(uint32_t op, uint32_t id, H pk, uint32_t reason, uint32_t of) const {
+    lg_hp(op, id, pk, reason);
+    lg1(of);
+  }
+  // switched (protocol.zig:355-378): op, ident | species, level | hp | max hp | status
+  OAK_HD void lg_switched(uint32_t id, H pk) const {
+    lg2(LG_Switch, id);
+    lg2(this->ld8(pk, PK_SPECIES), this->ld8(pk, PK_LEVEL));
+    lg16(this->ld16(pk, PK_HP));
+    lg16(this->ld16(pk, PK_STATS + ST_HP));
+    lg1(this->ld8(pk, PK_STATUS));
+  }
+  OAK_HD void lg_boost(uint32_t id, uint32_t reason, int num) const { lg4(LG_Boost, id, reason, (uint32_t)(num + 6)); }
+};
+
+template <int STRIDE, bool LOG>
+struct MemFor {
+  typedef Mem<STRIDE> type;
+};
+template <int STRIDE>
+struct MemFor<STRIDE, true> {
+  typedef MemL<STRIDE> type;
 };
 
 }  // namespace oakb200

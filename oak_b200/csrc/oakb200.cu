@@ -51,7 +51,7 @@ cudaError_t launch_step(oakb200_ctx* ctx, size_t n, void* battles, void* duratio
 
 template <bool CHANCE, bool WRITE>
 cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
-                           uint32_t max_steps, void* score2, void* turns, void* steps, const uint32_t* available = nullptr) {
+                           uint32_t max_steps, void* score2, void* turns, void* steps, uint32_t* available = nullptr) {
   cudaStream_t stream = ctx->stream;
   uint32_t* ticket = ctx->ticket + ctx->ticket_slot;
   // OAKB200_ROLLOUT_GROUPED=1 selects the variant that regroups a CTA's battles by action class before every update.
@@ -176,6 +176,94 @@ cudaError_t oakb200_launch_replay_split(oakb200_ctx* ctx, const uint8_t* stream,
   return cudaGetLastError();
 }
 
+// ---- batch of one for the scalar libpkmn symbols (pkmn_compat.cu). Staging layout in the pinned block:
+//   [0,384) battle  [384,392) durations  392 c1  393 c2  394 result  [400,416) overrides  [416,432) actions
+//   [432,436) log length  [448,448+256) log   [704,722) choices  [722,724) counts
+static int scalar_pin(oakb200_ctx* ctx) {
+  if (ctx->scalar_pin) return OAKB200_OK;
+  CU(ctx, cudaMallocHost(&ctx->scalar_pin, 1024));
+  return OAKB200_OK;
+}
+
+int oakb200_scalar_update(oakb200_ctx* ctx, uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, const uint8_t* overrides,
+                          uint8_t* actions, uint8_t* result, uint8_t* log, uint32_t log_cap, uint32_t* log_len) {
+  if (!ctx || !battle || !result) return OAKB200_EINVAL;
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (int rc = scalar_pin(ctx)) return rc;
+  uint8_t* pin = ctx->scalar_pin;
+  cudaStream_t st = ctx->stream;
+  memcpy(pin, battle, 384);
+  if (durations) memcpy(pin + 384, durations, 8); else memset(pin + 384, 0, 8);
+  pin[392] = c1;
+  pin[393] = c2;
+  pin[394] = RESULT_DEFAULT;  // the stored result byte only gates "battle already over"; the caller decides that
+  if (overrides) memcpy(pin + 400, overrides, 16);
+  CU(ctx, cudaMemcpyAsync(ctx->battles, pin, 384, cudaMemcpyHostToDevice, st));
+  CU(ctx, cudaMemcpyAsync(ctx->durations, pin + 384, 8, cudaMemcpyHostToDevice, st));
+  CU(ctx, cudaMemcpyAsync(ctx->c1, pin + 392, 1, cudaMemcpyHostToDevice, st));
+  CU(ctx, cudaMemcpyAsync(ctx->c2, pin + 393, 1, cudaMemcpyHostToDevice, st));
+  CU(ctx, cudaMemcpyAsync(ctx->results, pin + 394, 1, cudaMemcpyHostToDevice, st));
+  if (overrides) CU(ctx, cudaMemcpyAsync(ctx->overrides, pin + 400, 16, cudaMemcpyHostToDevice, st));
+  if (log) {
+    if (log_cap > 256) log_cap = 256;  // one update writes at most PKMN_GEN1_MAX_LOGS = 180 bytes
+    if (ctx->log_bytes < 512) {
+      if (ctx->logs) CU(ctx, cudaFree(ctx->logs));
+      ctx->logs = nullptr;
+      ctx->log_bytes = 0;
+      CU(ctx, cudaMalloc(&ctx->logs, 512));
+      ctx->log_bytes = 512;
+    }
+    int rc = oakb200_step_log_device(ctx, 1, ctx->battles, ctx->durations, ctx->results, ctx->c1, ctx->c2,
+                                     overrides ? ctx->overrides : nullptr, ctx->actions, ctx->logs + 16, log_cap, ctx->logs);
+    if (rc) return rc;
+    CU(ctx, cudaMemcpyAsync(pin + 432, ctx->logs, 4, cudaMemcpyDeviceToHost, st));
+    if (log_cap) CU(ctx, cudaMemcpyAsync(pin + 448, ctx->logs + 16, log_cap, cudaMemcpyDeviceToHost, st));
+  } else {
+    int rc = oakb200_step_device(ctx, 1, ctx->battles, ctx->durations, ctx->results, ctx->c1, ctx->c2,
+                                 overrides ? ctx->overrides : nullptr, ctx->actions);
+    if (rc) return rc;
+  }
+  CU(ctx, cudaMemcpyAsync(pin, ctx->battles, 384, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaMemcpyAsync(pin + 384, ctx->durations, 8, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaMemcpyAsync(pin + 394, ctx->results, 1, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaMemcpyAsync(pin + 416, ctx->actions, 16, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaStreamSynchronize(st));
+  ctx->n = 1;
+  memcpy(battle, pin, 384);
+  if (durations) memcpy(durations, pin + 384, 8);
+  if (actions) memcpy(actions, pin + 416, 16);
+  *result = pin[394];
+  if (log) {
+    uint32_t len;
+    memcpy(&len, pin + 432, 4);
+    if (len > log_cap) len = log_cap;
+    memcpy(log, pin + 448, len);
+    if (log_len) *log_len = len;
+  }
+  return OAKB200_OK;
+}
+
+int oakb200_scalar_choices(oakb200_ctx* ctx, const uint8_t* battle, uint8_t result, uint8_t* choices18, uint8_t* counts2) {
+  if (!ctx || !battle) return OAKB200_EINVAL;
+  CU(ctx, cudaSetDevice(ctx->device));
+  if (int rc = scalar_pin(ctx)) return rc;
+  uint8_t* pin = ctx->scalar_pin;
+  cudaStream_t st = ctx->stream;
+  memcpy(pin, battle, 384);
+  pin[394] = result;
+  CU(ctx, cudaMemcpyAsync(ctx->battles, pin, 384, cudaMemcpyHostToDevice, st));
+  CU(ctx, cudaMemcpyAsync(ctx->results, pin + 394, 1, cudaMemcpyHostToDevice, st));
+  int rc = oakb200_choices_device(ctx, 1, ctx->battles, ctx->results, ctx->choices, ctx->counts);
+  if (rc) return rc;
+  CU(ctx, cudaMemcpyAsync(pin + 704, ctx->choices, 18, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaMemcpyAsync(pin + 722, ctx->counts, 2, cudaMemcpyDeviceToHost, st));
+  CU(ctx, cudaStreamSynchronize(st));
+  ctx->n = 1;
+  memcpy(choices18, pin + 704, 18);
+  memcpy(counts2, pin + 722, 2);
+  return OAKB200_OK;
+}
+
 extern "C" {
 
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
@@ -221,7 +309,7 @@ int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
 void oakb200_destroy(oakb200_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  void* bufs[] = {ctx->battles, ctx->durations, ctx->results, ctx->c1,    ctx->c2,    ctx->overrides, ctx->actions, ctx->choices,
+  void* bufs[] = {ctx->logs, ctx->battles, ctx->durations, ctx->results, ctx->c1,    ctx->c2,    ctx->overrides, ctx->actions, ctx->choices,
                   ctx->counts,  ctx->seeds,     ctx->score2,  ctx->turns, ctx->steps, ctx->teams,     ctx->ticket,  ctx->total_steps,
                   ctx->eval_values, ctx->eval_logits, ctx->eval_counts};
   oakb200_net_release(ctx);
@@ -235,6 +323,7 @@ void oakb200_destroy(oakb200_ctx* ctx) {
     for (cudaEvent_t ev : ctx->eval_ev)
       if (ev) cudaEventDestroy(ev);
   }
+  if (ctx->scalar_pin) cudaFreeHost(ctx->scalar_pin);
   if (ctx->pipe_ready) {
     cudaStreamDestroy(ctx->copy_stream);
     cudaEventDestroy(ctx->pipe_start);
@@ -356,6 +445,53 @@ int oakb200_step(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const u
   return OAKB200_OK;
 }
 
+int oakb200_step_log_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
+                            const void* c2, const void* overrides, void* actions_out, void* logs, uint32_t log_stride,
+                            void* log_lens) {
+  if (!ctx || !battles || !durations || !results || !c1 || !c2 || !logs || !log_lens)
+    return fail(ctx, OAKB200_EINVAL, "step_log: null argument");
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  auto k = step_log_kernel<BLOCK>;
+  CU(ctx, allow_smem(k));
+  k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>((uint8_t*)battles, (uint8_t*)durations, (uint8_t*)results, (const uint8_t*)c1,
+                                                     (const uint8_t*)c2, (const uint8_t*)overrides, (uint8_t*)actions_out,
+                                                     (uint8_t*)logs, log_stride, (uint32_t*)log_lens, (uint32_t)n);
+  ctx->launches++;
+  CU(ctx, cudaGetLastError());
+  return OAKB200_OK;
+}
+
+int oakb200_step_log(oakb200_ctx* ctx, const uint8_t* c1, const uint8_t* c2, const uint8_t* overrides, uint8_t* results_out,
+                     uint8_t* actions_out, uint8_t* logs_out, uint32_t log_stride, uint32_t* log_lens_out) {
+  if (!ctx || !c1 || !c2 || !logs_out || !log_lens_out) return fail(ctx, OAKB200_EINVAL, "step_log: null argument");
+  const size_t n = ctx->n;
+  if (n == 0) return OAKB200_OK;
+  CU(ctx, cudaSetDevice(ctx->device));
+  const size_t need = n * (size_t)log_stride + n * 4;
+  if (ctx->log_bytes < need) {
+    if (ctx->logs) CU(ctx, cudaFree(ctx->logs));
+    ctx->logs = nullptr;
+    ctx->log_bytes = 0;
+    CU(ctx, cudaMalloc(&ctx->logs, need));
+    ctx->log_bytes = need;
+  }
+  uint8_t* lens = ctx->logs;  // [n] u32 first (aligned), then the log rows
+  uint8_t* rows = ctx->logs + n * 4;
+  CU(ctx, cudaMemcpyAsync(ctx->c1, c1, n, cudaMemcpyHostToDevice, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(ctx->c2, c2, n, cudaMemcpyHostToDevice, ctx->stream));
+  if (overrides) CU(ctx, cudaMemcpyAsync(ctx->overrides, overrides, n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = oakb200_step_log_device(ctx, n, ctx->battles, ctx->durations, ctx->results, ctx->c1, ctx->c2,
+                                   overrides ? ctx->overrides : nullptr, actions_out ? ctx->actions : nullptr, rows, log_stride, lens);
+  if (rc) return rc;
+  if (results_out) CU(ctx, cudaMemcpyAsync(results_out, ctx->results, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (actions_out) CU(ctx, cudaMemcpyAsync(actions_out, ctx->actions, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(logs_out, rows, n * (size_t)log_stride, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaMemcpyAsync(log_lens_out, lens, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx, cudaStreamSynchronize(ctx->stream));
+  return OAKB200_OK;
+}
+
 int oakb200_step_random_device(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* seeds,
                                uint32_t step_index, void* actions_out, void* chosen_out) {
   if (!ctx || !battles || !durations || !results || !seeds) return fail(ctx, OAKB200_EINVAL, "step_random: null argument");
@@ -415,16 +551,18 @@ int oakb200_rollout_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, con
   if (!ctx->pipe_ready) {
     CU(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     CU(ctx, cudaEventCreateWithFlags(&ctx->pipe_start, cudaEventDisableTiming));
-    CU(ctx, cudaMallocHost(&ctx->pipe_marks, MAX_CHUNKS * sizeof(uint32_t)));
+    CU(ctx, cudaMallocHost(&ctx->pipe_marks, (MAX_CHUNKS + 1) * sizeof(uint32_t)));
     ctx->pipe_ready = true;
   }
   size_t chunk = (size_t)1 << 16;
   if (const char* c = getenv("OAKB200_PIPE_CHUNK")) chunk = (size_t)atol(c) > 0 ? (size_t)atol(c) : chunk;  // tuning knob
   if ((n + chunk - 1) / chunk > (size_t)MAX_CHUNKS) chunk = (n + MAX_CHUNKS - 1) / MAX_CHUNKS;
+  // chunk boundaries on 128 records: no 32-byte sector of results / seeds / durations ever spans two copies
+  chunk = (chunk + 127) / 128 * 128;
   const int chunks = (int)((n + chunk - 1) / chunk);
-  uint32_t* avail = ctx->ticket + 1;
+  uint32_t* avail = ctx->ticket + 2;  // [0] records available, [1] "a lane gave up waiting"
   // the counter is cleared in context-stream order; the copies start after that and after everything queued before
-  CU(ctx, cudaMemsetAsync(avail, 0, sizeof(uint32_t), ctx->stream));
+  CU(ctx, cudaMemsetAsync(avail, 0, 2 * sizeof(uint32_t), ctx->stream));
   // defaults are filled here, before the launch: the copy stream must carry DMA copies only, nothing that needs an SM
   if (!durations) CU(ctx, cudaMemsetAsync(ctx->durations, 0, n * 8, ctx->stream));
   if (!results) CU(ctx, cudaMemsetAsync(ctx->results, RESULT_DEFAULT, n, ctx->stream));
@@ -445,9 +583,12 @@ int oakb200_rollout_host(oakb200_ctx* ctx, size_t n, const uint8_t* battles, con
   if (score2_out) CU(ctx, cudaMemcpyAsync(score2_out, ctx->score2, n, cudaMemcpyDeviceToHost, ctx->stream));
   if (turns_out) CU(ctx, cudaMemcpyAsync(turns_out, ctx->turns, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
   if (steps_out) CU(ctx, cudaMemcpyAsync(steps_out, ctx->steps, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  uint32_t* gave_up = ctx->pipe_marks + MAX_CHUNKS;
+  CU(ctx, cudaMemcpyAsync(gave_up, avail + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->copy_stream));
   ctx->n = n;
+  if (*gave_up) return fail(ctx, OAKB200_ECUDA, "rollout_host: the upload stalled; playouts abandoned");
   return OAKB200_OK;
 }
 

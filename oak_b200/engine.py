@@ -76,6 +76,8 @@ def load_library():
         "oakb200_rows_status": (i32, [vp, ctypes.POINTER(ctypes.c_int64)]),
         "oakb200_rows_build_host": (i32, [vp, vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64),
                                          ctypes.POINTER(ctypes.c_int64)]),
+        "oakb200_step_log": (i32, [vp, vp, vp, vp, vp, vp, vp, u32, vp]),
+        "oakb200_step_log_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp, vp, u32, vp]),
         "oakb200_eval": (i32, [vp, vp, vp, vp]),
         "oakb200_eval_device": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
         "oakb200_eval_host": (i32, [vp, sz, vp, vp, vp, vp, vp, vp]),
@@ -196,6 +198,21 @@ class BattleEngine:
         act = np.empty((n, 16), np.uint8) if want_actions else None
         self._check(self.lib.oakb200_step(self._h, _ptr(c1), _ptr(c2), _ptr(overrides), _ptr(res), _ptr(act)))
         return (res, act) if want_actions else res
+
+    def update_log(self, c1, c2, overrides=None, log_stride=180):
+        """update() with libpkmn's binary protocol log -> (results[n], actions[n,16], logs[n,log_stride] u8, lens[n] u32).
+        A battle whose log does not fit log_stride bytes gets the result byte 0x0C (pkmn_error)."""
+        n = self.n
+        c1 = _np(c1, np.uint8, (n,))
+        c2 = _np(c2, np.uint8, (n,))
+        overrides = None if overrides is None else _np(overrides, np.uint8, (n, 16))
+        res = np.empty((n,), np.uint8)
+        act = np.empty((n, 16), np.uint8)
+        logs = np.zeros((n, max(int(log_stride), 1)), np.uint8)
+        lens = np.empty((n,), np.uint32)
+        self._check(self.lib.oakb200_step_log(self._h, _ptr(c1), _ptr(c2), _ptr(overrides), _ptr(res), _ptr(act), _ptr(logs),
+                                              int(log_stride), _ptr(lens)))
+        return res, act, logs, lens
 
     def rollout(self, seeds, max_steps=100000, write_state=False, track_chance=False):
         """Random playouts to a terminal result -> (score2[n] u8, turns[n] u16, steps[n] u32)."""

@@ -49,6 +49,30 @@ uint8_t shim_update_nochance(uint8_t* battle, uint8_t c1, uint8_t c2) {
   uint8_t d[8] = {0};
   return run_update<false, false>(battle, c1, c2, d, nullptr, nullptr);
 }
+// LOG build of the engine: the update's protocol log goes to log[0..cap); *len = bytes written; an overflow gives 0b1100
+uint8_t shim_update_log(uint8_t* battle, uint8_t c1, uint8_t c2, uint8_t* durations, uint8_t* actions, const uint8_t* overrides,
+                        uint8_t* log, uint32_t cap, uint32_t* len) {
+  Engine<ST, true, true, true> e;
+  Tile tile(battle);
+  uint32_t d[2];
+  memcpy(d, durations, 8);
+  e.begin(tile.column(), d[0], d[1]);
+  e.sink.buf = log;
+  e.sink.cap = cap;
+  e.sink.pos = 0;
+  e.sink.overflow = 0;
+  if (overrides) memcpy(e.ovr, overrides, 16);
+  uint32_t r = e.update(c1, c2);
+  if (e.sink.overflow) r = RESULT_LOG_OVERFLOW;
+  e.end();
+  tile.store(battle);
+  d[0] = e.dur[0];
+  d[1] = e.dur[1];
+  memcpy(durations, d, 8);
+  if (actions) memcpy(actions, e.act, 16);
+  *len = e.sink.pos;
+  return (uint8_t)r;
+}
 uint8_t shim_choices(const uint8_t* battle, int player, int request, uint8_t* out) {
   Engine<ST, false, true> e;
   Tile tile(battle);

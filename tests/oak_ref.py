@@ -73,6 +73,20 @@ class Oracle:
         durations[:] = opt[16:24]
         return int(r), opt[0:16].copy()
 
+    def update_log(self, battle, c1, c2, durations, overrides=None, cap=180):
+        """update with the binary protocol log -> (result, actions[16], log bytes); result 0x0C if the log overflowed cap."""
+        opt = np.zeros(40, np.uint8)
+        opt[16:24] = durations
+        if overrides is not None:
+            opt[24:40] = overrides
+        log = np.zeros(max(cap, 1), np.uint8)
+        pos = ctypes.c_size_t(0)
+        self.lib.oracle_gen1_update_log.restype = ctypes.c_uint8
+        r = self.lib.oracle_gen1_update_log(self._p(battle), ctypes.c_uint8(c1), ctypes.c_uint8(c2), self._p(opt), self._p(log),
+                                            ctypes.c_size_t(cap), ctypes.byref(pos))
+        durations[:] = opt[16:24]
+        return int(r), opt[0:16].copy(), log[:pos.value].tobytes()
+
     def step(self, battle, durations, result, pick):
         act = np.zeros(16, np.uint8)
         c = np.zeros(2, np.uint8)
@@ -121,6 +135,19 @@ class HostShim:
 
     def update_nochance(self, battle, c1, c2):
         return int(self.lib.shim_update_nochance(battle.ctypes.data, c1, c2))
+
+    def update_log(self, battle, c1, c2, durations, overrides=None, cap=180):
+        """LOG build of the engine -> (result, actions, log bytes)."""
+        act = np.zeros(16, np.uint8)
+        log = np.zeros(max(cap, 1), np.uint8)
+        n = ctypes.c_uint32(0)
+        ov = None if overrides is None else np.ascontiguousarray(overrides, np.uint8).ctypes.data
+        self.lib.shim_update_log.restype = ctypes.c_uint8
+        self.lib.shim_update_log.argtypes = [ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint8, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p]
+        r = self.lib.shim_update_log(battle.ctypes.data, c1, c2, durations.ctypes.data, act.ctypes.data, ov, log.ctypes.data, cap,
+                                     ctypes.byref(n))
+        return int(r), act, log[:n.value].tobytes()
 
 
 def oracle_rollout_batch(orc, battles, durations, results, seeds, max_steps=100000, threads=None):

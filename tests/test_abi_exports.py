@@ -25,11 +25,17 @@ def test_every_declared_symbol_is_exported():
     assert len(names) >= 40 and "oakb200_eval_device" in names and "pkmn_gen1_battle_update" in names
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, missing
+    # data symbols of pkmn.h (engine/src/lib/c.zig:4-14): Oak sizes its choice arrays with PKMN_GEN1_MAX_CHOICES
+    for name, value in (("PKMN_GEN1_MAX_CHOICES", 9), ("PKMN_GEN1_CHOICES_SIZE", 16), ("PKMN_GEN1_MAX_LOGS", 180),
+                        ("PKMN_GEN1_LOGS_SIZE", 256), ("PKMN_MAX_CHOICES", 9), ("PKMN_CHOICES_SIZE", 16), ("PKMN_MAX_LOGS", 180),
+                        ("PKMN_LOGS_SIZE", 256)):
+        assert ctypes.c_size_t.in_dll(lib, name).value == value, name
+    assert bytes((ctypes.c_uint8 * 4).in_dll(lib, "PKMN_OPTIONS")) == b"\x01\x01\x01\x01"
 
 
 def test_pure_helpers_need_no_device():
     lib = oak_b200.load_library()
-    lib.pkmn_result_type.restype = lib.pkmn_result_p1.restype = lib.pkmn_result_p2.restype = ctypes.c_uint8
+    lib.pkmn_result_type.restype = lib.pkmn_result_p1.restype = lib.pkmn_result_p2.restype = ctypes.c_int  # enums, pkmn.h:108-112
     assert (lib.pkmn_result_type(0x51), lib.pkmn_result_p1(0x51), lib.pkmn_result_p2(0x91)) == (1, 1, 2)
     opts = (ctypes.c_uint8 * 128)()
     lib.pkmn_gen1_battle_options_chance_durations.restype = ctypes.c_void_p

@@ -244,4 +244,33 @@ def test_pipelined_host_rollout_equals_resident_rollout(orc):
     got = eng.rollout_host(b[:1000], None, None, seeds[:1000])
     for a, w in zip(got, want):
         assert np.array_equal(a, w[:1000])
+    # chunk sizes that are not a multiple of 128 records: the library rounds them, and the records that share a
+    # sector with the previous chunk's tail still come out right
+    import os
+    for chunk in ("9999", "10001", "333"):
+        os.environ["OAKB200_PIPE_CHUNK"] = chunk
+        try:
+            got = eng.rollout_host(b, d, r, seeds)
+        finally:
+            del os.environ["OAKB200_PIPE_CHUNK"]
+        for a, w in zip(got, want):
+            assert np.array_equal(a, w), chunk
+    eng.close()
+
+
+def test_pipelined_host_rollout_beyond_32_default_chunks(orc):
+    """n > 2^21: the chunk becomes ceil(n / 32) (not a multiple of 128 before the fix). Inputs are the first 2^16
+    sample battles tiled, so the expected outputs are those of one resident rollout, tiled."""
+    import oak_b200
+    base = 1 << 16
+    n = (1 << 21) + 12_345
+    b0, d0, r0 = oracle_sample_batch(orc, 0, base)
+    s0 = sample_seeds(0, base)
+    eng = oak_b200.BattleEngine(n)
+    eng.upload(b0, d0, r0)
+    want = eng.rollout(s0)
+    idx = np.arange(n) % base
+    got = eng.rollout_host(b0[idx], d0[idx], r0[idx], s0[idx])
+    for a, w in zip(got, want):
+        assert np.array_equal(a, w[idx])
     eng.close()

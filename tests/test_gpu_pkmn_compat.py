@@ -94,3 +94,54 @@ def test_null_options_and_calc_overrides():
             r2 = pk.update(gb, c1, c2)
             r, _ = orc.update(ob, c1, c2, od, overrides=calc[:16])
         assert r2 == r and np.array_equal(gb, ob)
+
+
+def test_choices_truncation_and_pass_request():
+    """pkmn.h:270-288: at most `len` entries are written, the return value is the number of choices there are; a PASS request
+    has the single choice 0."""
+    orc, pk = Oracle(), Pkmn()
+    b, d, r = orc.sample_battle(2)
+    full = orc.choices(b, 0, 1)
+    assert len(full) >= 5
+    out = np.full(9, 0xEE, np.uint8)
+    n = pk.lib.pkmn_gen1_battle_choices(b.ctypes.data, 0, 1, out.ctypes.data, 3)
+    assert n == len(full) and out[:3].tolist() == full[:3] and np.all(out[3:] == 0xEE)
+    for player in (0, 1):
+        assert pk.choices(b, player, 0) == [0] == orc.choices(b, player, 0)
+    assert pk.lib.pkmn_gen1_battle_choices(b.ctypes.data, 2, 1, out.ctypes.data, 9) == 0  # not a player
+    assert pk.lib.pkmn_gen1_battle_choices(b.ctypes.data, 0, 1, out.ctypes.data, 0) == 0  # no room at all
+
+
+def test_scalar_calls_from_many_threads_do_not_interfere():
+    """One context per calling thread: eight threads each play their own battle through the scalar symbols concurrently."""
+    import threading
+    orc = Oracle()
+    errors = []
+
+    def play(i):
+        try:
+            pk = Pkmn()
+            local = Oracle()
+            ob, od, r = local.sample_battle(i)
+            gb = ob.copy()
+            pk.options_set(chance=np.zeros(40, np.uint8))
+            seed = sample_seed(i)
+            for step in range(60):
+                if r & 15:
+                    break
+                c = [local.choices(ob, p, (r >> (4 + 2 * p)) & 3) for p in (0, 1)]
+                w = pick_word(seed, step)
+                c1, c2 = c[0][w % len(c[0])], c[1][(w >> 32) % len(c[1])]
+                pk.options_set()
+                r2 = pk.update(gb, c1, c2)
+                r, _ = local.update(ob, c1, c2, od)
+                assert r2 == r and np.array_equal(gb, ob) and np.array_equal(pk.durations(), od), (i, step)
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=play, args=(i,)) for i in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
