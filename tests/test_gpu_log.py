@@ -44,7 +44,7 @@ def _lockstep(n, steps, first=0):
 
 
 def test_c1_trace_log_bytes():
-    assert _lockstep(1, 400) > 3000
+    assert _lockstep(1, 400) > 1500  # battle 0 ends after ~90 updates: 2 048 log bytes
 
 
 def test_lockstep_1024_x_80_log_bytes():
