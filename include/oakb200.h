@@ -303,6 +303,26 @@ int oakb200_rows_build_host(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_
                             const oakb200_training_rows* out, uint64_t capacity_rows, uint64_t* n_games, uint64_t* n_rows,
                             int64_t* first_bad_game);
 
+
+/* oakb200_rows_build_device without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). The staged row states and the control words live in a file-scope `static __device__` array of the library
+ * (256 B + OAKB200_ROWS_STATIC_MAX x 432 B = 6.75 MiB, held by every GPU that loads the library until the process exits);
+ * the call itself makes no cudaMalloc / cudaFree / allocating library call: it enqueues two 4-byte memsets, the replay
+ * kernel, the encode kernel and one 4-byte device-to-device copy on the context stream, and does not synchronise.
+ * Same arguments, same rows, bit for bit, as oakb200_rows_build_device; all pointers are DEVICE pointers the caller owns.
+ * n_rows > OAKB200_ROWS_STATIC_MAX returns OAKB200_ECAPACITY (oakb200_last_error says so) and enqueues nothing.
+ * first_bad_game_out (device u32, nullable) receives what oakb200_rows_status reports for the other entry points: the
+ * lowest index of a game whose replay missed its stored result or byte count, 0xFFFFFFFF if none.
+ * The array is shared by every call on that GPU, from any context or thread, and keeps the previous call's contents (this
+ * call resets what it needs): calls that can overlap on the GPU — different streams, different contexts — race on it;
+ * issue them on one stream or order them with events. The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that one call outside graph capture. */
+#define OAKB200_ROWS_STATIC_MAX 16384
+int oakb200_rows_build_static(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_bytes, const uint64_t* game_off,
+                              const uint32_t* row_base, const int32_t* only_update, uint64_t n_games, uint64_t n_rows,
+                              const oakb200_training_rows* out, uint32_t* first_bad_game_out);
+
 #ifdef __cplusplus
 }
 #endif

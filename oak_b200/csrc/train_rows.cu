@@ -255,4 +255,64 @@ int oakb200_rows_build_host(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_
   return oakb200_rows_status(ctx, first_bad_game);
 }
 
+// ---- oakb200_rows_build_static: the two-kernel build above with its scratch in a file-scope device array -------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc). Every GPU that loads
+// this library holds the array until the process exits: 256 control bytes + OAKB200_ROWS_STATIC_MAX staged states of 432 B
+// = 6.75 MiB. In HOST code `g_rows_static` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current (rows_static_base below).
+static __device__ __align__(256) uint8_t g_rows_static[256 + (size_t)OAKB200_ROWS_STATIC_MAX * OAKB200_ROW_STATE_BYTES];
+
+namespace {
+
+const int STATIC_MAX_DEVICES = 64;
+uint8_t* g_rows_static_addr[STATIC_MAX_DEVICES];  // per device, 0 = not looked up yet (benign race: same value every time)
+
+int rows_static_base(oakb200_ctx* ctx, uint8_t** base) {
+  if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return fail(ctx, OAKB200_EINVAL, "rows_build_static: device index out of range");
+  uint8_t* p = g_rows_static_addr[ctx->device];
+  if (!p) {
+    CU(ctx, cudaGetSymbolAddress((void**)&p, g_rows_static));  // the context's device is current (caller)
+    if (!p) return fail(ctx, OAKB200_ECUDA, "rows_build_static: cudaGetSymbolAddress gave a null address");
+    g_rows_static_addr[ctx->device] = p;
+  }
+  *base = p;
+  return OAKB200_OK;
+}
+
+}  // namespace
+
+int oakb200_rows_build_static(oakb200_ctx* ctx, const uint8_t* stream, uint64_t n_bytes, const uint64_t* game_off,
+                              const uint32_t* row_base, const int32_t* only_update, uint64_t n_games, uint64_t n_rows,
+                              const oakb200_training_rows* out, uint32_t* first_bad_game_out) {
+  if (!ctx) return OAKB200_EINVAL;
+  if (!out || (!stream && n_games) || (!game_off && n_games) || (!row_base && n_games) || n_bytes >= (1ull << 32) ||
+      n_games > 0x7FFFFFFFull)
+    return fail(ctx, OAKB200_EINVAL, "rows_build_static: bad arguments");
+  if (n_rows > (uint64_t)OAKB200_ROWS_STATIC_MAX)
+    return fail(ctx, OAKB200_ECAPACITY, "rows_build_static: n_rows exceeds OAKB200_ROWS_STATIC_MAX (16384); use oakb200_rows_build_device");
+  CU(ctx, cudaSetDevice(ctx->device));
+  uint8_t* base = nullptr;
+  if (int rc = rows_static_base(ctx, &base)) return rc;
+  uint32_t* words = reinterpret_cast<uint32_t*>(base);  // [0] game ticket, [1] lowest bad game; the array keeps the last call's
+  uint8_t* states = base + 256;                          // contents, so both are reset here, in stream order
+  CU(ctx, cudaMemsetAsync(words, 0, sizeof(uint32_t), ctx->stream));
+  CU(ctx, cudaMemsetAsync(words + 1, 0xFF, sizeof(uint32_t), ctx->stream));
+  if (n_games != 0 && n_rows != 0) {
+    // every staged state the encoder reads is written by this call's replay first: nothing stale is consumed
+    CU(ctx, oakb200_launch_replay(ctx, stream, game_off, row_base, only_update, (uint32_t)n_games, words, states));
+    int per_sm = 0;
+    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rows_encode_kernel, ENC_WARPS * 32, 0));
+    if (per_sm < 1) per_sm = 1;
+    unsigned grid = (unsigned)(per_sm * ctx->sm_count);
+    const unsigned need = (unsigned)((n_rows + ENC_WARPS - 1) / ENC_WARPS);
+    if (grid > need) grid = need;
+    rows_encode_kernel<<<grid, ENC_WARPS * 32, 0, ctx->stream>>>(states, stream, *out, (uint32_t)n_rows);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+  }
+  if (first_bad_game_out)
+    CU(ctx, cudaMemcpyAsync(first_bad_game_out, words + 1, sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+  return OAKB200_OK;
+}
+
 }  // extern "C"

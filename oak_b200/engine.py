@@ -73,6 +73,7 @@ def load_library():
         "oakb200_frames_drain": (i32, [vp, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u32)]),
         "oakb200_rows_index_host": (i32, [vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
         "oakb200_rows_build_device": (i32, [vp, vp, u64, vp, vp, vp, u64, u64, vp]),
+        "oakb200_rows_build_static": (i32, [vp, vp, u64, vp, vp, vp, u64, u64, vp, vp]),
         "oakb200_rows_status": (i32, [vp, ctypes.POINTER(ctypes.c_int64)]),
         "oakb200_rows_build_host": (i32, [vp, vp, u64, vp, vp, u64, ctypes.POINTER(u64), ctypes.POINTER(u64),
                                          ctypes.POINTER(ctypes.c_int64)]),
@@ -392,6 +393,13 @@ class BattleEngine:
         st = self._rows_struct(out)
         self._check(self.lib.oakb200_rows_build_device(self._h, _ptr(stream), int(n_bytes), _ptr(game_off), _ptr(row_base),
                                                        _ptr(only_update), int(n_games), int(n_rows), ctypes.addressof(st)))
+
+    def rows_build_static(self, stream, n_bytes, game_off, row_base, n_games, n_rows, out, only_update=None, first_bad_out=None):
+        """oakb200_rows_build_static: the same build with the library's static device scratch (no allocation; n_rows <= 16384)."""
+        st = self._rows_struct(out)
+        self._check(self.lib.oakb200_rows_build_static(self._h, _ptr(stream), int(n_bytes), _ptr(game_off), _ptr(row_base),
+                                                       _ptr(only_update), int(n_games), int(n_rows), ctypes.addressof(st),
+                                                       _ptr(first_bad_out)))
 
     def rows_status(self):
         bad = ctypes.c_int64()
