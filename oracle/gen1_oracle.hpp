@@ -235,6 +235,9 @@ struct Engine {
   Options& o;
   Rolls32* fx;
   LogBuf* lg;
+  // flag cross-check instrumentation (tests/test_oracle_flags.py): how often this update reached a site where the build
+  // flags change behaviour — an `advance` call (ADVANCE), a hit roll that landed exactly on the accuracy (MISS: the 1/256 miss)
+  uint32_t n_advance = 0, n_hit_edge = 0;
 
   Engine(Battle& battle, Options& options, Rolls32* fixed = nullptr, LogBuf* log = nullptr)
       : b(battle), o(options), fx(fixed), lg(log) {}
@@ -368,6 +371,7 @@ struct Engine {
     return (uint32_t)(b.rng >> 32);
   }
   void advance(int n) {
+    n_advance += (uint32_t)n;
     if (!ADVANCE) return;
     for (int i = 0; i < n; i++) (void)next();
   }
@@ -489,7 +493,14 @@ struct Engine {
   bool roll_hit(int p, uint8_t accuracy) {
     const uint32_t acc = MISS ? accuracy : (uint32_t)accuracy + 1;
     const uint32_t ov = overridden(p, A_hit);
-    const bool ok = ov ? (ov == OPT_TRUE) : chance(acc, 256);
+    bool ok;
+    if (ov) {
+      ok = ov == OPT_TRUE;
+    } else {
+      const uint32_t r = range(0, 256);  // chance(acc, 256) = range(0, 256) < acc
+      ok = r < acc;
+      if (r == accuracy) n_hit_edge++;
+    }
     ch_bool(p, A_hit, ok);
     return ok;
   }

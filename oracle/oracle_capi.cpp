@@ -68,10 +68,43 @@ uint8_t oracle_gen1_update_kat_log(uint8_t* battle, uint8_t c1, uint8_t c2, Opti
   return r;
 }
 
+// libpkmn-default-flag update with the live PRNG and the protocol log
+uint8_t oracle_gen1_update_default_log(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o, uint8_t* buf, size_t cap, size_t* pos) {
+  LogBuf lg{buf, cap, *pos};
+  Engine<true, true, true, false, false, true> e(*reinterpret_cast<Battle*>(battle), *o, nullptr, &lg);
+  uint8_t r;
+  try {
+    r = e.update(c1, c2);
+  } catch (const LogOverflow&) {
+    r = RESULT_LOG_OVERFLOW;
+  }
+  *pos = lg.pos;
+  return r;
+}
+
 // libpkmn-default-flag update with the live PRNG (used to diff flag sets on roll-free scenarios).
 uint8_t oracle_gen1_update_default(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o) {
   DefaultEngine e(*reinterpret_cast<Battle*>(battle), *o);
   return e.update(c1, c2);
+}
+
+// One update under a chosen flag set with the live PRNG, reporting the flag-sensitive sites it reached.
+// which = 0: Oak's flags {miss=false, advance=false, ebc=false, key=true}; 1: libpkmn's defaults {miss, advance, ebc, key=false}.
+// counters[0] = advance calls (counted whether or not the build honours them), [1] = hit rolls that landed on the accuracy.
+uint8_t oracle_gen1_update_flags(uint8_t* battle, uint8_t c1, uint8_t c2, Options* o, int which, uint32_t* counters) {
+  uint8_t r;
+  if (which == 0) {
+    OakEngine e(*reinterpret_cast<Battle*>(battle), *o);
+    r = e.update(c1, c2);
+    counters[0] = e.n_advance;
+    counters[1] = e.n_hit_edge;
+  } else {
+    DefaultEngine e(*reinterpret_cast<Battle*>(battle), *o);
+    r = e.update(c1, c2);
+    counters[0] = e.n_advance;
+    counters[1] = e.n_hit_edge;
+  }
+  return r;
 }
 
 // PSRNG known-answer helpers (rng.zig:34-59)

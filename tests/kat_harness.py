@@ -428,6 +428,11 @@ class BoostsV:
         x = (v >> (4 * BOOST_FIELDS.index(name))) & 15
         return x - 16 if x >= 8 else x
 
+    def __eq__(self, o):
+        if isinstance(o, BoostsV):
+            return bytes(self._b[self._o:self._o + 4]) == bytes(o._b[o._o:o._o + 4])
+        return NotImplemented
+
     def __setattr__(self, name, val):
         name = name.rstrip("_")
         v = struct.unpack_from("<I", self._b, self._o)[0]
@@ -868,6 +873,12 @@ def expect(v):
         raise KatFailure("expect(false)")
 
 
+def expectStatsEqualExceptHp(a, b):
+    for f in ("atk", "def_", "spe", "spc"):
+        if getattr(a, f) != getattr(b, f):
+            raise KatFailure(f"stats.{f}: expected {getattr(a, f)}, found {getattr(b, f)}")
+
+
 def expectEqualSlices(_ty, a, b):
     if [int(x) for x in a] != [int(x) for x in b]:
         raise KatFailure(f"expected {[int(x) for x in a]}, found {[int(x) for x in b]}")
@@ -877,7 +888,7 @@ def namespace():
     g = dict(Test=Test, move=move, swtch=swtch, forced=forced, Result=Result, Status=Status, Move=Move,
              Species=Species, ranged=ranged, metronome=metronome, MIN=MIN, MAX=MAX, NOP=NOP, HIT=HIT, CRIT=CRIT,
              MIN_DMG=MIN_DMG, MAX_DMG=MAX_DMG, P1=P1, P2=P2, L=L, ID=ID, Types=Types, EMPTY=EMPTY, expectEqual=expectEqual, expect=expect,
-             expectEqualSlices=expectEqualSlices, showdown=True, SkipCase=SkipCase, Choice=None,
+             expectEqualSlices=expectEqualSlices, expectStatsEqualExceptHp=expectStatsEqualExceptHp, showdown=True, SkipCase=SkipCase, Choice=None,
              choices=[0] * 16)
     return g
 
