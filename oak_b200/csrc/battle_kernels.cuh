@@ -72,6 +72,10 @@ __device__ __forceinline__ void store_column(const uint32_t* col, uint8_t* recor
   }
 }
 
+struct CgLoad {  // record words through L2 (see load_column_cg)
+  static __device__ __forceinline__ uint32_t ld(const uint32_t* p) { return __ldcg(p); }
+};
+
 // Both players' legal choices for `result`'s request kinds, then the playout pick (mcts.h:467-477)
 template <class E>
 __device__ __forceinline__ void pick_choices(const E& e, uint32_t result, uint64_t pick, uint32_t& c1, uint32_t& c2) {
@@ -229,15 +233,17 @@ __device__ __forceinline__ bool wait_available(uint32_t* available, uint32_t i) 
 // battle from a global ticket counter the moment its current one ends (lane refill), so a warp
 // stays full although playout lengths differ by an order of magnitude. The loop body is
 // "maybe refill, then exactly one update" so that all lanes re-converge once per update.
-template <int BLOCK, bool CHANCE, bool WRITE_STATE>
-__global__ void __launch_bounds__(BLOCK, 3)
-rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
+// SPLIT: the on-chip column holds only the 48 words an update can write (gen1_state.cuh); stored stats, move ids, species,
+// types and level are read from the battle's record in global memory. 24 KB per CTA instead of 48: 8 CTAs = 32 warps per SM.
+template <int BLOCK, bool CHANCE, bool WRITE_STATE, bool SPLIT>
+__global__ void __launch_bounds__(BLOCK, SPLIT ? 8 : 3)
+rollout_kernel(uint8_t* battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
                unsigned long long* __restrict__ total_steps, uint32_t* available) {
   extern __shared__ uint32_t tile[];
   uint32_t* col = tile + threadIdx.x;
-  Engine<BLOCK, false, CHANCE> e;
+  Engine<BLOCK, false, CHANCE, false, SPLIT> e;
   e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
 
   uint32_t i = 0, result = 0, step = 0;
@@ -249,9 +255,14 @@ rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, u
     if (!have && !exhausted) {
       i = atomicAdd(ticket, 1u);
       if (i < n && wait_available(available, i)) {
-        load_column_cg<BLOCK>(col, battles + (size_t)i * 384);
+        if (SPLIT) {
+          split_fill<BLOCK, CgLoad>(col, reinterpret_cast<const uint32_t*>(battles + (size_t)i * 384));
+        } else {
+          load_column_cg<BLOCK>(col, battles + (size_t)i * 384);
+        }
         const uint2 d = __ldcg(reinterpret_cast<const uint2*>(durations + (size_t)i * 8));
         e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
+        e.m.set_const(battles + (size_t)i * 384);
         result = __ldcg(results + i);
         seed = __ldcg(seeds + i);
         step = 0;
@@ -277,7 +288,11 @@ rollout_kernel(uint8_t* __restrict__ battles, uint8_t* __restrict__ durations, u
         if (steps_out) steps_out[i] = step;
         if (WRITE_STATE) {
           e.end();
-          store_column<BLOCK>(col, battles + (size_t)i * 384);
+          if (SPLIT) {
+            split_merge<BLOCK, CgLoad>(col, reinterpret_cast<uint32_t*>(battles + (size_t)i * 384));
+          } else {
+            store_column<BLOCK>(col, battles + (size_t)i * 384);
+          }
           *reinterpret_cast<uint2*>(durations + (size_t)i * 8) = make_uint2(e.dur[0], e.dur[1]);
           results[i] = (uint8_t)result;
         }

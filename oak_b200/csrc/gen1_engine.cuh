@@ -25,9 +25,10 @@ static const int NO_RESULT = -1;
 
 // LOG: write the binary protocol log of every update into `sink` (set sink.buf / cap / pos before update()); a separate
 // instantiation, so the kernels built without it carry none of it.
-template <int STRIDE, bool CALC, bool CHANCE, bool LOG = false>
+// SPLIT: the on-chip column holds only the fields an update can write (gen1_state.cuh); call m.set_const(record) after begin().
+template <int STRIDE, bool CALC, bool CHANCE, bool LOG = false, bool SPLIT = false>
 struct Engine {
-  typedef typename MemFor<STRIDE, LOG>::type M;
+  typedef typename MemFor<STRIDE, LOG, SPLIT>::type M;
   M m;
   LogSink sink;
   uint64_t rng;
@@ -37,7 +38,8 @@ struct Engine {
   uint64_t ovr[2];  // calc overrides (CALC only)
 
   // ---------------------------------------------------------------- load / store of register copies
-  OAK_HD void attach_sink(Mem<STRIDE>&) {}
+  template <bool S>
+  OAK_HD void attach_sink(Mem<STRIDE, S>&) {}
   OAK_HD void attach_sink(MemL<STRIDE>& w) { w.sink = &sink; }
   OAK_HD void begin(uint8_t* column_base, uint32_t d0, uint32_t d1) {
     m.set(column_base);
@@ -56,14 +58,14 @@ struct Engine {
 
   // ---------------------------------------------------------------- field helpers (forward to Mem)
   static OAK_HD H sb(int p) { return M::sb(p); }
-  static OAK_HD H pokemon(int p, int idx) { return M::pokemon(p, idx); }
+  static OAK_HD PH pokemon(int p, int idx) { return M::pokemon(p, idx); }
   OAK_HD uint32_t ident(int p) const { return m.ident(p); }
   OAK_HD void log_lastmiss_miss(int p) const {  // checkHit's miss report (:1413-1415)
     if (!LOG) return;
     m.lg1(LG_LastMiss);
     m.lg2(LG_Miss, ident(p));
   }
-  OAK_HD H stored(int p) const { return m.stored(p); }
+  OAK_HD PH stored(int p) const { return m.stored(p); }
   OAK_HD uint32_t vlo(int p) const { return m.vlo(p); }
   OAK_HD void set_vlo(int p, uint32_t v) const { m.set_vlo(p, v); }
   OAK_HD uint32_t vhi(int p) const { return m.vhi(p); }
@@ -77,8 +79,8 @@ struct Engine {
   OAK_HD void set_vhi_field(int p, int shift, int bits, uint32_t x) const { m.set_vhi_field(p, shift, bits, x); }
   OAK_HD uint32_t vstate(int p) const { return m.vstate(p); }
   OAK_HD void set_vstate(int p, uint32_t s) const { m.set_vstate(p, s); }
-  OAK_HD uint32_t status_of(H pk) const { return m.status_of(pk); }
-  OAK_HD uint32_t hp_of(H pk) const { return m.hp_of(pk); }
+  OAK_HD uint32_t status_of(PH pk) const { return m.status_of(pk); }
+  OAK_HD uint32_t hp_of(PH pk) const { return m.hp_of(pk); }
   OAK_HD uint32_t last_selected(int p) const { return m.last_selected(p); }
   OAK_HD uint32_t active_types(int p) const { return m.active_types(p); }
   OAK_HD uint32_t active_stat(int p, int st) const { return m.active_stat(p, st); }

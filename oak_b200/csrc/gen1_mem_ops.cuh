@@ -40,7 +40,7 @@ OAK_HD uint32_t mem_apply_damage_impl(M m, int t, int subp, uint32_t last_damage
     m.lg3(LG_Activate, m.ident(subp), ACT_Substitute);
     return last_damage;
   }
-  const H pk = m.stored(t);
+  const PH pk = m.stored(t);
   const uint32_t hp = m.ld16(pk, PK_HP);
   if (last_damage > hp) last_damage = hp;
   m.st16(pk, PK_HP, hp - last_damage);
@@ -59,7 +59,7 @@ OAK_HD_NOINLINE uint32_t mem_apply_damage_reason(M m, int t, int subp, uint32_t 
 
 // unmodifiedStats :2692-2696
 template <class M>
-OAK_HD H mem_unmodified_stats(M m, int p) {  // handle of the Pokemon whose (PK_STATS) block applies
+OAK_HD PH mem_unmodified_stats(M m, int p) {  // handle of the Pokemon whose (PK_STATS) block applies
   if (!m.vflag(p, VL_TRANSFORM)) return m.stored(p);
   const uint32_t id = m.vhi_field(p, VHI_TRANSFORM);
   return M::pokemon((int)(id >> 3), (int)(id & 7u) - 1);
@@ -106,7 +106,7 @@ OAK_HD_NOINLINE void mem_boost(M m, int p, uint32_t eff) {
       }
       return;
     }
-    const uint32_t v = m.ld16(mem_unmodified_stats(m, p), PK_STATS + ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
+    const uint32_t v = m.stat_at(mem_unmodified_stats(m, p), ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
     m.st16(s, so, v < 999 ? v : 999);
   }
   m.st32(s, A_BOOSTS, boost_set(b, which, nb));
@@ -154,7 +154,7 @@ OAK_HD_NOINLINE void mem_unboost(M m, int f, uint32_t eff) {
       }
       return;
     }
-    const uint32_t v = m.ld16(mem_unmodified_stats(m, f), PK_STATS + ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
+    const uint32_t v = m.stat_at(mem_unmodified_stats(m, f), ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
     m.st16(s, so, v > 1 ? v : 1);
   }
   m.st32(s, A_BOOSTS, boost_set(b, which, nb));
@@ -172,7 +172,7 @@ OAK_HD void mem_build_rage(M m, int who) {
 // handleResidual :1585-1637
 template <class M>
 OAK_HD_NOINLINE void mem_handle_residual(M m, int p) {
-  const H pk = m.stored(p);
+  const PH pk = m.stored(p);
   const uint32_t st = m.ld8(pk, PK_STATUS);
   const uint32_t lo = m.vlo(p);
   if (!(st & (SB_BRN | SB_PSN)) && !(lo & VL_LEECH_SEED)) return;
@@ -191,7 +191,7 @@ OAK_HD_NOINLINE void mem_handle_residual(M m, int p) {
     if (M::LOGGING && damage > 0) m.lg_hp(LG_Damage, m.ident(p), pk, (st & SB_BRN) ? (uint32_t)DMG_Burn : (uint32_t)DMG_Poison);
   }
   if (lo & VL_LEECH_SEED) {
-    const H fk = m.stored(p ^ 1);
+    const PH fk = m.stored(p ^ 1);
     const uint32_t fhp = m.ld16(fk, PK_HP);
     if (fhp == 0) return;
     uint32_t damage = tick;
@@ -234,7 +234,7 @@ OAK_HD_NOINLINE int mem_check_faint(M m, int p) {
     m.set_vhi(w, 0);
     m.st8(M::sb(w), S_LAST_USED, MOVE_None);
     m.st8(M::sb(f), S_LAST_USED, MOVE_None);
-    const H pk = m.stored(w);
+    const PH pk = m.stored(w);
     const uint32_t st = m.ld8(pk, PK_STATUS);
     m.st8(pk, PK_STATUS, 0);
     uint32_t spe = m.ld16(pk, PK_STATS + ST_SPE);
@@ -269,7 +269,7 @@ OAK_HD_NOINLINE void mem_switch_in(M m, int p, int slot) {
   const uint32_t in = m.ld8(s, S_ORDER + slot - 1);
   m.st8(s, S_ORDER, in);
   m.st8(s, S_ORDER + slot - 1, out);
-  const H pk = M::pokemon(p, (int)in - 1);
+  const PH pk = M::pokemon(p, (int)in - 1);
   m.st8(B_LAST_MOVES + 2 * p, 1);
   m.st8(s, S_LAST_USED, MOVE_None);
   m.st8(M::sb(p ^ 1), S_LAST_USED, MOVE_None);
@@ -347,7 +347,7 @@ OAK_HD_NOINLINE void mem_haze(M m, int p) {
   m.lg1(LG_ClearAllBoost);
   for (int i = 0; i < 2; i++) {
     const H s = M::sb(i);
-    const H pk = m.stored(i);
+    const PH pk = m.stored(i);
     m.st32(s, A_BOOSTS, 0);
     for (int k = 0; k < 10; k += 2) m.st16(s, A_STATS + k, m.ld16(pk, PK_STATS + k));
     const uint32_t st = m.ld8(pk, PK_STATUS);
@@ -381,7 +381,7 @@ OAK_HD_NOINLINE void mem_haze(M m, int p) {
 // Effects.heal :2084-2106
 template <class M>
 OAK_HD_NOINLINE void mem_heal(M m, int p) {
-  const H pk = m.stored(p);
+  const PH pk = m.stored(p);
   const uint32_t hp = m.ld16(pk, PK_HP), maxhp = m.ld16(pk, PK_STATS + ST_HP);
   const uint32_t delta = (maxhp - hp) & 0xFFFFu;
   const uint32_t id = M::LOGGING ? m.ident(p) : 0u;
@@ -410,7 +410,7 @@ OAK_HD_NOINLINE bool mem_substitute(M m, int p) {
     m.lg3(LG_Fail, id, FAIL_Substitute);
     return false;
   }
-  const H pk = m.stored(p);
+  const PH pk = m.stored(p);
   const uint32_t maxhp = m.ld16(pk, PK_STATS + ST_HP), hp = m.ld16(pk, PK_HP);
   const uint32_t cost = (maxhp / 4) & 255u;
   if (hp < (maxhp - 1) / 4 + 1) {

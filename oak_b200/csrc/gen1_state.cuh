@@ -185,10 +185,36 @@ enum : uint32_t {
 struct H {
   int v;
 };
+// Handle of one party Pokémon: v = its position in the on-chip column (scaled like H), c = the byte offset of its 24-byte
+// record inside the 384-byte battle (only the SPLIT layout reads it).
+struct PH {
+  int v, c;
+};
 
-template <int STRIDE>
-struct Mem {
+// SPLIT layout: what an update can never write stays where it is — in the battle's own record in global memory — and only
+// the rest is staged on chip. Per party Pokémon (24 B: data.zig:185-203) the stored stats, move ids, species, types and
+// level are fixed for the whole battle (Transform, Mimic, Conversion and stat changes write the ACTIVE block only,
+// mechanics.zig:2156-2179,2438-2465,2692-2696); PP, HP and status (7 B) change. On chip a battle is then 48 words instead of 96:
+//   per side 22 words: 6 x {word 0: pp[4], word 1: hp lo, hp hi, status, -} | active 8 words | order[6], last_selected, last_used
+//   tail 4 words: turn, last_damage | last_moves | rng
+// which doubles the battles (warps) an SM holds. The constant fields are read through the read-only path (ld.global.nc):
+// they hit L1/L2, the record was fetched when the column was filled.
+template <bool SPLIT>
+struct ConstRecord {};
+template <>
+struct ConstRecord<true> {
+  const uint8_t* crec;  // the battle's 384-byte record (global memory on the device)
+};
+
+template <int STRIDE, bool SPLIT = false>
+struct Mem : ConstRecord<SPLIT> {
   static const int W = STRIDE * 4;
+  static const bool IS_SPLIT = SPLIT;
+  static const int WORDS = SPLIT ? 48 : 96;           // words per battle on chip
+  static const int SIDE_WORDS = SPLIT ? 22 : 46;      // per side
+  static const int PK_WORDS = SPLIT ? 2 : 6;          // per party Pokémon
+  static const int ACTIVE_WORD = SPLIT ? 12 : 36;     // word of `active` inside a side (S_ACTIVE / 4 in the record)
+  static const int TAIL_WORD = SPLIT ? 44 : 92;       // word of `turn` (B_TURN / 4 in the record)
   static OAK_HD int enc(int off) { return (off >> 2) * W + (off & 3); }
 
 #ifdef __CUDA_ARCH__
@@ -203,8 +229,12 @@ struct Mem {
   OAK_HD void st8a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
   OAK_HD void st16a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
   OAK_HD void st32a(uint32_t a, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-  OAK_HD uint32_t at(int off) const { return sbase + (uint32_t)enc(off); }
+  // raw battle offsets: battle-level fields (B_*) in either layout; anything below B_TURN only in the full layout
+  OAK_HD uint32_t at(int off) const { return sbase + (uint32_t)(enc(off) + (TAIL_WORD - B_TURN / 4) * W); }
   OAK_HD uint32_t at(H h, int off) const { return sbase + (uint32_t)(h.v + enc(off)); }
+  OAK_HD uint32_t atv(int v) const { return sbase + (uint32_t)v; }
+  OAK_HD uint32_t cld8(int off) const { return SPLIT ? (uint32_t)__ldg(crec_ptr() + off) : 0u; }
+  OAK_HD uint32_t cld16(int off) const { return SPLIT ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(crec_ptr() + off)) : 0u; }
 #else
   uint8_t* base;  // host (tests only): address of byte 0 of word 0 of this battle's column
   OAK_HD void set(uint8_t* column) { base = column; }
@@ -214,9 +244,18 @@ struct Mem {
   OAK_HD void st8a(uint8_t* a, uint32_t v) const { *a = (uint8_t)v; }
   OAK_HD void st16a(uint8_t* a, uint32_t v) const { *reinterpret_cast<uint16_t*>(a) = (uint16_t)v; }
   OAK_HD void st32a(uint8_t* a, uint32_t v) const { *reinterpret_cast<uint32_t*>(a) = v; }
-  OAK_HD uint8_t* at(int off) const { return base + enc(off); }
+  OAK_HD uint8_t* at(int off) const { return base + (enc(off) + (TAIL_WORD - B_TURN / 4) * W); }
   OAK_HD uint8_t* at(H h, int off) const { return base + (h.v + enc(off)); }
+  OAK_HD uint8_t* atv(int v) const { return base + v; }
+  OAK_HD uint32_t cld8(int off) const { return SPLIT ? (uint32_t)crec_ptr()[off] : 0u; }
+  OAK_HD uint32_t cld16(int off) const { return SPLIT ? (uint32_t)crec_ptr()[off] | ((uint32_t)crec_ptr()[off + 1] << 8) : 0u; }
 #endif
+  OAK_HD const uint8_t* crec_of(const ConstRecord<true>& c) const { return c.crec; }
+  OAK_HD const uint8_t* crec_of(const ConstRecord<false>&) const { return nullptr; }
+  OAK_HD const uint8_t* crec_ptr() const { return crec_of(*this); }
+  OAK_HD void set_record(ConstRecord<true>& c, const uint8_t* record) { c.crec = record; }
+  OAK_HD void set_record(ConstRecord<false>&, const uint8_t*) {}
+  OAK_HD void set_const(const uint8_t* record) { set_record(*this, record); }
   // raw byte offset from the start of the battle (battle-level fields, cold paths)
   OAK_HD uint32_t ld8(int off) const { return ld8a(at(off)); }
   OAK_HD void st8(int off, uint32_t v) const { st8a(at(off), v); }
@@ -238,10 +277,42 @@ struct Mem {
   OAK_HD void st32(H h, int off, uint32_t v) const { st32a(at(h, off), v); }
 
   // ---- handles
-  static OAK_HD H sb(int p) { return H{p * ((SIDE_SIZE / 4) * W)}; }                       // side p
-  static OAK_HD H pokemon(int p, int idx) { return H{p * ((SIDE_SIZE / 4) * W) + idx * ((PK_SIZE / 4) * W)}; }  // party index 0..5
+  // side p: a handle such that (sb(p), A_* / S_* offset) lands on the side's active / order / last-move words in either layout
+  static OAK_HD H sb(int p) { return H{(p * SIDE_WORDS + ACTIVE_WORD - S_ACTIVE / 4) * W}; }
+  static OAK_HD PH pokemon(int p, int idx) { return PH{(p * SIDE_WORDS + idx * PK_WORDS) * W, p * SIDE_SIZE + idx * PK_SIZE}; }  // party index 0..5
   static OAK_HD H hadd(H h, int aligned_off) { return H{h.v + (aligned_off >> 2) * W}; }   // + word-aligned byte offset
-  OAK_HD H stored(int p) const { return pokemon(p, (int)ld8(sb(p), S_ORDER) - 1); }
+  OAK_HD PH stored(int p) const { return pokemon(p, (int)ld8(sb(p), S_ORDER) - 1); }
+
+  // ---- party Pokémon fields: (handle, PK_* byte offset). With a compile-time offset the layout test folds away.
+  static OAK_HD bool pk_is_const(int off) { return off < PK_MOVES || off > PK_STATUS || (off < PK_HP && !(off & 1)); }
+  static OAK_HD int pk_dyn(int off) {  // position of a dynamic byte inside the two on-chip words of the SPLIT layout
+    return off < PK_HP ? ((off - PK_MOVES) >> 1) : W + (off - PK_HP);
+  }
+  OAK_HD uint32_t ld8(PH h, int off) const {
+    if (!SPLIT) return ld8a(at(H{h.v}, off));
+    return pk_is_const(off) ? cld8(h.c + off) : ld8a(atv(h.v + pk_dyn(off)));
+  }
+  OAK_HD void st8(PH h, int off, uint32_t v) const {  // PP and status are the only bytes ever written
+    if (!SPLIT) st8a(at(H{h.v}, off), v);
+    else st8a(atv(h.v + pk_dyn(off)), v);
+  }
+  OAK_HD uint32_t ld16(PH h, int off) const {  // stats (constant), hp, or a {move id, pp} pair
+    if (!SPLIT) return ld16a(at(H{h.v}, off));
+    if (off == PK_HP) return ld16a(atv(h.v + W));
+    if (off < PK_MOVES) return cld16(h.c + off);
+    return cld8(h.c + off) | (ld8a(atv(h.v + pk_dyn(off + 1))) << 8);
+  }
+  // run-time indexed fields: PP of move slot k (0..3), stat at byte offset st (ST_*) of the stored stats
+  OAK_HD uint32_t pp_at(PH h, int k) const { return SPLIT ? ld8a(atv(h.v + k)) : ld8a(at(H{h.v}, PK_MOVES + 2 * k + 1)); }
+  OAK_HD void set_pp_at(PH h, int k, uint32_t v) const {
+    if (SPLIT) st8a(atv(h.v + k), v);
+    else st8a(at(H{h.v}, PK_MOVES + 2 * k + 1), v);
+  }
+  OAK_HD uint32_t stat_at(PH h, int st) const { return SPLIT ? cld16(h.c + PK_STATS + st) : ld16a(at(H{h.v}, PK_STATS + st)); }
+  OAK_HD void st16(PH h, int off, uint32_t v) const {  // hp is the only 16-bit field ever written
+    if (!SPLIT) st16a(at(H{h.v}, off), v);
+    else st16a(atv(h.v + W), v);
+  }
 
   // ---- field helpers
   OAK_HD uint32_t vlo(int p) const { return ld32(sb(p), A_VOL); }
@@ -260,8 +331,8 @@ struct Mem {
     set_vlo(p, (vlo(p) & 0x00FFFFFFu) | (s << 24));
     set_vhi(p, (vhi(p) & ~255u) | ((s >> 8) & 255u));
   }
-  OAK_HD uint32_t status_of(H pk) const { return ld8(pk, PK_STATUS); }
-  OAK_HD uint32_t hp_of(H pk) const { return ld16(pk, PK_HP); }
+  OAK_HD uint32_t status_of(PH pk) const { return ld8(pk, PK_STATUS); }
+  OAK_HD uint32_t hp_of(PH pk) const { return ld16(pk, PK_HP); }
   OAK_HD uint32_t last_selected(int p) const { return ld8(sb(p), S_LAST_SELECTED); }
   OAK_HD uint32_t active_types(int p) const { return ld8(sb(p), A_TYPES); }
   OAK_HD uint32_t active_stat(int p, int st) const { return ld16(sb(p), A_STATS + st); }
@@ -274,11 +345,49 @@ struct Mem {
   OAK_HD void lg2(uint32_t, uint32_t) const {}
   OAK_HD void lg3(uint32_t, uint32_t, uint32_t) const {}
   OAK_HD void lg4(uint32_t, uint32_t, uint32_t, uint32_t) const {}
-  OAK_HD void lg_hp(uint32_t, uint32_t, H, uint32_t) const {}
-  OAK_HD void lg_hp_of(uint32_t, uint32_t, H, uint32_t, uint32_t) const {}
-  OAK_HD void lg_switched(uint32_t, H) const {}
+  OAK_HD void lg_hp(uint32_t, uint32_t, PH, uint32_t) const {}
+  OAK_HD void lg_hp_of(uint32_t, uint32_t, PH, uint32_t, uint32_t) const {}
+  OAK_HD void lg_switched(uint32_t, PH) const {}
   OAK_HD void lg_boost(uint32_t, uint32_t, int) const {}
 };
+
+// ---- SPLIT layout: record <-> column. LD::ld(const uint32_t*) reads one record word (the kernels pass a cache policy).
+struct PlainLoad {
+  static OAK_HD uint32_t ld(const uint32_t* p) { return *p; }
+};
+// the dynamic fields of the record (96 words at `rec`) -> the 48-word column
+template <int STRIDE, class LD>
+OAK_HD void split_fill(uint32_t* col, const uint32_t* rec) {
+  for (int p = 0; p < 2; p++) {
+    for (int idx = 0; idx < 6; idx++) {
+      const uint32_t* r = rec + p * (SIDE_SIZE / 4) + idx * (PK_SIZE / 4);
+      // record bytes 8..23: spc | id0 pp0 | id1 pp1 id2 pp2 | id3 pp3 hp | status species types level
+      const uint32_t w2 = LD::ld(r + 2), w3 = LD::ld(r + 3), w4 = LD::ld(r + 4), w5 = LD::ld(r + 5);
+      uint32_t* c = col + (p * 22 + idx * 2) * STRIDE;
+      c[0] = (w2 >> 24) | ((w3 >> 8) & 0xFFu) << 8 | (w3 >> 24) << 16 | ((w4 >> 8) & 0xFFu) << 24;
+      c[STRIDE] = (w4 >> 16) | (w5 & 0xFFu) << 16;
+    }
+    for (int k = 0; k < 10; k++) col[(p * 22 + 12 + k) * STRIDE] = LD::ld(rec + p * (SIDE_SIZE / 4) + S_ACTIVE / 4 + k);
+  }
+  for (int k = 0; k < 4; k++) col[(44 + k) * STRIDE] = LD::ld(rec + B_TURN / 4 + k);
+}
+// the column's fields written back into a record that already holds the constant bytes (in place: `rec` is read and written)
+template <int STRIDE, class LD>
+OAK_HD void split_merge(const uint32_t* col, uint32_t* rec) {
+  for (int p = 0; p < 2; p++) {
+    for (int idx = 0; idx < 6; idx++) {
+      uint32_t* r = rec + p * (SIDE_SIZE / 4) + idx * (PK_SIZE / 4);
+      const uint32_t* c = col + (p * 22 + idx * 2) * STRIDE;
+      const uint32_t pp = c[0], hs = c[STRIDE];
+      r[2] = (LD::ld(r + 2) & 0x00FFFFFFu) | (pp << 24);
+      r[3] = (LD::ld(r + 3) & 0x00FF00FFu) | ((pp >> 8) & 0xFFu) << 8 | ((pp >> 16) & 0xFFu) << 24;
+      r[4] = (LD::ld(r + 4) & 0x000000FFu) | (pp >> 24) << 8 | (hs & 0xFFFFu) << 16;
+      r[5] = (LD::ld(r + 5) & 0xFFFFFF00u) | ((hs >> 16) & 0xFFu);
+    }
+    for (int k = 0; k < 10; k++) rec[p * (SIDE_SIZE / 4) + S_ACTIVE / 4 + k] = col[(p * 22 + 12 + k) * STRIDE];
+  }
+  for (int k = 0; k < 4; k++) rec[B_TURN / 4 + k] = col[(44 + k) * STRIDE];
+}
 
 // Binary protocol log of one update (reference engine/src/lib/common/protocol.zig:313-863). The sink is the caller's
 // buffer (`Writer`, :831-863): a write that does not fit is refused whole and raises `overflow`, after which nothing more
@@ -333,18 +442,18 @@ struct MemL : Mem<STRIDE> {
   }
   OAK_HD void lg16(uint32_t v) const { lg2(v & 255u, v >> 8); }
   // damage / heal (protocol.zig:432-458): op, ident | hp | max hp | status, reason [| of]
-  OAK_HD void lg_hp(uint32_t op, uint32_t id, H pk, uint32_t reason) const {
+  OAK_HD void lg_hp(uint32_t op, uint32_t id, PH pk, uint32_t reason) const {
     lg2(op, id);
     lg16(this->ld16(pk, PK_HP));
     lg16(this->ld16(pk, PK_STATS + ST_HP));
     lg2(this->ld8(pk, PK_STATUS), reason);
   }
-  OAK_HD void lg_hp_of(uint32_t op, uint32_t id, H pk, uint32_t reason, uint32_t of) const {
+  OAK_HD void lg_hp_of(uint32_t op, uint32_t id, PH pk, uint32_t reason, uint32_t of) const {
     lg_hp(op, id, pk, reason);
     lg1(of);
   }
   // switched (protocol.zig:355-378): op, ident | species, level | hp | max hp | status
-  OAK_HD void lg_switched(uint32_t id, H pk) const {
+  OAK_HD void lg_switched(uint32_t id, PH pk) const {
     lg2(LG_Switch, id);
     lg2(this->ld8(pk, PK_SPECIES), this->ld8(pk, PK_LEVEL));
     lg16(this->ld16(pk, PK_HP));
@@ -354,12 +463,12 @@ struct MemL : Mem<STRIDE> {
   OAK_HD void lg_boost(uint32_t id, uint32_t reason, int num) const { lg4(LG_Boost, id, reason, (uint32_t)(num + 6)); }
 };
 
-template <int STRIDE, bool LOG>
+template <int STRIDE, bool LOG, bool SPLIT = false>
 struct MemFor {
-  typedef Mem<STRIDE> type;
+  typedef Mem<STRIDE, SPLIT> type;
 };
 template <int STRIDE>
-struct MemFor<STRIDE, true> {
+struct MemFor<STRIDE, true, false> {
   typedef MemL<STRIDE> type;
 };
 

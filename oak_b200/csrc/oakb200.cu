@@ -61,8 +61,14 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
     const char* g = getenv("OAKB200_ROLLOUT_GROUPED");
     return g && g[0] == '1';
   }();
-  auto k = grouped ? rollout_grouped_kernel<BLOCK, CHANCE, WRITE> : rollout_kernel<BLOCK, CHANCE, WRITE>;
-  size_t tile_bytes = TILE_BYTES + (grouped ? (size_t)(5 * BLOCK + 64) * 4 : 0);
+  // OAKB200_ROLLOUT_SPLIT=0 selects the full 96-word on-chip layout (16 warps per SM) instead of the default 48-word one
+  static const bool split = [] {
+    const char* g = getenv("OAKB200_ROLLOUT_SPLIT");
+    return !(g && g[0] == '0');
+  }();
+  auto k = grouped ? rollout_grouped_kernel<BLOCK, CHANCE, WRITE>
+                   : (split ? rollout_kernel<BLOCK, CHANCE, WRITE, true> : rollout_kernel<BLOCK, CHANCE, WRITE, false>);
+  size_t tile_bytes = grouped ? TILE_BYTES + (size_t)(5 * BLOCK + 64) * 4 : (split ? TILE_BYTES / 2 : TILE_BYTES);
   // tuning/diagnostic knob: pad the dynamic shared memory to lower the resident CTAs per SM
   if (const char* pad = getenv("OAKB200_ROLLOUT_SMEM_PAD")) tile_bytes += (size_t)atol(pad);
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes);

@@ -204,7 +204,7 @@ __device__ __forceinline__ void prepare_pokemon(PokemonFeatures& f, uint32_t sme
                                                 uint32_t dur, int grp) {
   const uint32_t hi = smem + A1_HI;
   const uint32_t id0 = m.ld8(Mem<ROWS>::sb(s), S_ORDER + slot - 1);
-  const H pk = Mem<ROWS>::pokemon(s, id0 ? (int)id0 - 1 : 0);
+  const PH pk = Mem<ROWS>::pokemon(s, id0 ? (int)id0 - 1 : 0);
   const bool alive = id0 != 0 && m.ld16(pk, PK_HP) != 0;
 #pragma unroll
   for (int k = 0; k < 4; k++) { f.at[k] = 0; f.val[k] = 0x3F80u; }
@@ -754,7 +754,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
         const uint32_t dur = s ? durw.y : durw.x;
         for (int slot = 1; slot <= 6; slot++) {
           const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
-          H pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
+          PH pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
           const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
           const bool alive = hpv != 0;
           float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;

@@ -113,7 +113,7 @@ class HostShim:
         src = os.path.join(d, "engine_host_shim.cpp")
         deps = [src] + [os.path.join(ROOT, "oak_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "oak_b200", "csrc"))]
         if not os.path.exists(so) or any(os.path.getmtime(x) > os.path.getmtime(so) for x in deps):
-            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
+            subprocess.check_call(["g++", "-O2", "-fno-strict-aliasing", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
         self.lib = lib = ctypes.CDLL(so)
         lib.shim_update.restype = ctypes.c_uint8
         lib.shim_update.argtypes = [ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint8, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
@@ -132,6 +132,22 @@ class HostShim:
         ov = None if overrides is None else np.ascontiguousarray(overrides, np.uint8).ctypes.data
         r = self.lib.shim_update(battle.ctypes.data, c1, c2, durations.ctypes.data, act.ctypes.data, ov)
         return int(r), act
+
+    def update_split(self, battle, c1, c2, durations, overrides=None):
+        """The SPLIT on-chip layout (constant Pokémon fields left in the record): same contract as update()."""
+        act = np.zeros(16, np.uint8)
+        ov = None if overrides is None else np.ascontiguousarray(overrides, np.uint8).ctypes.data
+        self.lib.shim_update_split.restype = ctypes.c_uint8
+        self.lib.shim_update_split.argtypes = self.lib.shim_update.argtypes
+        r = self.lib.shim_update_split(battle.ctypes.data, c1, c2, durations.ctypes.data, act.ctypes.data, ov)
+        return int(r), act
+
+    def choices_split(self, battle, player, request):
+        out = np.zeros(16, np.uint8)
+        self.lib.shim_choices_split.restype = ctypes.c_uint8
+        self.lib.shim_choices_split.argtypes = self.lib.shim_choices.argtypes
+        n = self.lib.shim_choices_split(battle.ctypes.data, player, request, out.ctypes.data)
+        return [int(x) for x in out[:n]]
 
     def update_nochance(self, battle, c1, c2):
         return int(self.lib.shim_update_nochance(battle.ctypes.data, c1, c2))

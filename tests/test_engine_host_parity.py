@@ -180,6 +180,39 @@ def test_random_team_playouts_cover_all_moves(libs):
     assert total > 10000
 
 
+class _SplitShim:
+    """HostShim whose update / choices go through the SPLIT on-chip layout."""
+
+    def __init__(self, shim):
+        self.update = shim.update_split
+        self.choices = shim.choices_split
+
+
+def test_split_layout_same_battle(libs):
+    """The SPLIT layout (48 on-chip words; stored stats / move ids / species / types / level read from the record) evolves
+    every byte of the battle, the durations and the actions exactly as the oracle does: sample teams, and random teams over
+    all 164 moves (Transform, Mimic, Conversion, Haze, boosts under Transform: everything that touches the constant side)."""
+    orc, shim = libs
+    split = _SplitShim(shim)
+    total = 0
+    for i in range(0, 256, 5):
+        b, d, r = orc.sample_battle(i)
+        steps, res = playout_compare(orc, split, b, d, r, sample_seed(i))
+        assert (res & 15) in (1, 2, 3)
+        total += steps
+    rng = np.random.default_rng(8)
+    for k in range(300):
+        s1, m1 = random_team(rng)
+        s2, m2 = random_team(rng)
+        seed = splitmix64(7000 + k)
+        b = orc.battle_init(s1, m1, s2, m2, seed)
+        d = np.zeros(8, np.uint8)
+        r, _ = orc.update(b, 0, 0, d)
+        steps, res = playout_compare(orc, split, b, d, r, seed ^ 0x1234, overrides_every=3 if k % 4 == 0 else 0)
+        total += steps
+    assert total > 15000
+
+
 def test_nochance_variant_same_battle(libs):
     """The CHANCE=false build (used by the fast rollout kernel) must evolve the battle identically."""
     orc, shim = libs
