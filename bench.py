@@ -36,6 +36,19 @@ F_EVAL_TC = 2625536   # FLOP per evaluation the tensor-core kernel actually issu
                       # program, i.e. three products per split-bf16 GEMM and the K/N padding included
 
 
+def issue_stats():
+    """Issue-slot / lane-efficiency figures of the rollout kernel from the newest ncu summary tools/ncu_issue.py wrote under
+    profiles/ (with its capture date and commit), or None: nothing is quoted that was not measured."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_rollout_issue.json")))
+    if not files:
+        return None
+    doc = json.load(open(files[-1]))
+    doc["file"] = os.path.relpath(files[-1], ROOT)
+    doc["note"] = "from a separate ncu capture (see captured / commit / command), not re-measured in this run"
+    return doc
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -116,7 +129,8 @@ def run_reference(args, rank, world):
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "rollouts_per_s": total_roll / total_t,
         "config": {"workload": "random playouts to terminal of synthetic RBY OU sample-team battles (BASELINE configs[1])",
-                   "battles_per_step": n, "note": "bounded sample of the GPU arm's 2^20-battle step"},
+                   "battles_per_gpu": n, "parallelism": "all host cores, one playout stream per thread",
+                   "note": "the GPU arm's step: 2^20 playouts of the same synthetic battles (successive steps take successive battle indices)"},
         "cpu_baseline": {"value": v, "unit": "battle-steps/s", "cores": threads, "kind": "port",
                          "sample": f"{args.steps} x {n} playouts, CPU restatement of libpkmn/Oak (Zig toolchain unavailable)"},
         "e2e": {"value": v, "unit": "battle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -144,7 +158,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--battles", type=int, default=1 << 20, help="battles per GPU per step")
     ap.add_argument("--impl", default="oak_b200", choices=["oak_b200", "reference"])
-    ap.add_argument("--ref-battles", type=int, default=1 << 18)
+    ap.add_argument("--ref-battles", type=int, default=1 << 20, help="playouts per step of the reference arm (the GPU arm's step)")
     ap.add_argument("--cpu-sample", type=int, default=1 << 23)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -201,26 +215,52 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def one_step():
-        eng.rollout_device(rb, rd, rr, seeds, 100000, 0, score, turns, steps_t)
+    # The K steps are issued alternately on two CUDA streams (two contexts over the same resident arrays, separate outputs):
+    # a launch ends with a ~5 ms tail in which only its longest playouts are still running (profiles/r1p_rollout_tail.txt), and
+    # the next launch's CTAs take the SMs it frees. Every step is a full launch over all n battles; the timed region is
+    # first launch -> both streams drained.
+    stream_b = torch.cuda.Stream(dev)
+    eng_b = oak_b200.BattleEngine(1, device=local)
+    eng_b.set_stream(stream_b.cuda_stream)
+    outs = [(score, turns, steps_t), (torch.empty_like(score), torch.empty_like(turns), torch.empty_like(steps_t))]
+    lanes = [(eng, stream), (eng_b, stream_b)]
 
-    for _ in range(args.warmup):
-        one_step()
+    def one_step(k=0):
+        e_, _ = lanes[k & 1]
+        e_.rollout_device(rb, rd, rr, seeds, 100000, 0, *outs[k & 1])
+
+    for k in range(args.warmup):
+        one_step(k)
     barrier()
-    launches0 = eng.launch_count
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(stream)
+    one_step(0)  # one launch with the GPU to itself (untimed warm-up step): its duration includes the serial tail
+    a1.record(stream)
+    barrier()
+    alone_ms = a0.elapsed_time(a1)
+    launches0 = eng.launch_count + eng_b.launch_count
     sampler = ClockSampler(local) if rank == 0 else None
-    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev_start, ev_end, ev_b = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
-    evs[0].record(stream)
+    ev_start.record(stream)
+    stream_b.wait_event(ev_start)
     for k in range(args.steps):
-        one_step()
-        evs[k + 1].record(stream)
+        st_ = lanes[k & 1][1]
+        evs[k][0].record(st_)
+        one_step(k)
+        evs[k][1].record(st_)
+    ev_b.record(stream_b)
+    stream.wait_event(ev_b)
+    ev_end.record(stream)
     barrier()
     clocks = sampler.stop() if sampler else None
-    launches = eng.launch_count - launches0
-    ms_total = evs[0].elapsed_time(evs[-1])
-    kernel_ms = [evs[k].elapsed_time(evs[k + 1]) for k in range(args.steps)]
+    launches = eng.launch_count + eng_b.launch_count - launches0
+    ms_total = ev_start.elapsed_time(ev_end)
+    kernel_ms = [a.elapsed_time(b) for a, b in evs]  # per launch, on the launch's own stream (launches overlap at their ends)
     steps_per_pass = int(steps_t.to(torch.int64).sum().item())
+    assert args.steps < 2 or torch.equal(outs[0][2], outs[1][2]), "the two streams' launches disagree"
+    eng_b.close()
 
     # ---- e2e through the C ABI with pinned HOST buffers (upload + rollout + download per step)
     phb = torch.from_numpy(hb).pin_memory()
@@ -323,9 +363,11 @@ def main():
     from oak_b200.sharding import StreamGatherer
     gatherer = StreamGatherer(dst=0, device=dev)
 
-    def sp_pass():
+    def sp_pass(keep_arrivals=False):
         # every drain goes to the writer rank as it is produced (one gather per drain, one drain behind the generator)
         streams, games, at_writer = [], 0, 0
+        arrived.clear()
+        keeping[0] = keep_arrivals
         for s_ in range(SP_STEPS):
             sp.step()
             if (s_ + 1) % 8 == 0:
@@ -333,10 +375,19 @@ def main():
                 streams.append(st_.clone())
                 games += g_
                 got = gatherer.submit(st_)  # the previous drain's bytes, gathered while these 8 steps ran
-                at_writer += sum(len(x) for x in got) if got is not None else 0
+                at_writer += keep(got)
         got = gatherer.flush()
-        at_writer += sum(len(x) for x in got) if got is not None else 0
+        at_writer += keep(got)
         return streams, games, at_writer
+
+    arrived, keeping = [], [False]  # writer rank: every rank's drained streams as they came off the gather (untimed pass only)
+
+    def keep(got):
+        if got is None:
+            return 0
+        if keeping[0]:
+            arrived.extend(np.array(x, copy=True) for x in got if len(x))
+        return sum(len(x) for x in got)
 
     sp_pass()  # warm-up: the same pass (the writer rank's page-locked gather buffer is allocated here, once)
     barrier()
@@ -347,6 +398,26 @@ def main():
     sp_s = time.perf_counter() - t0
     local_stream = torch.cat(sp_streams).cpu().numpy() if sp_streams else np.empty(0, np.uint8)
     launches += sp.eng.launch_count - l0
+    # outside the timed region: the bytes that ARRIVED at the writer rank (all ranks' drains, through NCCL when world > 1)
+    # are whole games that replay on the device to their stored results, and are as many bytes as the ranks drained
+    chk_streams, _, chk_bytes = sp_pass(keep_arrivals=True)  # one more pass, untimed, whose arrivals are kept and replayed
+    barrier()
+    gather_ok = None
+    if rank == 0:
+        from oak_b200.training_rows import BattleFrames
+        got_stream = np.concatenate(arrived) if arrived else np.empty(0, np.uint8)
+        gather_ok = len(got_stream) == chk_bytes and len(got_stream) > 0
+        if gather_ok:
+            from oak_b200.engine import rows_index_host as _rih
+            _, _, _rows = _rih(got_stream)
+            bf = BattleFrames(max(_rows, 1), device=local, engine=eng)
+            try:
+                gather_ok = bf.fill(got_stream) == _rows  # raises if a game does not replay to its stored result
+            except ValueError:
+                gather_ok = False
+            del bf
+        if world == 1:
+            gather_ok = gather_ok and len(got_stream) == sum(int(x.numel()) for x in chk_streams)
 
     # ---- secondary: training rows (pyoak EncodedBattleFrames.from_bytes / sample): the games this rank's
     # self-play finishes are replayed on the device and encoded into the learner's dense tensors. Input: the self-play
@@ -454,9 +525,30 @@ def main():
         _orc = _O()
         _net = NetOracle(_orc, blob)
         cb, cd, cr = (x.cpu().numpy() for x in (eb, ed, er))
-        t0 = time.perf_counter()
-        _net.eval_batch(cb, cd, cr, threads=os.cpu_count() or 1)
-        eval_cpu = EV / (time.perf_counter() - t0)
+        _thr = os.cpu_count() or 1
+        # positions grouped by the battle they come from (team pair = index & 255): the reference fills its embedding memo
+        # once per search root (network.h:48-50) and every evaluation under that root hits it
+        _grp = (np.arange(EV) & 255).astype(np.uint32)
+        _ord = np.argsort(_grp, kind="stable")
+        gb, gd, gr, gg = cb[_ord], cd[_ord], cr[_ord], _grp[_ord]
+        _one = slice(0, min(EV, 8192))  # 1-thread sample: 32 groups of 256... (sorted: whole groups)
+
+        def _time(fn):
+            t0 = time.perf_counter()
+            fn()
+            return time.perf_counter() - t0
+        eval_cpu = {
+            "cache_free_all_cores": EV / _time(lambda: _net.eval_batch(cb, cd, cr, threads=_thr)),
+            "cache_free_1_thread": (_one.stop) / _time(lambda: _net.eval_batch(cb[_one], cd[_one], cr[_one], threads=1)),
+            "memoised_256_per_root_all_cores": EV / _time(lambda: _net.eval_batch_cached(gb, gd, gr, gg, threads=_thr)),
+            "memoised_4096_per_root_all_cores": 16 * EV / _time(lambda: _net.eval_batch_cached(gb, gd, gr, gg, threads=_thr, repeat=16)),
+            "memoised_4096_per_root_1_thread": 16 * _one.stop / _time(lambda: _net.eval_batch_cached(gb[_one], gd[_one], gr[_one], gg[_one], threads=1, repeat=16)),
+            "cores": _thr,
+            "note": "memoised = the reference's algorithm: sparse first layers + PokemonCache (240 keyed embeddings per party slot, "
+                    "filled once per root: 2 880 embeddings, the cost of ~290 cache-free evaluations) + ActivePokemonCache map "
+                    "(nn/battle/cache.h); N_per_root = evaluations sharing one fill, as a search of N iterations does; cache_free = every embedding recomputed, "
+                    "what the GPU kernel does. The reference prints ~85 K evals/s per thread for the memoised path (TUTORIAL.md:418-427)",
+        }
 
     # ---- reduce over ranks: max time, sum of work
     t = torch.tensor([ms_total, e2e_s * 1e3, lock_ms, sr_s * 1e3, tr_ms, tr_e2e_s * 1e3], dtype=torch.float64, device=dev)
@@ -470,7 +562,7 @@ def main():
     if rank == 0:
         pk, pk_src = peaks()
         value = tot_steps / (ms_total_max * 1e-3)
-        kern_s = statistics.mean(kernel_ms) * 1e-3
+        kern_s = ms_total_max / args.steps * 1e-3  # time per launch over the timed region (launches overlap only at their tails)
         achieved = B_ROLLOUT * n / kern_s / 1e9
         cpu = None
         if not args.no_cpu_baseline:
@@ -480,36 +572,43 @@ def main():
             for chunk in range(max(1, args.cpu_sample >> 20)):  # 2^20-playout chunks (412 MB each)
                 s_, dt_ = cpu_rollouts(orc_, chunk << 20, min(args.cpu_sample, 1 << 20), threads)
                 s, dt = s + s_, dt + dt_
+            s1, dt1 = cpu_rollouts(orc_, 0, 1 << 15, 1)
             cpu = {"value": s / dt, "unit": "battle-steps/s", "cores": threads, "kind": "port",
                    "rollouts_per_s": args.cpu_sample / dt,
+                   "one_thread": {"battle_steps_per_s": s1 / dt1, "rollouts_per_s": (1 << 15) / dt1, "sample": "32768 playouts"},
                    "sample": f"{args.cpu_sample} playouts ({s} battle-steps, {dt:.1f} s) of the same synthetic workload; "
                              "CPU restatement of libpkmn/Oak (Zig toolchain unavailable)"}
         line = {
             "metric": "battle-steps/sec", "value": value, "unit": "battle-steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "legs": {"rollouts_per_s": tot_rollouts / (ms_total_max * 1e-3), "e2e_battle_steps_per_s": tot_e2e_steps / (e2e_ms_max * 1e-3),
+                     "evals_per_s": world * EV / (eval_ms * 1e-3), "evals_e2e": world * EV / eval_e2e_s,
+                     "search_iters_per_s": tot_sr / (sr_ms_max * 1e-3), "selfplay_updates_per_s": world * SP_G * SP_STEPS / sp_s,
+                     "rows_per_s": tot_tr_rows / (tr_ms_max * 1e-3), "lockstep_steps_per_s": tot_battles / (lock_ms_max * 1e-3),
+                     "gather_replay_ok": gather_ok},
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "rollouts_per_s": tot_rollouts / (ms_total_max * 1e-3),
             "mean_steps_per_rollout": tot_steps / tot_rollouts,
             "config": {"workload": "configs[1]: 2^20 lockstep random-playout RBY OU sample-team battles per GPU, played to "
                                    "terminal by the fused rollout kernel (choices x2 + pick + update per battle-step)",
                        "battles_per_gpu": n, "parallelism": f"battle-sharded x{world}, no data-path collective",
+                       "streams": "steps issued alternately on two CUDA streams: one launch's serial tail overlaps the next launch's body",
                        "l2": f"inputs {n * 393 / 1e6:.0f} MB per pass > 126 MB L2 (no flush needed)"},
             "e2e": {"value": tot_e2e_steps / (e2e_ms_max * 1e-3), "unit": "battle-steps/s",
                     "rollouts_per_s": tot_battles * e2e_iters / (e2e_ms_max * 1e-3),
                     "h2d_bytes_per_step": int(tot_battles * (384 + 8 + 1 + 8)), "d2h_bytes_per_step": int(tot_battles * (1 + 2 + 4)),
                     "iters": e2e_iters, "timing": "wall clock around oakb200_rollout_host (pinned host records in, score/turns/steps out; chunked upload pipelined behind the playouts), synchronised"},
-            "roofline": {"bound": "hbm", "kernel": "rollout_kernel<128,false,false>", "achieved": achieved, "peak": pk["hbm_gbs"],
+            "roofline": {"bound": "hbm", "kernel": "rollout_kernel<128,false,false,SPLIT>", "achieved": achieved, "peak": pk["hbm_gbs"],
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
                          "traffic": int(424_100_608 * n / (1 << 20)), "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum = 414.9 + 9.2 MB "
-                         "for one launch of 2^20 playouts (ncu --set full, profiles/r1m_rollout_kernel_ncu_summary.txt), scaled to this n",
+                         "for one launch of 2^20 playouts (ncu --set full, profiles/r1m_rollout_kernel_ncu_summary.txt; the SPLIT kernel "
+                         "reads the same records once: profiles/r2c_rollout_issue.json has 106.9 MB for 2^18), scaled to this n",
                          "peak_source": pk_src,
-                         "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": statistics.mean(kernel_ms),
+                         "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": ms_total_max / args.steps,
+                         "launch_ms_on_own_stream": statistics.mean(kernel_ms), "launch_ms_alone": alone_ms,
                          "note": "fused playouts read each 393-byte record once per ~120 updates: the kernel is bound by SM "
                                  "instruction issue under divergence, not HBM (see profiles/)",
-                         "issue": {"issue_slots_busy": 0.262, "threads_per_warp_inst": 11.1, "stall_no_instruction_share": 0.52,
-                                   "registers": 63, "warps_per_sm": 15.6, "code_bytes": 65024,
-                                   "source": "ncu --set full of this command, profiles/r1m_rollout_kernel_ncu_summary.txt (SURVEY 8d asks "
-                                             "for issue-slot utilisation and lane efficiency beside the HBM figure); static, not re-measured per run"}},
+                         "issue": issue_stats()},
             "lockstep_step_kernel": {"ms_per_launch": lock_ms_max, "battles": int(tot_battles),
                                      "battle_steps_per_s": tot_battles / (lock_ms_max * 1e-3),
                                      "achieved_gbs": B_STEP * n / (lock_ms * 1e-3) / 1e9,
@@ -529,7 +628,7 @@ def main():
                                        "dense_equivalent_tflops": F_EVAL * EV / (eval_ms * 1e-3) / 1e12,
                                        "note": "executed = every tcgen05.mma issued (3 products per split-bf16 GEMM, K and N "
                                                "padding included); dense-equivalent = SURVEY 8d F_eval"},
-                          "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (cache-free, sparse first layers), all host cores"},
+                          "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (oracle/nn_oracle.hpp)"},
             "tree_search": {"iterations_per_s": tot_sr / (sr_ms_max * 1e-3), "roots_total": int(tot_sr / SR_ITERS),
                             "descents_in_flight_per_root": SR_P, "iterations_per_root": SR_ITERS,
                             "mean_root_value": float(sr_out["empirical_value"].mean()),

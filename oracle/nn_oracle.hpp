@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <map>
 #include <vector>
 
 #include "gen1_oracle.hpp"
@@ -220,6 +221,10 @@ struct BattleNet {
     std::vector<float> e;
     embed(b, durations, e);
     if (embedding_out) *embedding_out = e;
+    return main(e, b, m, n, c1, c2, l1, l2);
+  }
+  // main-net.h:66-107 on a given battle embedding
+  float main(const std::vector<float>& e, const Battle& b, int m, int n, const uint8_t* c1, const uint8_t* c2, float* l1, float* l2) const {
     std::vector<float> b0(fc0.out), b1(fc1.out), vb(v2.out), pb(p1a.out > p2a.out ? p1a.out : p2a.out);
     fc0.dense(e.data(), b0.data(), activation);
     fc1.dense(b0.data(), b1.data(), activation);
@@ -308,6 +313,97 @@ struct BattleNet {
     for (int k = 0; k < n; k++) i2[k] = policy_index(b.sides[1], c2[k]);
     const float value = main_discrete(q.data(), m, n, i1, i2, l1, l2);
     return 1.0f / (1.0f + std::exp(-value));
+  }
+};
+
+// ---- the reference's inference path WITH its embedding memo (nn/battle/cache.h:80-131,186-221; network.h:48-50,131-175):
+// per party Pokémon a table of all 16 has-PP x 15 status keys (240 embeddings) filled once per search from the root battle
+// (`fill_cache`), and a map from (active block, key of the stored Pokémon) to the active embedding filled on demand. The
+// main net is then the only dense work per evaluation. Used as the CPU baseline of the leaf-evaluation bench leg; note the
+// reference's active key omits the confusion / disable / attacking / binding duration one-hots, so a memo hit can return the
+// embedding of another duration — tests compare it with the cache-free function where the keys do not collide.
+struct CachedBattleNet {
+  const BattleNet& net;
+  std::vector<float> pokemon[2][6];  // [240][pod]
+  struct ActiveKey {
+    uint8_t bytes[33];
+    bool operator<(const ActiveKey& o) const { return memcmp(bytes, o.bytes, 33) < 0; }
+  };
+  std::map<ActiveKey, std::vector<float>> active[2][6];
+
+  explicit CachedBattleNet(const BattleNet& n) : net(n) {}
+
+  void fill(const Battle& root) {  // BattleCache::fill -> PokemonCache::fill (cache.h:80-124)
+    static const uint8_t STATUS[8] = {0, 1u << ST_PSN, 1u << ST_BRN, 1u << ST_FRZ, 1u << ST_PAR, 0x81, 0x82, 0x83};
+    const uint32_t pod = net.pk1.out;
+    std::vector<float> h(net.pk0.out);
+    for (int s = 0; s < 2; s++)
+      for (int i = 0; i < 6; i++) {
+        active[s][i].clear();
+        pokemon[s][i].assign((size_t)240 * pod, 0.0f);
+        Pokemon p = root.sides[s].pokemon[i];
+        if (p.species == 0) continue;
+        for (int m = 0; m < 16; m++) {
+          for (int k = 0; k < 4; k++) p.moves[k].pp = (uint8_t)(m & (1 << k));
+          auto entry = [&](uint8_t sleep) {
+            Sparse sp;
+            uint16_t off = 0;
+            enc_pokemon(p, sleep, sp, off);
+            net.pk0.sparse(sp, h.data(), net.activation);
+            net.pk1.dense(h.data(), pokemon[s][i].data() + (size_t)pokemon_key(p, sleep) * pod, net.activation);
+          };
+          for (uint8_t st : STATUS) {
+            p.status = st;
+            entry(0);
+          }
+          p.status = 1;  // Status::Sleep1
+          for (uint8_t sleep = 1; sleep <= 7; sleep++) entry(sleep);
+        }
+      }
+  }
+
+  void embed(const Battle& b, const uint8_t* durations, std::vector<float>& out) {  // network.h:131-175
+    const uint32_t pod = net.pk1.out, aod = net.ac1.out, side_dim = (1 + aod) + 5 * (1 + pod);
+    out.assign(2 * side_dim, 0.0f);
+    uint32_t d[2];
+    memcpy(d, durations, 8);
+    for (int s = 0; s < 2; s++) {
+      const Side& side = b.sides[s];
+      float* e = out.data() + s * side_dim;
+      const int id0 = side.order[0] - 1;
+      const Pokemon& st = side.pokemon[id0];
+      if (st.hp != 0) {
+        e[0] = (float)st.hp / st.stats.hp;
+        ActiveKey key;
+        memcpy(key.bytes, &side.active, 32);
+        key.bytes[32] = pokemon_key(st, (uint8_t)sleeps_get(d[s], 0));
+        auto it = active[s][id0].find(key);
+        if (it == active[s][id0].end()) {
+          Sparse sp;
+          enc_active_pokemon(st, side.active, d[s], sp);
+          std::vector<float> h(net.ac0.out), emb(aod);
+          net.ac0.sparse(sp, h.data(), net.activation);
+          net.ac1.dense(h.data(), emb.data(), net.activation);
+          it = active[s][id0].emplace(key, std::move(emb)).first;
+        }
+        memcpy(e + 1, it->second.data(), aod * 4);
+      }
+      for (int slot = 2; slot <= 6; slot++) {
+        float* se = e + (1 + aod) + (slot - 2) * (1 + pod);
+        const uint8_t id = side.order[slot - 1];
+        if (id == 0) continue;
+        const Pokemon& pk = side.pokemon[id - 1];
+        if (pk.hp == 0) continue;
+        se[0] = (float)pk.hp / pk.stats.hp;
+        memcpy(se + 1, pokemon[s][id - 1].data() + (size_t)pokemon_key(pk, (uint8_t)sleeps_get(d[s], slot - 1)) * pod, pod * 4);
+      }
+    }
+  }
+
+  float eval(const Battle& b, const uint8_t* durations, int m, int n, const uint8_t* c1, const uint8_t* c2, float* l1, float* l2) {
+    std::vector<float> e;
+    embed(b, durations, e);
+    return net.main(e, b, m, n, c1, c2, l1, l2);
   }
 };
 

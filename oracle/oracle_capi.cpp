@@ -275,6 +275,53 @@ void oracle_net_eval_batch(void* h, const uint8_t* battles, const uint8_t* durat
 }
 }
 
+extern "C" {
+// The same batch through the reference's memoised path (CachedBattleNet). group[i] identifies the battle (team pair) position i
+// comes from; positions must be sorted by group. Each thread takes whole groups: fill_cache from the group's first position
+// (what a search does once at its root, network.h:48-50), then every position of the group through the memo, `repeat` times.
+void oracle_net_eval_cached_batch(void* h, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
+                                  const uint32_t* group, size_t n, int threads, int repeat, float* values, float* logits,
+                                  uint8_t* counts) {
+  const BattleNet* net = static_cast<BattleNet*>(h);
+  std::vector<size_t> starts;
+  for (size_t i = 0; i < n; i++)
+    if (i == 0 || group[i] != group[i - 1]) starts.push_back(i);
+  starts.push_back(n);
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    CachedBattleNet cached(*net);
+    for (;;) {
+      const size_t g = next.fetch_add(1);
+      if (g + 1 >= starts.size()) return;
+      Battle root;
+      memcpy(&root, battles + starts[g] * 384, 384);
+      cached.fill(root);
+      // repeat > 1: the group's positions are evaluated `repeat` times under the one fill, i.e. repeat x as many evaluations
+      // per root as the batch holds (a search makes thousands per root); the active memo is warm after the first pass, as it
+      // is for a search revisiting its nodes
+      for (int rep = 0; rep < (repeat < 1 ? 1 : repeat); rep++)
+      for (size_t i = starts[g]; i < starts[g + 1]; i++) {
+        Battle b;
+        memcpy(&b, battles + i * 384, 384);
+        Options o{};
+        OakEngine e(b, o);
+        uint8_t c1[9], c2[9];
+        const int m = e.choices(P1, (results[i] >> 4) & 3, c1);
+        const int k = e.choices(P2, (results[i] >> 6) & 3, c2);
+        float* lo = logits + i * 18;
+        for (int j = 0; j < 18; j++) lo[j] = 0.0f;
+        values[i] = cached.eval(b, durations + i * 8, m, k, c1, c2, lo, lo + 9);
+        counts[2 * i] = (uint8_t)m;
+        counts[2 * i + 1] = (uint8_t)k;
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < (threads < 1 ? 1 : threads); t++) pool.emplace_back(work);
+  for (auto& t : pool) t.join();
+}
+}
+
 // ---- training frames + policy sampling (frames_oracle.hpp) ----
 #include "frames_oracle.hpp"
 extern "C" {

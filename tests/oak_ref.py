@@ -236,6 +236,21 @@ class NetOracle:
           v.ctypes.data, lg.ctypes.data, cnt.ctypes.data)
         return v, lg, cnt
 
+    def eval_batch_cached(self, battles, durations, results, group, threads=None, repeat=1):
+        """The reference's memoised inference path (PokemonCache / ActivePokemonCache); positions sorted by `group`
+        (the battle they come from: one fill_cache per group)."""
+        n = battles.shape[0]
+        v = np.zeros(n, np.float32)
+        lg = np.zeros((n, 2, 9), np.float32)
+        cnt = np.zeros((n, 2), np.uint8)
+        group = np.ascontiguousarray(group, np.uint32)
+        f = self.lib.oracle_net_eval_cached_batch
+        f.restype = None
+        f.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_size_t, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 3
+        f(self.h, battles.ctypes.data, durations.ctypes.data, results.ctypes.data, group.ctypes.data, n, threads or os.cpu_count() or 1,
+          int(repeat), v.ctypes.data, lg.ctypes.data, cnt.ctypes.data)
+        return v, lg, cnt
+
     def eval_one(self, battle, durations, c1, c2):
         l1 = np.zeros(9, np.float32)
         l2 = np.zeros(9, np.float32)

@@ -122,3 +122,29 @@ def test_oak_side_restatements_against_live_reference_code(orc):
         got = b[i].copy()
         orc.randomize_hidden(got, d[i])
         assert np.array_equal(got, want), i
+
+
+def test_memoised_path_equals_the_cache_free_function():
+    """The reference's PokemonCache / ActivePokemonCache path (oracle CachedBattleNet, the bench's CPU baseline) against the
+    cache-free forward: benched-Pokémon embeddings come from the 240-entry tables and must agree everywhere; the active memo's
+    key omits the duration one-hots (cache.h:186-195), so positions are grouped per battle and the comparison allows the few
+    collisions that property causes."""
+    from oak_ref import NetOracle, Oracle, make_net_blob, oracle_sample_batch, pick_word, sample_seeds
+    orc = Oracle()
+    net = NetOracle(orc, make_net_blob(np.random.default_rng(5)))
+    n = 96
+    b, d, r = oracle_sample_batch(orc, 0, n)
+    seeds = sample_seeds(0, n)
+    B, D, R, G = [], [], [], []
+    for i in range(n):  # 30 positions along each battle's playout: one group (= one fill_cache) per battle
+        for s in range(30):
+            if (r[i] & 15) != 0:
+                break
+            B.append(b[i].copy()); D.append(d[i].copy()); R.append(r[i]); G.append(i)
+            r[i], _, _, _ = orc.step(b[i], d[i], int(r[i]), pick_word(int(seeds[i]), s))
+    B, D, R = np.array(B), np.array(D), np.array(R, np.uint8)
+    v0, l0, c0 = net.eval_batch(B, D, R, threads=2)
+    v1, l1, c1 = net.eval_batch_cached(B, D, R, np.array(G, np.uint32), threads=2)
+    assert np.array_equal(c0, c1)
+    same = np.isclose(v0, v1, rtol=1e-5, atol=1e-6) & np.all(np.isclose(l0, l1, rtol=1e-5, atol=1e-6), axis=(1, 2))
+    assert same.mean() > 0.97, same.mean()
