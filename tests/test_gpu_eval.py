@@ -155,3 +155,38 @@ def test_pipelined_host_evaluation_matches_upload_then_eval(orc, eng):
         v2, l2, c2 = eng.evaluate_host(b[:777], None, None)  # pageable memory, defaults
         assert np.array_equal(v2, v0[:777]) and np.array_equal(l2, l0[:777]) and np.array_equal(c2, c0[:777])
     eng.set_eval_mode(0)
+
+
+def device_midgame_states(n, steps):
+    """n sample battles advanced `steps` random-playout steps by the GPU step kernel (itself parity-tested against the oracle
+    step for step in tests/test_gpu_parity.py): the bench's C3 input, cheap to make at full size."""
+    import torch
+    import oak_b200
+    from oak_ref import sample_teams
+    e = oak_b200.BattleEngine(n)
+    seeds = sample_seeds(0, n)
+    e.build_battles(sample_teams(0, n), seeds)
+    b, d, r = (torch.from_numpy(x).cuda() for x in e.download())
+    s = torch.from_numpy(seeds.view(np.int64)).cuda()
+    for k in range(steps):
+        e.step_random_device(b, d, r, s, k)
+    e.synchronize()
+    out = tuple(x.cpu().numpy() for x in (b, d, r))
+    e.close()
+    return out
+
+
+def test_config_c3_full_batch_65536(orc, eng):
+    """BASELINE configs[2] at its full size, the batch bench.py times: 65 536 positions = 512 tiles of 128, 3.46 rounds over
+    148 persistent CTAs (the uneven last round and the head warps' one-tile-behind hand-over at the end of each CTA's list),
+    through the resident path and through oakb200_eval_host (chunked upload / evaluate / download)."""
+    n = 1 << 16
+    b, d, r = device_midgame_states(n, 19)
+    net = NetOracle(orc, make_net_blob(np.random.default_rng(1234)))
+    ov, olg, ocnt = net.eval_batch(b, d, r)
+    eng.load_network(make_net_blob(np.random.default_rng(1234)))
+    eng.set_eval_mode(2)
+    eng.upload(b, d, r)
+    compare(*eng.evaluate(), ov, olg, ocnt)
+    compare(*eng.evaluate_host(b, d, r), ov, olg, ocnt)
+    eng.set_eval_mode(0)

@@ -93,40 +93,62 @@ def test_batched_particles_conserve_and_agree():
     assert diff.mean() < 0.04 and diff.max() < 0.15, (diff.mean(), diff.max())
 
 
+SEARCH_KATS = [  # cpp/src/search-test.cc:50-109: (p1 = (species, move, hp, slept, conf), p2, expected value, tolerance)
+    (("Starmie", "SeismicToss", 1, None, 5), ("Snorlax", "BodySlam", 1, None, None), 1.0, 0.0),
+    (("Starmie", "SeismicToss", 1, None, 4), ("Snorlax", "BodySlam", 1, None, None), .5 + .5 / 2, 0.03),
+    (("Starmie", "SeismicToss", 1, None, 3), ("Snorlax", "BodySlam", 1, None, None), .33 + .66 / 2, 0.03),
+    (("Starmie", "SeismicToss", 1, None, 2), ("Snorlax", "BodySlam", 1, None, None), .25 + .75 / 2, 0.03),
+    (("Starmie", "SeismicToss", 1, None, 1), ("Snorlax", "BodySlam", 1, None, None), .5, 0.03),
+    (("Starmie", "SeismicToss", 1, 6, None), ("Snorlax", "SeismicToss", 1, None, None), 0.0, 0.0),
+] + [(("Starmie", "SeismicToss", 101, k, None), ("Snorlax", "SeismicToss", 1, None, None), 1.0 / (7 - k), 0.0 if k == 6 else 0.03)
+     for k in range(7)]
+
+
 def kat_position(orc, p1, p2):
-    """One Pokémon per side: (species, move, hp, sleeps or None) as cpp/include/util/parse.h builds `name move Nhp slpK`."""
+    """One Pokémon per side: (species, move, hp, sleeps or None[, observed confusion duration]) as cpp/include/util/parse.h
+    builds `name move Nhp slpK (conf:C)`: slpK = Status::Sleep7 + Duration.sleeps[0] = K + 1 (parse.h:71-79, init.h:156-165),
+    (conf:C) = the Confusion volatile + Duration.confusion = C (parse.h:190-198); the hidden counters are whatever — every
+    search iteration redraws them from the durations (durations.h:25-97)."""
+    p1, p2 = tuple(p1) + (None,) * (5 - len(p1)), tuple(p2) + (None,) * (5 - len(p2))
     sp = lambda name: NAMES["species"].index(name)
     mv = lambda name: NAMES["moves"].index(name)
     sets = []
-    for name, move, _, _ in (p1, p2):
+    for name, move, _, _, _ in (p1, p2):
         sets.append((np.array([sp(name), 0, 0, 0, 0, 0], np.uint8), np.array([[mv(move), 0, 0, 0]] + [[0, 0, 0, 0]] * 5, np.uint8)))
     b = orc.battle_init(sets[0][0], sets[0][1], sets[1][0], sets[1][1], 0x123456)
     d = np.zeros(8, np.uint8)
     r, _ = orc.update(b, 0, 0, d)  # send out the leads
-    for side, (_, _, hp, sleeps) in enumerate((p1, p2)):
+    for side, (_, _, hp, sleeps, conf) in enumerate((p1, p2)):
         o = 184 * side
         b[o + 18], b[o + 19] = hp & 255, hp >> 8
         if sleeps is not None:
             b[o + 20] = 7                      # Status::Sleep7
             d[4 * side] |= (sleeps + 1) & 7    # Duration.sleeps[0] = turns slept + 1 (parse.h:79, init.h:156-165)
+        if conf is not None:
+            b[o + 144 + 16] |= 1 << 7          # Volatiles.Confusion (data.zig:325-383, bit 7)
+            dw = int.from_bytes(d[4 * side:4 * side + 4].tobytes(), "little") | (conf << 18)  # Duration.confusion (chance.zig:279-287)
+            d[4 * side:4 * side + 4] = np.frombuffer(dw.to_bytes(4, "little"), np.uint8)
     return b, d, r
 
 
-@pytest.mark.parametrize("slept,expected", [(3, 1 / 4), (5, 1 / 2), (6, 1.0)])
-def test_reference_sleep_known_answers(slept, expected):
-    """`starmie seismictoss 101hp slpK | snorlax seismictoss 1hp` -> 1 / (7 - K) (search-test.cc:91-109)."""
+def test_reference_search_known_answers():
+    """All 13 statistical known answers of the reference (cpp/src/search-test.cc:50-109: five observed-confusion positions,
+    eight observed-sleep positions; tolerance 0.03, exact where the reference says error = 0) as 13 roots of one batched search."""
     import oak_b200
     from oak_b200.search import TreeSearch
     orc = Oracle()
-    b, d, r = kat_position(orc, ("Starmie", "SeismicToss", 101, slept), ("Snorlax", "SeismicToss", 1, None))
-    eng = oak_b200.BattleEngine(64)
-    ts = TreeSearch(eng, 1, particles=64)
-    ts.set_roots(b[None], d[None], np.array([r], np.uint8), np.array([42], np.uint64))
+    pos = [kat_position(orc, p1, p2) for p1, p2, _, _ in SEARCH_KATS]
+    b, d = np.stack([x[0] for x in pos]), np.stack([x[1] for x in pos])
+    r = np.array([x[2] for x in pos], np.uint8)
+    eng = oak_b200.BattleEngine(13 * 64)
+    ts = TreeSearch(eng, 13, particles=64)
+    ts.set_roots(b, d, r, np.arange(42, 55, dtype=np.uint64))
     ts.run(1 << 14)
     out = ts.output()
     ts.close()
     eng.close()
-    assert abs(out["empirical_value"][0] - expected) <= (0 if expected == 1.0 else 0.03)
+    for i, (p1, p2, expected, tol) in enumerate(SEARCH_KATS):
+        assert abs(out["empirical_value"][i] - expected) <= tol + 1e-12, (p1, out["empirical_value"][i], expected)
 
 
 def oracle_search_net(orc, net, discrete, b, d, r, seed, iters, c, rr, orl):
@@ -196,3 +218,45 @@ def test_network_leaves_need_a_network():
         ts.set_leaf(7)
     ts.close()
     eng.close()
+
+
+def test_config_c4_scale_4096_roots():
+    """BASELINE configs[3] at the size bench.py runs: 4 096 roots. (a) x 64 descents in flight, 4 waves: every root's visits
+    are conserved, values lie in [0, visits], policies sum to 1, and the 262 144 resident particles really are distinct
+    playouts (value matrices differ between roots). (b) the same 4 096 roots with ONE descent in flight for 24 iterations:
+    every root's matrices and node count equal the sequential oracle's — the root sharding over host threads and stream
+    groups changes nothing at scale."""
+    import oak_b200
+    from oak_b200.search import TreeSearch
+    from test_gpu_eval import device_midgame_states
+    orc = Oracle()
+    n, P = 4096, 64
+    b, d, r = device_midgame_states(n, 19)
+    live = (r & 15) == 0
+    b, d, r = b[live], d[live], r[live]
+    n = b.shape[0]
+    assert n > 4000
+    seeds = sample_seeds(90_000, n)
+    eng = oak_b200.BattleEngine(n * P)
+    ts = TreeSearch(eng, n, particles=P)
+    ts.set_roots(b, d, r, seeds)
+    ts.run(4 * P)
+    o = ts.output()
+    waves, levels = ts.stats()
+    ts.close()
+    assert waves == 4 and levels >= waves
+    assert np.all(o["iterations"] == 4 * P) and np.all(o["visit_matrix"].reshape(n, -1).sum(1) == 4 * P)
+    assert np.all((o["value_matrix"] >= 0) & (o["value_matrix"] <= o["visit_matrix"]))
+    np.testing.assert_allclose(o["empirical"].sum(-1), 1.0, atol=1e-9)
+    assert np.all((o["empirical_value"] >= 0) & (o["empirical_value"] <= 1)) and 0.3 < o["empirical_value"].mean() < 0.7
+    assert len({o["value_matrix"][i].tobytes() for i in range(0, n, 37)}) > 100
+    one = TreeSearch(eng, n, particles=1)
+    one.set_roots(b, d, r, seeds)
+    one.run(24, c=1.0, root_rolls=3, other_rolls=1)
+    o1 = one.output()
+    one.close()
+    eng.close()
+    for i in range(n):
+        visit, value, nodes = oracle_search(orc, b[i], d[i], r[i], seeds[i], 24, 1.0, 3, 1)
+        assert np.array_equal(o1["visit_matrix"][i], visit) and np.array_equal(o1["value_matrix"][i], value), i
+        assert o1["nodes"][i] == nodes, i
