@@ -488,7 +488,8 @@ def main():
     sr_seeds = seeds_np[:SR_ROOTS][sr_live]
     ts = TreeSearch(eng, sr_b.shape[0], particles=SR_P)
     ts.set_roots(sr_b, sr_d, sr_r, sr_seeds)
-    ts.run(SR_P)
+    ts.run(SR_ITERS)  # warm-up: the same search once; the search object keeps its tree arenas, as it does from turn to turn
+    ts.set_roots(sr_b, sr_d, sr_r, sr_seeds)
     barrier()
     l0 = eng.launch_count
     t0 = time.perf_counter()

@@ -227,7 +227,7 @@ void oakb200_search_destroy(oakb200_search* search);
 /* MCTS::Input rows (mcts.h:62-66) + one stream seed per root; resets the trees. HOST pointers. */
 int oakb200_search_set_roots(oakb200_search* search, size_t n, const uint8_t* battles, const uint8_t* durations,
                              const uint8_t* results, const uint64_t* seeds);
-/* `iterations` more iterations per root (rounded up to a multiple of particles). ucb_c: UCB::Bandit::Params::c;
+/* Exactly `iterations` more iterations per root (the last wave spawns only what is left). ucb_c: UCB::Bandit::Params::c;
  * root_rolls / other_rolls: SearchOptions (1, 2, 3, 20, or 39 = unclamped; the reference default is 3 / 1);
  * host_threads <= 0: all cores. */
 int oakb200_search_run(oakb200_search* search, uint32_t iterations, float ucb_c, uint32_t root_rolls, uint32_t other_rolls,
@@ -236,6 +236,12 @@ int oakb200_search_run(oakb200_search* search, uint32_t iterations, float ucb_c,
  * iterations[n], empirical_value[n] f64, empirical[n][2][9] f64 (process_output, mcts.h:623-661), nodes[n]. Any may be NULL. */
 int oakb200_search_output(oakb200_search* search, uint8_t* k, uint8_t* choices, uint32_t* visit_matrix, double* value_matrix,
                           uint64_t* iterations, double* empirical_value, double* empirical, uint64_t* nodes);
+/* The bandit of every tree node (cpp/include/search/bandit/*.h; strings of cpp/src/search.cc:236-300): kind 0 "ucb-<c>"
+ * (the default, with the c passed to oakb200_search_run), 1 "ucb1-<c>", 2 "pucb-<c>", 3 "exp3-<gamma>-<alpha>", 4
+ * "pexp3-<gamma>-<alpha>"; f1 = c or gamma, f2 = alpha (ignored by the UCB family; the reference's default is 0.05). pucb and
+ * pexp3 are primed with the network's policy logits at the root and at every new leaf (mcts.h:190-209,409-421): they need a
+ * loaded network and leaf mode 1. Resets the trees of roots already set. Not built: root matrix-UCB (mcts.h:498-566). */
+int oakb200_search_set_bandit(oakb200_search* search, int kind, float f1, float f2);
 /* Leaf evaluation of the search: 0 = MonteCarlo playout (default), 1 = the loaded network's value (value_inference at a new
  * leaf, mcts.h:409-424, with the chance durations tracked down the path; a battle that ended on the way scores 1 / 0 /
  * 0.5). Mode 1 needs oakb200_net_load[_discrete] first; all leaves of a wave are one batched evaluation. */

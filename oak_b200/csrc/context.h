@@ -30,6 +30,7 @@ struct oakb200_ctx {
   uint32_t* steps = nullptr;
   uint8_t* teams = nullptr;
   uint32_t* ticket = nullptr;
+  int rollout_cta_cap = 0;  // > 0: at most this many rollout CTAs per SM (search.cu leaves room for its level kernels)
   int ticket_slot = 0;  // which of the 64 ticket words a rollout launch uses (search.cu runs rollouts on several streams)
   unsigned long long* total_steps = nullptr;
   uint64_t launches = 0;

@@ -77,6 +77,7 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, tile_bytes);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
+  if (ctx->rollout_cta_cap > 0 && per_sm > ctx->rollout_cta_cap) per_sm = ctx->rollout_cta_cap;
   // persistent grid: exactly the resident CTAs of the chip (a multiple of the SM count), never more
   // CTAs than there is work
   unsigned grid = (unsigned)(ctx->sm_count * per_sm);

@@ -1,8 +1,8 @@
 // Batched-leaf tree search: host trees, GPU transitions and leaves (BASELINE configs[3]).
 //
 // Reference algorithm: MCTS::Search::{run, run_root_iteration, run_iteration, init_stats_and_rollout}
-// (cpp/include/search/mcts.h:154-496) with the joint UCB bandit (cpp/include/search/bandit/ucb.h:15-71,
-// cpp/include/search/joint.h) on a Node heap keyed by (p1 index, p2 index, 16-byte chance observation)
+// (cpp/include/search/mcts.h:154-496) with its joint bandits (cpp/include/search/bandit/{ucb,ucb1,pucb,exp3,pexp3}.h,
+// cpp/include/search/joint.h; the contextual ones primed with the network's policy logits, mcts.h:190-209,409-421) on a Node heap keyed by (p1 index, p2 index, 16-byte chance observation)
 // (mcts.h:93-99,355-361), MonteCarlo evaluation, Search::battle_options_set's clamped damage rolls
 // (mcts.h:569-604; default_search = {root_rolls 3, other_rolls 1}, mcts.h:133).
 //
@@ -16,7 +16,9 @@
 //
 // Random streams (the reference draws them from one std::mt19937 per thread, cpp/include/util/random.h): for root
 // seed s and that root's n-th iteration, battle rng = splitmix64(s ^ K * (2n + 1)), playout seed =
-// splitmix64(s ^ K * (2n + 2)), K = 0xD1B54A32D192ED03; the playout then picks as oakb200_rollout does.
+// splitmix64(s ^ K * (2n + 2)), K = 0xD1B54A32D192ED03; the playout then picks as oakb200_rollout does; the Exp3 family's
+// selection at depth d for player q draws u = (splitmix64(s ^ K(2n+1) ^ 0x9FB21C651E98DF25 (2d + q + 1)) >> 11) 2^-53.
+// Not built: the root matrix-UCB variant (mcts.h:498-566), which needs the LRSNash solver inside the iteration loop.
 #include <cuda_runtime.h>
 
 #include <atomic>
@@ -43,67 +45,197 @@ uint64_t splitmix64(uint64_t x) {
 }
 const uint64_t STREAM_K = 0xD1B54A32D192ED03ull;
 
-// UCB::Bandit (ucb.h:15-66)
+// The reference's bandits (cpp/include/search/bandit/{ucb,ucb1,pucb,exp3,pexp3}.h) as one record with the algorithm as
+// data: the trees of one search all use the same one. a[] = scores (UCB family) or gains (Exp3 family).
+enum BanditKind { B_UCB = 0, B_UCB1 = 1, B_PUCB = 2, B_EXP3 = 3, B_PEXP3 = 4 };
+struct BanditParams {
+  int kind = B_UCB;
+  float c = 1.0f;                  // UCB / UCB1 / PUCB
+  float gamma = 1.0f, alpha = 0.05f;  // Exp3 / PExp3 (cpp/src/search.cc:279-300)
+  bool contextual() const { return kind == B_PUCB || kind == B_PEXP3; }
+  bool counts_visits() const { return kind <= B_PUCB; }
+};
 struct Bandit {
-  float scores[9];
+  float a[9];
   uint32_t visits[9];
   uint8_t k = 0;
-  void init(int n) {
+  // PUCB's priors live in Root::priors (one float[18] per node, allocated only for the contextual kinds)
+  void init(int n, const BanditParams& bp, float* priors) {
     k = (uint8_t)n;
-    for (int i = 0; i < n; i++) {
-      scores[i] = 0.5f;
-      visits[i] = 1;
+    switch (bp.kind) {
+      case B_UCB: case B_PUCB:  // ucb.h:28-32, pucb.h:30-34
+        for (int i = 0; i < n; i++) { a[i] = 0.5f; visits[i] = 1; }
+        if (bp.kind == B_PUCB)
+          for (int i = 0; i < n; i++) priors[i] = 1.0f / n;  // until the leaf evaluation of this node arrives
+        break;
+      case B_UCB1:  // ucb1.h:31-35
+        for (int i = 0; i < n; i++) { a[i] = 0.0f; visits[i] = 0; }
+        break;
+      default:  // exp3.h:36-40
+        for (int i = 0; i < 9; i++) a[i] = i < n ? 0.0f : -INFINITY;
+        break;
     }
   }
-  int select(float c) const {
+  // softmax_logits: pucb.h:38-40 (priors = softmax of the legal logits), pexp3.h:44-48 (gains = logits / eta)
+  void set_logits(const float* logits, const BanditParams& bp, float* priors) {
+    if (bp.kind == B_PUCB) {
+      float sum = 0;
+      for (int i = 0; i < k; i++) { priors[i] = std::exp(logits[i]); sum += priors[i]; }
+      for (int i = 0; i < k; i++) priors[i] /= sum;
+    } else if (bp.kind == B_PEXP3) {
+      const float eta = bp.gamma / k;
+      for (int i = 0; i < k; i++) a[i] = logits[i] / eta;
+    }
+  }
+  // u: the uniform draw of this selection (Exp3 family only); *prob: probability of the selected arm (Exp3 family)
+  int select(const BanditParams& bp, double u, float* prob, const float* priors) const {
+    *prob = 1.0f;
     if (k == 1) return 0;
-    uint64_t N = 0;
-    for (int i = 0; i < k; i++) N += visits[i];
-    const float sqrtN = (float)std::sqrt((double)N);
-    float max = 0;
     int index = 0;
-    for (int i = 0; i < k; i++) {
-      const float e = c * sqrtN / k;
-      const float a = (e + scores[i]) / visits[i];
-      if (a > max) {
-        max = a;
-        index = i;
+    if (bp.kind == B_UCB || bp.kind == B_PUCB) {  // ucb.h:41-61, pucb.h:47-67
+      uint64_t N = 0;
+      for (int i = 0; i < k; i++) N += visits[i];
+      const float sqrtN = (float)std::sqrt((double)N);
+      // the same operations in the same order as the reference, arm by arm; values first (a loop the compiler
+      // vectorises), then the first maximum
+      float v[9];
+      if (bp.kind == B_UCB) {
+        const float e = bp.c * sqrtN / k;
+        for (int i = 0; i < k; i++) v[i] = (e + a[i]) / (float)visits[i];
+      } else {
+        for (int i = 0; i < k; i++) v[i] = (bp.c * priors[i] * sqrtN + a[i]) / (float)visits[i];
       }
+      float max = 0;
+      for (int i = 0; i < k; i++)
+        if (v[i] > max) { max = v[i]; index = i; }
+    } else if (bp.kind == B_UCB1) {  // ucb1.h:44-71
+      float q[9];
+      uint64_t N = 0;
+      for (int i = k - 1; i >= 0; --i) {
+        if (visits[i] == 0) return i;
+        q[i] = a[i] / visits[i];
+        N += visits[i];
+      }
+      const float lnN = std::log((float)N);
+      float max = 0;
+      for (int i = 0; i < k; i++) {
+        const float v = std::sqrt(bp.c * lnN / visits[i]) + q[i];
+        if (v > max) { max = v; index = i; }
+      }
+    } else {  // exp3.h:44-61, pexp3.h:50-67; softmax over all nine gains (the unused ones are -inf), util/softmax.h:17-27
+      const float eta = bp.gamma / k, delta = bp.alpha / k;
+      float policy[9], sum = 0;
+      for (int i = 0; i < 9; i++) { policy[i] = std::exp(a[i] * eta); sum += policy[i]; }
+      for (int i = 0; i < 9; i++) policy[i] = (1.0f - bp.alpha) * (policy[i] / sum) + delta;
+      double p = u;  // sample_pdf, util/random.h:39-49
+      for (int i = 0; i < 9; i++) {
+        p -= (double)policy[i];
+        if (p <= 0) { index = i; break; }
+      }
+      if (index > k - 1) index = k - 1;
+      *prob = policy[index];
     }
     return index;
   }
+  void update(int index, float value, float prob, const BanditParams& bp) {
+    if (bp.counts_visits()) {  // the visit itself was counted at selection (virtual visit)
+      a[index] += value;
+    } else if ((a[index] += (value - 0.5f) / prob) > 0) {  // exp3.h:63-70
+      const float max = a[index];
+      for (int i = 0; i < 9; i++) a[i] -= max;
+    }
+  }
 };
 
-struct Child {
-  uint8_t i, j;
-  uint8_t obs[16];
-  int32_t node;
-};
+// One tree per root, nodes in one arena; a child is found through an open-addressed table keyed by
+// (parent, p1 index, p2 index, 16-byte chance observation) — the reference's std::map key (mcts.h:93-99,355-361).
 struct Node {
   Bandit p1, p2;
-  std::vector<Child> children;
+  int32_t parent = -1;
+  uint8_t i = 0, j = 0;
+  uint8_t obs[16] = {0};
   bool is_init() const { return p1.k != 0; }
 };
 struct PathEntry {
   int32_t node;
   uint8_t i, j;
+  float prob1, prob2;
 };
 
 struct Root {
-  std::vector<Node> nodes;  // nodes[0] = root
+  std::vector<Node> nodes;     // nodes[0] = root
+  std::vector<float> priors;   // contextual bandits only: [node][player][9]
+  std::vector<int32_t> table;  // open addressing, -1 = empty; size a power of two > 2 x nodes
+  float* pri(int32_t node, int player) { return priors.empty() ? nullptr : priors.data() + ((size_t)node * 2 + player) * 9; }
+  // back to an empty tree over the same arenas (their pages stay mapped: a search object is reused turn after turn)
+  void reset(const BanditParams& bp) {
+    nodes.clear();
+    priors.clear();
+    std::fill(table.begin(), table.end(), -1);
+    nodes.emplace_back();
+    if (bp.contextual()) priors.resize(18);
+    nodes[0].p1.init(k1, bp, pri(0, 0));
+    nodes[0].p2.init(k2, bp, pri(0, 1));
+    memset(visit, 0, sizeof(visit));
+    memset(value, 0, sizeof(value));
+    iterations = target = total_depth = 0;
+  }
+  std::vector<PathEntry> path; // [level][particle] of the wave in flight
   uint8_t k1 = 0, k2 = 0;
   uint8_t choices[18] = {0};
   uint32_t visit[81] = {0};
   double value[81] = {0};
-  uint64_t iterations = 0;
+  uint64_t iterations = 0, target = 0;
   uint64_t seed = 0;
   uint64_t total_depth = 0;
+
+  static uint64_t key_hash(int32_t parent, uint8_t i, uint8_t j, const uint8_t* obs) {
+    uint64_t a, b;
+    memcpy(&a, obs, 8);
+    memcpy(&b, obs + 8, 8);
+    uint64_t h = (uint64_t)(uint32_t)parent * 0x9E3779B97F4A7C15ull + i * 0x100000001B3ull + j * 0xD6E8FEB86659FD93ull;
+    h ^= a * 0xBF58476D1CE4E5B9ull;
+    h = (h << 31) | (h >> 33);
+    h ^= b * 0x94D049BB133111EBull;
+    return h ^ (h >> 29);
+  }
+  void rehash(size_t size) {
+    table.assign(size, -1);
+    for (size_t n = 1; n < nodes.size(); n++) {
+      size_t at = key_hash(nodes[n].parent, nodes[n].i, nodes[n].j, nodes[n].obs) & (size - 1);
+      while (table[at] >= 0) at = (at + 1) & (size - 1);
+      table[at] = (int32_t)n;
+    }
+  }
+  // the child of `parent` along (i, j, obs), created if new
+  int32_t child(int32_t parent, uint8_t i, uint8_t j, const uint8_t* obs) {
+    if (table.size() < 2 * (nodes.size() + 1)) rehash(table.empty() ? 256 : table.size() * 2);
+    const size_t mask = table.size() - 1;
+    size_t at = key_hash(parent, i, j, obs) & mask;
+    for (;; at = (at + 1) & mask) {
+      const int32_t n = table[at];
+      if (n < 0) break;
+      const Node& c = nodes[n];
+      if (c.parent == parent && c.i == i && c.j == j && memcmp(c.obs, obs, 16) == 0) return n;
+    }
+    const int32_t n = (int32_t)nodes.size();
+    nodes.emplace_back();
+    if (!priors.empty()) priors.resize(priors.size() + 18);
+    Node& c = nodes.back();
+    c.parent = parent;
+    c.i = i;
+    c.j = j;
+    memcpy(c.obs, obs, 16);
+    table[at] = n;
+    return n;
+  }
 };
 
 struct Particle {
   int32_t cur = 0;
-  bool active = false;
-  std::vector<PathEntry> path;
+  int32_t fresh = -1;     // the node this descent initialised (its priors arrive with the leaf evaluation)
+  uint16_t len = 0;       // path entries
+  bool active = false, spawned = false;
 };
 
 // persistent worker pool: parallel_for over roots
@@ -191,8 +323,11 @@ struct oakb200_search {
   uint64_t *d_rng = nullptr, *d_pseed = nullptr;
   // network leaves
   int leaf_mode = 0;  // 0 MonteCarlo playout, 1 network value
-  float *d_value = nullptr, *d_logits = nullptr, *h_value = nullptr;
+  float *d_value = nullptr, *d_logits = nullptr, *h_value = nullptr, *h_logits = nullptr;
   uint8_t* d_ecnt = nullptr;
+  BanditParams bandit;
+  bool bandit_set = false;   // false: joint UCB with the c given to oakb200_search_run
+  bool root_primed = false;  // contextual bandits: the roots' priors have been evaluated (mcts.h:190-209)
   // pinned host mirrors
   uint8_t *h_idx1 = nullptr, *h_idx2 = nullptr, *h_rolls = nullptr, *h_res = nullptr, *h_act = nullptr, *h_cnt = nullptr, *h_score = nullptr;
   uint64_t *h_rng = nullptr, *h_pseed = nullptr;
@@ -210,7 +345,7 @@ void search_free(oakb200_search* s) {
                  s->d_score, s->d_rng, s->d_pseed, s->d_value, s->d_logits, s->d_ecnt};
   for (void* p : dev)
     if (p) cudaFree(p);
-  void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed, s->h_value};
+  void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed, s->h_value, s->h_logits};
   for (void* p : host)
     if (p) cudaFreeHost(p);
   delete s->pool;
@@ -274,7 +409,7 @@ int oakb200_search_set_roots(oakb200_search* s, size_t n, const uint8_t* battles
   CU(ctx, cudaMemcpyAsync(cnt.data(), s->d_cnt, n * 2, cudaMemcpyDeviceToHost, ctx->stream));
   CU(ctx, cudaStreamSynchronize(ctx->stream));
   s->n_roots = n;
-  s->roots.assign(n, Root());
+  if (s->roots.size() < n) s->roots.resize(n);  // the roots' arenas (nodes, table, paths) are kept from search to search
   for (size_t r = 0; r < n; r++) {
     if ((results[r] & 15u) != 0) return fail(ctx, OAKB200_EINVAL, "search_set_roots: a root battle is already over");
     Root& R = s->roots[r];
@@ -282,11 +417,28 @@ int oakb200_search_set_roots(oakb200_search* s, size_t n, const uint8_t* battles
     R.k1 = cnt[2 * r];
     R.k2 = cnt[2 * r + 1];
     memcpy(R.choices, ch.data() + 18 * r, 18);
-    R.nodes.reserve(1024);
-    R.nodes.emplace_back();
-    R.nodes[0].p1.init(R.k1);
-    R.nodes[0].p2.init(R.k2);
+    if (R.nodes.capacity() < 256) R.nodes.reserve(256);
+    R.reset(s->bandit);
   }
+  s->root_primed = false;
+  return OAKB200_OK;
+}
+
+// Which bandit the trees use (cpp/src/search.cc:236-300: "ucb-<c>", "ucb1-<c>", "pucb-<c>", "exp3-<gamma>[-<alpha>]",
+// "pexp3-<gamma>[-<alpha>]"): kind 0..4 in that order, f1 = c or gamma, f2 = alpha (Exp3 family; the reference's default is
+// 0.05). The contextual ones (pucb, pexp3) take their priors from the network's policy head at the root and at every new
+// leaf (mcts.h:190-209,409-421), so they need leaf mode 1. Resets the trees of roots already set.
+int oakb200_search_set_bandit(oakb200_search* s, int kind, float f1, float f2) {
+  if (!s) return OAKB200_EINVAL;
+  oakb200_ctx* ctx = s->ctx;
+  if (kind < B_UCB || kind > B_PEXP3 || !(f1 > 0) || (kind >= B_EXP3 && !(f2 >= 0 && f2 < 1)))
+    return fail(ctx, OAKB200_EINVAL, "search_set_bandit: kind 0..4 (ucb, ucb1, pucb, exp3, pexp3), f1 > 0, 0 <= alpha < 1");
+  s->bandit.kind = kind;
+  s->bandit.c = s->bandit.gamma = f1;
+  s->bandit.alpha = f2;
+  s->bandit_set = true;
+  s->root_primed = false;
+  for (size_t r = 0; r < s->n_roots; r++) s->roots[r].reset(s->bandit);
   return OAKB200_OK;
 }
 
@@ -315,24 +467,50 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
   const uint32_t P = s->P;
   const size_t R = s->n_roots;
   const uint32_t MAX_DEPTH = 100;  // mcts.h:309
+  if (iterations == 0) return OAKB200_OK;
   const uint32_t waves = (iterations + P - 1) / P;
-  if (waves == 0) return OAKB200_OK;
+  if (!s->bandit_set) {
+    s->bandit.kind = B_UCB;
+    s->bandit.c = ucb_c;
+  }
+  const BanditParams bp = s->bandit;
+  if (bp.contextual() && s->leaf_mode != 1)
+    return fail(ctx, OAKB200_EINVAL, "search_run: pucb / pexp3 take their priors from the network: oakb200_search_set_leaf(search, 1) first");
+  // exactly `iterations` more per root (the reference runs its budget to the iteration, mcts.h:237-241): the last wave
+  // spawns only what is left
+  for (size_t r = 0; r < R; r++) s->roots[r].target = s->roots[r].iterations + iterations;
 
-  // The roots are cut into groups that take turns: while the device runs one group's kernels (a tree level, or the
-  // playouts, which are most of a wave's device time) the host threads select / expand / back-propagate in another
-  // group's trees. Each group has its own stream and walks the same per-wave phases; a group's next host phase starts
-  // by waiting for that group's stream only. Trees of different roots never interact and every random stream is a
-  // function of (root seed, iteration), so the grouping does not change any result.
+  // contextual bandits: the root's priors from one batched evaluation of the root positions (mcts.h:190-209)
+  if (bp.contextual() && !s->root_primed) {
+    int rc = oakb200_eval_device(ctx, R, s->d_root_b, s->d_root_d, s->d_root_r, s->d_value, s->d_logits, s->d_ecnt);
+    if (rc) return rc;
+    CU(ctx, cudaMemcpyAsync(s->h_logits, s->d_logits, R * 18 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t r = 0; r < R; r++) {
+      s->roots[r].nodes[0].p1.set_logits(s->h_logits + 18 * r, bp, s->roots[r].pri(0, 0));
+      s->roots[r].nodes[0].p2.set_logits(s->h_logits + 18 * r + 9, bp, s->roots[r].pri(0, 1));
+    }
+    s->root_primed = true;
+  }
+
+  // The roots are cut into groups, each with its own stream and its own position in the per-wave phases (spawn, then per
+  // tree level select -> device step -> expand, then the leaves, then back-propagation). The scheduler below advances
+  // whichever group's device work has finished: while the device runs one group's kernels the host threads select /
+  // expand / back-propagate in another group's trees, and one group's level kernels run on the SMs another group's
+  // playout launch frees in its tail. Trees of different roots never interact and every random stream is a function of
+  // (root seed, iteration), so the grouping does not change any result.
   struct Group {
     size_t r0, r1;           // roots [r0, r1)
     cudaStream_t stream;
     uint32_t wave = 0, depth = 0;
     int phase = 0;           // 0 spawn, 1 select + step, 2 expand, 3 back-propagate, 4 finished
+    bool reached_leaves = false;  // has launched a leaf phase at least once (the next group starts then: see below)
   };
-  // Measured on B200, 4 096 roots x 64 (tools/bench_search.py): 1 group 8.14 M iterations/s, 2 groups 8.82 M, 3 groups 7.8 M,
-  // 4 groups 7.1 M. The gain is small because a wave's device time is almost all playouts, a persistent kernel that
-  // holds every SM until it ends: another group's tree levels cannot run beside it, only its host phases can.
-  int n_groups = 2;
+  // Measured on B200, 4 096 roots x 64 (tools/search_timeline.py): groups that start together stay in lockstep — all of
+  // them in the host-bound tree levels, then all of them waiting for their playouts — so group g + 1 starts its first wave
+  // only when group g has launched its first leaves, and from then on one group's leaves run under another's tree levels.
+  // 4 096 roots x 64, 16 waves on B200 + 16 host threads: 1 group 9.05 M iterations/s, 2: 8.7, 3: 9.9, 4: 10.8, 6: 9.6
+  int n_groups = 4;
   if (const char* g = getenv("OAKB200_SEARCH_GROUPS")) n_groups = atoi(g);
   if (n_groups < 1) n_groups = 1;
   if (n_groups > 8) n_groups = 8;
@@ -348,22 +526,32 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
   if (n_groups > 1) CU(ctx, cudaStreamSynchronize(ctx->stream));  // set_roots' uploads are on the context's stream
   cudaStream_t saved_stream = ctx->stream;
   const int saved_slot = ctx->ticket_slot;
+  const int saved_cap = ctx->rollout_cta_cap;
+  // a playout launch that takes every CTA slot of every SM would hold back the other groups' small level kernels for its
+  // whole body: leave room for them
+  if (n_groups > 1) {
+    ctx->rollout_cta_cap = 6;
+    if (const char* c = getenv("OAKB200_SEARCH_ROLLOUT_CTAS")) ctx->rollout_cta_cap = atoi(c);
+  }
   int rc_out = OAKB200_OK;
   auto fail_cuda = [&](cudaError_t e, const char* what) {
     if (e != cudaSuccess && rc_out == OAKB200_OK) rc_out = fail(ctx, OAKB200_ECUDA, what, e);
     return e != cudaSuccess;
   };
+  // the uniform draw of one Exp3-family selection: a function of (root seed, iteration, depth, player)
+  auto exp3_u = [](uint64_t seed, uint64_t nth, uint32_t depth, int player) {
+    const uint64_t x = splitmix64(seed ^ (STREAM_K * (2 * nth + 1)) ^ (0x9FB21C651E98DF25ull * (2 * (uint64_t)depth + player + 1)));
+    return (double)(x >> 11) * (1.0 / 9007199254740992.0);
+  };
 
-  long long wait_ns = 0, host_ns = 0;  // diagnostics: OAKB200_SEARCH_DEBUG=1 prints them
-  // one host phase of group G (after its previous device work has finished) + the device work that follows it
+  long long host_ns = 0, idle_ns = 0;  // diagnostics: OAKB200_SEARCH_DEBUG=1 prints them
+  // one host phase of group G (its previous device work has finished) + the device work that follows it
   auto advance = [&](Group& G, int gi) {
     const size_t r0 = G.r0, nr = G.r1 - G.r0, b0 = r0 * P, nb = nr * P;
     ctx->stream = G.stream;
     ctx->ticket_slot = 8 + gi;
-    const auto t_wait = std::chrono::steady_clock::now();
     if (fail_cuda(cudaStreamSynchronize(G.stream), "search_run: stream")) return;
     const auto t_host = std::chrono::steady_clock::now();
-    wait_ns += (t_host - t_wait).count();
     struct HostTimer {
       std::chrono::steady_clock::time_point t0;
       long long& acc;
@@ -374,6 +562,7 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
+        const uint64_t left = root.target - root.iterations;
         for (uint32_t p = 0; p < P; p++) {
           const size_t b = r * P + p;
           const uint64_t nth = root.iterations + p;
@@ -381,8 +570,9 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
           s->h_pseed[b] = splitmix64(root.seed ^ (STREAM_K * (2 * nth + 2)));
           Particle& q = s->particles[b];
           q.cur = 0;
-          q.active = true;
-          q.path.clear();
+          q.fresh = -1;
+          q.len = 0;
+          q.active = q.spawned = p < left;
         }
       });
       if (fail_cuda(cudaMemcpyAsync(s->d_rng + b0, s->h_rng + b0, nb * 8, cudaMemcpyHostToDevice, G.stream), "search_run: copy")) return;
@@ -401,35 +591,21 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
+        const PathEntry* level = root.path.data() + (size_t)depth * P;
         for (uint32_t p = 0; p < P; p++) {
           const size_t b = r * P + p;
           Particle& q = s->particles[b];
           if (!q.active) continue;
-          const PathEntry& pe = q.path.back();
-          const uint8_t* obs = s->h_act + b * 16;
-          int32_t child = -1;
-          for (const Child& c : root.nodes[pe.node].children)
-            if (c.i == pe.i && c.j == pe.j && memcmp(c.obs, obs, 16) == 0) {
-              child = c.node;
-              break;
-            }
-          if (child < 0) {
-            child = (int32_t)root.nodes.size();
-            root.nodes.emplace_back();
-            Child c;
-            c.i = pe.i;
-            c.j = pe.j;
-            memcpy(c.obs, obs, 16);
-            c.node = child;
-            root.nodes[pe.node].children.push_back(c);
-          }
+          const PathEntry& pe = level[p];
+          const int32_t child = root.child(pe.node, pe.i, pe.j, s->h_act + b * 16);
           q.cur = child;
           Node& cn = root.nodes[child];
           const bool over = (s->h_res[b] & 15u) != 0;
           if (cn.is_init() && !over) continue;  // keep descending (mcts.h:328)
-          if (!over) {                           // new leaf: init its bandits, then a playout (mcts.h:399, :463-465)
-            cn.p1.init(s->h_cnt[2 * b]);
-            cn.p2.init(s->h_cnt[2 * b + 1]);
+          if (!over) {                           // new leaf: init its bandits, then evaluate it (mcts.h:399-424, :463-465)
+            cn.p1.init(s->h_cnt[2 * b], bp, root.pri(child, 0));
+            cn.p2.init(s->h_cnt[2 * b + 1], bp, root.pri(child, 1));
+            q.fresh = child;
           }
           root.total_depth += depth + 1;
           q.active = false;
@@ -445,6 +621,8 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
+        if (root.path.size() < (size_t)(depth + 1) * P) root.path.resize((size_t)(depth + 1) * P);
+        PathEntry* level = root.path.data() + (size_t)depth * P;
         size_t cnt = 0;
         for (uint32_t p = 0; p < P; p++) {
           const size_t b = r * P + p;
@@ -455,10 +633,22 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
             continue;
           }
           Node& node = root.nodes[q.cur];
-          const int i = node.p1.select(ucb_c), j = node.p2.select(ucb_c);
-          node.p1.visits[i]++;  // the visit is counted now (virtual visit), the value at back-propagation
-          node.p2.visits[j]++;
-          q.path.push_back({q.cur, (uint8_t)i, (uint8_t)j});
+          double u1 = 0, u2 = 0;
+          if (!bp.counts_visits()) {
+            const uint64_t nth = root.iterations + p;
+            u1 = exp3_u(root.seed, nth, depth, 0);
+            u2 = exp3_u(root.seed, nth, depth, 1);
+          }
+          PathEntry& pe = level[p];
+          const int i = node.p1.select(bp, u1, &pe.prob1, root.pri(q.cur, 0)), j = node.p2.select(bp, u2, &pe.prob2, root.pri(q.cur, 1));
+          if (bp.counts_visits()) {  // the visit is counted now (virtual visit), the value at back-propagation
+            node.p1.visits[i]++;
+            node.p2.visits[j]++;
+          }
+          pe.node = q.cur;
+          pe.i = (uint8_t)i;
+          pe.j = (uint8_t)j;
+          q.len = (uint16_t)(depth + 1);
           s->h_idx1[b] = (uint8_t)i;
           s->h_idx2[b] = (uint8_t)j;
           s->h_rolls[b] = (uint8_t)(depth == 0 ? root_rolls : other_rolls);
@@ -482,14 +672,19 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       }
       // ---- every descent of the group has reached a leaf
       if (s->leaf_mode == 1) {
-        // the network's value of every leaf (mcts.h:409-424: UCB is not a contextual bandit, so value_inference) with
-        // the durations tracked down the path; a finished battle's score replaces it at back-propagation
+        // the network's value of every leaf (mcts.h:409-424) with the durations tracked down the path, and for the
+        // contextual bandits its policy logits over the leaf's legal choices; a finished battle's score replaces the
+        // value at back-propagation
         const int rc = oakb200_eval_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_value + b0, s->d_logits + b0 * 18,
                                            s->d_ecnt + b0 * 2);
         if (rc) { rc_out = rc; return; }
         if (fail_cuda(cudaMemcpyAsync(s->h_value + b0, s->d_value + b0, nb * 4, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
         if (fail_cuda(cudaMemcpyAsync(s->h_res + b0, s->d_r + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
+        if (bp.contextual() &&
+            fail_cuda(cudaMemcpyAsync(s->h_logits + b0 * 18, s->d_logits + b0 * 18, nb * 18 * 4, cudaMemcpyDeviceToHost, G.stream), "search_run: copy"))
+          return;
         G.phase = 3;
+        G.reached_leaves = true;
         return;
       }
       // playouts (a finished battle returns its score at once)
@@ -498,32 +693,40 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       if (rc) { rc_out = rc; return; }
       if (fail_cuda(cudaMemcpyAsync(s->h_score + b0, s->d_score + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
       G.phase = 3;
+      G.reached_leaves = true;
       return;
     }
     if (G.phase == 3) {
-      // ---- back-propagation (mcts.h:363-384)
+      // ---- back-propagation (mcts.h:363-384), particle by particle in index order
       s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
         for (uint32_t p = 0; p < P; p++) {
           const size_t b = r * P + p;
+          const Particle& q = s->particles[b];
+          if (!q.spawned) continue;
           float v1;
           if (s->leaf_mode == 1) {
             const uint32_t t = s->h_res[b] & 15u;
             v1 = t == 0 ? s->h_value[b] : (t == 1 ? 1.0f : (t == 2 ? 0.0f : 0.5f));
+            if (bp.contextual() && q.fresh >= 0 && t == 0) {  // stats.softmax_logits at the new leaf (mcts.h:415-421)
+              root.nodes[q.fresh].p1.set_logits(s->h_logits + b * 18, bp, root.pri(q.fresh, 0));
+              root.nodes[q.fresh].p2.set_logits(s->h_logits + b * 18 + 9, bp, root.pri(q.fresh, 1));
+            }
           } else {
             v1 = (float)s->h_score[b] * 0.5f;
           }
           const float v2 = 1.0f - v1;
-          const Particle& q = s->particles[b];
-          for (const PathEntry& pe : q.path) {
+          for (int lv = (int)q.len - 1; lv >= 0; lv--) {  // deepest first, as the recursion unwinds
+            const PathEntry& pe = root.path[(size_t)lv * P + p];
             Node& node = root.nodes[pe.node];
-            node.p1.scores[pe.i] += v1;
-            node.p2.scores[pe.j] += v2;
+            node.p1.update(pe.i, v1, pe.prob1, bp);
+            node.p2.update(pe.j, v2, pe.prob2, bp);
           }
-          if (!q.path.empty()) {
-            root.visit[q.path[0].i * 9 + q.path[0].j]++;
-            root.value[q.path[0].i * 9 + q.path[0].j] += v1;
+          if (q.len) {
+            const PathEntry& pe = root.path[p];
+            root.visit[pe.i * 9 + pe.j]++;
+            root.value[pe.i * 9 + pe.j] += v1;
           }
           root.iterations++;
         }
@@ -534,20 +737,49 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     }
   };
 
-  for (;;) {
-    bool any = false;
+  // OAKB200_SEARCH_DEBUG=2: a timeline of (start ms, end ms, group, phase entered) for every host phase
+  struct Trace { double t0, t1; int g, phase; };
+  std::vector<Trace> trace;
+  const bool tracing = getenv("OAKB200_SEARCH_DEBUG") && atoi(getenv("OAKB200_SEARCH_DEBUG")) >= 2;
+  const auto t_begin = std::chrono::steady_clock::now();
+  auto ms_now = [&] { return (std::chrono::steady_clock::now() - t_begin).count() * 1e-6; };
+  // scheduler: advance any group whose stream has drained; when none has, wait for one
+  int live = n_groups;
+  while (live > 0 && rc_out == OAKB200_OK) {
+    bool progressed = false;
     for (int g = 0; g < n_groups && rc_out == OAKB200_OK; g++) {
-      if (groups[g].phase == 4) continue;
-      any = true;
-      advance(groups[g], g);
+      Group& G = groups[g];
+      if (G.phase == 4) continue;
+      if (g > 0 && G.wave == 0 && G.phase == 0 && !groups[g - 1].reached_leaves && groups[g - 1].phase != 4) continue;  // stagger
+      const cudaError_t q = cudaStreamQuery(G.stream);
+      if (q == cudaErrorNotReady) continue;
+      if (fail_cuda(q, "search_run: stream")) break;
+      const double t0 = tracing ? ms_now() : 0;
+      const int ph = G.phase;
+      advance(G, g);
+      if (tracing) trace.push_back({t0, ms_now(), g, ph});
+      progressed = true;
+      if (G.phase == 4) live--;
     }
-    if (!any || rc_out != OAKB200_OK) break;
+    if (!progressed && live > 0) {
+      const auto t0 = std::chrono::steady_clock::now();
+      std::this_thread::yield();
+      idle_ns += (std::chrono::steady_clock::now() - t0).count();
+    }
   }
   ctx->stream = saved_stream;
   ctx->ticket_slot = saved_slot;
+  ctx->rollout_cta_cap = saved_cap;
   if (getenv("OAKB200_SEARCH_DEBUG"))
-    fprintf(stderr, "[oakb200] search_run: %u waves x %d groups, host phases %.1f ms, waiting for the device %.1f ms\n", waves, n_groups,
-            host_ns * 1e-6, wait_ns * 1e-6);
+    fprintf(stderr, "[oakb200] search_run: %u waves x %d groups, host phases %.1f ms, idle (every group on the device) %.1f ms\n", waves,
+            n_groups, host_ns * 1e-6, idle_ns * 1e-6);
+  if (tracing) {
+    const double total = ms_now();
+    fprintf(stderr, "[oakb200] timeline of the last wave (ms from run start; total %.2f):\n", total);
+    size_t from = trace.size() > (size_t)(14 * n_groups) ? trace.size() - 14 * n_groups : 0;
+    for (size_t k = from; k < trace.size(); k++)
+      fprintf(stderr, "  g%d phase %d  %8.2f -> %8.2f  (%.2f)\n", trace[k].g, trace[k].phase, trace[k].t0, trace[k].t1, trace[k].t1 - trace[k].t0);
+  }
   if (n_groups > 1)
     for (auto& G : groups) {
       cudaStreamSynchronize(G.stream);
@@ -683,6 +915,7 @@ int oakb200_search_set_leaf(oakb200_search* s, int mode) {
       CU(ctx, cudaMalloc(&s->d_logits, B * 18 * 4));
       CU(ctx, cudaMalloc(&s->d_ecnt, B * 2));
       CU(ctx, cudaMallocHost(&s->h_value, B * 4));
+      CU(ctx, cudaMallocHost(&s->h_logits, B * 18 * 4));
     }
   }
   s->leaf_mode = mode;

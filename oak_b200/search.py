@@ -52,6 +52,21 @@ class TreeSearch:
         self._check(self.lib.oakb200_search_set_roots(self._h, n, _ptr(battles), _ptr(durations), _ptr(results), _ptr(seeds)))
         self.n = n
 
+    BANDITS = {"ucb": 0, "ucb1": 1, "pucb": 2, "exp3": 3, "pexp3": 4}
+
+    def set_bandit(self, spec):
+        """The reference's bandit strings (cpp/src/search.cc:236-300): "ucb-<c>", "ucb1-<c>", "pucb-<c>", "exp3-<gamma>[-<alpha>]",
+        "pexp3-<gamma>[-<alpha>]". pucb / pexp3 need set_leaf(1) (their priors are the network's policy)."""
+        parts = spec.split("-")
+        if len(parts) < 2 or parts[0] not in self.BANDITS:
+            raise ValueError(f"Could not parse bandit string: {spec}")
+        f1 = float(parts[1])
+        f2 = float(parts[2]) if len(parts) >= 3 else 0.05
+        fn = self.lib.oakb200_search_set_bandit
+        fn.restype = ctypes.c_int
+        fn.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_float]
+        self._check(fn(self._h, self.BANDITS[parts[0]], f1, f2))
+
     def run(self, iterations, c=1.0, root_rolls=3, other_rolls=1, host_threads=0):
         self._check(self.lib.oakb200_search_run(self._h, int(iterations), float(c), int(root_rolls), int(other_rolls), int(host_threads)))
 

@@ -26,35 +26,111 @@ namespace mcts_oracle {
 
 using namespace oracle;
 
+// The five bandits of cpp/include/search/bandit/: ucb.h:15-66, ucb1.h:15-75, pucb.h:15-78, exp3.h:17-75, pexp3.h:17-82.
+enum Kind { K_UCB = 0, K_UCB1 = 1, K_PUCB = 2, K_EXP3 = 3, K_PEXP3 = 4 };
+struct Params {
+  int kind = K_UCB;
+  float c = 1.0f, gamma = 1.0f, alpha = 0.05f;
+};
 struct Bandit {
-  std::array<float, 9> scores{};
+  std::array<float, 9> scores{};  // gains for the Exp3 family
+  std::array<float, 9> priors{};
   std::array<uint32_t, 9> visits{};
   uint8_t k = 0;
-  void init(int n) {
+  void init(int n, const Params& pr) {
     k = (uint8_t)n;
-    std::fill(scores.begin(), scores.begin() + n, 0.5f);
-    std::fill(visits.begin(), visits.begin() + n, 1u);
+    if (pr.kind == K_UCB || pr.kind == K_PUCB) {
+      std::fill(scores.begin(), scores.begin() + n, 0.5f);
+      std::fill(visits.begin(), visits.begin() + n, 1u);
+      std::fill(priors.begin(), priors.begin() + n, 1.0f / n);  // until softmax_logits arrives (same evaluation)
+    } else if (pr.kind == K_UCB1) {
+      std::fill(scores.begin(), scores.begin() + n, 0.0f);
+      std::fill(visits.begin(), visits.begin() + n, 0u);
+    } else {
+      std::fill(scores.begin(), scores.begin() + n, 0.0f);
+      std::fill(scores.begin() + n, scores.end(), -INFINITY);
+    }
   }
-  int select(float c) const {
+  void softmax_logits(const Params& pr, const float* logits) {
+    if (pr.kind == K_PUCB) {  // util/softmax.h:5-15
+      float sum = 0;
+      for (int i = 0; i < k; ++i) {
+        priors[i] = std::exp(logits[i]);
+        sum += priors[i];
+      }
+      for (int i = 0; i < k; ++i) priors[i] /= sum;
+    } else if (pr.kind == K_PEXP3) {  // pexp3.h:44-48
+      const float eta = pr.gamma / k;
+      for (int i = 0; i < k; ++i) scores[i] = logits[i] / eta;
+    }
+  }
+  int select(const Params& pr, double u, float& prob) const {
+    prob = 1;
     int index = 0;
     if (k == 1) return 0;
-    uint64_t N = 0;
-    for (int i = 0; i < k; ++i) N += visits[i];
-    float sqrtN = std::sqrt(N);
-    float max = 0;
-    for (int i = 0; i < k; ++i) {
-      float e = c * sqrtN / k;
-      float a = (e + scores[i]) / visits[i];
-      if (a > max) {
-        max = a;
-        index = i;
+    if (pr.kind == K_UCB || pr.kind == K_PUCB) {
+      uint64_t N = 0;
+      for (int i = 0; i < k; ++i) N += visits[i];
+      float sqrtN = std::sqrt(N);
+      float max = 0;
+      for (int i = 0; i < k; ++i) {
+        float e = pr.kind == K_UCB ? pr.c * sqrtN / k : pr.c * priors[i] * sqrtN;
+        float a = (e + scores[i]) / visits[i];
+        if (a > max) {
+          max = a;
+          index = i;
+        }
       }
+    } else if (pr.kind == K_UCB1) {
+      std::array<float, 9> q{};
+      uint64_t N{};
+      for (int i = k - 1; i >= 0; --i) {
+        if (visits[i] == 0) return i;
+        q[i] = (float)scores[i] / visits[i];
+        N += visits[i];
+      }
+      float lnN = std::log(N);
+      float max = 0;
+      for (int i = 0; i < k; ++i) {
+        float e = std::sqrt(pr.c * lnN / visits[i]);
+        float a = e + q[i];
+        if (a > max) {
+          max = a;
+          index = i;
+        }
+      }
+    } else {
+      std::array<float, 9> policy;
+      const float eta{pr.gamma / k};
+      const float delta{pr.alpha / k};
+      float sum = 0;  // util/softmax.h:17-27 over all nine gains
+      for (int i = 0; i < 9; ++i) {
+        policy[i] = std::exp(scores[i] * eta);
+        sum += policy[i];
+      }
+      for (int i = 0; i < 9; ++i) policy[i] = (1 - pr.alpha) * (policy[i] / sum) + delta;
+      double p = u;  // sample_pdf, util/random.h:39-49
+      uint32_t pick = 0;
+      for (uint32_t i = 0; i < 9; ++i) {
+        p -= static_cast<double>(policy[i]);
+        if (p <= 0) {
+          pick = i;
+          break;
+        }
+      }
+      index = std::min<int>((int)pick, k - 1);
+      prob = policy[index];
     }
     return index;
   }
-  void update(int index, float value) {
-    scores[index] += value;
-    ++visits[index];
+  void update(const Params& pr, int index, float value, float prob) {
+    if (pr.kind <= K_PUCB) {
+      scores[index] += value;
+      ++visits[index];
+    } else if ((scores[index] += (value - 0.5f) / prob) > 0) {
+      const float max = scores[index];
+      for (auto& v : scores) v -= max;
+    }
   }
 };
 
@@ -66,7 +142,9 @@ struct Node {
 };
 
 struct Search {
-  float c;
+  float c = 1.0f;  // UCB's c when `params` is left at its default
+  Params params;
+  bool params_set = false;
   uint32_t root_rolls, other_rolls;
   uint64_t seed, iterations = 0;
   Node root;
@@ -96,9 +174,16 @@ struct Search {
     options.overrides[1] = roll_byte(nr, rb[7]);
   }
 
+  double exp3_u(size_t depth, int player) const {  // the product's documented stream (search.cu header)
+    const uint64_t x = splitmix64(seed ^ (0xD1B54A32D192ED03ull * (2 * iterations + 1)) ^ (0x9FB21C651E98DF25ull * (2 * (uint64_t)depth + player + 1)));
+    return (double)(x >> 11) * (1.0 / 9007199254740992.0);
+  }
+  bool contextual() const { return params.kind == K_PUCB || params.kind == K_PEXP3; }
+
   std::pair<float, float> run_iteration(Node& heap, Battle& battle, uint8_t& result, size_t depth) {
     if (heap.is_init()) {
-      const int i = heap.p1.select(c), j = heap.p2.select(c);
+      float prob1, prob2;
+      const int i = heap.p1.select(params, exp3_u(depth, 0), prob1), j = heap.p2.select(params, exp3_u(depth, 1), prob2);
       uint8_t ch1[9], ch2[9];
       {
         OakEngine e(battle, options);
@@ -118,8 +203,8 @@ struct Search {
         nodes++;
       }
       const auto v = run_iteration(it->second, battle, result, depth + 1);
-      heap.p1.update(i, v.first);
-      heap.p2.update(j, v.second);
+      heap.p1.update(params, i, v.first, prob1);
+      heap.p2.update(params, j, v.second, prob2);
       if (depth == 0) {
         ++visit[i * 9 + j];
         value[i * 9 + j] += v.first;
@@ -128,16 +213,22 @@ struct Search {
     }
     switch (result & 15) {
       case 0: {
-        uint8_t ch[9];
+        uint8_t ch1[9], ch2[9];
         OakEngine e(battle, options);
-        const int m = e.choices(P1, (result >> 4) & 3, ch), n = e.choices(P2, (result >> 6) & 3, ch);
-        heap.p1.init(m);
-        heap.p2.init(n);
+        const int m = e.choices(P1, (result >> 4) & 3, ch1), n = e.choices(P2, (result >> 6) & 3, ch2);
+        heap.p1.init(m, params);
+        heap.p2.init(n, params);
         uint8_t dur[8];
         memcpy(dur, options.durations, 8);
         if (net) {
           float l1[9], l2[9];
-          const float v = net_discrete ? net->eval_discrete(battle, dur, 0, 0, nullptr, nullptr, l1, l2) : net->eval(battle, dur, 0, 0, nullptr, nullptr, l1, l2);
+          const bool ctx = contextual();  // value_policy_inference + softmax_logits (mcts.h:415-421), else value_inference
+          const float v = net_discrete ? net->eval_discrete(battle, dur, ctx ? m : 0, ctx ? n : 0, ch1, ch2, l1, l2)
+                                       : net->eval(battle, dur, ctx ? m : 0, ctx ? n : 0, ch1, ch2, l1, l2);
+          if (ctx) {
+            heap.p1.softmax_logits(params, l1);
+            heap.p2.softmax_logits(params, l2);
+          }
           return {v, 1 - v};
         }
         oak_rollout(battle, dur, &result, playout_seed, 100000);
@@ -151,15 +242,26 @@ struct Search {
   }
 
   void run(const uint8_t* battle384, const uint8_t* durations8, uint8_t result0, uint32_t n_iter) {
-    if (!root.is_init()) {  // mcts.h:186-188
+    if (!params_set) {
+      params.kind = K_UCB;
+      params.c = c;
+    }
+    if (!root.is_init()) {  // mcts.h:186-209
       Battle b;
       memcpy(&b, battle384, 384);
       Options o{};
       OakEngine e(b, o);
-      uint8_t ch[9];
-      const int m = e.choices(P1, (result0 >> 4) & 3, ch), n = e.choices(P2, (result0 >> 6) & 3, ch);
-      root.p1.init(m);
-      root.p2.init(n);
+      uint8_t ch1[9], ch2[9];
+      const int m = e.choices(P1, (result0 >> 4) & 3, ch1), n = e.choices(P2, (result0 >> 6) & 3, ch2);
+      root.p1.init(m, params);
+      root.p2.init(n, params);
+      if (contextual() && net) {
+        float l1[9], l2[9];
+        if (net_discrete) net->eval_discrete(b, durations8, m, n, ch1, ch2, l1, l2);
+        else net->eval(b, durations8, m, n, ch1, ch2, l1, l2);
+        root.p1.softmax_logits(params, l1);
+        root.p2.softmax_logits(params, l2);
+      }
     }
     for (uint32_t t = 0; t < n_iter; t++) {
       Battle b;

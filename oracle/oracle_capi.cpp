@@ -517,3 +517,24 @@ extern "C" void oracle_mcts_run_net(void* net, int discrete, const uint8_t* batt
   memcpy(value81, s.value, sizeof(s.value));
   if (nodes) *nodes = s.nodes;
 }
+
+// the same search with any of the reference's bandits (kind 0 ucb, 1 ucb1, 2 pucb, 3 exp3, 4 pexp3; f1 = c or gamma, f2 = alpha);
+// net may be null (MonteCarlo leaves; not with the contextual kinds)
+extern "C" void oracle_mcts_run_bandit(void* net, int discrete, const uint8_t* battle384, const uint8_t* durations8, uint8_t result,
+                                       uint64_t seed, uint32_t iterations, int kind, float f1, float f2, uint32_t root_rolls,
+                                       uint32_t other_rolls, uint32_t* visit81, double* value81, uint64_t* nodes) {
+  mcts_oracle::Search s;
+  s.params.kind = kind;
+  s.params.c = s.params.gamma = f1;
+  s.params.alpha = f2;
+  s.params_set = true;
+  s.root_rolls = root_rolls;
+  s.other_rolls = other_rolls;
+  s.seed = seed;
+  s.net = static_cast<BattleNet*>(net);
+  s.net_discrete = discrete != 0;
+  s.run(battle384, durations8, result, iterations);
+  memcpy(visit81, s.visit, sizeof(s.visit));
+  memcpy(value81, s.value, sizeof(s.value));
+  if (nodes) *nodes = s.nodes;
+}

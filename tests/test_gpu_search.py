@@ -260,3 +260,109 @@ def test_config_c4_scale_4096_roots():
         visit, value, nodes = oracle_search(orc, b[i], d[i], r[i], seeds[i], 24, 1.0, 3, 1)
         assert np.array_equal(o1["visit_matrix"][i], visit) and np.array_equal(o1["value_matrix"][i], value), i
         assert o1["nodes"][i] == nodes, i
+
+
+def oracle_search_bandit(orc, net, discrete, b, d, r, seed, iters, kind, f1, f2, rr, orl):
+    f = orc.lib.oracle_mcts_run_bandit
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint8, ctypes.c_uint64, ctypes.c_uint32,
+                  ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_void_p]
+    visit, value, nodes = np.zeros(81, np.uint32), np.zeros(81, np.float64), np.zeros(1, np.uint64)
+    f(net.h if net is not None else None, int(discrete), b.ctypes.data, d.ctypes.data, int(r), int(seed), iters, kind, f1, f2, rr, orl,
+      visit.ctypes.data, value.ctypes.data, nodes.ctypes.data)
+    return visit.reshape(9, 9), value.reshape(9, 9), int(nodes[0])
+
+
+@pytest.mark.parametrize("spec,kind,f1,f2", [("ucb1-2.0", 1, 2.0, 0.05), ("exp3-1.0-0.1", 3, 1.0, 0.1), ("exp3-0.3", 3, 0.3, 0.05)])
+def test_other_bandits_equal_the_sequential_oracle(spec, kind, f1, f2):
+    """UCB1 (ucb1.h) and Exp3 (exp3.h; the reference's default agent bandit is "exp3-1.0-0.1", search-test.cc:29) with
+    MonteCarlo leaves, one descent in flight: every selection — Exp3's sampled ones included, drawn from the documented
+    counter-based stream — matches the oracle, so the matrices and node counts are identical."""
+    import oak_b200
+    from oak_b200.search import TreeSearch
+    orc = Oracle()
+    n, iters = 6, 300
+    b, d, r = midgame(orc, n, first=300)
+    seeds = np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x2468ACE)
+    eng = oak_b200.BattleEngine(64)
+    ts = TreeSearch(eng, n, particles=1)
+    ts.set_bandit(spec)
+    ts.set_roots(b, d, r, seeds)
+    ts.run(iters, root_rolls=3, other_rolls=1)
+    out = ts.output()
+    for i in range(n):
+        visit, value, nodes = oracle_search_bandit(orc, None, False, b[i], d[i], r[i], seeds[i], iters, kind, f1, f2, 3, 1)
+        assert np.array_equal(out["visit_matrix"][i], visit), i
+        assert np.array_equal(out["value_matrix"][i], value), i
+        assert out["nodes"][i] == nodes and out["iterations"][i] == iters
+    ts.close()
+    eng.close()
+
+
+@pytest.mark.parametrize("spec,kind,f1,f2", [("pucb-1.5", 2, 1.5, 0.05), ("pexp3-1.0-0.1", 4, 1.0, 0.1)])
+def test_contextual_bandits_use_the_network_priors(spec, kind, f1, f2):
+    """PUCB / PExp3: priors = the network's policy logits over the legal choices at the root and at every new leaf
+    (mcts.h:190-209,409-421; pucb.h:38-40, pexp3.h:44-48). One descent in flight against the oracle with the same network.
+    Values and logits are floats computed in a different order on the GPU (~1e-6), so a near-tie can send the two searches
+    apart: required as for UCB with network leaves — at least half the roots identical selection for selection, all of them
+    statistically the same search — and the priors must matter: PUCB with this network differs from UCB with it."""
+    import oak_b200
+    from oak_b200.search import TreeSearch
+    from oak_ref import NetOracle, make_net_blob
+    orc = Oracle()
+    n, iters = 8, 300
+    b, d, r = midgame(orc, n, first=1200)
+    seeds = np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x1357911)
+    blob = make_net_blob(np.random.default_rng(11), scale=3.0)
+    net = NetOracle(orc, blob)
+    eng = oak_b200.BattleEngine(64)
+    eng.load_network(blob)
+    ts = TreeSearch(eng, n, particles=1)
+    ts.set_leaf(1)
+    ts.set_bandit(spec)
+    ts.set_roots(b, d, r, seeds)
+    ts.run(iters, root_rolls=3, other_rolls=1)
+    out = ts.output()
+    same = 0
+    for i in range(n):
+        visit, value, nodes = oracle_search_bandit(orc, net, False, b[i], d[i], r[i], seeds[i], iters, kind, f1, f2, 3, 1)
+        assert out["iterations"][i] == iters and out["visit_matrix"][i].sum() == iters
+        assert abs(out["empirical_value"][i] - value.sum() / iters) < 0.03
+        if np.array_equal(out["visit_matrix"][i], visit) and out["nodes"][i] == nodes:
+            same += 1
+            assert np.abs(out["value_matrix"][i] - value).max() < 1e-4 * iters
+    assert same >= n // 2, same
+    if kind == 2:
+        ts.set_bandit("ucb-1.5")
+        ts.set_roots(b, d, r, seeds)
+        ts.run(iters, root_rolls=3, other_rolls=1)
+        assert not np.array_equal(ts.output()["visit_matrix"], out["visit_matrix"])
+    ts.close()
+    eng.close()
+
+
+def test_iteration_budget_is_exact_and_contextual_needs_a_network():
+    """`iterations` is run to the iteration, not rounded up to whole waves (the reference runs exactly its budget,
+    mcts.h:237-241); pucb without network leaves is refused as the reference refuses it (search.cc:253-258)."""
+    import oak_b200
+    from oak_b200.engine import OakB200Error
+    from oak_b200.search import TreeSearch
+    orc = Oracle()
+    b, d, r = midgame(orc, 5, first=40)
+    eng = oak_b200.BattleEngine(5 * 64)
+    ts = TreeSearch(eng, 5, particles=64)
+    ts.set_roots(b, d, r, sample_seeds(1, 5))
+    total = 0
+    for it in (10, 1, 64, 100):
+        ts.run(it)
+        total += it
+        o = ts.output()
+        assert np.all(o["iterations"] == total) and np.all(o["visit_matrix"].reshape(5, -1).sum(1) == total)
+    ts.set_bandit("pucb-1.0")
+    with pytest.raises(OakB200Error):
+        ts.run(8)
+    with pytest.raises(ValueError):
+        ts.set_bandit("thompson-1")
+    ts.close()
+    eng.close()
