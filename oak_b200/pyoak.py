@@ -3,7 +3,9 @@ liboakb200 on the GPU, so that the reference's lab / learner scripts (src/oak/la
 find what they call:
 
     read_battle_data, SampleIndexer, sample, EncodedBattleFrames, BattleFrames, OutputBuffer, cpp_inference,
-    solve_matrix, Input, update, Agent, Heap, Output, search and the network / encoding dimensions.
+    solve_matrix, Input, update, Agent, Heap, Output, search, the network / encoding dimensions and the constant tables
+    (species_move_list, species_move_table, species_names, move_names, *_dim_labels, build_* dims; pyoak.cc:586-636),
+    generated from the reference's headers by tools/gen_oak_constants.py into oak_constants.py.
 
 Differences a caller sees, all deliberate:
   * EncodedBattleFrames / BattleFrames hold torch tensors in DEVICE memory (same names, shapes, dtypes) — the learner
@@ -11,10 +13,14 @@ Differences a caller sees, all deliberate:
   * `threads` of `sample` is accepted and ignored: the replay + encode of the drawn games is two kernel launches;
   * `cpp_inference` evaluates every frame in one tensor-core launch; `budget` only costs time in the reference (it
     reports the root's network value and priors, pyoak.cc:351-356), so it is parsed and otherwise unused;
-  * `search` runs the library's batched tree search on one root: bandits "ucb-<c>" with MonteCarlo or network leaves.
-    "ucb1", "pucb", "exp3", "pexp3", matrix-UCB, the transposition table and time budgets are not built and raise.
-Not here (host text utilities and the team-builder, off the battle path): parse_battle, battle_string, format, the
-species / move name tables, BuildTrajectories, read_build_trajectories.
+  * `search` runs the library's batched tree search on one root: bandits "ucb-<c>", "ucb1-<c>", "pucb-<c>",
+    "exp3-<gamma>[-<alpha>]", "pexp3-<gamma>[-<alpha>]" (cpp/src/search.cc:236-300) with MonteCarlo or network leaves
+    (pucb / pexp3 need a network: their priors are its policy). Matrix-UCB, the transposition table and time budgets are
+    not built and raise.
+  * the reference's src/oak/torch.py wraps these objects with torch.from_numpy; device tensors want `.host()` first
+    (EncodedBattleFrames.host() -> the same names as numpy arrays), or torch.as_tensor in place of torch.from_numpy.
+Not here (host text utilities and the team-builder, off the battle path): parse_battle, battle_string, format;
+BuildTrajectories / read_build_trajectories exist as names only and raise.
 There is no CPU path: everything below that touches a battle needs a CUDA device and the built library.
 """
 import os
@@ -25,18 +31,11 @@ from .engine import BattleEngine, OakB200Error, rows_index_host  # noqa: F401
 from .search import TreeSearch, solve_matrix  # noqa: F401
 from .training_rows import BattleFrames, EncodedBattleFrames  # noqa: F401
 
-# Encode::Battle::{Pokemon, ActivePokemon}::n_dim, NN::Battle::Default::*, Encode::Battle::Policy::n_dim (pyoak.cc:586-596)
-pokemon_in_dim = 198
-active_in_dim = 229
-pokemon_hidden_dim = 128
-pokemon_out_dim = 59
-active_hidden_dim = 128
-active_out_dim = 83
-side_out_dim = (1 + active_out_dim) + 5 * (1 + pokemon_out_dim)
-hidden_dim = 64
-value_hidden_dim = 32
-policy_hidden_dim = 64
-policy_out_dim = 315
+# Encode::Battle::{Pokemon, ActivePokemon}::n_dim, NN::Battle::Default::*, Encode::Battle::Policy::n_dim, the team-builder
+# tables and the name tables (pyoak.cc:586-636). active_in_dim is the ACTIVE NET's input (229 active features + the 198 of
+# the Pokémon itself = 427); the `active` tensor of EncodedBattleFrames holds the first 229 (encoded-frames.h:30).
+from .oak_constants import *  # noqa: F401,F403,E402
+from .oak_constants import active_out_dim, pokemon_out_dim, policy_out_dim  # noqa: E402
 
 
 def read_battle_data(path):
@@ -151,6 +150,18 @@ class OutputBuffer:
         for a in (self.pokemon, self.active_pokemon, self.sides, self.value, self.logit, self.policy_logit, self.policy):
             a.fill(0.0)
         self.logit[:, :, -1] = -np.inf
+
+
+class BuildTrajectories:
+    """The team-builder's trajectory container (pyoak.cc:697-707): off the battle path (SURVEY.md §8 out of scope). The name
+    exists so that the reference's src/oak/torch.py, which annotates with it, imports; constructing one raises."""
+
+    def __init__(self, size):
+        raise NotImplementedError("the team-builder (BuildTrajectories, read_build_trajectories) is outside the battle path")
+
+
+def read_build_trajectories(*args, **kwargs):
+    raise NotImplementedError("the team-builder (BuildTrajectories, read_build_trajectories) is outside the battle path")
 
 
 def cpp_inference(battle_frames, network_path, discrete=False, budget="0"):
@@ -276,11 +287,12 @@ def search(input, heap, agent, output=None, seed=None, particles=64):
     parts = str(agent.bandit).split("-")
     if len(parts) < 2:
         raise RuntimeError("Could not parse bandit string: " + str(agent.bandit))
-    if parts[0] != "ucb":
-        raise NotImplementedError(f"bandit '{parts[0]}' is not built (only ucb-<c>)")
+    if parts[0] not in TreeSearch.BANDITS:
+        raise RuntimeError("Could not parse bandit string: " + str(agent.bandit))
     if agent.matrix_ucb or agent.table:
         raise NotImplementedError("matrix-UCB and the transposition table are not built")
-    c = float(parts[1])
+    if parts[0] in ("pucb", "pexp3") and agent.is_monte_carlo():
+        raise RuntimeError(f"bandit '{parts[0]}' takes its priors from a network: set agent.eval to a network path")
     if heap._engine is None:
         heap._engine = BattleEngine(max(int(particles), 1))
     eng = heap._engine
@@ -293,7 +305,8 @@ def search(input, heap, agent, output=None, seed=None, particles=64):
         ts.set_roots(input.battle.reshape(1, 384), input.durations.reshape(1, 8), np.array([input.result], np.uint8),
                      np.array([seed], np.uint64))
         t0 = time.perf_counter()
-        ts.run(int(number), c=c)
+        ts.set_bandit(str(agent.bandit))
+        ts.run(int(number))
         o, (nash, nash_value) = ts.output(), ts.nash()
         out = Output()
         out.duration_ms = int((time.perf_counter() - t0) * 1e3)
@@ -304,6 +317,14 @@ def search(input, heap, agent, output=None, seed=None, particles=64):
         out.p1_empirical[:], out.p2_empirical[:] = o["empirical"][0, 0], o["empirical"][0, 1]
         out.p1_nash[:], out.p2_nash[:] = nash[0, 0], nash[0, 1]
         out.k = (int(o["k"][0, 0]), int(o["k"][0, 1]))
+        if parts[0] in ("pucb", "pexp3"):  # the root's priors: softmax of the network's legal logits (mcts.h:197-210)
+            value, logits, _ = eng.evaluate_host(input.battle.reshape(1, 384), input.durations.reshape(1, 8),
+                                                 np.array([input.result], np.uint8))
+            out.initial_value = float(value[0])
+            for side, name in enumerate(("p1_prior", "p2_prior")):
+                lg = logits[0, side, :out.k[side]].astype(np.float64)
+                e = np.exp(lg - lg.max())
+                getattr(out, name)[:out.k[side]] = e / e.sum()
         out.choices = o["choices"][0].copy()
         return out
     finally:

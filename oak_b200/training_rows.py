@@ -60,6 +60,16 @@ class EncodedBattleFrames:
         for name in self._fields(self.torch):
             getattr(self, name).zero_()
 
+    def host(self):
+        """The same attribute names as numpy arrays in host memory (plus `size`) — what the reference's wrappers that call
+        torch.from_numpy on each field (src/oak/torch.py:16-28) take. `iterations` comes back as the reference's uint32."""
+        import types
+        h = types.SimpleNamespace(size=self.size, rows=self.rows, games=self.games)
+        for name in self._fields(self.torch):
+            a = getattr(self, name).cpu().numpy()
+            setattr(h, name, a.view(np.uint32) if name == "iterations" else a)
+        return h
+
     def fill(self, data, only_update=None):
         """data: bytes / uint8 array (pinned tensors upload fastest) holding whole games. -> rows written.
         Raises if a game's replay does not end on its stored result (the reference asserts that)."""

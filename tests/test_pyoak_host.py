@@ -68,6 +68,6 @@ def test_budget_strings_and_output_buffer():
     o.value[:] = 3
     o.clear()
     assert not o.value.any() and o.policy.shape == o.policy_logit.shape == (5, 2, 9)
-    assert (oak.pokemon_in_dim, oak.active_in_dim, oak.policy_out_dim) == (198, 229, 315)
+    assert (oak.pokemon_in_dim, oak.active_in_dim, oak.policy_out_dim) == (198, 427, 315)  # pyoak.cc:587: the active net takes 229 + 198
     p1, p2, v = oak.solve_matrix(np.array([[1.0, 0.0], [0.0, 1.0]], np.float32))
     assert abs(v - 0.5) < 1e-6 and np.allclose(p1, 0.5) and np.allclose(p2, 0.5)
