@@ -353,43 +353,47 @@ def main():
     eval_e2e_s = (time.perf_counter() - t0) / 5
     launches += 6
     # ---- secondary: self-play generation (BASELINE configs[4]): lockstep games, network policy, frames recorded and
-    # packed on the device, drained per rank and gathered to rank 0 (the writer) over NCCL
+    # packed on the device, drained per rank into page-locked shared-memory rings the writer (rank 0) reads — no collective
     import json as _json
     from oak_b200.selfplay import SelfPlay
     pool = np.array(_json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
     SP_G, SP_STEPS = 65536, 96
     sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
 
-    from oak_b200.sharding import StreamGatherer
-    gatherer = StreamGatherer(dst=0, device=dev)
+    # frames reach the writer without a collective (per-GPU form): every rank DMAs its drains over its own PCIe
+    # link into a page-locked shared-memory ring (oak_b200.sharding.FrameSender); rank 0's writer thread reads all rings
+    from oak_b200.sharding import FrameCollector, FrameSender
+    sender = FrameSender(rank, device=dev, capacity=256 << 20)
+    barrier()  # start-up only: every ring exists before the writer attaches
+    arrived, keeping, at_writer = [], [False], [0] * world  # writer rank: bytes per rank; the streams in the untimed check pass
+
+    def writer_sink(r, view):
+        at_writer[r] += len(view)
+        if keeping[0]:
+            arrived.append(np.array(view, copy=True))
+    collector = FrameCollector(world, writer_sink) if rank == 0 else None
 
     def sp_pass(keep_arrivals=False):
-        # every drain goes to the writer rank as it is produced (one gather per drain, one drain behind the generator)
-        streams, games, at_writer = [], 0, 0
+        # every drain goes to this rank's ring as it is produced; the copy runs behind the generator's next steps
+        streams, games = [], 0
         arrived.clear()
         keeping[0] = keep_arrivals
+        for r_ in range(world):
+            at_writer[r_] = 0
         for s_ in range(SP_STEPS):
             sp.step()
             if (s_ + 1) % 8 == 0:
-                st_, g_ = sp.collect(device=True)  # the drained stream stays on the device until the writer rank has it
+                st_, g_ = sp.collect(device=True)  # the drained stream stays on the device; the DMA takes it to the ring
                 streams.append(st_.clone())
                 games += g_
-                got = gatherer.submit(st_)  # the previous drain's bytes, gathered while these 8 steps ran
-                at_writer += keep(got)
-        got = gatherer.flush()
-        at_writer += keep(got)
-        return streams, games, at_writer
+                sender.submit(st_)
+        sender.flush()
+        barrier()  # every rank has published its last drain
+        if collector is not None:
+            collector.wait_idle()  # ... and the writer has consumed it: the timed region ends with the bytes at the writer
+        return streams, games, sum(at_writer)
 
-    arrived, keeping = [], [False]  # writer rank: every rank's drained streams as they came off the gather (untimed pass only)
-
-    def keep(got):
-        if got is None:
-            return 0
-        if keeping[0]:
-            arrived.extend(np.array(x, copy=True) for x in got if len(x))
-        return sum(len(x) for x in got)
-
-    sp_pass()  # warm-up: the same pass (the writer rank's page-locked gather buffer is allocated here, once)
+    sp_pass()  # warm-up: the same pass
     barrier()
     l0 = sp.eng.launch_count
     t0 = time.perf_counter()
@@ -398,15 +402,20 @@ def main():
     sp_s = time.perf_counter() - t0
     local_stream = torch.cat(sp_streams).cpu().numpy() if sp_streams else np.empty(0, np.uint8)
     launches += sp.eng.launch_count - l0
-    # outside the timed region: the bytes that ARRIVED at the writer rank (all ranks' drains, through NCCL when world > 1)
-    # are whole games that replay on the device to their stored results, and are as many bytes as the ranks drained
+    # outside the timed region: the bytes that ARRIVED at the writer (all ranks' drains, read from their rings) are whole
+    # games that replay on the device to their stored results, and are as many bytes as the ranks drained
     chk_streams, _, chk_bytes = sp_pass(keep_arrivals=True)  # one more pass, untimed, whose arrivals are kept and replayed
+    sent_t = torch.tensor([float(sender.bytes)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(sent_t, op=dist.ReduceOp.SUM)  # after the timed region: how many bytes the ranks sent in total
+    sent_total = float(sent_t.item())
     barrier()
     gather_ok = None
     if rank == 0:
         from oak_b200.training_rows import BattleFrames
+        collector.stop()
         got_stream = np.concatenate(arrived) if arrived else np.empty(0, np.uint8)
-        gather_ok = len(got_stream) == chk_bytes and len(got_stream) > 0
+        gather_ok = len(got_stream) == chk_bytes and len(got_stream) > 0 and collector.bytes == int(sent_total)
         if gather_ok:
             from oak_b200.engine import rows_index_host as _rih
             _, _, _rows = _rih(got_stream)
@@ -418,6 +427,8 @@ def main():
             del bf
         if world == 1:
             gather_ok = gather_ok and len(got_stream) == sum(int(x.numel()) for x in chk_streams)
+    barrier()
+    sender.close()
 
     # ---- secondary: training rows (pyoak EncodedBattleFrames.from_bytes / sample): the games this rank's
     # self-play finishes are replayed on the device and encoded into the learner's dense tensors. Input: the self-play
@@ -640,7 +651,8 @@ def main():
                          "stream_bytes_at_writer": int(sp_bytes),
                          "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
                                  "step: choices + tensor-core eval + policy sample + frame record + update + finish kernels; "
-                                 "drain every 8 steps; frame streams gathered to rank 0"},
+                                 "drain every 8 steps; every rank DMAs its drains into its own page-locked shared-memory ring, one writer "
+                                 "thread on rank 0 reads all rings (no collective, no padding, no rank-0 PCIe funnel)"},
             "training_rows": {"rows_per_s": tot_tr_rows / (tr_ms_max * 1e-3), "rows_per_gpu": int(tr_rows), "games_per_gpu": int(len(tr_off)),
                               "ms_per_build": tr_ms_max, "e2e_rows_per_s": tot_tr_rows / (tr_e2e_ms_max * 1e-3),
                               "e2e_note": "pinned host .battle.data stream in (header walk, H2D), rows left in device memory for the "

@@ -470,7 +470,9 @@ eval_kernel(NetView nv, const uint8_t* __restrict__ battles, const uint8_t* __re
           const uint32_t type = c & 3, data = c >> 2;
           uint32_t idx = 0;  // policy.h:29-58
           if (type == CH_MOVE) {
-            const uint32_t mid = data >= 1 ? side[((int)side[S_ORDER] - 1) * PK_SIZE + PK_MOVES + 2 * (data - 1)] : 0;
+            // data == 0 (forced move): the reference reads moves[-1] = the low byte of stats.spc (policy.h:34-36), kept
+            const uint8_t* stored = side + ((int)side[S_ORDER] - 1) * PK_SIZE;
+            const uint32_t mid = data >= 1 ? stored[PK_MOVES + 2 * (data - 1)] : stored[PK_STATS + ST_SPC];
             idx = mid == 0 ? 0 : mid - 1;
           } else if (type == CH_SWITCH) {
             idx = 164 + side[((int)side[S_ORDER + data - 1] - 1) * PK_SIZE + PK_SPECIES] - 1;

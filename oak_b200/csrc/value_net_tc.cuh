@@ -826,7 +826,8 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             const uint32_t type = c & 3, data = c >> 2;
             idx[k] = 0;
             if (type == CH_MOVE) {
-              const uint32_t mid = data >= 1 ? m.ld8(m.stored(s), PK_MOVES + 2 * ((int)data - 1)) : 0;
+              // data == 0 (forced move): the reference reads moves[-1] = the low byte of stats.spc (policy.h:34-36), kept
+              const uint32_t mid = m.ld8(m.stored(s), data >= 1 ? PK_MOVES + 2 * ((int)data - 1) : PK_STATS + ST_SPC);
               idx[k] = mid == 0 ? 0 : mid - 1;
             } else if (type == CH_SWITCH) {
               const uint32_t pid = m.ld8(sb, S_ORDER + (int)data - 1);

@@ -119,9 +119,11 @@ static inline uint8_t pokemon_key(const Pokemon& p, uint8_t sleep) {  // key.h:2
 static inline uint16_t policy_index(const Side& side, uint8_t choice) {  // policy.h:29-58
   const int type = choice & 3, data = choice >> 2;
   if (type == 1) {
-    // data == 0 (Struggle) reads moves[-1] in the reference; its callers never evaluate that logit's
-    // meaning (one legal choice) — define it as index 0
-    const uint16_t id = data >= 1 ? Engine<false, false, false, true, false>::stored(const_cast<Side&>(side)).moves[data - 1].id : 0;
+    // data == 0 (the forced "move 0" of recharge / locked-in turns) indexes moves[-1] in the reference: the two bytes before
+    // Pokemon::moves, i.e. the low byte of stats.spc. That is what the compiled reference reads (its torch mirror gathers
+    // the same index from the training rows, src/oak/lab.py test-consistency), so it is what we read.
+    const Pokemon& st = Engine<false, false, false, true, false>::stored(const_cast<Side&>(side));
+    const uint16_t id = data >= 1 ? st.moves[data - 1].id : (uint16_t)(st.stats.spc & 0xFF);
     return id == 0 ? 0 : id - 1;
   }
   if (type == 2) return (uint16_t)(164 + Engine<false, false, false, true, false>::get(const_cast<Side&>(side), data).species - 1);

@@ -62,3 +62,34 @@ def test_reference_torch_module_runs_on_this_oak_module():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def test_oracle_inference_agrees_with_the_reference_torch_network_on_reference_rows():
+    """The CPU half of lab test-consistency on the oracle: oracle/nn_oracle.hpp's inference path on the raw frames the
+    reference's Frames::from_bytes produced (battle_frames_golden.npz) against the reference's torch network on the rows its
+    EncodedFrames::from_bytes produced, all 1107 rows of 8 games. Pins the encoder, the parameter format, the network and
+    the policy index — including the forced 'move 0' choice, where the reference indexes moves[-1] (policy.h:34-36)."""
+    from gen_consistency_golden import NET_SCALE, NET_SEED, game_bounds
+    from oak_ref import NetOracle, Oracle, make_net_blob
+    orc = Oracle()
+    G = np.load(os.path.join(ROOT, "tests", "golden", "training_rows_golden.npz"))
+    F = np.load(os.path.join(ROOT, "tests", "golden", "battle_frames_golden.npz"))
+    C = np.load(os.path.join(ROOT, "tests", "golden", "consistency_golden.npz"))
+    forced = 0
+    for tag, act in (("relu", 1), ("clamp", 2)):
+        net = NetOracle(orc, make_net_blob(np.random.default_rng(NET_SEED), activation=act, scale=NET_SCALE))
+        lo = 0
+        for g, (_, _, n) in enumerate(game_bounds(G["stream"])):
+            b, d = np.ascontiguousarray(F["battle"][lo:lo + n]), np.ascontiguousarray(F["durations"][lo:lo + n])
+            r = np.ascontiguousarray(F["result"][lo:lo + n, 0])
+            v, lg, cnt = net.eval_batch(b, d, r)
+            assert np.array_equal(cnt, G["k"][lo:lo + n, :, 0])
+            legal = np.arange(9)[None, None, :] < cnt[:, :, None]
+            lg = np.where(legal, lg, 0.0)
+            assert np.abs(v - C[f"value_{tag}_{g}"][:, 0]).max() < 2e-6, (tag, g)
+            assert np.abs(lg - C[f"policy_logit_{tag}_{g}"]).max() < 2e-5, (tag, g)
+            # rows whose only choice is the forced move 0 and whose moves[-1] read is not zero: the case the index fix is for
+            ci = G["choice_indices"][lo:lo + n]
+            forced += int(((cnt == 1) & (ci[:, :, 0] != 0) & (ci[:, :, 0] < 164)).sum())
+            lo += n
+    assert forced > 0

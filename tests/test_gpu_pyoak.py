@@ -115,7 +115,7 @@ def test_cpp_inference_matches_the_oracle_network(orc, tmp_path):
     frames.close()
 
 
-def test_update_and_search_on_one_input(orc):
+def test_update_and_search_on_one_input(orc, tmp_path):
     import oak_b200.pyoak as oak
     ob, od, r = orc.sample_battle(3)
     inp = oak.Input(ob.copy(), od.copy(), r)
@@ -139,7 +139,22 @@ def test_update_and_search_on_one_input(orc):
         assert abs(v.sum() - 1.0) < 1e-3 and (v >= 0).all()
     assert 0.0 <= out.empirical_value <= 1.0 and 0.0 <= out.nash_value <= 1.0
     assert np.array_equal(out.choices[0, :m], orc.choices(ob, 0, (r >> 4) & 3))
-    for bad in (oak.Agent(budget="1s"), oak.Agent(bandit="exp3-0.1"), oak.Agent(table=True)):
+    for bad in (oak.Agent(budget="1s"), oak.Agent(table=True), oak.Agent(matrix_ucb="2-1.0")):
         with pytest.raises(NotImplementedError):
             oak.search(inp, heap, bad)
+    for bad in (oak.Agent(bandit="thompson-1"), oak.Agent(bandit="pucb-1.0", eval="mc")):
+        with pytest.raises(RuntimeError):
+            oak.search(inp, heap, bad)
+    # the other bandit strings of cpp/src/search.cc:236-300; the contextual ones report the root's network priors
+    net_path = str(tmp_path / "net.battle.net")
+    make_net_blob(np.random.default_rng(5)).tofile(net_path)
+    for bandit, ev in (("ucb1-2.0", "mc"), ("exp3-0.1", "mc"), ("exp3-0.1-0.02", net_path), ("pucb-1.5", net_path), ("pexp3-0.1", net_path)):
+        out = oak.search(inp, heap, oak.Agent(budget="300", bandit=bandit, eval=ev), seed=11)
+        assert out.iterations == 300 and int(out.visit_matrix.sum()) == 300, bandit
+        assert abs(out.p1_empirical.sum() - 1.0) < 1e-3 and abs(out.p1_nash.sum() - 1.0) < 1e-3, bandit
+        if bandit.startswith("p"):
+            assert abs(out.p1_prior[:m].sum() - 1.0) < 1e-6 and abs(out.p2_prior[:n].sum() - 1.0) < 1e-6 and not out.p1_prior[m:].any()
+            assert 0.0 < out.initial_value < 1.0
+        else:
+            assert not out.p1_prior.any()
     heap._engine.close()

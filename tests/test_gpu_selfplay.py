@@ -88,3 +88,42 @@ def test_device_drain_and_gather_equal_the_host_drain():
     assert total > 100
     a.close()
     b.close()
+
+
+def test_device_drains_reach_the_writer_through_the_page_locked_ring():
+    """The collective-free frame path (sharding.FrameSender / FrameCollector): device drains are copied by DMA into this
+    rank's page-locked shared-memory ring and the writer thread reads them — the same bytes, in order, as the host drain of
+    a twin generator; a small ring (wraps + back-pressure) and the drain buffer being reused at once are both exercised."""
+    import torch
+    from oak_b200.selfplay import SelfPlay
+    from oak_b200.sharding import FrameCollector, FrameSender
+    pool = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    blob = make_net_blob(np.random.default_rng(5), scale=3.0)
+    a = SelfPlay(512, blob, pool, seed=43, max_updates=400)
+    b = SelfPlay(512, blob, pool, seed=43, max_updates=400)
+    tag = f"gputest{os.getpid()}"
+    sender = FrameSender(0, device=torch.device("cuda:0"), capacity=1 << 20, tag=tag)
+    assert sender.ring.pinned is not None and sender.ring.pinned.is_pinned()
+    arrived = []
+    collector = FrameCollector(1, lambda r, view: arrived.append(view.tobytes()), tag=tag)
+    want = []
+    for s in range(240):
+        a.step()
+        b.step()
+        if (s + 1) % 8 == 0:
+            sa, ga = a.collect()
+            sb, gb = b.collect(device=True)
+            assert ga == gb
+            if len(sa):
+                want.append(bytes(sa))
+            sender.submit(sb)
+            sb.fill_(0xEE)  # the caller's buffer is free again as soon as submit returns
+    sender.flush()
+    collector.wait_idle()
+    collector.stop()
+    assert arrived == want and sum(map(len, want)) > (1 << 20)  # more bytes than the ring holds: it wrapped
+    assert collector.bytes == sender.bytes
+    sender.close()
+    assert not [f for f in os.listdir("/dev/shm") if tag in f]
+    a.close()
+    b.close()

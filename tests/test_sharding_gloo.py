@@ -3,6 +3,7 @@ import os
 import socket
 
 import numpy as np
+import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
@@ -76,3 +77,64 @@ def test_weight_broadcast_and_frame_gather():
         assert out[r][0] == bytes(range(200)) * 3
     assert out[1][1] is None and out[1][2] is None
     assert out[0][1] == [bytes([1]) * 17, bytes([2]) * 1017] and out[0][2] == 2
+
+
+def _ring_worker(rank, world, port, out, tag):
+    """Every rank pushes ragged, sometimes empty drains into its own shared-memory ring; rank 0 also runs the collector.
+    No collective on the data path: the barriers only order start-up and shutdown."""
+    from oak_b200.sharding import FrameCollector, FrameSender
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sender = FrameSender(rank, capacity=4096, tag=tag)  # tiny: the 60 drains below wrap it many times and fill it
+    dist.barrier()
+    got = {r: [] for r in range(world)}
+    collector = FrameCollector(world, lambda r, view: got[r].append(view.tobytes()), tag=tag) if rank == 0 else None
+    rng = np.random.default_rng(100 + rank)
+    sent = []
+    for i in range(60):
+        n = 0 if i % 7 == 3 else int(rng.integers(1, 1500 if rank else 700))  # ragged across ranks, empty drains skipped
+        a = rng.integers(0, 256, n).astype(np.uint8)
+        if i % 2:
+            a = torch.from_numpy(a)  # host tensors take the same path
+        sender.submit(a)
+        if n:
+            sent.append(bytes(a.numpy().tobytes() if torch.is_tensor(a) else a.tobytes()))
+    sender.flush()
+    dist.barrier()
+    if collector is not None:
+        collector.stop()
+        out["got"] = {r: got[r] for r in range(world)}
+    out[rank] = sent
+    dist.barrier()
+    sender.close()
+    dist.destroy_process_group()
+
+
+def test_frame_rings_carry_ragged_and_empty_drains_without_a_collective():
+    import torch  # noqa: F401
+    world = 2
+    out = mp.Manager().dict()
+    tag = f"test{os.getpid()}"
+    mp.spawn(_ring_worker, args=(world, _free_port(), out, tag), nprocs=world, join=True)
+    for r in range(world):
+        assert out["got"][r] == out[r] and len(out[r]) > 40  # every message, whole, in order, per rank
+    assert not [f for f in os.listdir("/dev/shm") if tag in f]  # the rings are unlinked
+
+
+def test_frame_ring_rejects_oversized_and_times_out_when_nobody_reads():
+    import pytest
+    from oak_b200.sharding import FrameRing
+    ring = FrameRing(f"oakb200_test_{os.getpid()}", 1024, create=True)
+    try:
+        with pytest.raises(ValueError):
+            ring.push(np.zeros(2000, np.uint8))
+        ring.push(np.zeros(600, np.uint8))
+        with pytest.raises(RuntimeError):
+            ring.push(np.zeros(600, np.uint8), timeout_s=0.05)
+        seen = []
+        assert ring.poll(lambda v: seen.append(len(v))) == 1 and seen == [600] and ring.drained()
+        ring.push(np.arange(600, dtype=np.uint8))  # wraps: 608 + 608 > 1024
+        assert ring.poll(lambda v: seen.append(int(v[599]))) == 1 and seen[-1] == 599 % 256
+    finally:
+        ring.close()
