@@ -357,8 +357,13 @@ def main():
     import json as _json
     from oak_b200.selfplay import SelfPlay
     pool = np.array(_json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
-    SP_G, SP_STEPS = 65536, 96
-    sp = SelfPlay(SP_G, blob, pool, seed=99 + rank, device=local, max_updates=512, first_game=rank << 32)
+    # two lanes of 65 536 games on their own streams, software-pipelined: one lane's drain + refill (host work that waits
+    # for that lane's kernels) runs under the other lane's queued steps (oak_b200.selfplay.PipelinedSelfPlay)
+    from oak_b200.selfplay import PipelinedSelfPlay
+    SP_LANES, SP_LANE_G, SP_STEPS = 2, 65536, 96
+    SP_G = SP_LANES * SP_LANE_G
+    psp = PipelinedSelfPlay(SP_LANE_G, blob, pool, seed=99 + rank, device=local, lanes=SP_LANES, first_game=rank << 32, max_updates=512)
+    sp = psp.lanes[0]
 
     # frames reach the writer without a collective (per-GPU form): every rank DMAs its drains over its own PCIe
     # link into a page-locked shared-memory ring (oak_b200.sharding.FrameSender); rank 0's writer thread reads all rings
@@ -380,13 +385,11 @@ def main():
         keeping[0] = keep_arrivals
         for r_ in range(world):
             at_writer[r_] = 0
-        for s_ in range(SP_STEPS):
-            sp.step()
-            if (s_ + 1) % 8 == 0:
-                st_, g_ = sp.collect(device=True)  # the drained stream stays on the device; the DMA takes it to the ring
-                streams.append(st_.clone())
-                games += g_
-                sender.submit(st_)
+        def on_drain(st_, g_):  # the drained stream stays on the device; the DMA takes it to the ring
+            streams.append(st_.clone())
+            sender.submit(st_)
+        games = psp.run(SP_STEPS, on_drain, collect_every=8)
+        torch.cuda.synchronize(dev)
         sender.flush()
         barrier()  # every rank has published its last drain
         if collector is not None:
@@ -395,13 +398,13 @@ def main():
 
     sp_pass()  # warm-up: the same pass
     barrier()
-    l0 = sp.eng.launch_count
+    l0 = psp.launch_count
     t0 = time.perf_counter()
     sp_streams, sp_games, sp_bytes = sp_pass()
     barrier()
     sp_s = time.perf_counter() - t0
     local_stream = torch.cat(sp_streams).cpu().numpy() if sp_streams else np.empty(0, np.uint8)
-    launches += sp.eng.launch_count - l0
+    launches += psp.launch_count - l0
     # outside the timed region: the bytes that ARRIVED at the writer (all ranks' drains, read from their rings) are whole
     # games that replay on the device to their stored results, and are as many bytes as the ranks drained
     chk_streams, _, chk_bytes = sp_pass(keep_arrivals=True)  # one more pass, untimed, whose arrivals are kept and replayed
@@ -437,15 +440,17 @@ def main():
     from oak_b200.training_rows import EncodedBattleFrames
     TR_ROWS = 1 << 21
     tr_parts, tr_have = [local_stream], 0
-    for s_ in range(400):
-        if tr_have >= TR_ROWS:
-            break
-        sp.step()
-        if (s_ + 1) % 8 == 0:
-            st_, g_ = sp.collect()
-            tr_parts.append(np.array(st_, copy=True))
-            tr_have = rows_index_host(np.concatenate(tr_parts))[2] if g_ else tr_have
-    sp.close()
+    with torch.cuda.stream(psp.streams[0]):
+        for s_ in range(400):
+            if tr_have >= TR_ROWS:
+                break
+            sp.step()
+            if (s_ + 1) % 8 == 0:
+                st_, g_ = sp.collect()
+                tr_parts.append(np.array(st_, copy=True))
+                tr_have = rows_index_host(np.concatenate(tr_parts))[2] if g_ else tr_have
+        psp.streams[0].synchronize()
+    psp.close()
     tr_stream = np.concatenate(tr_parts)
     tr_off, tr_base, tr_rows = rows_index_host(tr_stream)
     if tr_rows > TR_ROWS:  # whole games only
@@ -647,7 +652,7 @@ def main():
                             "cpu_iterations_per_s": sr_cpu, "cpu_kind": "port (sequential MCTS restatement, all host cores)",
                             "note": "MonteCarlo leaves, joint UCB c=1, clamped rolls 3/1 (mcts.h:133); host trees, one kernel "
                                     "launch per tree level + hidden-variable draw + playouts per wave"},
-            "selfplay": {"game_updates_per_s": world * SP_G * SP_STEPS / sp_s, "games_per_gpu": SP_G, "steps": SP_STEPS,
+            "selfplay": {"game_updates_per_s": world * SP_G * SP_STEPS / sp_s, "games_per_gpu": SP_G, "lanes": SP_LANES, "steps": SP_STEPS,
                          "stream_bytes_at_writer": int(sp_bytes),
                          "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
                                  "step: choices + tensor-core eval + policy sample + frame record + update + finish kernels; "

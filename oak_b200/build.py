@@ -30,17 +30,32 @@ def stale():
     return any(os.path.getmtime(d) > t for d in _deps())
 
 
-def build(force=False, verbose=False):
-    """Compile oak_b200/liboakb200.so with nvcc for sm_100a. Returns the library path."""
-    if not force and not stale():
+def build(force=False, verbose=False, out=None, extra=None):
+    """Compile oak_b200/liboakb200.so with nvcc for sm_100a (one object per source, compiled in parallel, then linked).
+    Returns the library path. `out` / `extra`: a differently named library with extra nvcc flags (A/B variants)."""
+    lib = out or LIB
+    if out is None and not force and not stale():
         return LIB
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     srcs = [s for s in sources() if os.path.exists(s)]
-    extra = os.environ.get("OAKB200_NVCC_EXTRA", "").split()  # diagnostic builds only (e.g. -DOAKB200_TC_TIMING)
-    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + srcs
+    extra = list(extra or []) + os.environ.get("OAKB200_NVCC_EXTRA", "").split()  # diagnostic builds (e.g. -DOAKB200_TC_TIMING)
+    objdir = os.path.join(HERE, "_build", os.path.splitext(os.path.basename(lib))[0])
+    os.makedirs(objdir, exist_ok=True)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + extra + (["-Xptxas", "-v"] if verbose else [])
+
+    def compile_one(src):
+        obj = os.path.join(objdir, os.path.splitext(os.path.basename(src))[0] + ".o")
+        cmd = [nvcc] + flags + ["-c", "-o", obj, src]
+        print("[oak_b200.build]", " ".join(cmd), file=sys.stderr)
+        subprocess.check_call(cmd)
+        return obj
+    with ThreadPoolExecutor(max_workers=len(srcs)) as pool:
+        objs = list(pool.map(compile_one, srcs))
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib] + objs
     print("[oak_b200.build]", " ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":

@@ -246,8 +246,9 @@ int oakb200_frames_create(oakb200_ctx* ctx, size_t games, uint32_t max_updates) 
   f->games = games;
   f->max_updates = max_updates;
   f->cap = (HEADER + max_updates * 83u + 15u) & ~15u;
+  // the pack buffer holds every slot at once, so a drain can never fail for lack of room however long the caller waited
+  // between drains (a clamp here once made every later drain fail for good: nothing else shrinks the backlog)
   f->pack_cap = games * (size_t)f->cap;
-  if (f->pack_cap > ((size_t)1 << 30)) f->pack_cap = (size_t)1 << 30;
   CU(ctx, cudaMalloc(&f->buf, games * (size_t)f->cap));
   CU(ctx, cudaMalloc(&f->used, games * 4));
   CU(ctx, cudaMalloc(&f->nupd, games * 2));

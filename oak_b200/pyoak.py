@@ -115,10 +115,14 @@ def sample(encoded_frames, indexer, threads=1, max_battle_length=1 << 30, min_it
             game = np.asarray(m[off:off + nb])
             p, valid = 391, []
             for u in range(n_frames):
+                if p + 11 > nb:  # a corrupt record: the stored (m, n) walked out of the game
+                    raise ValueError(f"sample: update {u} of the game at byte {off} of {paths[pi]} lies outside its record")
                 hdr = int(game[p])
                 if int.from_bytes(game[p + 3:p + 7].tobytes(), "little") >= min_iterations:
                     valid.append(u)
                 p += 11 + 4 * ((hdr & 15) + (hdr >> 4) + 2)
+            if p != nb:
+                raise ValueError(f"sample: the game at byte {off} of {paths[pi]} does not end on its last update")
             if not valid:
                 continue
             games.append(game)

@@ -169,6 +169,62 @@ class SelfPlay:
         return done
 
 
+class PipelinedSelfPlay:
+    """`lanes` SelfPlay generators (default two) on their own CUDA streams, software-pipelined: while the host drains one
+    lane (the drain's size read-back, the ended-slot scan, new teams and seeds for the refill — all of which wait for that
+    lane's kernels and then keep the host busy) the other lanes' next steps are already queued on the device, so neither the
+    GPU nor the host waits for the other. Games are independent, so this is the same generation as one SelfPlay of
+    lanes * games_per_lane games; lane l plays game ids first_game + l * 2^28 + ..."""
+
+    def __init__(self, games_per_lane, net_blob, team_pool, seed=0, device=0, lanes=2, first_game=0, **kw):
+        import torch
+        self.torch = torch
+        self.dev = torch.device("cuda", device)
+        self.streams = [torch.cuda.Stream(self.dev) for _ in range(lanes)]
+        self.lanes = []
+        for l, st in enumerate(self.streams):
+            st.wait_stream(torch.cuda.current_stream(self.dev))
+            with torch.cuda.stream(st):
+                self.lanes.append(SelfPlay(games_per_lane, net_blob, team_pool, seed=seed + 7919 * l, device=device,
+                                           first_game=first_game + (l << 28), **kw))
+        self.queued = [0] * lanes  # steps queued on the lane since its last collect
+
+    @property
+    def launch_count(self):
+        return sum(sp.eng.launch_count for sp in self.lanes)
+
+    def run(self, steps, on_drain, collect_every=8):
+        """`steps` lockstep turns of EVERY lane; after each `collect_every` steps of a lane its finished games are drained and
+        on_drain(stream, games) is called inside that lane's stream context with the device stream (valid until the lane's
+        next drain). -> games finished."""
+        torch, done = self.torch, 0
+        assert steps % collect_every == 0
+        for _ in range(steps // collect_every):
+            for l, sp in enumerate(self.lanes):
+                with torch.cuda.stream(self.streams[l]):
+                    # the lane that was queued one block ago is drained only now: its kernels ran under the other lanes' host work
+                    if self.queued[l]:
+                        done += self._collect(l, on_drain)
+                    for _ in range(collect_every):
+                        sp.step()
+                    self.queued[l] = collect_every
+        for l in range(len(self.lanes)):
+            with torch.cuda.stream(self.streams[l]):
+                if self.queued[l]:
+                    done += self._collect(l, on_drain)
+        return done
+
+    def _collect(self, l, on_drain):
+        stream, games = self.lanes[l].collect(device=True)
+        self.queued[l] = 0
+        on_drain(stream, games)
+        return games
+
+    def close(self):
+        for sp in self.lanes:
+            sp.close()
+
+
 def runtime_policy(empirical, nash, mode="e", temp=1.0, min_prob=0.0):
     """RuntimePolicy::get_policy (reference cpp/include/util/policy.h:22-98) for rows of 9 probabilities: `mode` is a
     '-'-joined list of <letter>[weight] with e = empirical, n = nash, x = argmax of the empirical policy; then temperature,

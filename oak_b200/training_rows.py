@@ -107,10 +107,14 @@ class EncodedBattleFrames:
                 continue
             p, valid = o + 391, []
             for u in range(nu):
+                if p + 11 > o + nb:  # a corrupt record: the stored (m, n) walked out of the game
+                    raise ValueError(f"sample: update {u} of the game at byte {o} lies outside its record")
                 hdr = int(data[p])
                 if int.from_bytes(data[p + 3:p + 7].tobytes(), "little") >= min_iterations:
                     valid.append(u)
                 p += 11 + 4 * ((hdr & 15) + (hdr >> 4) + 2)
+            if p != o + nb:
+                raise ValueError(f"sample: the game at byte {o} does not end on its last update")
             if valid and len(keep) < self.size:
                 keep.append((o, nb))
                 picks.append(valid[int(rng.integers(0, len(valid)))])

@@ -127,3 +127,39 @@ def test_device_drains_reach_the_writer_through_the_page_locked_ring():
     assert not [f for f in os.listdir("/dev/shm") if tag in f]
     a.close()
     b.close()
+
+
+def test_pipelined_lanes_generate_what_separate_generators_do():
+    """PipelinedSelfPlay: two lanes on their own streams, one lane's drain + refill under the other's queued steps. Each
+    lane's drained bytes are exactly those of a lone SelfPlay with the lane's seed and game ids, and replay on the oracle."""
+    import torch
+    from oak_b200.selfplay import PipelinedSelfPlay, SelfPlay
+    pool = np.array(json.load(open(os.path.join(ROOT, "tests", "golden", "oak_teams.json")))["ou_sample_teams"], np.uint8)
+    blob = make_net_blob(np.random.default_rng(5), scale=3.0)
+    psp = PipelinedSelfPlay(384, blob, pool, seed=77, lanes=2, first_game=1000, max_updates=400)
+    got = {0: [], 1: []}
+
+    def on_drain(stream, games):
+        lane = [l for l, st in enumerate(psp.streams) if st == torch.cuda.current_stream()][0]
+        got[lane].append(stream.cpu().numpy().copy())
+    done = psp.run(200, on_drain, collect_every=8)
+    torch.cuda.synchronize()
+    assert done > 100
+    for lane in (0, 1):
+        lone = SelfPlay(384, blob, pool, seed=77 + 7919 * lane, first_game=1000 + (lane << 28), max_updates=400)
+        want = []
+        for s in range(200):
+            lone.step()
+            if (s + 1) % 8 == 0:
+                want.append(np.array(lone.collect()[0], copy=True))
+        lone.close()
+        assert np.array_equal(np.concatenate(got[lane]), np.concatenate(want)), lane
+    games = parse_battle_data(np.concatenate(got[0] + got[1]).tobytes())
+    assert len(games) == done
+    orc = Oracle()
+    for g in games[::7]:  # whole games that replay to their stored result
+        b, d, r = g["battle"].copy(), np.zeros(8, np.uint8), 0x50
+        for u in g["updates"]:
+            r, _ = orc.update(b, u["c1"], u["c2"], d)
+        assert r == g["result"] and (r & 15) != 0
+    psp.close()

@@ -71,3 +71,23 @@ def test_budget_strings_and_output_buffer():
     assert (oak.pokemon_in_dim, oak.active_in_dim, oak.policy_out_dim) == (198, 427, 315)  # pyoak.cc:587: the active net takes 229 + 198
     p1, p2, v = oak.solve_matrix(np.array([[1.0, 0.0], [0.0, 1.0]], np.float32))
     assert abs(v - 0.5) < 1e-6 and np.allclose(p1, 0.5) and np.allclose(p2, 0.5)
+
+
+def test_sample_returns_zero_on_a_corrupt_update_header(tmp_path, capsys):
+    """pyoak.sample's '0 on error' contract (pyoak.cc:187-190,254-259) also holds for a record whose stored (m, n) nibbles
+    walk the header scan out of the game: that is reported and 0 returned before any device work."""
+    import types
+    import oak_b200.pyoak as oak
+    game = np.array(split_games(G["stream"])[0], copy=True)
+    at = 391
+    for _ in range(int.from_bytes(bytes(game[4:6]), "little") - 1):
+        at += 11 + 4 * ((int(game[at]) & 15) + (int(game[at]) >> 4) + 2)
+    game[at] = 0xFF  # the last update claims m = n = 15: 139 bytes, past the end of the game
+    path = tmp_path / "bad.battle.data"
+    game.tofile(path)
+    ix = oak.SampleIndexer()
+    ix.get(str(path))
+    filled = []
+    frames = types.SimpleNamespace(size=4, fill=lambda *a, **k: filled.append(1) or 4)
+    assert oak.sample(frames, ix, rng=np.random.default_rng(1)) == 0 and not filled
+    assert "does not end on its last update" in capsys.readouterr().err
