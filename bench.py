@@ -378,6 +378,8 @@ def main():
             arrived.append(np.array(view, copy=True))
     collector = FrameCollector(world, writer_sink) if rank == 0 else None
 
+    sp_phases = [0.0] * 4
+
     def sp_pass(keep_arrivals=False):
         # every drain goes to this rank's ring as it is produced; the copy runs behind the generator's next steps
         streams, games = [], 0
@@ -388,21 +390,33 @@ def main():
         def on_drain(st_, g_):  # the drained stream stays on the device; the DMA takes it to the ring
             streams.append(st_.clone())
             sender.submit(st_)
+        tp = [time.perf_counter()]
         games = psp.run(SP_STEPS, on_drain, collect_every=8)
         torch.cuda.synchronize(dev)
+        tp.append(time.perf_counter())
         sender.flush()
+        tp.append(time.perf_counter())
         barrier()  # every rank has published its last drain
+        tp.append(time.perf_counter())
         if collector is not None:
             collector.wait_idle()  # ... and the writer has consumed it: the timed region ends with the bytes at the writer
+        tp.append(time.perf_counter())
+        sp_phases[:] = [round((tp[k + 1] - tp[k]) * 1e3, 2) for k in range(4)]  # generate, flush, barrier, writer (ms, this rank)
         return streams, games, sum(at_writer)
 
     sp_pass()  # warm-up: the same pass
     barrier()
     l0 = psp.launch_count
-    t0 = time.perf_counter()
-    sp_streams, sp_games, sp_bytes = sp_pass()
-    barrier()
-    sp_s = time.perf_counter() - t0
+    sp_runs = []
+    for _ in range(3):  # three timed passes, the median is reported (the host side of this leg varies from pass to pass)
+        barrier()
+        t0 = time.perf_counter()
+        sp_streams, sp_games, sp_bytes = sp_pass()
+        barrier()
+        sp_runs.append((time.perf_counter() - t0, list(sp_phases)))
+    sp_runs.sort(key=lambda x: x[0])
+    sp_s, sp_phases_timed = sp_runs[1]
+    sp_all_s = [round(x[0] * 1e3, 2) for x in sp_runs]
     local_stream = torch.cat(sp_streams).cpu().numpy() if sp_streams else np.empty(0, np.uint8)
     launches += psp.launch_count - l0
     # outside the timed region: the bytes that ARRIVED at the writer (all ranks' drains, read from their rings) are whole
@@ -653,6 +667,8 @@ def main():
                             "note": "MonteCarlo leaves, joint UCB c=1, clamped rolls 3/1 (mcts.h:133); host trees, one kernel "
                                     "launch per tree level + hidden-variable draw + playouts per wave"},
             "selfplay": {"game_updates_per_s": world * SP_G * SP_STEPS / sp_s, "games_per_gpu": SP_G, "lanes": SP_LANES, "steps": SP_STEPS,
+                         "passes_ms": sp_all_s, "rank0_ms": {"generate": sp_phases_timed[0], "flush": sp_phases_timed[1], "barrier": sp_phases_timed[2],
+                                      "writer": sp_phases_timed[3]},
                          "stream_bytes_at_writer": int(sp_bytes),
                          "note": "upper bound on recorded updates/s (slots whose game ended wait <= 8 steps for a refill); per "
                                  "step: choices + tensor-core eval + policy sample + frame record + update + finish kernels; "
