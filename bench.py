@@ -431,19 +431,30 @@ def main():
     if rank == 0:
         from oak_b200.training_rows import BattleFrames
         collector.stop()
-        got_stream = np.concatenate(arrived) if arrived else np.empty(0, np.uint8)
-        gather_ok = len(got_stream) == chk_bytes and len(got_stream) > 0 and collector.bytes == int(sent_total)
+        got_bytes = sum(len(x) for x in arrived)
+        gather_ok = got_bytes == chk_bytes and got_bytes > 0 and collector.bytes == int(sent_total)
         if gather_ok:
+            # every arrived message is whole games: replay them in slices the engine's capacity (n battles) holds
             from oak_b200.engine import rows_index_host as _rih
-            _, _, _rows = _rih(got_stream)
-            bf = BattleFrames(max(_rows, 1), device=local, engine=eng)
+            bf, at = None, 0
             try:
-                gather_ok = bf.fill(got_stream) == _rows  # raises if a game does not replay to its stored result
+                while at < len(arrived) and gather_ok:
+                    part, part_rows = [], 0
+                    while at < len(arrived):
+                        _r = _rih(arrived[at])[2]
+                        if part and part_rows + _r > n // 2:
+                            break
+                        part.append(arrived[at])
+                        part_rows += _r
+                        at += 1
+                    if bf is None or bf.size < part_rows:
+                        bf = BattleFrames(max(part_rows, n // 2), device=local, engine=eng)
+                    gather_ok = bf.fill(np.concatenate(part)) == part_rows  # raises if a game does not replay to its result
             except ValueError:
                 gather_ok = False
             del bf
         if world == 1:
-            gather_ok = gather_ok and len(got_stream) == sum(int(x.numel()) for x in chk_streams)
+            gather_ok = gather_ok and got_bytes == sum(int(x.numel()) for x in chk_streams)
     barrier()
     sender.close()
 

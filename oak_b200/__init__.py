@@ -5,12 +5,6 @@ package is the thin Python host side (ctypes + torch for device memory and strea
 implementation here: importing works anywhere, but creating a `BattleEngine` without a CUDA device or
 without the built library raises.
 """
-import os as _os
-
-# hardware work queues per process: the tree search runs ~32 streams at once and the default of 8 makes them wait for each
-# other (oakb200_create explains); must be in the environment before CUDA initialises, an explicit setting wins
-_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
-
 from .engine import BattleEngine, OakB200Error, load_library  # noqa: F401
 
 __all__ = ["BattleEngine", "OakB200Error", "load_library"]

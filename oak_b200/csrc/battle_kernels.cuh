@@ -7,7 +7,6 @@
 #include <stdint.h>
 
 #include "gen1_engine.cuh"
-#include "rollout_queue.h"
 #include "train_rows_encode.cuh"
 
 namespace oakb200 {
@@ -306,137 +305,6 @@ rollout_kernel(uint8_t* battles, uint8_t* __restrict__ durations, uint8_t* __res
   uint32_t s = my_steps;
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
   if ((threadIdx.x & 31) == 0 && total_steps) atomicAdd(total_steps, (unsigned long long)s);
-}
-
-// ---------------------------------------------------------------------------------------------
-// rollout_worker_kernel: rollout_kernel's playouts from the search's shared queue (rollout_queue.h). Always the SPLIT
-// layout, score only, no state written back.
-template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK, 8)
-rollout_worker_kernel(uint8_t* battles, const uint8_t* durations, const uint8_t* results, const uint64_t* seeds, uint32_t max_steps,
-                      uint8_t* score2_out, oakb200_rollout_queue q) {
-  extern __shared__ uint32_t tile[];
-  __shared__ uint32_t cta_admitted, cta_busy_warps, cta_warps;
-  // a CTA is admitted or leaves as a whole: its shared memory is held until its last warp ends, so a CTA with one live warp
-  // would cost an SM slot for a quarter of the work
-  if (threadIdx.x == 0) {
-    const uint32_t before = atomicAdd(q.live, 1u);
-    cta_admitted = before < q.max_live;
-    if (!cta_admitted) atomicSub(q.live, 1u);  // the workers already running hold their share of the SMs and take the batch
-    cta_busy_warps = 0;
-    cta_warps = BLOCK / 32;
-  }
-  __syncthreads();
-  if (!cta_admitted) return;
-  uint32_t* col = tile + threadIdx.x;
-  Engine<BLOCK, false, false, false, true> e;
-  e.begin(reinterpret_cast<uint8_t*>(col), 0, 0);
-  const uint32_t lane = threadIdx.x & 31u;
-  // lane g looks at group g
-  const uint32_t my_first = lane < q.n_groups ? q.group_first[lane] : 0u;
-  const uint32_t my_count = lane < q.n_groups ? q.group_first[lane + 1] - my_first : 0u;
-  const uint32_t rot = (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) & 31u;  // where this warp starts looking
-  uint32_t i = 0, result = 0, step = 0, iter = 0, group = 0, group_count = 0, idle_looks = 0;
-  uint64_t seed = 0;
-  bool have = false, counted_busy = false;
-  // -> a group with playouts left, or -1 (whole warp)
-  auto look = [&]() -> int {
-    const uint32_t handed = lane < q.n_groups ? *reinterpret_cast<volatile uint32_t*>(q.next + lane) : 0xFFFFFFFFu;
-    const uint32_t avail = __ballot_sync(0xFFFFFFFFu, handed < my_count);
-    if (!avail) return -1;
-    const uint32_t turned = (avail >> rot) | (rot ? avail << (32u - rot) : 0u);
-    return (int)((__ffs(turned) - 1 + rot) & 31u);
-  };
-  for (;;) {
-    if ((iter & q.poll_mask) == 0) {  // uniform over the warp: iter advances for all lanes together
-      const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !have);
-      if (idle) {
-        const int g = look();
-        if (g >= 0) {
-          uint32_t base = 0;
-          if (lane == 0) base = atomicAdd(q.next + g, (uint32_t)__popc(idle));
-          base = __shfl_sync(0xFFFFFFFFu, base, 0);
-          const uint32_t first = __shfl_sync(0xFFFFFFFFu, my_first, g), count = __shfl_sync(0xFFFFFFFFu, my_count, g);
-          const uint32_t mine = base + __popc(idle & ((1u << lane) - 1u));
-          if (!have && mine < count) {
-            i = first + mine;
-            group = (uint32_t)g;
-            group_count = count;
-            split_fill<BLOCK, CgLoad>(col, reinterpret_cast<const uint32_t*>(battles + (size_t)i * 384));
-            const uint2 d = __ldcg(reinterpret_cast<const uint2*>(durations + (size_t)i * 8));
-            e.begin(reinterpret_cast<uint8_t*>(col), d.x, d.y);
-            e.m.set_const(battles + (size_t)i * 384);
-            result = __ldcg(results + i);
-            seed = __ldcg(seeds + i);
-            step = 0;
-            have = true;
-          }
-        }
-      }
-    }
-    const bool warp_busy = __any_sync(0xFFFFFFFFu, have);
-    if (warp_busy != counted_busy) {  // this warp's share of the CTA's busy count
-      if (lane == 0) {
-        if (warp_busy) atomicAdd(&cta_busy_warps, 1u);
-        else atomicSub(&cta_busy_warps, 1u);
-      }
-      counted_busy = warp_busy;
-    }
-    if (!warp_busy) {
-      // Nothing to advance in this warp. While another warp of the CTA works, stay (the CTA's slot is held anyway) and
-      // look again after a pause; when none does, leave: the last warp takes the CTA out of `live` BEFORE one more look
-      // (not at once: the gaps between batches are shorter than a relaunch, so an idle CTA lingers for q.linger looks)
-      uint32_t stay = 0;
-      if (lane == 0) {
-        if (*reinterpret_cast<volatile uint32_t*>(&cta_busy_warps) != 0 || ++idle_looks <= q.linger) stay = 1;
-        else if (atomicSub(&cta_warps, 1u) == 1u) stay = 2;  // the CTA's last warp
-      }
-      stay = __shfl_sync(0xFFFFFFFFu, stay, 0);
-      if (stay == 2) {
-        if (lane == 0) {
-          atomicSub(q.live, 1u);
-          __threadfence();
-        }
-        __syncwarp();
-        if (look() < 0) break;
-        if (lane == 0) {
-          atomicAdd(q.live, 1u);
-          atomicAdd(&cta_warps, 1u);
-        }
-      } else if (stay == 0) {
-        break;
-      } else {
-        __nanosleep(q.idle_ns);
-      }
-      iter = 0;
-      continue;
-    }
-    iter++;
-    idle_looks = 0;
-    if (have) {
-      const bool live = (result & 15u) == 0 && step < max_steps;
-      if (live) {
-        uint32_t c1, c2;
-        pick_choices(e, result, pick_word(seed, step), c1, c2);
-        e.act[0] = e.act[1] = 0;  // pkmn_gen1_battle_options_set(null, null, null) (mcts.h:478)
-        result = e.update(c1, c2);
-        step++;
-      }
-      if (!live || (result & 15u) != 0 || step >= max_steps) {
-        const uint32_t t = result & 15u;
-        score2_out[i] = t == RES_WIN ? 2 : (t == RES_TIE ? 1 : (t == RES_LOSE ? 0 : 255));
-        have = false;
-        // the last playout of a batch to finish tells the host
-        __threadfence();
-        if (atomicAdd(q.done + group, 1u) + 1 == group_count) {
-          q.done[group] = 0;
-          __threadfence_system();
-          q.host_batches[group] = q.host_batches[group] + 1;
-          __threadfence_system();
-        }
-      }
-    }
-  }
 }
 
 // ---------------------------------------------------------------------------------------------

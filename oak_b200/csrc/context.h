@@ -66,11 +66,6 @@ cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_ba
 cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8_t* durations, uint8_t* results, const uint8_t* idx1,
                                        const uint8_t* idx2, const uint8_t* rolls, uint8_t* actions, uint8_t* counts, uint32_t n);
 
-#include "rollout_queue.h"
-cudaError_t oakb200_launch_rollout_worker(oakb200_ctx* ctx, cudaStream_t stream, int ctas, uint8_t* battles, const uint8_t* durations,
-                                          const uint8_t* results, const uint64_t* seeds, uint32_t max_steps, uint8_t* score2,
-                                          oakb200_rollout_queue q);
-
 // train_rows.cu -> oakb200.cu
 cudaError_t oakb200_launch_replay(oakb200_ctx* ctx, const uint8_t* stream, const uint64_t* game_off, const uint32_t* row_base,
                                   const int32_t* only_update, uint32_t n_games, uint32_t* words, uint8_t* rows);

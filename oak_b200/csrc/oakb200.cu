@@ -34,14 +34,6 @@ cudaError_t allow_smem(K kernel) {
 
 unsigned grid_for(size_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
 
-// Kernels that have to run on an SM next to resident playout CTAs (the search's level kernels under its playouts) ask for
-// the same shared-memory carve-out as the playout kernels, the largest one: an SM whose L1 / shared split would have to
-// change for the new kernel takes its CTAs only once it has drained, i.e. after the playouts.
-template <class K>
-cudaError_t max_carveout(K kernel) {
-  return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
-}
-
 template <bool RANDOM, bool CALC>
 cudaError_t launch_step(oakb200_ctx* ctx, size_t n, void* battles, void* durations, void* results, const void* c1,
                         const void* c2, const void* seeds, uint32_t step_index, const void* overrides, void* actions,
@@ -81,8 +73,6 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
   if (const char* pad = getenv("OAKB200_ROLLOUT_SMEM_PAD")) tile_bytes += (size_t)atol(pad);
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes);
   if (e != cudaSuccess) return e;
-  e = max_carveout(k);
-  if (e != cudaSuccess) return e;
   int per_sm = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, BLOCK, tile_bytes);
   if (e != cudaSuccess) return e;
@@ -108,25 +98,9 @@ cudaError_t launch_rollout(oakb200_ctx* ctx, size_t n, void* battles, void* dura
 cudaError_t oakb200_launch_search_spawn(oakb200_ctx* ctx, const uint8_t* root_battles, const uint8_t* root_durations,
                                         const uint8_t* root_results, const uint64_t* rng_values, uint32_t per_root,
                                         uint8_t* battles, uint8_t* durations, uint8_t* results, uint32_t n) {
-  cudaError_t e = max_carveout(search_spawn_kernel);
-  if (e != cudaSuccess) return e;
   search_spawn_kernel<<<(unsigned)(((size_t)n * 32 + 255) / 256), 256, 0, ctx->stream>>>(root_battles, root_durations, root_results,
                                                                                         rng_values, per_root, battles, durations,
                                                                                         results, n);
-  ctx->launches++;
-  return cudaGetLastError();
-}
-cudaError_t oakb200_launch_rollout_worker(oakb200_ctx* ctx, cudaStream_t stream, int ctas, uint8_t* battles, const uint8_t* durations,
-                                          const uint8_t* results, const uint64_t* seeds, uint32_t max_steps, uint8_t* score2,
-                                          oakb200_rollout_queue q) {
-  auto k = rollout_worker_kernel<BLOCK>;
-  const size_t tile_bytes = TILE_BYTES / 2;
-  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes);
-  if (e != cudaSuccess) return e;
-  e = max_carveout(k);
-  if (e != cudaSuccess) return e;
-  if (ctas < 1) ctas = 1;
-  k<<<(unsigned)ctas, BLOCK, tile_bytes, stream>>>(battles, durations, results, seeds, max_steps, score2, q);
   ctx->launches++;
   return cudaGetLastError();
 }
@@ -134,8 +108,6 @@ cudaError_t oakb200_launch_search_step(oakb200_ctx* ctx, uint8_t* battles, uint8
                                        const uint8_t* idx2, const uint8_t* rolls, uint8_t* actions, uint8_t* counts, uint32_t n) {
   auto k = search_step_kernel<BLOCK>;
   cudaError_t e = allow_smem(k);
-  if (e != cudaSuccess) return e;
-  e = max_carveout(k);
   if (e != cudaSuccess) return e;
   k<<<grid_for(n), BLOCK, TILE_BYTES, ctx->stream>>>(battles, durations, results, idx1, idx2, rolls, actions, counts, n);
   ctx->launches++;
@@ -304,10 +276,6 @@ extern "C" {
 int oakb200_create(int device, size_t n_max, oakb200_ctx** out) {
   if (!out || n_max == 0 || n_max > 0x7FFFFFFFull) return OAKB200_EINVAL;
   *out = nullptr;
-  // The tree search keeps ~32 streams busy at once; with the default 8 hardware queues, streams that share a queue wait for
-  // each other's kernels (measured: 35 -> 28 ms per search wave). Only effective if CUDA is not initialised yet — the
-  // Python package sets the same default at import for that reason; an explicit setting by the user wins.
-  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || device < 0 || device >= count) return OAKB200_ENODEVICE;
   oakb200_ctx* ctx = new (std::nothrow) oakb200_ctx();
@@ -645,7 +613,6 @@ int oakb200_randomize_hidden_device(oakb200_ctx* ctx, size_t n, void* battles, c
   if (!ctx || !battles || !durations) return fail(ctx, OAKB200_EINVAL, "randomize_hidden: null argument");
   if (n == 0) return OAKB200_OK;
   CU(ctx, cudaSetDevice(ctx->device));
-  CU(ctx, max_carveout(randomize_hidden_kernel));
   randomize_hidden_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((uint8_t*)battles, (const uint8_t*)durations, (uint32_t)n);
   ctx->launches++;
   CU(ctx, cudaGetLastError());

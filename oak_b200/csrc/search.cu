@@ -261,6 +261,75 @@ struct Particle {
   bool active = false, spawned = false;
 };
 
+// persistent worker pool: parallel_for over roots
+class Pool {
+ public:
+  explicit Pool(int threads) {
+    if (threads < 1) threads = 1;
+    for (int t = 1; t < threads; t++) workers_.emplace_back([this, t] { loop((size_t)t); });
+  }
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      stop_ = true;
+      gen_++;
+    }
+    cv_.notify_all();
+    for (auto& w : workers_) w.join();
+  }
+  void parallel_for(size_t n, const std::function<void(size_t)>& fn) {
+    if (workers_.empty() || n < 2) {
+      for (size_t i = 0; i < n; i++) fn(i);
+      return;
+    }
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      fn_ = &fn;
+      n_ = n;
+      pending_ = (int)workers_.size();
+      gen_++;
+    }
+    cv_.notify_all();
+    work(0);
+    std::unique_lock<std::mutex> l(mu_);
+    done_.wait(l, [this] { return pending_ == 0; });
+  }
+
+ private:
+  // Static slices: thread w (0 = the caller) always gets items [n w / T, n (w + 1) / T). The items are roots, whose trees
+  // (~200 KB each) then stay in the cache of the core that walked them last, phase after phase; handing roots out one by one
+  // from a shared counter moved every tree between cores at every phase (12.4 -> see profiles/r2h_search_host.txt).
+  void work(size_t slot) {
+    const size_t T = workers_.size() + 1;
+    const size_t lo = n_ * slot / T, hi = n_ * (slot + 1) / T;
+    for (size_t i = lo; i < hi; i++) (*fn_)(i);
+  }
+  void loop(size_t slot) {
+    uint64_t seen = 0;
+    for (;;) {
+      {
+        std::unique_lock<std::mutex> l(mu_);
+        cv_.wait(l, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (stop_) return;
+      }
+      work(slot);
+      {
+        std::lock_guard<std::mutex> l(mu_);
+        if (--pending_ == 0) done_.notify_one();
+      }
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex mu_;
+  std::condition_variable cv_, done_;
+  const std::function<void(size_t)>* fn_ = nullptr;
+  size_t n_ = 0;
+  int pending_ = 0;
+  uint64_t gen_ = 0;
+  bool stop_ = false;
+};
+
 }  // namespace
 
 struct oakb200_search {
@@ -284,10 +353,8 @@ struct oakb200_search {
   // pinned host mirrors
   uint8_t *h_idx1 = nullptr, *h_idx2 = nullptr, *h_rolls = nullptr, *h_res = nullptr, *h_act = nullptr, *h_cnt = nullptr, *h_score = nullptr;
   uint64_t *h_rng = nullptr, *h_pseed = nullptr;
-  // shared playout queue (rollout_queue.h): next[32] | done[32] | live | group_first[33] on the device, the groups' batch
-  // words page-locked
-  uint32_t* d_queue = nullptr;
-  uint32_t* h_signal = nullptr;  // [64 batch words]
+  Pool* pool = nullptr;
+  int pool_threads = 0;
   uint64_t levels = 0, waves = 0;
 };
 
@@ -303,8 +370,7 @@ void search_free(oakb200_search* s) {
   void* host[] = {s->h_idx1, s->h_idx2, s->h_rolls, s->h_res, s->h_act, s->h_cnt, s->h_score, s->h_rng, s->h_pseed, s->h_value, s->h_logits};
   for (void* p : host)
     if (p) cudaFreeHost(p);
-  if (s->d_queue) cudaFree(s->d_queue);
-  if (s->h_signal) cudaFreeHost(s->h_signal);
+  delete s->pool;
   delete s;
 }
 
@@ -337,8 +403,6 @@ int oakb200_search_create(oakb200_ctx* ctx, size_t roots, uint32_t particles, oa
   ok(hmalloc(&s->h_idx1, B)); ok(hmalloc(&s->h_idx2, B)); ok(hmalloc(&s->h_rolls, B)); ok(hmalloc(&s->h_res, B));
   ok(hmalloc(&s->h_act, B * 16)); ok(hmalloc(&s->h_cnt, B * 2)); ok(hmalloc(&s->h_score, B));
   ok(hmalloc(&s->h_rng, B * 8)); ok(hmalloc(&s->h_pseed, B * 8));
-  ok(dmalloc(&s->d_queue, (32 + 32 + 32 + 64) * 4));
-  ok(cudaHostAlloc(reinterpret_cast<void**>(&s->h_signal), 65 * 4, cudaHostAllocMapped));
   if (e != cudaSuccess) {
     search_free(s);
     return fail(ctx, OAKB200_ECUDA, "search_create: allocation", e);
@@ -417,6 +481,11 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     }
     if (host_threads < 1) host_threads = 1;
   }
+  if (!s->pool || s->pool_threads != host_threads) {
+    delete s->pool;
+    s->pool = new Pool(host_threads);
+    s->pool_threads = host_threads;
+  }
   const uint32_t P = s->P;
   const size_t R = s->n_roots;
   const uint32_t MAX_DEPTH = 100;  // mcts.h:309
@@ -446,137 +515,50 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     s->root_primed = true;
   }
 
-  // The roots are cut into groups, each with its own stream, its own copy of the launch context and its own position in
-  // the per-wave phases (spawn, then per tree level select -> device step -> expand, then the leaves, then
-  // back-propagation). Every host thread owns a few groups and advances whichever of them has no device work pending:
-  // there is no fork-join between the threads and no point at which the groups wait for each other, so one group's
-  // playouts run under other groups' tree levels, and a thread whose group is on the device works on its other group.
-  // Trees of different roots never interact and every random stream is a function of (root seed, iteration), so the
-  // grouping changes no result. (The first form — all threads on one group's phase at a time, 4 groups taking turns —
-  // left the host idle 11 of 23.6 ms per wave at 4 096 roots x 64: profiles/r2h_search_host.txt.)
+  // The roots are cut into groups, each with its own stream and its own position in the per-wave phases (spawn, then per
+  // tree level select -> device step -> expand, then the leaves, then back-propagation). The scheduler below advances
+  // whichever group's device work has finished: while the device runs one group's kernels the host threads select /
+  // expand / back-propagate in another group's trees, and one group's level kernels run on the SMs another group's
+  // playout launch frees in its tail. Trees of different roots never interact and every random stream is a function of
+  // (root seed, iteration), so the grouping does not change any result.
   struct Group {
     size_t r0, r1;           // roots [r0, r1)
-    cudaStream_t stream;     // tree levels: high priority, so that their small kernels go ahead of pending playout CTAs
-    cudaStream_t leaf_stream;  // playouts: low priority
-    cudaStream_t pending;    // the one of the two that carries the group's device work in flight
-    oakb200_ctx ctx;         // the library context with this group's stream / ticket word: launches need no lock
+    cudaStream_t stream;
     uint32_t wave = 0, depth = 0;
-    int phase = 0;           // 0 spawn, 1 select + step, 2 expand, 3 back-propagate, 4 finished, 5 leaves wait for CTA budget,
-                             // 6 leaves are in the shared playout queue
-    uint32_t batches = 0;    // playout batches enqueued so far (phase 6 waits for the device's count to match)
-    int leaf_ctas = 0;       // playout CTAs of this group in flight (returned to the budget at back-propagation)
-    bool stalled = false;    // the last advance() did nothing: no CTA budget
-    std::atomic<bool> at_leaves{false};  // has handed a batch of playouts / evaluations to the device at least once
+    int phase = 0;           // 0 spawn, 1 select + step, 2 expand, 3 back-propagate, 4 finished
+    bool reached_leaves = false;  // has launched a leaf phase at least once (the next group starts then: see below)
   };
-  // Playout CTAs live for milliseconds and are shared-memory heavy: once they fill every SM a tree level's kernel waits
-  // for one of them to end (measured: 5 ms per level round trip instead of 0.1 with 32 groups in flight). So the playout
-  // CTAs of ALL groups together are kept to 6 of the 8 an SM holds, which leaves room for one 48 KB step CTA per SM.
-  int lo_prio = 0, hi_prio = 0;
-  CU(ctx, cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-  int leaf_cta_budget_total = 6 * ctx->sm_count;
-  if (const char* c = getenv("OAKB200_SEARCH_LEAF_CTAS")) leaf_cta_budget_total = atoi(c);
-  std::atomic<int> leaf_cta_budget{leaf_cta_budget_total};
-  int n_threads = host_threads;
-  int per_thread = 1;  // streams in all (groups + 8 leaf streams + the caller's) stay below the 32 hardware queues
-  if (const char* g = getenv("OAKB200_SEARCH_GROUPS_PER_THREAD")) per_thread = atoi(g) > 0 ? atoi(g) : 1;
-  int n_groups = n_threads * per_thread;
+  // Measured on B200, 4 096 roots x 64 (tools/search_timeline.py): groups that start together stay in lockstep — all of
+  // them in the host-bound tree levels, then all of them waiting for their playouts — so group g + 1 starts its first wave
+  // only when group g has launched its first leaves, and from then on one group's leaves run under another's tree levels.
+  // 4 096 roots x 64, 16 waves on B200 + 16 host threads: 1 group 9.05 M iterations/s, 2: 8.7, 3: 9.9, 4: 10.8, 6: 9.6
+  int n_groups = 4;
   if (const char* g = getenv("OAKB200_SEARCH_GROUPS")) n_groups = atoi(g);
-  if (n_groups > 32) n_groups = 32;  // one lane of a playout worker looks at one group (rollout_queue.h)
-  if ((size_t)n_groups * 16 > R) n_groups = (int)((R + 15) / 16);  // at least 16 roots per group
   if (n_groups < 1) n_groups = 1;
-  if (n_threads > n_groups) n_threads = n_groups;
-  bool use_queue = s->leaf_mode == 0 && n_groups > 1;
-  if (const char* v = getenv("OAKB200_SEARCH_QUEUE")) use_queue = use_queue && v[0] != '0';
+  if (n_groups > 8) n_groups = 8;
+  if ((size_t)n_groups > R) n_groups = (int)R;
   std::vector<Group> groups(n_groups);
-  CU(ctx, cudaStreamSynchronize(ctx->stream));  // set_roots' uploads are on the context's stream
   for (int g = 0; g < n_groups; g++) {
-    Group& G = groups[g];
-    G.r0 = R * g / n_groups;
-    G.r1 = R * (g + 1) / n_groups;
-    G.stream = G.leaf_stream = nullptr;
-    CU(ctx, cudaStreamCreateWithPriority(&G.stream, cudaStreamNonBlocking, hi_prio));
-    if (!use_queue) CU(ctx, cudaStreamCreateWithPriority(&G.leaf_stream, cudaStreamNonBlocking, lo_prio));
-    G.pending = G.stream;
-    G.ctx = *ctx;
-    G.ctx.stream = G.stream;
-    G.ctx.own_stream = false;
-    G.ctx.ticket_slot = 8 + g;
-    G.ctx.launches = 0;
-    G.ctx.rollout_cta_cap = 6;
+    groups[g].r0 = R * g / n_groups;
+    groups[g].r1 = R * (g + 1) / n_groups;
+    groups[g].stream = nullptr;
+    if (n_groups == 1) groups[g].stream = ctx->stream;
+    else CU(ctx, cudaStreamCreateWithFlags(&groups[g].stream, cudaStreamNonBlocking));
   }
-  // MonteCarlo leaves of several groups go through the shared playout queue (rollout_queue.h): a batch = one enqueue on the
-  // group's stream + one worker launch on a stream of the leaf pool, sized by what is left of the CTA budget (workers in
-  // flight, all groups together, are kept to 6 of the 8 CTAs an SM holds so that a 48 KB step CTA still fits beside them;
-  // a batch always gets a few CTAs of its own, so every entry has a worker launched after it).
-  // OAKB200_SEARCH_QUEUE=0 keeps one playout launch per batch for A/B runs.
-  oakb200_rollout_queue queue{};
-  std::vector<cudaEvent_t> enqueued(n_groups, nullptr);
-  std::vector<cudaStream_t> leaf_streams;
-  if (use_queue) {
-    queue.next = s->d_queue;
-    queue.done = s->d_queue + 32;
-    queue.live = s->d_queue + 64;
-    uint32_t* d_first = s->d_queue + 96;
-    queue.group_first = d_first;
-    queue.n_groups = (uint32_t)n_groups;
-    queue.max_live = (uint32_t)leaf_cta_budget_total;  // CTAs
-    queue.poll_mask = 3;
-    queue.idle_ns = 5000;
-    if (const char* v = getenv("OAKB200_Q_POLL")) queue.poll_mask = (uint32_t)atoi(v);
-    if (const char* v = getenv("OAKB200_Q_IDLE_NS")) queue.idle_ns = (uint32_t)atoi(v);
-    queue.linger = 0;  // measured: lingering idle CTAs (400 x 5 us) cost more than the relaunches they save (42.6 vs 24.3 ms/wave)
-    if (const char* v = getenv("OAKB200_Q_LINGER")) queue.linger = (uint32_t)atoi(v);
-    queue.host_batches = s->h_signal;
-    uint32_t first[33];
-    for (int g = 0; g <= n_groups; g++) first[g] = (uint32_t)((R * (size_t)g / n_groups) * P);
-    for (int k = 0; k < 65; k++) s->h_signal[k] = 0;
-    CU(ctx, cudaMemsetAsync(s->d_queue, 0xFF, 32 * 4, ctx->stream));  // next[]: nothing to hand out
-    CU(ctx, cudaMemsetAsync(s->d_queue + 32, 0, 64 * 4, ctx->stream));
-    CU(ctx, cudaMemcpyAsync(d_first, first, (n_groups + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, cudaStreamSynchronize(ctx->stream));
-    for (auto& ev : enqueued) CU(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    leaf_streams.resize(4);
-    for (auto& L : leaf_streams) CU(ctx, cudaStreamCreateWithPriority(&L, cudaStreamNonBlocking, lo_prio));
+  if (n_groups > 1) CU(ctx, cudaStreamSynchronize(ctx->stream));  // set_roots' uploads are on the context's stream
+  cudaStream_t saved_stream = ctx->stream;
+  const int saved_slot = ctx->ticket_slot;
+  const int saved_cap = ctx->rollout_cta_cap;
+  // a playout launch that takes every CTA slot of every SM would hold back the other groups' small level kernels for its
+  // whole body: leave room for them
+  if (n_groups > 1) {
+    ctx->rollout_cta_cap = 6;
+    if (const char* c = getenv("OAKB200_SEARCH_ROLLOUT_CTAS")) ctx->rollout_cta_cap = atoi(c);
   }
-  // Workers are launched for several groups' batches at once (a flush): a batch of one group is too small to keep a launch
-  // busy past its longest playout, and few launches mean a leaf stream is reused only when its previous worker has long
-  // ended (a worker queued behind another one does not run). A flush happens when a quarter of the groups have entries
-  // pending, when every live group is waiting for playouts (nothing else can arrive), or when entries have been pending
-  // for 0.3 ms (looked at by idle threads). Every entry has a worker launched after it, which is what guarantees it is run.
-  std::mutex leaf_mu;
-  std::vector<cudaEvent_t> pending_events;
-  size_t pending_entries = 0;
-  int waiting_groups = 0, live_groups = n_groups, leaf_next = 0;
-  const int flush_at = n_groups >= 4 ? n_groups / 4 : 1;
-  std::chrono::steady_clock::time_point pending_since;
-  std::atomic<int> rc_out{OAKB200_OK};
-  std::mutex error_mu;
+  int rc_out = OAKB200_OK;
   auto fail_cuda = [&](cudaError_t e, const char* what) {
-    if (e != cudaSuccess) {
-      std::lock_guard<std::mutex> l(error_mu);
-      if (rc_out.load() == OAKB200_OK) rc_out = fail(ctx, OAKB200_ECUDA, what, e);
-    }
+    if (e != cudaSuccess && rc_out == OAKB200_OK) rc_out = fail(ctx, OAKB200_ECUDA, what, e);
     return e != cudaSuccess;
-  };
-  auto flush_pending = [&]() {  // leaf_mu held
-    if (pending_events.empty()) return;
-    cudaStream_t L = leaf_streams[leaf_next];
-    leaf_next = (leaf_next + 1) % (int)leaf_streams.size();
-    bool bad = false;
-    for (cudaEvent_t ev : pending_events) bad = bad || fail_cuda(cudaStreamWaitEvent(L, ev, 0), "search_run: event");
-    int ctas = (int)((pending_entries + 127) / 128);
-    if (ctas > leaf_cta_budget_total) ctas = leaf_cta_budget_total;
-    bad = bad || fail_cuda(oakb200_launch_rollout_worker(ctx, L, ctas, s->d_b, s->d_d, s->d_r, s->d_pseed, 100000, s->d_score, queue),
-                           "search_run: worker");
-    pending_events.clear();
-    pending_entries = 0;
-  };
-  auto fail_rc = [&](int rc, const Group& G) {  // a library call on the group's context failed: keep its message
-    std::lock_guard<std::mutex> l(error_mu);
-    if (rc_out.load() == OAKB200_OK) {
-      ctx->error = G.ctx.error;
-      rc_out = rc;
-    }
   };
   // the uniform draw of one Exp3-family selection: a function of (root seed, iteration, depth, player)
   auto exp3_u = [](uint64_t seed, uint64_t nth, uint32_t depth, int player) {
@@ -584,32 +566,22 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     return (double)(x >> 11) * (1.0 / 9007199254740992.0);
   };
 
-  // diagnostics (OAKB200_SEARCH_DEBUG=1 prints them), summed over the host threads: time in host phases, of that inside
-  // the tree loops of spawn / select / expand / back-propagate, and time with none of a thread's groups ready
-  std::atomic<long long> host_ns{0}, idle_ns{0};
-  std::atomic<long long> tree_ns[4];
-  for (auto& t : tree_ns) t = 0;
-  auto timed_for = [&](int which, size_t n, const std::function<void(size_t)>& fn) {
-    const auto t0 = std::chrono::steady_clock::now();
-    for (size_t k = 0; k < n; k++) fn(k);
-    tree_ns[which] += (std::chrono::steady_clock::now() - t0).count();
-  };
+  long long host_ns = 0, idle_ns = 0;  // diagnostics: OAKB200_SEARCH_DEBUG=1 prints them
   // one host phase of group G (its previous device work has finished) + the device work that follows it
   auto advance = [&](Group& G, int gi) {
     const size_t r0 = G.r0, nr = G.r1 - G.r0, b0 = r0 * P, nb = nr * P;
-    oakb200_ctx* gc = &G.ctx;
-    if (fail_cuda(cudaStreamSynchronize(G.pending), "search_run: stream")) return;
-    G.pending = G.stream;
-    gc->stream = G.stream;
+    ctx->stream = G.stream;
+    ctx->ticket_slot = 8 + gi;
+    if (fail_cuda(cudaStreamSynchronize(G.stream), "search_run: stream")) return;
     const auto t_host = std::chrono::steady_clock::now();
     struct HostTimer {
       std::chrono::steady_clock::time_point t0;
-      std::atomic<long long>& acc;
+      long long& acc;
       ~HostTimer() { acc += (std::chrono::steady_clock::now() - t0).count(); }
     } host_timer{t_host, host_ns};
     if (G.phase == 0) {
       // ---- spawn: fresh rng per particle, hidden variables redrawn from the root's observed durations
-      timed_for(0, nr, [&](size_t k) {
+      s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
         const uint64_t left = root.target - root.iterations;
@@ -627,10 +599,10 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
       });
       if (fail_cuda(cudaMemcpyAsync(s->d_rng + b0, s->h_rng + b0, nb * 8, cudaMemcpyHostToDevice, G.stream), "search_run: copy")) return;
       if (fail_cuda(cudaMemcpyAsync(s->d_pseed + b0, s->h_pseed + b0, nb * 8, cudaMemcpyHostToDevice, G.stream), "search_run: copy")) return;
-      if (fail_cuda(oakb200_launch_search_spawn(gc, s->d_root_b + r0 * 384, s->d_root_d + r0 * 8, s->d_root_r + r0, s->d_rng + b0, P,
+      if (fail_cuda(oakb200_launch_search_spawn(ctx, s->d_root_b + r0 * 384, s->d_root_d + r0 * 8, s->d_root_r + r0, s->d_rng + b0, P,
                                                 s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, (uint32_t)nb), "search_run: spawn")) return;
-      const int rc = oakb200_randomize_hidden_device(gc, nb, s->d_b + b0 * 384, s->d_d + b0 * 8);
-      if (rc) { fail_rc(rc, G); return; }
+      const int rc = oakb200_randomize_hidden_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8);
+      if (rc) { rc_out = rc; return; }
       G.depth = 0;
       G.phase = 1;
       // fall through to the first selection: it needs nothing from the device
@@ -638,7 +610,7 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     if (G.phase == 2) {
       // ---- expand: match the observation to a child, create it if new (mcts.h:355-361)
       const uint32_t depth = G.depth;
-      timed_for(2, nr, [&](size_t k) {
+      s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
         const PathEntry* level = root.path.data() + (size_t)depth * P;
@@ -681,8 +653,8 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     if (G.phase == 1) {
       // ---- select: one tree level per launch
       const uint32_t depth = G.depth;
-      size_t n_active = 0;
-      timed_for(1, nr, [&](size_t k) {
+      std::atomic<size_t> n_active{0};
+      s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
         if (root.path.size() < (size_t)(depth + 1) * P) root.path.resize((size_t)(depth + 1) * P);
@@ -723,12 +695,12 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
         }
         n_active += cnt;
       });
-      if (n_active != 0) {
+      if (n_active.load() != 0) {
         if (gi == 0) s->levels++;
         bool bad = fail_cuda(cudaMemcpyAsync(s->d_idx1 + b0, s->h_idx1 + b0, nb, cudaMemcpyHostToDevice, G.stream), "search_run: copy");
         bad = bad || fail_cuda(cudaMemcpyAsync(s->d_idx2 + b0, s->h_idx2 + b0, nb, cudaMemcpyHostToDevice, G.stream), "search_run: copy");
         bad = bad || fail_cuda(cudaMemcpyAsync(s->d_rolls + b0, s->h_rolls + b0, nb, cudaMemcpyHostToDevice, G.stream), "search_run: copy");
-        bad = bad || fail_cuda(oakb200_launch_search_step(gc, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_idx1 + b0, s->d_idx2 + b0,
+        bad = bad || fail_cuda(oakb200_launch_search_step(ctx, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_idx1 + b0, s->d_idx2 + b0,
                                                           s->d_rolls + b0, s->d_act + b0 * 16, s->d_cnt + b0 * 2, (uint32_t)nb), "search_run: step");
         bad = bad || fail_cuda(cudaMemcpyAsync(s->h_res + b0, s->d_r + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy");
         bad = bad || fail_cuda(cudaMemcpyAsync(s->h_act + b0 * 16, s->d_act + b0 * 16, nb * 16, cudaMemcpyDeviceToHost, G.stream), "search_run: copy");
@@ -742,74 +714,30 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
         // the network's value of every leaf (mcts.h:409-424) with the durations tracked down the path, and for the
         // contextual bandits its policy logits over the leaf's legal choices; a finished battle's score replaces the
         // value at back-propagation
-        const int rc = oakb200_eval_device(gc, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_value + b0, s->d_logits + b0 * 18,
+        const int rc = oakb200_eval_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_value + b0, s->d_logits + b0 * 18,
                                            s->d_ecnt + b0 * 2);
-        if (rc) { fail_rc(rc, G); return; }
+        if (rc) { rc_out = rc; return; }
         if (fail_cuda(cudaMemcpyAsync(s->h_value + b0, s->d_value + b0, nb * 4, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
         if (fail_cuda(cudaMemcpyAsync(s->h_res + b0, s->d_r + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
         if (bp.contextual() &&
             fail_cuda(cudaMemcpyAsync(s->h_logits + b0 * 18, s->d_logits + b0 * 18, nb * 18 * 4, cudaMemcpyDeviceToHost, G.stream), "search_run: copy"))
           return;
-        G.at_leaves = true;
         G.phase = 3;
+        G.reached_leaves = true;
         return;
       }
-      G.phase = 5;
-    }
-    if (G.phase == 5 && use_queue) {
-      // publish the batch: next[g] = 0, ordered after the tree levels' kernels on the group's stream
-      if (fail_cuda(cudaMemsetAsync(queue.next + gi, 0, 4, G.stream), "search_run: publish")) return;
-      if (fail_cuda(cudaEventRecord(enqueued[gi], G.stream), "search_run: event")) return;
-      {
-        std::lock_guard<std::mutex> l(leaf_mu);
-        if (pending_events.empty()) pending_since = std::chrono::steady_clock::now();
-        pending_events.push_back(enqueued[gi]);
-        pending_entries += nb;
-        waiting_groups++;
-        if ((int)pending_events.size() >= flush_at || waiting_groups >= live_groups) flush_pending();
-      }
-      G.batches++;
-      G.at_leaves = true;
-      G.phase = 6;
-      return;
-    }
-    if (G.phase == 6) {  // the batch is finished (the scheduler saw its count): bring the scores over
-      {
-        std::lock_guard<std::mutex> l(leaf_mu);
-        waiting_groups--;
-      }
+      // playouts (a finished battle returns its score at once)
+      const int rc = oakb200_rollout_device(ctx, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_pseed + b0, 100000, 0,
+                                            s->d_score + b0, nullptr, nullptr);
+      if (rc) { rc_out = rc; return; }
       if (fail_cuda(cudaMemcpyAsync(s->h_score + b0, s->d_score + b0, nb, cudaMemcpyDeviceToHost, G.stream), "search_run: copy")) return;
       G.phase = 3;
-      return;
-    }
-    if (G.phase == 5) {
-      // playouts (a finished battle returns its score at once), once the CTA budget has room for this group's launch
-      const int want_ctas = (int)std::min<size_t>((nb + 127) / 128, (size_t)gc->rollout_cta_cap * ctx->sm_count);
-      const int want = std::min(want_ctas, leaf_cta_budget_total);
-      if (leaf_cta_budget.fetch_sub(want) < want) {
-        leaf_cta_budget.fetch_add(want);
-        G.stalled = true;
-        return;  // other groups' playouts hold the SMs: come back
-      }
-      G.leaf_ctas = want;
-      gc->stream = G.leaf_stream;
-      const int rc = oakb200_rollout_device(gc, nb, s->d_b + b0 * 384, s->d_d + b0 * 8, s->d_r + b0, s->d_pseed + b0, 100000, 0,
-                                            s->d_score + b0, nullptr, nullptr);
-      gc->stream = G.stream;
-      if (rc) { fail_rc(rc, G); return; }
-      if (fail_cuda(cudaMemcpyAsync(s->h_score + b0, s->d_score + b0, nb, cudaMemcpyDeviceToHost, G.leaf_stream), "search_run: copy")) return;
-      G.pending = G.leaf_stream;
-      G.at_leaves = true;
-      G.phase = 3;
+      G.reached_leaves = true;
       return;
     }
     if (G.phase == 3) {
-      if (G.leaf_ctas) {
-        leaf_cta_budget.fetch_add(G.leaf_ctas);
-        G.leaf_ctas = 0;
-      }
       // ---- back-propagation (mcts.h:363-384), particle by particle in index order
-      timed_for(3, nr, [&](size_t k) {
+      s->pool->parallel_for(nr, [&](size_t k) {
         const size_t r = r0 + k;
         Root& root = s->roots[r];
         auto prefetch_path = [&](uint32_t p) {  // the nodes particle p's value will be added to
@@ -860,102 +788,54 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
     }
   };
 
-  // one scheduler per host thread over the groups it owns (g % n_threads == t): advance any whose stream has drained;
-  // with none ready, give the core away briefly
-  // OAKB200_SEARCH_DEBUG=2: thread 0's timeline, (start ms, end ms, group, phase entered, depth) of its last host phases
-  struct Trace { double t0, t1; int g, phase; uint32_t depth; };
+  // OAKB200_SEARCH_DEBUG=2: a timeline of (start ms, end ms, group, phase entered) for every host phase
+  struct Trace { double t0, t1; int g, phase; };
   std::vector<Trace> trace;
   const bool tracing = getenv("OAKB200_SEARCH_DEBUG") && atoi(getenv("OAKB200_SEARCH_DEBUG")) >= 2;
   const auto t_begin = std::chrono::steady_clock::now();
   auto ms_now = [&] { return (std::chrono::steady_clock::now() - t_begin).count() * 1e-6; };
-  int idle_us = 50;
-  if (const char* v = getenv("OAKB200_SEARCH_IDLE_US")) idle_us = atoi(v);
-  auto thread_main = [&](int t) {
-    if (cudaSetDevice(ctx->device) != cudaSuccess) {
-      fail_cuda(cudaGetLastError(), "search_run: cudaSetDevice");
-      return;
+  // scheduler: advance any group whose stream has drained; when none has, wait for one
+  int live = n_groups;
+  while (live > 0 && rc_out == OAKB200_OK) {
+    bool progressed = false;
+    for (int g = 0; g < n_groups && rc_out == OAKB200_OK; g++) {
+      Group& G = groups[g];
+      if (G.phase == 4) continue;
+      if (g > 0 && G.wave == 0 && G.phase == 0 && !groups[g - 1].reached_leaves && groups[g - 1].phase != 4) continue;  // stagger
+      const cudaError_t q = cudaStreamQuery(G.stream);
+      if (q == cudaErrorNotReady) continue;
+      if (fail_cuda(q, "search_run: stream")) break;
+      const double t0 = tracing ? ms_now() : 0;
+      const int ph = G.phase;
+      advance(G, g);
+      if (tracing) trace.push_back({t0, ms_now(), g, ph});
+      progressed = true;
+      if (G.phase == 4) live--;
     }
-    int live = 0;
-    for (int g = t; g < n_groups; g += n_threads) live++;
-    while (live > 0 && rc_out.load() == OAKB200_OK) {
-      bool progressed = false;
-      for (int g = t; g < n_groups && rc_out.load() == OAKB200_OK; g += n_threads) {
-        Group& G = groups[g];
-        if (G.phase == 4) continue;
-        // Groups that start together stay together — all in their tree levels (device idle), then all waiting for their
-        // playouts (host idle). So every second group starts only when its neighbour has reached its first leaves; from
-        // then on one half's playouts run under the other half's tree levels.
-        if ((g & 1) && G.wave == 0 && G.phase == 0 && !groups[g - 1].at_leaves.load() && groups[g - 1].phase != 4) continue;
-        if (G.phase == 6 && queue.host_batches[g] != G.batches) continue;
-        const cudaError_t q = cudaStreamQuery(G.pending);
-        if (q == cudaErrorNotReady) continue;
-        if (fail_cuda(q, "search_run: stream")) break;
-        const double t0 = tracing && t == 0 ? ms_now() : 0;
-        const int ph = G.phase;
-        const uint32_t dp = G.depth;
-        advance(G, g);
-        if (G.stalled) {
-          G.stalled = false;
-          continue;
-        }
-        if (tracing && t == 0) trace.push_back({t0, ms_now(), g, ph, dp});
-        progressed = true;
-        if (G.phase == 4) {
-          live--;
-          if (use_queue) {
-            std::lock_guard<std::mutex> l(leaf_mu);
-            live_groups--;
-            if (waiting_groups >= live_groups) flush_pending();
-          }
-        }
-      }
-      if (!progressed && live > 0 && use_queue && leaf_mu.try_lock()) {
-        if (!pending_events.empty() && std::chrono::steady_clock::now() - pending_since > std::chrono::microseconds(300)) flush_pending();
-        leaf_mu.unlock();
-      }
-      if (!progressed && live > 0) {
-        // sleep rather than spin: a device phase lasts 0.1 ms (a tree level) to several ms (playouts), the host cores
-        // are shared with the other threads' tree work (and, in a container, with a CPU quota that spinning would burn)
-        const auto t0 = std::chrono::steady_clock::now();
-        if (idle_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(idle_us));
-        else std::this_thread::yield();
-        idle_ns += (std::chrono::steady_clock::now() - t0).count();
-      }
+    if (!progressed && live > 0) {
+      const auto t0 = std::chrono::steady_clock::now();
+      std::this_thread::yield();
+      idle_ns += (std::chrono::steady_clock::now() - t0).count();
     }
-  };
-  {
-    std::vector<std::thread> threads;
-    for (int t = 1; t < n_threads; t++) threads.emplace_back(thread_main, t);
-    thread_main(0);
-    for (auto& th : threads) th.join();
   }
-  const double total_ms = (std::chrono::steady_clock::now() - t_begin).count() * 1e-6;
+  ctx->stream = saved_stream;
+  ctx->ticket_slot = saved_slot;
+  ctx->rollout_cta_cap = saved_cap;
   if (getenv("OAKB200_SEARCH_DEBUG"))
-    fprintf(stderr, "[oakb200] search_run: %u waves, %d groups on %d host threads, %.1f ms; per thread: host phases %.1f ms (tree loops: "
-                    "spawn %.1f select %.1f expand %.1f back-propagate %.1f; the rest = copies and launches), no group ready %.1f ms\n",
-            waves, n_groups, n_threads, total_ms, host_ns * 1e-6 / n_threads, tree_ns[0] * 1e-6 / n_threads, tree_ns[1] * 1e-6 / n_threads,
-            tree_ns[2] * 1e-6 / n_threads, tree_ns[3] * 1e-6 / n_threads, idle_ns * 1e-6 / n_threads);
+    fprintf(stderr, "[oakb200] search_run: %u waves x %d groups, host phases %.1f ms, idle (every group on the device) %.1f ms\n", waves,
+            n_groups, host_ns * 1e-6, idle_ns * 1e-6);
   if (tracing) {
-    fprintf(stderr, "[oakb200] thread 0, last host phases (ms from run start; phase entered: 0 spawn 1 select 2 expand 3 back-propagate):\n");
-    for (size_t k = trace.size() > 40 ? trace.size() - 40 : 0; k < trace.size(); k++)
-      fprintf(stderr, "  g%-2d phase %d depth %u  %8.2f -> %8.2f  (%.2f)\n", trace[k].g, trace[k].phase, trace[k].depth, trace[k].t0, trace[k].t1,
-              trace[k].t1 - trace[k].t0);
+    const double total = ms_now();
+    fprintf(stderr, "[oakb200] timeline of the last wave (ms from run start; total %.2f):\n", total);
+    size_t from = trace.size() > (size_t)(14 * n_groups) ? trace.size() - 14 * n_groups : 0;
+    for (size_t k = from; k < trace.size(); k++)
+      fprintf(stderr, "  g%d phase %d  %8.2f -> %8.2f  (%.2f)\n", trace[k].g, trace[k].phase, trace[k].t0, trace[k].t1, trace[k].t1 - trace[k].t0);
   }
-  for (auto L : leaf_streams) {
-    cudaStreamSynchronize(L);
-    cudaStreamDestroy(L);
-  }
-  for (auto ev : enqueued)
-    if (ev) cudaEventDestroy(ev);
-  for (auto& G : groups) {
-    cudaStreamSynchronize(G.stream);
-    cudaStreamDestroy(G.stream);
-    if (G.leaf_stream) {
-      cudaStreamSynchronize(G.leaf_stream);
-      cudaStreamDestroy(G.leaf_stream);
+  if (n_groups > 1)
+    for (auto& G : groups) {
+      cudaStreamSynchronize(G.stream);
+      cudaStreamDestroy(G.stream);
     }
-    ctx->launches += G.ctx.launches;
-  }
   return rc_out;
 }
 

@@ -4,7 +4,7 @@ sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/tests')
 import oak_b200
 from oak_b200.search import TreeSearch
 from oak_ref import sample_seeds, sample_teams
-roots = 4096
+roots = int(os.environ.get("ROOTS", "4096"))
 eng = oak_b200.BattleEngine(roots)
 seeds = sample_seeds(0, roots)
 eng.build_battles(sample_teams(0, roots), seeds)
