@@ -560,6 +560,7 @@ def main():
     ts.run(SR_ITERS)
     barrier()
     sr_s = time.perf_counter() - t0
+    sr_timing = ts.timing()
     launches += eng.launch_count - l0
     sr_out = ts.output()
     sr_done = float(sr_b.shape[0] * SR_ITERS)
@@ -695,6 +696,11 @@ def main():
                                                "padding included); dense-equivalent = SURVEY 8d F_eval"},
                           "cpu_evals_per_s": eval_cpu, "cpu_kind": "port (oracle/nn_oracle.hpp)"},
             "tree_search": {"iterations_per_s": tot_sr / (sr_ms_max * 1e-3), "roots_total": int(tot_sr / SR_ITERS),
+                            "rank0_ms_per_wave": {"total": round(sr_timing["total_ms"] / max(sr_timing["waves"], 1), 2),
+                                                  "host_phases": round(sr_timing["host_ms"] / max(sr_timing["waves"], 1), 2),
+                                                  "all_groups_on_device": round(sr_timing["device_wait_ms"] / max(sr_timing["waves"], 1), 2),
+                                                  "note": "host_phases = tree work of the thread pool + copies and launches, one group at a "
+                                                          "time; the rest of the wave the calling thread polls streams that are still busy"},
                             "descents_in_flight_per_root": SR_P, "iterations_per_root": SR_ITERS,
                             "mean_root_value": float(sr_out["empirical_value"].mean()),
                             "cpu_iterations_per_s": sr_cpu, "cpu_kind": "port (sequential MCTS restatement, all host cores)",

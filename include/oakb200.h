@@ -255,6 +255,10 @@ int oakb200_solve_matrix(int rows, int cols, const int* payoff, int denom, float
 /* process_output's Nash half for every root (mcts.h:628-656: average values discretised to 1/256, then solved):
  * nash[n][2][9] f32 (zero past k), nash_value[n] f32. Either may be NULL. */
 int oakb200_search_nash(oakb200_search* search, float* nash, float* nash_value);
+/* Where the wall time of the last oakb200_search_run went (no counterpart in the reference; a measurement aid):
+ * out4 = {total ms, ms the calling thread spent in host phases (tree work of the pool + copies and launches),
+ * ms it spent with every root group's work on the device, waves}. */
+int oakb200_search_timing(oakb200_search* search, double* out4);
 
 /* ---- training rows: stored games -> the dense tensors the learner trains on ------------------------------------------
  * Replaces pyoak's EncodedBattleFrames.from_bytes / sample (reference cpp/include/py/battle/encoded-frames.h:24-133,

@@ -356,6 +356,8 @@ struct oakb200_search {
   Pool* pool = nullptr;
   int pool_threads = 0;
   uint64_t levels = 0, waves = 0;
+  double last_host_ms = 0, last_idle_ms = 0, last_total_ms = 0;  // of the last oakb200_search_run
+  uint32_t last_waves = 0;
 };
 
 namespace {
@@ -413,6 +415,15 @@ int oakb200_search_create(oakb200_ctx* ctx, size_t roots, uint32_t particles, oa
 }
 
 void oakb200_search_destroy(oakb200_search* s) { search_free(s); }
+
+int oakb200_search_timing(oakb200_search* s, double* out4) {
+  if (!s || !out4) return OAKB200_EINVAL;
+  out4[0] = s->last_total_ms;
+  out4[1] = s->last_host_ms;
+  out4[2] = s->last_idle_ms;
+  out4[3] = (double)s->last_waves;
+  return OAKB200_OK;
+}
 
 int oakb200_search_set_roots(oakb200_search* s, size_t n, const uint8_t* battles, const uint8_t* durations, const uint8_t* results,
                              const uint64_t* seeds) {
@@ -821,6 +832,10 @@ int oakb200_search_run(oakb200_search* s, uint32_t iterations, float ucb_c, uint
   ctx->stream = saved_stream;
   ctx->ticket_slot = saved_slot;
   ctx->rollout_cta_cap = saved_cap;
+  s->last_host_ms = host_ns * 1e-6;
+  s->last_idle_ms = idle_ns * 1e-6;
+  s->last_total_ms = (std::chrono::steady_clock::now() - t_begin).count() * 1e-6;
+  s->last_waves = waves;
   if (getenv("OAKB200_SEARCH_DEBUG"))
     fprintf(stderr, "[oakb200] search_run: %u waves x %d groups, host phases %.1f ms, idle (every group on the device) %.1f ms\n", waves,
             n_groups, host_ns * 1e-6, idle_ns * 1e-6);

@@ -79,6 +79,15 @@ class TreeSearch:
                                                                                   "iterations", "empirical_value", "empirical", "nodes")]))
         return out
 
+    def timing(self):
+        """-> dict(total_ms, host_ms, device_wait_ms, waves) of the last run (oakb200_search_timing)."""
+        out = (ctypes.c_double * 4)()
+        f = self.lib.oakb200_search_timing
+        f.restype = ctypes.c_int
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        self._check(f(self._h, out))
+        return dict(total_ms=out[0], host_ms=out[1], device_wait_ms=out[2], waves=int(out[3]))
+
     def set_leaf(self, mode):
         """0 = MonteCarlo playouts, 1 = the loaded network's value at every new leaf."""
         f = self.lib.oakb200_search_set_leaf
