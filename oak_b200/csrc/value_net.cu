@@ -550,7 +550,27 @@ struct Packer {
     return pm;
   }
 
-  void stage(const PackedMatrix& pm, uint32_t a_hi, uint32_t a_lo, int lo_ksteps, uint32_t dcol, bool overwrite, uint8_t end_flag) {
+  // the same with the A operand in Tensor Memory (tc::hidden_tmem_col): a_off16 = the chunk's first K step
+  void stage_tmem(const PackedMatrix& pm, uint32_t dcol, bool overwrite, uint8_t end_flag) {
+    for (size_t j = 0; j < pm.pieces.size(); j++) {
+      const auto& pc = pm.pieces[j];
+      tc::Chunk c;
+      c.gofs16 = pc.gofs16;
+      c.bytes16 = (uint16_t)pc.bytes16;
+      c.ksteps = (uint8_t)pc.ksteps;
+      c.n8 = (uint8_t)(pm.N / 8);
+      c.a_off16 = (uint16_t)pc.k0;
+      c.alo_off16 = 0;
+      c.lo_steps = (uint8_t)pc.ksteps;
+      c.flags = (uint8_t)(tc::F_A_TMEM | tc::F_WAIT_A2 | (j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
+                          (j + 1 == pm.pieces.size() ? end_flag : 0));
+      c.dcol = (uint16_t)dcol;
+      prog.push_back(c);
+    }
+  }
+
+  void stage(const PackedMatrix& pm, uint32_t a_hi, uint32_t a_lo, int lo_ksteps, uint32_t dcol, bool overwrite, uint8_t end_flag,
+             uint8_t begin_on = 0) {
     for (size_t j = 0; j < pm.pieces.size(); j++) {
       const auto& pc = pm.pieces[j];
       tc::Chunk c;
@@ -564,7 +584,7 @@ struct Packer {
       if (lo < 0) lo = 0;
       if (lo > (int)pc.ksteps) lo = (int)pc.ksteps;
       c.lo_steps = (uint8_t)lo;
-      c.flags = (uint8_t)((j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
+      c.flags = (uint8_t)(begin_on | (j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
                           (j + 1 == pm.pieces.size() ? end_flag : 0));
       c.dcol = (uint16_t)dcol;
       prog.push_back(c);
@@ -613,14 +633,21 @@ cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
     P.stage(ac0p, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, false, tc::F_END_D);
     P.stage(ac1, tc::A2_HI, tc::A2_LO, 8, tc::D_WORK, true, tc::F_END_D);
     P.stage(fa[s], tc::AEA_HI, tc::AEA_LO, 6, tc::D_TRUNK, s == 0, tc::F_END_T);
+    // the benched slots, software-pipelined (value_net_tc.cuh, worker loop): L1(0) | L2(p) L1(p + 1) T(p) ...; the hidden
+    // layer goes from the first layer's accumulator to the second layer's A operand without leaving Tensor Memory
+    P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
     for (int p = 0; p < 5; p++) {
-      P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
-      P.stage(pk1, tc::A2_HI, tc::A2_LO, 8, tc::D_WORK, true, tc::F_END_D);
-      P.stage(fp[s][p], tc::AEP_HI, tc::AEP_LO, 4, tc::D_TRUNK, false, tc::F_END_T);
+      P.stage_tmem(pk1, tc::D_EMB, true, tc::F_END_E);
+      if (p < 4) P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+      P.stage(fp[s][p], tc::AEP_HI, tc::AEP_LO, 4, tc::D_TRUNK, false, tc::F_END_T, tc::F_WAIT_E);
     }
   }
   P.stage(fc1, tc::AT_HI, tc::AT_LO, 4, tc::D_WORK, true, tc::F_END_D);
   P.stage(heads, tc::AEP_HI, tc::AEP_LO, 4, tc::D_HEADS, true, tc::F_END_D);
+  if (getenv("OAKB200_EVAL_DEBUG"))
+    for (size_t i = 0; i < P.prog.size(); i++)
+      fprintf(stderr, "[prog %3zu] ksteps %u n %u a_off16 %u lo_steps %u flags 0x%02x dcol %u bytes %u\n", i, P.prog[i].ksteps,
+              P.prog[i].n8 * 8, P.prog[i].a_off16, P.prog[i].lo_steps, P.prog[i].flags, P.prog[i].dcol, P.prog[i].bytes16 * 16);
   if (P.prog.size() > tc::PROG_MAX) {
     n->tc_ok = false;
     return cudaSuccess;

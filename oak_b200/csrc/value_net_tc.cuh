@@ -51,7 +51,13 @@ struct Chunk {        // 16 bytes; one weight chunk = `ksteps` K=16 steps of a [
   uint8_t flags;
   uint16_t dcol;      // TMEM column of D
 };
-enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8 };
+enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8, F_A_TMEM = 16, F_WAIT_A2 = 32, F_WAIT_E = 64, F_END_E = 128 };
+// The benched slots are software-pipelined, so two hand-overs of one direction can be outstanding at once; each kind has its
+// own mbarrier (a parity wait must never fall two phases behind): a stage begins on bar_a (features / everything else),
+// bar_a2 (F_WAIT_A2: hidden layer in Tensor Memory) or bar_ae (F_WAIT_E: benched embedding operand); its end is committed to
+// bar_d, bar_e (F_END_E: second layer of a benched slot) or bar_t.
+// F_A_TMEM: the A operand is the hidden layer the workers left in Tensor Memory in place of the first layer's accumulator
+// (hidden_tmem_col below); a_off16 then holds the index of the chunk's first K step, both planes exist for every step
 
 const int ROWS = 128;
 #ifndef OAKB200_TC_GROUPS
@@ -75,8 +81,8 @@ const uint32_t OFF_PROG = OFF_RING + RING_SLOTS * RING_SLOT;
 const uint32_t PROG_MAX = 192;
 const uint32_t OFF_CONST = OFF_PROG + PROG_MAX * 16;
 const uint32_t CONST_FLOATS = 740;
-const uint32_t OFF_BAR = OFF_CONST + CONST_FLOATS * 4;  // full[4], empty[4], a_ready, d_ready, t_done, heads_ready, heads_free
-const uint32_t OFF_TMEM_SLOT = OFF_BAR + 13 * 8;
+const uint32_t OFF_BAR = OFF_CONST + CONST_FLOATS * 4;  // full[4], empty[4], a_ready, d_ready, t_done, heads_ready, heads_free, a2_ready, ae_ready, e_done
+const uint32_t OFF_TMEM_SLOT = OFF_BAR + 16 * 8;
 const uint32_t OFF_ROWIDX = OFF_TMEM_SLOT + 8;          // [2 players][128 rows][12] u16: last-layer rows of the legal choices
 const uint32_t SMEM_BYTES = OFF_ROWIDX + 2 * ROWS * 24;
 static_assert(OFF_ROWIDX % 8 == 0, "row index records are written as 32-bit words");
@@ -92,6 +98,12 @@ const uint32_t AT_HI = OFF_UNION, AT_LO = OFF_UNION + 8 * CORE;    // trunk hidd
 const uint32_t AEP_HI = OFF_EMB, AEP_LO = OFF_EMB + 8 * CORE;      // benched embedding / second trunk operand, K = 64
 // TMEM columns
 const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // one CTA per SM: all of Tensor Memory
+const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (64 columns): beside the first layer's, not over it
+// Hidden activations of a benched slot stay in Tensor Memory as the split-bf16 A operand of the second layer (two K elements
+// per 32-bit column, K step i = 8 columns): the hi plane over the upper half of the first layer's accumulator, the lo plane
+// in the free columns behind the head accumulators (layout of an A operand in Tensor Memory: tools/probes/ts_mma_probe*.cu).
+const uint32_t H_HI = 64, H_LO = 416;
+__host__ __device__ inline uint32_t hidden_tmem_col(uint32_t kstep) { return H_HI + 8u * kstep; }
 // constants block (floats)
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
 const int K_POK = 208, K_ACT = 240;
@@ -427,6 +439,44 @@ __device__ __forceinline__ void epilogue_half(uint32_t taddr, int q, const float
   else if (mode == 1) epilogue_half_m<1>(taddr, q, bias, bound, hi, lo, r);
   else epilogue_half_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
+// First-layer epilogue of a benched slot, Tensor Memory to Tensor Memory (see hidden_tmem_col): group g's 64 accumulator
+// columns [64 g, 64 g + 64) -> bias, activation -> K elements 64 g .. 64 g + 63 of the two planes. The hi plane overlies the
+// columns group 1 reads, so every worker has its accumulators in registers (SYNC: a barrier of all workers) before any store.
+template <class SYNC>
+__device__ __forceinline__ void epilogue_hidden_tmem(uint32_t tl, int grp, const float* bias, float bound, SYNC sync) {
+  uint32_t v0[32], v1[32];
+  const uint32_t t0 = tl + D_WORK + 64u * (uint32_t)grp;
+  umma::tmem_ld32(t0, v0);
+  umma::tmem_ld32(t0 + 32u, v1);
+  umma::tmem_ld_wait();
+  sync();
+#pragma unroll
+  for (int b = 0; b < 2; b++) {
+    uint32_t h[16], l[16];
+    const float4* b4 = reinterpret_cast<const float4*>(bias + 64 * grp + 32 * b);
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
+      const uint32_t* v = b ? v1 : v0;
+      const float x0 = epi_act<0>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
+      const float x1 = epi_act<0>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
+      const float x2 = epi_act<0>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
+      const float x3 = epi_act<0>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
+      const float x4 = epi_act<0>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
+      const float x5 = epi_act<0>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
+      const float x6 = epi_act<0>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
+      const float x7 = epi_act<0>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
+      split2(x0, x1, h[4 * g + 0], l[4 * g + 0]);
+      split2(x2, x3, h[4 * g + 1], l[4 * g + 1]);
+      split2(x4, x5, h[4 * g + 2], l[4 * g + 2]);
+      split2(x6, x7, h[4 * g + 3], l[4 * g + 3]);
+    }
+    // K elements 64 grp + 32 b .. + 31 = columns 32 grp + 16 b .. + 15 of each plane
+    umma::tmem_st16(tl + H_HI + 32u * (uint32_t)grp + 16u * (uint32_t)b, h);
+    umma::tmem_st16(tl + H_LO + 32u * (uint32_t)grp + 16u * (uint32_t)b, l);
+  }
+  umma::tmem_st_wait();
+}
 // mode is warp-uniform (a property of the loaded network)
 __device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
                                                int mode = 0) {
@@ -455,7 +505,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bar = smem + OFF_BAR;
   const uint32_t bar_full = bar, bar_empty = bar + 32, bar_a = bar + 64, bar_d = bar + 72, bar_t = bar + 80;
-  const uint32_t bar_h = bar + 88, bar_hfree = bar + 96;
+  const uint32_t bar_h = bar + 88, bar_hfree = bar + 96, bar_a2 = bar + 104, bar_ae = bar + 112, bar_e = bar + 120;
   const uint32_t ntiles = (n + ROWS - 1) / ROWS;
   // CTA `crank` of cluster `blockIdx.x / CL` takes tile base + crank of every group of CL tiles the cluster visits; a
   // tile index >= ntiles is a dummy (rows clamp to the last evaluation, nothing is written) so that the CTAs of a
@@ -470,6 +520,9 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       umma::mbar_init(bar_empty + 8 * i, CL);
     }
     umma::mbar_init(bar_a, WORKERS / 32);
+    umma::mbar_init(bar_a2, WORKERS / 32);
+    umma::mbar_init(bar_ae, WORKERS / 32);
+    umma::mbar_init(bar_e, 1);
     umma::mbar_init(bar_d, 1);
     umma::mbar_init(bar_t, 1);
     umma::mbar_init(bar_h, 2 * ROWS / 32);  // one arrival per warp of worker groups 0 and 1
@@ -520,7 +573,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
   } else if (warp == W_MMA) {
     // ===== MMA issuer =====
     if (umma::elect_one()) {
-      uint32_t g = 0, stage = 0;
+      uint32_t g = 0, stage = 0, stage_a2 = 0, stage_e = 0;
 #ifdef OAKB200_TC_TIMING  // diagnostic build only: where the issuer's time goes, by N of the stage (printed by CTA 0)
       long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0, tm4 = 0;  // wait workers, wait weights, issue, drain, commit
       uint32_t tm_d = 0, tm_t = 0;
@@ -529,13 +582,36 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #endif
       for (uint32_t t = tile0; t < ntiles; t += tile_step) {
         for (int c = 0; c < P.nchunks; c++, g++) {
-          const Chunk ch = prog[c];
+          // The chunk record is read with one explicit 16-byte load and decoded by shifts: with the struct copy
+          // `const Chunk ch = prog[c]` ptxas 12.9 was seen to take dcol from a register the load never wrote
+          // (profiles/r2l_eval_tc_tmem.txt), which sent every accumulator but column 0 astray.
+          struct { uint32_t ksteps, n8, a_off16, alo_off16, lo_steps, flags, dcol; } ch;
+          {
+            uint32_t w0, w1, w2, w3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(smem + OFF_PROG + 16u * (uint32_t)c));
+            (void)w0;
+            ch.ksteps = (w1 >> 16) & 0xffu;
+            ch.n8 = w1 >> 24;
+            ch.a_off16 = w2 & 0xffffu;
+            ch.alo_off16 = w2 >> 16;
+            ch.lo_steps = w3 & 0xffu;
+            ch.flags = (w3 >> 8) & 0xffu;
+            ch.dcol = w3 >> 16;
+          }
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm2);
 #endif
           if (ch.flags & F_STAGE_BEGIN) {
-            OAKB200_TC_WAIT(bar_a, stage & 1);
-            stage++;
+            if (ch.flags & F_WAIT_A2) {
+              OAKB200_TC_WAIT(bar_a2, stage_a2 & 1);
+              stage_a2++;
+            } else if (ch.flags & F_WAIT_E) {
+              OAKB200_TC_WAIT(bar_ae, stage_e & 1);
+              stage_e++;
+            } else {
+              OAKB200_TC_WAIT(bar_a, stage & 1);
+              stage++;
+            }
           }
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm0);
@@ -566,6 +642,18 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #endif
           uint32_t acc = (ch.flags & F_OVERWRITE) ? 0u : 1u;
           const uint32_t lo_steps = ch.lo_steps, ksteps = ch.ksteps;
+          if (ch.flags & F_A_TMEM) {  // A = the hidden layer in Tensor Memory
+            for (uint32_t i = 0; i < ksteps; i++) {
+              const uint32_t a_t = tmem + hidden_tmem_col((uint32_t)ch.a_off16 + i);
+              umma::mma_bf16_ts(d, a_t, dbh, idesc, acc);
+              umma::mma_bf16_ts(d, a_t, dbl, idesc, 1u);
+              umma::mma_bf16_ts(d, a_t - H_HI + H_LO, dbh, idesc, 1u);
+              acc = 1u;
+              dbh += b_step;
+              dbl += b_step;
+            }
+          }
+          const uint32_t ss_steps = (ch.flags & F_A_TMEM) ? 0u : ksteps;  // the K steps whose A operand is in shared memory
 #ifdef OAKB200_TC_NO_MMA  // timing experiment only: no tensor-core work is issued, results are garbage
           if (ksteps) { da = dal = dbh = dbl = 0; }
           for (uint32_t i = 0; i < 0; i++) {
@@ -577,7 +665,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
             dbh += b_step;
             continue;
 #else
-          for (uint32_t i = 0; i < ksteps; i++) {
+          for (uint32_t i = 0; i < ss_steps; i++) {
 #endif
 #ifdef OAKB200_TC_WIDE_TIMING  // timing experiment only: A_hi x [B_hi | B_lo] as ONE instruction of twice the N, results are garbage
             if (N <= 128) umma::mma_bf16(d, da, dbh, umma::idesc_bf16_f32(2 * N), acc);
@@ -599,6 +687,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
           else umma::mma_commit(bar_empty + 8 * slot);
           if (ch.flags & F_END_D) umma::mma_commit(bar_d);
+          if (ch.flags & F_END_E) umma::mma_commit(bar_e);
           if (ch.flags & F_END_T) umma::mma_commit(bar_t);
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm4);
@@ -705,12 +794,20 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #else
 #define WT_LAP(k) do { } while (0)
 #endif
-    auto publish = [&]() {  // operand written / TMEM read: hand over to the MMA issuer
+    auto publish_on = [&](uint32_t which) {  // operand written / TMEM read: hand over to the MMA issuer
       umma::tc_fence_before();
       umma::fence_proxy_async();
       __syncwarp();  // one arrival per warp
-      if (lane == 0) umma::mbar_arrive(bar_a);
+      if (lane == 0) umma::mbar_arrive(which);
       WT_LAP(2);
+    };
+    auto publish = [&]() { publish_on(bar_a); };
+    uint32_t ephase = 0;
+    auto wait_e = [&]() {
+      OAKB200_TC_WAIT(bar_e, ephase & 1);
+      ephase++;
+      umma::tc_fence_after();
+      WT_LAP(0);
     };
     auto wait_d = [&]() {
       OAKB200_TC_WAIT(bar_d, dphase & 1);
@@ -752,48 +849,83 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       for (int s = 0; s < 2; s++) {
         const H sb = Mem<ROWS>::sb(s);
         const uint32_t dur = s ? durw.y : durw.x;
-        for (int slot = 1; slot <= 6; slot++) {
+        // hp fraction and activation bound of party slot `slot` (an empty slot contributes a zero block, network.h:131-175)
+        auto slot_state = [&](int slot, float& hp, float& bound) {
           const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
           PH pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
           const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
           const bool alive = hpv != 0;
-          float hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+          hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
           if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
-          const float bound = alive ? act_bound : 0.0f;  // an empty slot contributes a zero block (network.h:131-175)
-          if (slot == 1) {
-            build_active(smem, r, m, s, dur, alive, grp);
-            WT_LAP(3);
-            wait_t();
-            publish();
-            prepare_pokemon(feat, smem, r, m, s, 1, dur, grp);  // under the Active block's MMAs
-            WT_LAP(3);
-            wait_d();
-          }
-#ifndef OAKB200_TC_NO_BUILD  // timing experiment only
-          emit_pokemon(feat, smem, r, grp);  // slots 2..6 were prepared under the previous slot's first-layer MMAs
-#endif
+          bound = alive ? act_bound : 0.0f;
+          return alive;
+        };
+        {
+          // ---- the active Pokémon: features in two K parts, hidden layer through shared memory (its second layer is
+          // 96 wide, which leaves no room in Tensor Memory beside the first layer's accumulator)
+          float hp, bound;
+          const bool alive = slot_state(1, hp, bound);
+          build_active(smem, r, m, s, dur, alive, grp);
           WT_LAP(3);
           wait_t();
           publish();
-          if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);
+          prepare_pokemon(feat, smem, r, m, s, 1, dur, grp);  // under the Active block's MMAs
           WT_LAP(3);
           wait_d();
-          epi(D_WORK, (128 / GROUPS) * grp, (128 / GROUPS) * (grp + 1), cst + (slot == 1 ? C_AC0 : C_PK0), act_bound, smem + A2_HI,
-              smem + A2_LO, 0);
+#ifndef OAKB200_TC_NO_BUILD  // timing experiment only
+          emit_pokemon(feat, smem, r, grp);
+#endif
+          WT_LAP(3);
+          publish();
+          prepare_pokemon(feat, smem, r, m, s, 2, dur, grp);
+          WT_LAP(3);
+          wait_d();
+          epi(D_WORK, (128 / GROUPS) * grp, (128 / GROUPS) * (grp + 1), cst + C_AC0, act_bound, smem + A2_HI, smem + A2_LO, 0);
           publish();
           wait_d();
-          if (slot == 1) {  // 96 columns: 64 + 32 (two groups) or 32 + 32 + 32 + none; the hp column goes with its block's thread
+          {  // 96 columns: 64 + 32 (two groups) or 32 + 32 + 32 + none; the hp column goes with its block's thread
             const int c0 = GROUPS == 2 ? 64 * grp : 32 * grp, c1 = GROUPS == 2 ? (grp ? 96 : 64) : (grp < 3 ? c0 + 32 : c0);
             epi(D_WORK, c0, c1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, m_emb);
             if (P.aod >= c0 && P.aod < c1) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
-          } else {          // 64 columns
-            const int c0 = (64 / GROUPS) * grp, c1 = c0 + 64 / GROUPS;
-            epi(D_WORK, c0, c1, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, m_emb);
-            if (P.pod >= c0 && P.pod < c1) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
           }
           publish();
           t_pending = true;
-          if (slot == 1) wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
+          wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
+        }
+        // ---- the five benched Pokémon, software-pipelined: the hidden layer of slot p stays in Tensor Memory, so the
+        // feature buffer is free as soon as slot p's first layer has run and slot p + 1's features are written — and its
+        // first layer runs — under slot p's second layer and second epilogue. MMA order (= the chunk program):
+        // L1(0) | L2(0) L1(1) T(0) | L2(1) L1(2) T(1) | ... | L2(4) T(4).
+#ifndef OAKB200_TC_NO_BUILD
+        emit_pokemon(feat, smem, r, grp);  // slot 2, prepared under the active block's first layer
+#endif
+        WT_LAP(3);
+        publish();
+        for (int slot = 2; slot <= 6; slot++) {
+          if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);  // registers only, under L1(slot)
+          WT_LAP(3);
+          wait_d();  // L1(slot)
+          epilogue_hidden_tmem(tl, grp, cst + C_PK0, act_bound, workers_sync);
+          WT_LAP(1);
+          publish_on(bar_a2);  // -> L2(slot), A from Tensor Memory
+          if (slot < 6) {
+#ifndef OAKB200_TC_NO_BUILD
+            emit_pokemon(feat, smem, r, grp);
+#endif
+            WT_LAP(3);
+            publish();  // -> L1(slot + 1), queued behind L2(slot)
+          }
+          float hp, bound;
+          slot_state(slot, hp, bound);
+          wait_e();  // L2(slot)
+          wait_t();  // T(slot - 1): the embedding operand is free
+          {
+            const int c0 = (64 / GROUPS) * grp, c1 = c0 + 64 / GROUPS;
+            epi(D_EMB, c0, c1, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, m_emb);
+            if (P.pod >= c0 && P.pod < c1) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
+          }
+          publish_on(bar_ae);  // -> T(slot)
+          t_pending = true;
         }
       }
       // ---- trunk (main-net.h:66-107)
