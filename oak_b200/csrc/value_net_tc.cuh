@@ -100,10 +100,12 @@ const uint32_t AEP_HI = OFF_EMB, AEP_LO = OFF_EMB + 8 * CORE;      // benched em
 const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // one CTA per SM: all of Tensor Memory
 const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (64 columns): beside the first layer's, not over it
 // Hidden activations of a benched slot stay in Tensor Memory as the split-bf16 A operand of the second layer (two K elements
-// per 32-bit column, K step i = 8 columns): the hi plane over the upper half of the first layer's accumulator, the lo plane
-// in the free columns behind the head accumulators (layout of an A operand in Tensor Memory: tools/probes/ts_mma_probe*.cu).
-const uint32_t H_HI = 64, H_LO = 416;
-__host__ __device__ inline uint32_t hidden_tmem_col(uint32_t kstep) { return H_HI + 8u * kstep; }
+// per 32-bit column, K step i = 8 columns), IN PLACE of the first layer's accumulator: worker group g turns its 64 fp32
+// columns [64 g, 64 g + 64) into the hi plane of K steps 4 g .. 4 g + 3 (columns 64 g .. + 31) and their lo plane (columns
+// 64 g + 32 .. + 63), so a thread only ever overwrites columns it has itself read (no barrier between the groups).
+// Layout of an A operand in Tensor Memory: tools/probes/ts_mma_probe*.cu.
+const uint32_t H_LO_OFS = 32;
+__host__ __device__ inline uint32_t hidden_tmem_col(uint32_t kstep) { return D_WORK + 64u * (kstep >> 2) + 8u * (kstep & 3u); }
 // constants block (floats)
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
 const int K_POK = 208, K_ACT = 240;
@@ -440,16 +442,14 @@ __device__ __forceinline__ void epilogue_half(uint32_t taddr, int q, const float
   else epilogue_half_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
 // First-layer epilogue of a benched slot, Tensor Memory to Tensor Memory (see hidden_tmem_col): group g's 64 accumulator
-// columns [64 g, 64 g + 64) -> bias, activation -> K elements 64 g .. 64 g + 63 of the two planes. The hi plane overlies the
-// columns group 1 reads, so every worker has its accumulators in registers (SYNC: a barrier of all workers) before any store.
-template <class SYNC>
-__device__ __forceinline__ void epilogue_hidden_tmem(uint32_t tl, int grp, const float* bias, float bound, SYNC sync) {
+// columns [64 g, 64 g + 64) -> bias, activation -> K elements 64 g .. 64 g + 63 of the two planes, over the same columns.
+__device__ __forceinline__ void epilogue_hidden_tmem(uint32_t tl, int grp, const float* bias, float bound) {
+  static_assert(GROUPS == 2, "the in-place hidden layer is laid out for two worker groups of 64 columns");
   uint32_t v0[32], v1[32];
   const uint32_t t0 = tl + D_WORK + 64u * (uint32_t)grp;
   umma::tmem_ld32(t0, v0);
   umma::tmem_ld32(t0 + 32u, v1);
   umma::tmem_ld_wait();
-  sync();
 #pragma unroll
   for (int b = 0; b < 2; b++) {
     uint32_t h[16], l[16];
@@ -471,9 +471,9 @@ __device__ __forceinline__ void epilogue_hidden_tmem(uint32_t tl, int grp, const
       split2(x4, x5, h[4 * g + 2], l[4 * g + 2]);
       split2(x6, x7, h[4 * g + 3], l[4 * g + 3]);
     }
-    // K elements 64 grp + 32 b .. + 31 = columns 32 grp + 16 b .. + 15 of each plane
-    umma::tmem_st16(tl + H_HI + 32u * (uint32_t)grp + 16u * (uint32_t)b, h);
-    umma::tmem_st16(tl + H_LO + 32u * (uint32_t)grp + 16u * (uint32_t)b, l);
+    // K elements 64 grp + 32 b .. + 31 = columns 16 b .. + 15 of the group's half of each plane
+    umma::tmem_st16(t0 + 16u * (uint32_t)b, h);
+    umma::tmem_st16(t0 + H_LO_OFS + 16u * (uint32_t)b, l);
   }
   umma::tmem_st_wait();
 }
@@ -647,7 +647,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
               const uint32_t a_t = tmem + hidden_tmem_col((uint32_t)ch.a_off16 + i);
               umma::mma_bf16_ts(d, a_t, dbh, idesc, acc);
               umma::mma_bf16_ts(d, a_t, dbl, idesc, 1u);
-              umma::mma_bf16_ts(d, a_t - H_HI + H_LO, dbh, idesc, 1u);
+              umma::mma_bf16_ts(d, a_t + H_LO_OFS, dbh, idesc, 1u);
               acc = 1u;
               dbh += b_step;
               dbl += b_step;
@@ -905,7 +905,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);  // registers only, under L1(slot)
           WT_LAP(3);
           wait_d();  // L1(slot)
-          epilogue_hidden_tmem(tl, grp, cst + C_PK0, act_bound, workers_sync);
+          epilogue_hidden_tmem(tl, grp, cst + C_PK0, act_bound);
           WT_LAP(1);
           publish_on(bar_a2);  // -> L2(slot), A from Tensor Memory
           if (slot < 6) {
