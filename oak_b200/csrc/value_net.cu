@@ -550,8 +550,9 @@ struct Packer {
     return pm;
   }
 
-  // the same with the A operand in Tensor Memory (tc::hidden_tmem_col): a_off16 = the chunk's first K step
-  void stage_tmem(const PackedMatrix& pm, uint32_t dcol, bool overwrite, uint8_t end_flag) {
+  // the same with the A operand in Tensor Memory: `operand` = tc::tmem_operand(first column, K steps per block), a_off16 =
+  // the chunk's first K step; both planes exist for every step
+  void stage_tmem(const PackedMatrix& pm, uint32_t operand, uint32_t dcol, bool overwrite, uint8_t end_flag, uint8_t begin_on) {
     for (size_t j = 0; j < pm.pieces.size(); j++) {
       const auto& pc = pm.pieces[j];
       tc::Chunk c;
@@ -560,9 +561,9 @@ struct Packer {
       c.ksteps = (uint8_t)pc.ksteps;
       c.n8 = (uint8_t)(pm.N / 8);
       c.a_off16 = (uint16_t)pc.k0;
-      c.alo_off16 = 0;
+      c.alo_off16 = (uint16_t)operand;
       c.lo_steps = (uint8_t)pc.ksteps;
-      c.flags = (uint8_t)(tc::F_A_TMEM | tc::F_WAIT_A2 | (j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
+      c.flags = (uint8_t)(tc::F_A_TMEM | begin_on | (j == 0 ? tc::F_STAGE_BEGIN : 0) | (j == 0 && overwrite ? tc::F_OVERWRITE : 0) |
                           (j + 1 == pm.pieces.size() ? end_flag : 0));
       c.dcol = (uint16_t)dcol;
       prog.push_back(c);
@@ -637,13 +638,13 @@ cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
     // layer goes from the first layer's accumulator to the second layer's A operand without leaving Tensor Memory
     P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
     for (int p = 0; p < 5; p++) {
-      P.stage_tmem(pk1, tc::D_EMB, true, tc::F_END_E);
+      P.stage_tmem(pk1, tc::tmem_operand(tc::D_WORK, tc::HID_NC / 16), tc::D_EMB, true, tc::F_END_E, tc::F_WAIT_A2);
       if (p < 4) P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
-      P.stage(fp[s][p], tc::AEP_HI, tc::AEP_LO, 4, tc::D_TRUNK, false, tc::F_END_T, tc::F_WAIT_E);
+      P.stage_tmem(fp[s][p], tc::tmem_operand(tc::D_EMB, tc::EMB_NC / 16), tc::D_TRUNK, false, p == 4 ? tc::F_END_T : 0, tc::F_WAIT_E);
     }
   }
-  P.stage(fc1, tc::AT_HI, tc::AT_LO, 4, tc::D_WORK, true, tc::F_END_D);
-  P.stage(heads, tc::AEP_HI, tc::AEP_LO, 4, tc::D_HEADS, true, tc::F_END_D);
+  P.stage_tmem(fc1, tc::tmem_operand(tc::D_TRUNK, tc::EMB_NC / 16), tc::D_WORK, true, tc::F_END_D, 0);
+  P.stage_tmem(heads, tc::tmem_operand(tc::D_WORK, tc::EMB_NC / 16), tc::D_HEADS, true, tc::F_END_D, 0);
   if (getenv("OAKB200_EVAL_DEBUG"))
     for (size_t i = 0; i < P.prog.size(); i++)
       fprintf(stderr, "[prog %3zu] ksteps %u n %u a_off16 %u lo_steps %u flags 0x%02x dcol %u bytes %u\n", i, P.prog[i].ksteps,

@@ -56,8 +56,8 @@ enum : uint8_t { F_STAGE_BEGIN = 1, F_OVERWRITE = 2, F_END_D = 4, F_END_T = 8, F
 // own mbarrier (a parity wait must never fall two phases behind): a stage begins on bar_a (features / everything else),
 // bar_a2 (F_WAIT_A2: hidden layer in Tensor Memory) or bar_ae (F_WAIT_E: benched embedding operand); its end is committed to
 // bar_d, bar_e (F_END_E: second layer of a benched slot) or bar_t.
-// F_A_TMEM: the A operand is the hidden layer the workers left in Tensor Memory in place of the first layer's accumulator
-// (hidden_tmem_col below); a_off16 then holds the index of the chunk's first K step, both planes exist for every step
+// F_A_TMEM: the A operand is one the workers left in Tensor Memory in place of the previous layer's accumulator; alo_off16 =
+// tmem_operand(...) below, a_off16 = the index of the chunk's first K step, both planes exist for every step
 
 const int ROWS = 128;
 #ifndef OAKB200_TC_GROUPS
@@ -69,14 +69,16 @@ const int WORKERS = GROUPS * ROWS;
 const int THREADS = WORKERS + 64 + ROWS;
 const int W_STREAM = WORKERS / 32, W_MMA = WORKERS / 32 + 1, W_HEADS = WORKERS / 32 + 2;  // W_HEADS .. +3: the head warps
 static_assert(W_HEADS % 4 == 2, "head warp w serves TMEM lane quarter w % 4");
-const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden) / active embedding / trunk input
-const uint32_t OFF_EMB = 65536;      // benched-Pokemon embedding / second trunk operand
-const uint32_t OFF_TILE = 98304;     // 128 battle records as word-transposed columns (gen1_state.cuh)
-const uint32_t OFF_RING = 147456;    // weight chunk ring
+const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden of the active Pokemon) / active embedding
+const uint32_t OFF_TILE = 65536;     // 128 battle records as word-transposed columns (gen1_state.cuh)
+const uint32_t OFF_RING = 114688;    // weight chunk ring
 #ifndef OAKB200_TC_RING_SLOTS
-#define OAKB200_TC_RING_SLOTS 2
+#define OAKB200_TC_RING_SLOTS 3
 #endif
-const uint32_t RING_SLOTS = OAKB200_TC_RING_SLOTS, RING_SLOT = 65536 / RING_SLOTS;  // 4 x 16 KB or 2 x 32 KB
+// 3 x 32 KB: a bulk copy costs the copy engine ~400 cycles whatever its size (tools/probes/bulk_rate_probe.cu),
+// so big chunks; three slots let the streamer run two chunks ahead of the MMA issuer
+const uint32_t RING_SLOTS = OAKB200_TC_RING_SLOTS, RING_SLOT = 98304 / RING_SLOTS;
+static_assert(RING_SLOTS >= 2 && RING_SLOTS <= 4, "four full / empty barrier pairs are laid out");
 const uint32_t OFF_PROG = OFF_RING + RING_SLOTS * RING_SLOT;
 const uint32_t PROG_MAX = 192;
 const uint32_t OFF_CONST = OFF_PROG + PROG_MAX * 16;
@@ -94,18 +96,17 @@ const uint32_t CORE = ROWS * 16;
 const uint32_t A1_HI = OFF_UNION, A1_LO = OFF_UNION + 30 * CORE;   // K <= 240 hi, 16 lo
 const uint32_t A2_HI = OFF_UNION, A2_LO = OFF_UNION + 16 * CORE;   // K = 128
 const uint32_t AEA_HI = OFF_UNION, AEA_LO = OFF_UNION + 12 * CORE; // active embedding, K = 96
-const uint32_t AT_HI = OFF_UNION, AT_LO = OFF_UNION + 8 * CORE;    // trunk hidden, K = 64
-const uint32_t AEP_HI = OFF_EMB, AEP_LO = OFF_EMB + 8 * CORE;      // benched embedding / second trunk operand, K = 64
 // TMEM columns
 const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // one CTA per SM: all of Tensor Memory
 const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (64 columns): beside the first layer's, not over it
-// Hidden activations of a benched slot stay in Tensor Memory as the split-bf16 A operand of the second layer (two K elements
-// per 32-bit column, K step i = 8 columns), IN PLACE of the first layer's accumulator: worker group g turns its 64 fp32
-// columns [64 g, 64 g + 64) into the hi plane of K steps 4 g .. 4 g + 3 (columns 64 g .. + 31) and their lo plane (columns
-// 64 g + 32 .. + 63), so a thread only ever overwrites columns it has itself read (no barrier between the groups).
+// Operands that stay in Tensor Memory. An accumulator block of NC fp32 columns owned by one worker group (NC = 64: half of
+// a hidden layer, 32: half of a benched embedding) is rewritten IN PLACE by that group as the split-bf16 A operand of the
+// next layer (two K elements per 32-bit column, a K = 16 step = 8 columns): hi plane in the block's first NC / 2 columns,
+// lo plane in the other NC / 2, so a thread only ever overwrites columns it has itself read (no barrier between groups).
+// K step k of such an operand, kpb = NC / 16 steps per block: hi at base + 16 kpb (k / kpb) + 8 (k % kpb), lo 8 kpb on.
 // Layout of an A operand in Tensor Memory: tools/probes/ts_mma_probe*.cu.
-const uint32_t H_LO_OFS = 32;
-__host__ __device__ inline uint32_t hidden_tmem_col(uint32_t kstep) { return D_WORK + 64u * (kstep >> 2) + 8u * (kstep & 3u); }
+const int HID_NC = 128 / GROUPS, EMB_NC = 64 / GROUPS;  // columns per worker group of a hidden layer / a benched embedding
+__host__ __device__ inline uint32_t tmem_operand(uint32_t base, uint32_t kpb) { return base | (kpb << 12); }  // Chunk::alo_off16
 // constants block (floats)
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
 const int K_POK = 208, K_ACT = 240;
@@ -441,41 +442,63 @@ __device__ __forceinline__ void epilogue_half(uint32_t taddr, int q, const float
   else if (mode == 1) epilogue_half_m<1>(taddr, q, bias, bound, hi, lo, r);
   else epilogue_half_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
-// First-layer epilogue of a benched slot, Tensor Memory to Tensor Memory (see hidden_tmem_col): group g's 64 accumulator
-// columns [64 g, 64 g + 64) -> bias, activation -> K elements 64 g .. 64 g + 63 of the two planes, over the same columns.
-__device__ __forceinline__ void epilogue_hidden_tmem(uint32_t tl, int grp, const float* bias, float bound) {
-  static_assert(GROUPS == 2, "the in-place hidden layer is laid out for two worker groups of 64 columns");
-  uint32_t v0[32], v1[32];
-  const uint32_t t0 = tl + D_WORK + 64u * (uint32_t)grp;
-  umma::tmem_ld32(t0, v0);
-  umma::tmem_ld32(t0 + 32u, v1);
-  umma::tmem_ld_wait();
-#pragma unroll
-  for (int b = 0; b < 2; b++) {
-    uint32_t h[16], l[16];
-    const float4* b4 = reinterpret_cast<const float4*>(bias + 64 * grp + 32 * b);
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-      const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
-      const uint32_t* v = b ? v1 : v0;
-      const float x0 = epi_act<0>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
-      const float x1 = epi_act<0>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
-      const float x2 = epi_act<0>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
-      const float x3 = epi_act<0>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
-      const float x4 = epi_act<0>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
-      const float x5 = epi_act<0>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
-      const float x6 = epi_act<0>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
-      const float x7 = epi_act<0>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
-      split2(x0, x1, h[4 * g + 0], l[4 * g + 0]);
-      split2(x2, x3, h[4 * g + 1], l[4 * g + 1]);
-      split2(x4, x5, h[4 * g + 2], l[4 * g + 2]);
-      split2(x6, x7, h[4 * g + 3], l[4 * g + 3]);
+// In-place epilogue (see tmem_operand): NC = 16 j fp32 accumulator columns at t0 -> + bias, activation (MODE as epi_act)
+// -> hi plane in columns [t0, t0 + NC / 2), lo plane in [t0 + NC / 2, t0 + NC). hp_col in [0, NC): that K element is the
+// hp / max-hp input of the next layer instead (network.h:147,165); pass -1 for none.
+template <int MODE, int NC>
+__device__ __forceinline__ void epilogue_inplace_m(uint32_t t0, const float* bias, float bound, int hp_col, float hp) {
+  static_assert(NC == 16 || NC == 32 || NC == 48 || NC == 64, "blocks of 16, 32, 48 or 64 accumulator columns");
+  uint32_t v[64];
+  if (NC == 16) {
+    umma::tmem_ld16(t0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+  } else {
+    uint32_t(&a)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+    umma::tmem_ld32(t0, a);
+    if (NC == 64) {
+      uint32_t(&b)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[32]);
+      umma::tmem_ld32(t0 + 32u, b);
+    } else if (NC == 48) {
+      uint32_t(&b)[16] = *reinterpret_cast<uint32_t(*)[16]>(&v[32]);
+      umma::tmem_ld16(t0 + 32u, b);
     }
-    // K elements 64 grp + 32 b .. + 31 = columns 16 b .. + 15 of the group's half of each plane
-    umma::tmem_st16(t0 + 16u * (uint32_t)b, h);
-    umma::tmem_st16(t0 + H_LO_OFS + 16u * (uint32_t)b, l);
+  }
+  umma::tmem_ld_wait();
+  uint32_t h[32], l[32];
+#pragma unroll
+  for (int g = 0; g < NC / 8; g++) {
+    const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g), bb = *reinterpret_cast<const float4*>(bias + 8 * g + 4);
+    float x[8];
+    x[0] = epi_act<MODE>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
+    x[1] = epi_act<MODE>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
+    x[2] = epi_act<MODE>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
+    x[3] = epi_act<MODE>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
+    x[4] = epi_act<MODE>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
+    x[5] = epi_act<MODE>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
+    x[6] = epi_act<MODE>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
+    x[7] = epi_act<MODE>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
+#pragma unroll
+    for (int j = 0; j < 8; j++) x[j] = (8 * g + j == hp_col) ? hp : x[j];
+#pragma unroll
+    for (int j = 0; j < 4; j++) split2(x[2 * j], x[2 * j + 1], h[4 * g + j], l[4 * g + j]);
+  }
+  if (NC == 16) {
+    umma::tmem_st8(t0, *reinterpret_cast<uint32_t(*)[8]>(&h[0]));
+    umma::tmem_st8(t0 + 8u, *reinterpret_cast<uint32_t(*)[8]>(&l[0]));
+  } else {
+    umma::tmem_st16(t0, *reinterpret_cast<uint32_t(*)[16]>(&h[0]));
+    if (NC == 64) umma::tmem_st16(t0 + 16u, *reinterpret_cast<uint32_t(*)[16]>(&h[16]));
+    if (NC == 48) umma::tmem_st8(t0 + 16u, *reinterpret_cast<uint32_t(*)[8]>(&h[16]));
+    umma::tmem_st16(t0 + NC / 2, *reinterpret_cast<uint32_t(*)[16]>(&l[0]));
+    if (NC == 64) umma::tmem_st16(t0 + NC / 2 + 16u, *reinterpret_cast<uint32_t(*)[16]>(&l[16]));
+    if (NC == 48) umma::tmem_st8(t0 + NC / 2 + 16u, *reinterpret_cast<uint32_t(*)[8]>(&l[16]));
   }
   umma::tmem_st_wait();
+}
+template <int NC>
+__device__ __forceinline__ void epilogue_inplace(uint32_t t0, const float* bias, float bound, int mode, int hp_col = -1, float hp = 0.0f) {
+  if (mode == 0) epilogue_inplace_m<0, NC>(t0, bias, bound, hp_col, hp);
+  else if (mode == 1) epilogue_inplace_m<1, NC>(t0, bias, bound, hp_col, hp);
+  else epilogue_inplace_m<2, NC>(t0, bias, bound, hp_col, hp);
 }
 // mode is warp-uniform (a property of the loaded network)
 __device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
@@ -548,10 +571,22 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
     // ===== weight streamer: packed chunks L2 -> ring =====
     if (lane == 0) {
       uint32_t g = 0;
+#ifdef OAKB200_TC_TRACE  // diagnostic build only: clock64 stamps of the issuer over the stages of one tile of CTA 0
+      long long tr_i[400];
+      int tr_n = 0, tr_tile = 0;
+#define TR_I(tag) do { if (blockIdx.x == 0 && tr_tile == 2 && tr_n < 400) tr_i[tr_n++] = (clock64() << 4) | (tag); } while (0)
+#else
+#define TR_I(tag) do { } while (0)
+#endif
       for (uint32_t t = tile0; t < ntiles; t += tile_step) {
+#ifdef OAKB200_TC_TRACE
+        tr_tile++;
+#endif
         for (int c = 0; c < P.nchunks; c++, g++) {
-          const uint32_t slot = g & (RING_SLOTS - 1);
+          const uint32_t slot = g % RING_SLOTS;
+          TR_I(6);
           if (g >= RING_SLOTS) umma::mbar_wait(bar_empty + 8 * slot, ((g / RING_SLOTS) - 1) & 1);
+          TR_I(7);
           const uint32_t bytes = (uint32_t)prog[c].bytes16 << 4;
 #ifdef OAKB200_TC_NO_STREAM  // timing experiment only: the ring is never filled, results are garbage
           umma::mbar_arrive(bar_full + 8 * slot);
@@ -569,6 +604,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
           }
         }
       }
+#ifdef OAKB200_TC_TRACE
+      if (blockIdx.x == 0)
+        for (int i = 0; i < tr_n; i++) printf("[trace S] %d %lld\n", (int)(tr_i[i] & 15), tr_i[i] >> 4);
+#endif
     }
   } else if (warp == W_MMA) {
     // ===== MMA issuer =====
@@ -580,7 +619,17 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       long long tm_c = clock64();
 #define TM_LAP(acc) do { const long long now_ = clock64(); acc += now_ - tm_c; tm_c = now_; } while (0)
 #endif
+#ifdef OAKB200_TC_TRACE  // diagnostic build only: clock64 stamps of the issuer over the stages of one tile of CTA 0
+      long long tr_i[400];
+      int tr_n = 0, tr_tile = 0;
+#define TR_I(tag) do { if (blockIdx.x == 0 && tr_tile == 2 && tr_n < 400) tr_i[tr_n++] = (clock64() << 4) | (tag); } while (0)
+#else
+#define TR_I(tag) do { } while (0)
+#endif
       for (uint32_t t = tile0; t < ntiles; t += tile_step) {
+#ifdef OAKB200_TC_TRACE
+        tr_tile++;
+#endif
         for (int c = 0; c < P.nchunks; c++, g++) {
           // The chunk record is read with one explicit 16-byte load and decoded by shifts: with the struct copy
           // `const Chunk ch = prog[c]` ptxas 12.9 was seen to take dcol from a register the load never wrote
@@ -601,6 +650,7 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm2);
 #endif
+          if (ch.flags & F_STAGE_BEGIN) TR_I(1);
           if (ch.flags & F_STAGE_BEGIN) {
             if (ch.flags & F_WAIT_A2) {
               OAKB200_TC_WAIT(bar_a2, stage_a2 & 1);
@@ -616,9 +666,11 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm0);
 #endif
-          const uint32_t slot = g & (RING_SLOTS - 1);
+          if (ch.flags & F_STAGE_BEGIN) TR_I(2);
+          const uint32_t slot = g % RING_SLOTS;
           umma::mbar_wait(bar_full + 8 * slot, (g / RING_SLOTS) & 1);
           umma::tc_fence_after();
+          TR_I(4);
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm1);
 #endif
@@ -642,15 +694,25 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #endif
           uint32_t acc = (ch.flags & F_OVERWRITE) ? 0u : 1u;
           const uint32_t lo_steps = ch.lo_steps, ksteps = ch.ksteps;
-          if (ch.flags & F_A_TMEM) {  // A = the hidden layer in Tensor Memory
+          if (ch.flags & F_A_TMEM) {  // A = an operand the workers left in Tensor Memory (tmem_operand)
+            const uint32_t kpb = ch.alo_off16 >> 12, lo_ofs = 8u * kpb;
+            uint32_t j = ch.a_off16 % kpb, a_t = tmem + (ch.alo_off16 & 0x3FFu) + 16u * kpb * (ch.a_off16 / kpb) + 8u * j;
             for (uint32_t i = 0; i < ksteps; i++) {
-              const uint32_t a_t = tmem + hidden_tmem_col((uint32_t)ch.a_off16 + i);
+#ifdef OAKB200_TC_NO_COLLECTOR  // A/B switch: every MMA fetches its own A operand
               umma::mma_bf16_ts(d, a_t, dbh, idesc, acc);
               umma::mma_bf16_ts(d, a_t, dbl, idesc, 1u);
-              umma::mma_bf16_ts(d, a_t + H_LO_OFS, dbh, idesc, 1u);
+#else
+              umma::mma_bf16_ts_pair(d, a_t, dbh, dbl, idesc, acc);
+#endif
+              umma::mma_bf16_ts(d, a_t + lo_ofs, dbh, idesc, 1u);
               acc = 1u;
               dbh += b_step;
               dbl += b_step;
+              a_t += 8u;
+              if (++j == kpb) {  // next block: skip this block's lo plane
+                j = 0;
+                a_t += lo_ofs;
+              }
             }
           }
           const uint32_t ss_steps = (ch.flags & F_A_TMEM) ? 0u : ksteps;  // the K steps whose A operand is in shared memory
@@ -670,9 +732,11 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #ifdef OAKB200_TC_WIDE_TIMING  // timing experiment only: A_hi x [B_hi | B_lo] as ONE instruction of twice the N, results are garbage
             if (N <= 128) umma::mma_bf16(d, da, dbh, umma::idesc_bf16_f32(2 * N), acc);
             else { umma::mma_bf16(d, da, dbh, idesc, acc); umma::mma_bf16(d, da, dbl, idesc, 1u); }
-#else
+#elif defined(OAKB200_TC_NO_COLLECTOR)
             umma::mma_bf16(d, da, dbh, idesc, acc);
             umma::mma_bf16(d, da, dbl, idesc, 1u);
+#else
+            umma::mma_bf16_pair(d, da, dbh, dbl, idesc, acc);  // A_hi x B_hi, A_hi x B_lo: A is read once
 #endif
             if (i < lo_steps) umma::mma_bf16(d, dal, dbh, idesc, 1u);
             acc = 1u;
@@ -684,10 +748,12 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm2);
 #endif
+          TR_I(5);
           if (CL > 1) umma::mma_commit_multicast(bar_empty + 8 * slot, cmask);
           else umma::mma_commit(bar_empty + 8 * slot);
           if (ch.flags & F_END_D) umma::mma_commit(bar_d);
           if (ch.flags & F_END_E) umma::mma_commit(bar_e);
+          if (ch.flags & (F_END_D | F_END_E | F_END_T)) TR_I(3);
           if (ch.flags & F_END_T) umma::mma_commit(bar_t);
 #ifdef OAKB200_TC_TIMING
           TM_LAP(tm4);
@@ -696,6 +762,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #endif
         }
       }
+#ifdef OAKB200_TC_TRACE
+      if (blockIdx.x == 0)
+        for (int i = 0; i < tr_n; i++) printf("[trace I] %d %lld\n", (int)(tr_i[i] & 15), tr_i[i] >> 4);
+#endif
 #ifdef OAKB200_TC_TIMING
       if (blockIdx.x == 0)
         printf("[eval_tc timing] issuer: wait workers %lld, wait weights %lld, issue %lld, drain %lld, commit %lld cycles\n", tm0, tm1, tm2,
@@ -836,7 +906,17 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       if (c < c1) epilogue_half(tl + dcol, c >> 4, bias, bound, hi, lo, r, mode);
       WT_LAP(1);
     };
+#ifdef OAKB200_TC_TRACE
+    long long tr_w[96];
+    int tr_wn = 0, tr_wtile = 0;
+#define TR_W(tag) do { if (blockIdx.x == 0 && threadIdx.x == 0 && tr_wtile == 2 && tr_wn < 96) tr_w[tr_wn++] = (clock64() << 4) | (tag); } while (0)
+#else
+#define TR_W(tag) do { } while (0)
+#endif
     for (uint32_t tb = tile0; tb < ntiles; tb += tile_step) {
+#ifdef OAKB200_TC_TRACE
+      tr_wtile++;
+#endif
       const uint32_t t = tb + crank;
       const uint32_t e = t * ROWS + (uint32_t)r;
       const uint32_t ec = e < n ? e : n - 1;
@@ -904,36 +984,44 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
         for (int slot = 2; slot <= 6; slot++) {
           if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);  // registers only, under L1(slot)
           WT_LAP(3);
+          TR_W(1);
           wait_d();  // L1(slot)
-          epilogue_hidden_tmem(tl, grp, cst + C_PK0, act_bound);
+          TR_W(2);
+          epilogue_inplace<HID_NC>(tl + D_WORK + (uint32_t)(HID_NC * grp), cst + C_PK0 + HID_NC * grp, act_bound, 0);
           WT_LAP(1);
+          TR_W(3);
           publish_on(bar_a2);  // -> L2(slot), A from Tensor Memory
+          TR_W(4);
           if (slot < 6) {
 #ifndef OAKB200_TC_NO_BUILD
             emit_pokemon(feat, smem, r, grp);
 #endif
             WT_LAP(3);
+            TR_W(5);
             publish();  // -> L1(slot + 1), queued behind L2(slot)
           }
           float hp, bound;
           slot_state(slot, hp, bound);
+          TR_W(6);
           wait_e();  // L2(slot)
-          wait_t();  // T(slot - 1): the embedding operand is free
-          {
-            const int c0 = (64 / GROUPS) * grp, c1 = c0 + 64 / GROUPS;
-            epi(D_EMB, c0, c1, cst + C_PK1, bound, smem + AEP_HI, smem + AEP_LO, m_emb);
-            if (P.pod >= c0 && P.pod < c1) put_hp(smem + AEP_HI, smem + AEP_LO, r, P.pod, hp);
-          }
-          publish_on(bar_ae);  // -> T(slot)
-          t_pending = true;
+          TR_W(7);
+          epilogue_inplace<EMB_NC>(tl + D_EMB + (uint32_t)(EMB_NC * grp), cst + C_PK1 + EMB_NC * grp, bound, m_emb, P.pod - EMB_NC * grp, hp);
+          WT_LAP(1);
+          TR_W(8);
+          publish_on(bar_ae);  // -> T(slot), A = the embedding in Tensor Memory; the last one of the side commits to bar_t
+          TR_W(9);
         }
+        t_pending = true;
       }
       // ---- trunk (main-net.h:66-107)
       wait_t();
-      epi(D_TRUNK, (64 / GROUPS) * grp, (64 / GROUPS) * (grp + 1), cst + C_FC0, act_bound, smem + AT_HI, smem + AT_LO, m_main);
+      // both trunk layers' activations become the next layer's A operand where their accumulator was (tmem_operand)
+      epilogue_inplace<EMB_NC>(tl + D_TRUNK + (uint32_t)(EMB_NC * grp), cst + C_FC0 + EMB_NC * grp, act_bound, m_main);
+      WT_LAP(1);
       publish();
       wait_d();
-      epi(D_WORK, (64 / GROUPS) * grp, (64 / GROUPS) * (grp + 1), cst + C_FC1, act_bound, smem + AEP_HI, smem + AEP_LO, m_main);
+      epilogue_inplace<EMB_NC>(tl + D_WORK + (uint32_t)(EMB_NC * grp), cst + C_FC1 + EMB_NC * grp, act_bound, m_main);
+      WT_LAP(1);
       // The head warps read the previous tile's head accumulators and row indices while this tile runs; both are rewritten
       // from here on (a fresh barrier passes the parity-1 wait of the first tile).
       umma::mbar_wait(bar_hfree, (iter + 1) & 1);
@@ -978,6 +1066,10 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       iter++;
       WT_LAP(5);
     }
+#ifdef OAKB200_TC_TRACE
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+      for (int i = 0; i < tr_wn; i++) printf("[trace W] %d %lld\n", (int)(tr_w[i] & 15), tr_w[i] >> 4);
+#endif
 #ifdef OAKB200_TC_TIMING
     if (blockIdx.x == 0 && threadIdx.x == 0)
       printf("[eval_tc timing] worker 0: waiting on MMAs %lld, epilogues %lld, publish %lld, feature build %lld, tile load %lld, wait for the head warps %lld, row indices %lld cycles\n",
