@@ -629,19 +629,20 @@ cudaError_t tc_pack(oakb200_net* n, const HostAffine* a, const NetDims& d) {
     if (o < 96) return o - 32 < d.pohd ? rdf(a[8].w, (size_t)(o - 32) * hd + k) : 0.0f;
     return o - 96 < d.pohd ? rdf(a[10].w, (size_t)(o - 96) * hd + k) : 0.0f;
   });
-  for (int s = 0; s < 2; s++) {
-    P.stage(ac0a, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
-    P.stage(ac0p, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, false, tc::F_END_D);
-    P.stage(ac1, tc::A2_HI, tc::A2_LO, 8, tc::D_WORK, true, tc::F_END_D);
-    P.stage(fa[s], tc::AEA_HI, tc::AEA_LO, 6, tc::D_TRUNK, s == 0, tc::F_END_T);
-    // the benched slots, software-pipelined (value_net_tc.cuh, worker loop): L1(0) | L2(p) L1(p + 1) T(p) ...; the hidden
-    // layer goes from the first layer's accumulator to the second layer's A operand without leaving Tensor Memory
-    P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
-    for (int p = 0; p < 5; p++) {
-      P.stage_tmem(pk1, tc::tmem_operand(tc::D_WORK, tc::HID_NC / 16), tc::D_EMB, true, tc::F_END_E, tc::F_WAIT_A2);
-      if (p < 4) P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
-      P.stage_tmem(fp[s][p], tc::tmem_operand(tc::D_EMB, tc::EMB_NC / 16), tc::D_TRUNK, false, p == 4 ? tc::F_END_T : 0, tc::F_WAIT_E);
-    }
+  // The twelve party slots of a tile as one software pipeline (value_net_tc.cuh, worker loop): q = 6 s + slot - 1, slot 1 =
+  // the active Pokemon. L1(0)a L1(0)b | L2(q) L1(q + 1) T(q) ...: every layer output is the next layer's A operand in place
+  // in Tensor Memory; an active slot's first layer has two K parts (Active block, then its Pokemon block, accumulated).
+  P.stage(ac0a, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+  P.stage(ac0p, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, false, tc::F_END_D);
+  for (int q = 0; q < 12; q++) {
+    const int s = q / 6, slot = q % 6;  // slot 0 = the active Pokemon
+    if (slot == 0) P.stage_tmem(ac1, tc::tmem_operand(tc::D_WORK, tc::HID_NC / 16), tc::D_ACT, true, tc::F_END_E, tc::F_WAIT_A2);
+    else P.stage_tmem(pk1, tc::tmem_operand(tc::D_WORK, tc::HID_NC / 16), tc::D_EMB, true, tc::F_END_E, tc::F_WAIT_A2);
+    if (q == 5) P.stage(ac0a, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+    else if (q < 11) P.stage(pk0, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, true, tc::F_END_D);
+    if (slot == 0) P.stage_tmem(fa[s], tc::tmem_operand(tc::D_ACT, tc::ACT_NC / 16), tc::D_TRUNK, s == 0, 0, tc::F_WAIT_E);
+    else P.stage_tmem(fp[s][slot - 1], tc::tmem_operand(tc::D_EMB, tc::EMB_NC / 16), tc::D_TRUNK, false, q == 11 ? tc::F_END_T : 0, tc::F_WAIT_E);
+    if (q == 5) P.stage(ac0p, tc::A1_HI, tc::A1_LO, 1, tc::D_WORK, false, tc::F_END_D);
   }
   P.stage_tmem(fc1, tc::tmem_operand(tc::D_TRUNK, tc::EMB_NC / 16), tc::D_WORK, true, tc::F_END_D, 0);
   P.stage_tmem(heads, tc::tmem_operand(tc::D_WORK, tc::EMB_NC / 16), tc::D_HEADS, true, tc::F_END_D, 0);

@@ -97,7 +97,7 @@ const uint32_t A1_HI = OFF_UNION, A1_LO = OFF_UNION + 30 * CORE;   // K <= 240 h
 const uint32_t A2_HI = OFF_UNION, A2_LO = OFF_UNION + 16 * CORE;   // K = 128
 const uint32_t AEA_HI = OFF_UNION, AEA_LO = OFF_UNION + 12 * CORE; // active embedding, K = 96
 // TMEM columns
-const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256;  // one CTA per SM: all of Tensor Memory
+const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256, D_ACT = 416;  // one CTA per SM: all of Tensor Memory
 const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (64 columns): beside the first layer's, not over it
 // Operands that stay in Tensor Memory. An accumulator block of NC fp32 columns owned by one worker group (NC = 64: half of
 // a hidden layer, 32: half of a benched embedding) is rewritten IN PLACE by that group as the split-bf16 A operand of the
@@ -106,6 +106,8 @@ const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (6
 // K step k of such an operand, kpb = NC / 16 steps per block: hi at base + 16 kpb (k / kpb) + 8 (k % kpb), lo 8 kpb on.
 // Layout of an A operand in Tensor Memory: tools/probes/ts_mma_probe*.cu.
 const int HID_NC = 128 / GROUPS, EMB_NC = 64 / GROUPS;  // columns per worker group of a hidden layer / a benched embedding
+const int ACT_NC = 96 / GROUPS;                          // ... of the active Pokemon's embedding (K = 96 of the trunk)
+static_assert(GROUPS == 2, "the in-place operand blocks (64 / 48 / 32 columns per group) are laid out for two worker groups");
 __host__ __device__ inline uint32_t tmem_operand(uint32_t base, uint32_t kpb) { return base | (kpb << 12); }  // Chunk::alo_off16
 // constants block (floats)
 const int C_PK0 = 0, C_PK1 = 128, C_AC0 = 192, C_AC1 = 320, C_FC0 = 416, C_FC1 = 480, C_HEADS = 544, C_V3W = 704, C_V3B = 736;
@@ -926,93 +928,83 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       workers_sync();
       WT_LAP(4);
       PokemonFeatures feat;
-      for (int s = 0; s < 2; s++) {
-        const H sb = Mem<ROWS>::sb(s);
-        const uint32_t dur = s ? durw.y : durw.x;
+      // ---- the twelve party slots of the tile as ONE software pipeline: q = 6 s + slot - 1, slot 1 = the active Pokémon of
+      // side s. Every layer output stays in Tensor Memory as the next layer's A operand (tmem_operand), so the only shared
+      // buffer is the feature block A1, free again as soon as a first layer has run. Per slot q the workers do
+      //   wait L1(q) -> E1(q) -> [L2(q)] ; features of q + 1 -> [L1(q + 1)] ; wait L2(q) -> E2(q) -> [T(q)] ; prepare q + 2
+      // and the MMA order (= the chunk program, value_net.cu tc_pack) is
+      //   L1(0)a L1(0)b | L2(q) L1(q + 1) T(q) ... ; an active slot's first layer comes in two K parts (a: the Active block,
+      //   b: its Pokémon block, accumulated), the second part goes out after T(q).
+      auto slot_state = [&](int s, int slot, float& hp, float& bound) {
         // hp fraction and activation bound of party slot `slot` (an empty slot contributes a zero block, network.h:131-175)
-        auto slot_state = [&](int slot, float& hp, float& bound) {
-          const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
-          PH pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
-          const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
-          const bool alive = hpv != 0;
-          hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
-          if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
-          bound = alive ? act_bound : 0.0f;
-          return alive;
-        };
-        {
-          // ---- the active Pokémon: features in two K parts, hidden layer through shared memory (its second layer is
-          // 96 wide, which leaves no room in Tensor Memory beside the first layer's accumulator)
-          float hp, bound;
-          const bool alive = slot_state(1, hp, bound);
-          build_active(smem, r, m, s, dur, alive, grp);
-          WT_LAP(3);
-          wait_t();
-          publish();
-          prepare_pokemon(feat, smem, r, m, s, 1, dur, grp);  // under the Active block's MMAs
-          WT_LAP(3);
-          wait_d();
+        const H sb = Mem<ROWS>::sb(s);
+        const uint32_t id = m.ld8(sb, S_ORDER + slot - 1);
+        PH pk = Mem<ROWS>::pokemon(s, id ? (int)id - 1 : 0);
+        const uint32_t hpv = id ? m.ld16(pk, PK_HP) : 0;
+        const bool alive = hpv != 0;
+        hp = alive ? (float)hpv / (float)m.ld16(pk, PK_STATS) : 0.0f;
+        if (disc) hp = floorf(hp * 127.0f);  // network.h:147,165
+        bound = alive ? act_bound : 0.0f;
+        return alive;
+      };
+      auto active_features = [&](int s) {  // part a of an active slot's first layer, then its Pokémon block is prepared
+        float hp, bound;
+        const bool alive = slot_state(s, 1, hp, bound);
+        const uint32_t dur = s ? durw.y : durw.x;
+        build_active(smem, r, m, s, dur, alive, grp);
+        WT_LAP(3);
+        publish();
+        prepare_pokemon(feat, smem, r, m, s, 1, dur, grp);  // under the Active block's MMAs
+        WT_LAP(3);
+      };
+      auto pokemon_features = [&]() {
 #ifndef OAKB200_TC_NO_BUILD  // timing experiment only
-          emit_pokemon(feat, smem, r, grp);
-#endif
-          WT_LAP(3);
-          publish();
-          prepare_pokemon(feat, smem, r, m, s, 2, dur, grp);
-          WT_LAP(3);
-          wait_d();
-          epi(D_WORK, (128 / GROUPS) * grp, (128 / GROUPS) * (grp + 1), cst + C_AC0, act_bound, smem + A2_HI, smem + A2_LO, 0);
-          publish();
-          wait_d();
-          {  // 96 columns: 64 + 32 (two groups) or 32 + 32 + 32 + none; the hp column goes with its block's thread
-            const int c0 = GROUPS == 2 ? 64 * grp : 32 * grp, c1 = GROUPS == 2 ? (grp ? 96 : 64) : (grp < 3 ? c0 + 32 : c0);
-            epi(D_WORK, c0, c1, cst + C_AC1, bound, smem + AEA_HI, smem + AEA_LO, m_emb);
-            if (P.aod >= c0 && P.aod < c1) put_hp(smem + AEA_HI, smem + AEA_LO, r, P.aod, hp);
-          }
-          publish();
-          t_pending = true;
-          wait_t();  // the active embedding lives in the union buffer the next slot rebuilds
-        }
-        // ---- the five benched Pokémon, software-pipelined: the hidden layer of slot p stays in Tensor Memory, so the
-        // feature buffer is free as soon as slot p's first layer has run and slot p + 1's features are written — and its
-        // first layer runs — under slot p's second layer and second epilogue. MMA order (= the chunk program):
-        // L1(0) | L2(0) L1(1) T(0) | L2(1) L1(2) T(1) | ... | L2(4) T(4).
-#ifndef OAKB200_TC_NO_BUILD
-        emit_pokemon(feat, smem, r, grp);  // slot 2, prepared under the active block's first layer
+        emit_pokemon(feat, smem, r, grp);
 #endif
         WT_LAP(3);
         publish();
-        for (int slot = 2; slot <= 6; slot++) {
-          if (slot < 6) prepare_pokemon(feat, smem, r, m, s, slot + 1, dur, grp);  // registers only, under L1(slot)
-          WT_LAP(3);
-          TR_W(1);
-          wait_d();  // L1(slot)
-          TR_W(2);
-          epilogue_inplace<HID_NC>(tl + D_WORK + (uint32_t)(HID_NC * grp), cst + C_PK0 + HID_NC * grp, act_bound, 0);
-          WT_LAP(1);
-          TR_W(3);
-          publish_on(bar_a2);  // -> L2(slot), A from Tensor Memory
-          TR_W(4);
-          if (slot < 6) {
-#ifndef OAKB200_TC_NO_BUILD
-            emit_pokemon(feat, smem, r, grp);
-#endif
-            WT_LAP(3);
-            TR_W(5);
-            publish();  // -> L1(slot + 1), queued behind L2(slot)
-          }
-          float hp, bound;
-          slot_state(slot, hp, bound);
-          TR_W(6);
-          wait_e();  // L2(slot)
-          TR_W(7);
-          epilogue_inplace<EMB_NC>(tl + D_EMB + (uint32_t)(EMB_NC * grp), cst + C_PK1 + EMB_NC * grp, bound, m_emb, P.pod - EMB_NC * grp, hp);
-          WT_LAP(1);
-          TR_W(8);
-          publish_on(bar_ae);  // -> T(slot), A = the embedding in Tensor Memory; the last one of the side commits to bar_t
-          TR_W(9);
+      };
+      active_features(0);
+      wait_d();  // L1(0)a
+      pokemon_features();  // -> L1(0)b
+      prepare_pokemon(feat, smem, r, m, 0, 2, durw.x, grp);
+      WT_LAP(3);
+      for (int q = 0; q < 12; q++) {
+        const int s = q >= 6 ? 1 : 0, slot = q - 6 * s + 1;
+        const bool act = slot == 1, last = q == 11, next_act = q == 5;
+        TR_W(1);
+        wait_d();  // L1(q), for an active slot its second part
+        TR_W(2);
+        epilogue_inplace<HID_NC>(tl + D_WORK + (uint32_t)(HID_NC * grp), cst + (act ? C_AC0 : C_PK0) + HID_NC * grp, act_bound, 0);
+        WT_LAP(1);
+        TR_W(3);
+        publish_on(bar_a2);  // -> L2(q), A = the hidden layer in Tensor Memory
+        TR_W(4);
+        if (next_act) active_features(1);       // -> L1(6)a
+        else if (!last) pokemon_features();     // -> L1(q + 1), queued behind L2(q)
+        TR_W(5);
+        float hp, bound;
+        slot_state(s, slot, hp, bound);
+        TR_W(6);
+        wait_e();  // L2(q)
+        TR_W(7);
+        if (act) epilogue_inplace<ACT_NC>(tl + D_ACT + (uint32_t)(ACT_NC * grp), cst + C_AC1 + ACT_NC * grp, bound, m_emb, P.aod - ACT_NC * grp, hp);
+        else epilogue_inplace<EMB_NC>(tl + D_EMB + (uint32_t)(EMB_NC * grp), cst + C_PK1 + EMB_NC * grp, bound, m_emb, P.pod - EMB_NC * grp, hp);
+        WT_LAP(1);
+        TR_W(8);
+        publish_on(bar_ae);  // -> T(q), A = the embedding in Tensor Memory; T(11) commits to bar_t
+        TR_W(9);
+        if (next_act) {
+          wait_d();  // L1(6)a
+          pokemon_features();  // -> L1(6)b
+          prepare_pokemon(feat, smem, r, m, 1, 2, durw.y, grp);
+        } else if (q + 2 < 12 && q + 2 != 6) {  // registers only, under L1(q + 1)
+          const int s2 = q + 2 >= 6 ? 1 : 0;
+          prepare_pokemon(feat, smem, r, m, s2, q + 2 - 6 * s2 + 1, s2 ? durw.y : durw.x, grp);
         }
-        t_pending = true;
+        WT_LAP(3);
       }
+      t_pending = true;
       // ---- trunk (main-net.h:66-107)
       wait_t();
       // both trunk layers' activations become the next layer's A operand where their accumulator was (tmem_operand)
