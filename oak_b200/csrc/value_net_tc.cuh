@@ -18,12 +18,18 @@
 // One-hot feature columns are exact in bf16, so the first layer needs its A_lo plane only for the 14 real-valued
 // columns, which the host-side packing permutes to the front of K.
 //
-// Roles: warps 0-15 workers, FOUR threads per row (thread r of group g = warps 4g..4g+3 serves evaluation r; the groups
-// split every epilogue by accumulator columns and the zero-fill of the feature tile by core columns, group 0 writes the
-// features), warp 16 lane 0 streams weight chunks L2 -> shared memory with cp.async.bulk through a 4-slot mbarrier ring
-// (and owns the TMEM allocation), warp 17 lane 0 issues tcgen05.mma. The worker side of the per-slot chain is bound by
-// instruction latency, not issue slots, so four warps per scheduler instead of two shorten it (profiles/r1o_*).
-// The per-tile schedule is a static chunk program built on the host at oakb200_net_load.
+// Where the operands live: only the first-layer features of one party slot are in shared memory (scattered one-hot
+// stores); every layer OUTPUT is rewritten in place in Tensor Memory as the split-bf16 A operand of the next layer
+// (tcgen05.st after the epilogue, tcgen05.mma with A in TMEM; see tmem_operand), so the feature buffer is free as soon as a
+// first layer has run and the twelve slots of a tile form one software pipeline (worker loop below).
+//
+// Roles: warps 0-7 workers, two threads per row (thread r of group g = warps 4g..4g+3 serves evaluation r = TMEM lane r;
+// the groups split every epilogue by accumulator columns and the feature block by core columns), warp 8 lane 0 streams
+// weight chunks L2 -> shared memory with cp.async.bulk through a 3-slot mbarrier ring (and owns the TMEM allocation),
+// warp 9's elected lane issues tcgen05.mma, warps 10-13 run the last-layer dot products of the previous tile.
+// The per-tile schedule is a static chunk program built on the host at oakb200_net_load (value_net.cu tc_pack).
+// What bounds it (profiles/r2n_eval_tc_pipeline.txt): the workers' serial instruction latency per slot and the MMA count
+// (an M = 128, K = 16 step costs 50-64 cycles whatever its N), not tensor throughput, shared-memory or L2 bandwidth.
 #pragma once
 
 #include "gen1_mem_ops.cuh"
@@ -69,7 +75,7 @@ const int WORKERS = GROUPS * ROWS;
 const int THREADS = WORKERS + 64 + ROWS;
 const int W_STREAM = WORKERS / 32, W_MMA = WORKERS / 32 + 1, W_HEADS = WORKERS / 32 + 2;  // W_HEADS .. +3: the head warps
 static_assert(W_HEADS % 4 == 2, "head warp w serves TMEM lane quarter w % 4");
-const uint32_t OFF_UNION = 0;        // A1 (first-layer features) / A2 (hidden of the active Pokemon) / active embedding
+const uint32_t OFF_UNION = 0;        // A1: the first-layer features of one party slot (the only operand in shared memory)
 const uint32_t OFF_TILE = 65536;     // 128 battle records as word-transposed columns (gen1_state.cuh)
 const uint32_t OFF_RING = 114688;    // weight chunk ring
 #ifndef OAKB200_TC_RING_SLOTS
@@ -94,8 +100,6 @@ static_assert(SMEM_BYTES <= 232448, "fits the 227 KB of one CTA");
 // operand planes (byte offsets from the start of dynamic shared memory); one core column = 128 rows x 16 B
 const uint32_t CORE = ROWS * 16;
 const uint32_t A1_HI = OFF_UNION, A1_LO = OFF_UNION + 30 * CORE;   // K <= 240 hi, 16 lo
-const uint32_t A2_HI = OFF_UNION, A2_LO = OFF_UNION + 16 * CORE;   // K = 128
-const uint32_t AEA_HI = OFF_UNION, AEA_LO = OFF_UNION + 12 * CORE; // active embedding, K = 96
 // TMEM columns
 const uint32_t TMEM_COLS = 512, D_WORK = 0, D_TRUNK = 192, D_HEADS = 256, D_ACT = 416;  // one CTA per SM: all of Tensor Memory
 const uint32_t D_EMB = 128;  // second-layer accumulator of the benched slots (64 columns): beside the first layer's, not over it
@@ -352,97 +356,14 @@ __device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
 }
 
-// One 32-column block of an accumulator: D[:, 32q .. 32q+31] -> min(max(D + bias, 0), bound) -> split planes, core
-// columns 4q .. 4q+3. bound = 1 for the clamp activation, +inf for ReLU, 0 for an empty slot's row.
-// MODE (discrete networks): 1 = then floor(127 x), the u8 an embedding becomes (cache.h:106,234); 2 = the int8 net's
+// One accumulator element -> activation: min(max(D + bias, 0), bound); bound = 1 for the clamp activation, +inf for ReLU,
+// 0 for an empty slot's row. MODE (discrete networks): 1 = then floor(127 x), the u8 an embedding becomes (cache.h:106,234); 2 = the int8 net's
 // ClippedReLU clamp((D + bias) >> 6, 0, 127) instead. Both leave small integers: the hi plane is exact, the lo plane zero.
 template <int MODE>
 __device__ __forceinline__ float epi_act(float v, float b, float bound) {
   if (MODE == 2) return fminf(fmaxf(floorf((v + b) * 0.015625f), 0.0f), 127.0f);
   const float x = fminf(fmaxf(v + b, 0.0f), bound);
   return MODE == 1 ? floorf(127.0f * x) : x;
-}
-template <int MODE>
-__device__ __forceinline__ void epilogue_values_m(const uint32_t (&v)[32], int q, const float* bias, float bound, uint32_t hi, uint32_t lo,
-                                                  int r) {
-  const float4* b4 = reinterpret_cast<const float4*>(bias + 32 * q);
-#pragma unroll
-  for (int g = 0; g < 4; g++) {
-    const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
-    const float x0 = epi_act<MODE>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
-    const float x1 = epi_act<MODE>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
-    const float x2 = epi_act<MODE>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
-    const float x3 = epi_act<MODE>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
-    const float x4 = epi_act<MODE>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
-    const float x5 = epi_act<MODE>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
-    const float x6 = epi_act<MODE>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
-    const float x7 = epi_act<MODE>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
-    uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
-    split2(x0, x1, h0, l0);
-    split2(x2, x3, h1, l1);
-    split2(x4, x5, h2, l2);
-    split2(x6, x7, h3, l3);
-    const uint32_t o = (uint32_t)(((4 * q + g) * ROWS + r) << 4);
-    stv4(hi + o, h0, h1, h2, h3);
-    stv4(lo + o, l0, l1, l2, l3);
-  }
-}
-template <int MODE>
-__device__ __forceinline__ void epilogue_block_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
-  uint32_t v[32];
-  umma::tmem_ld32(taddr + 32u * q, v);
-  umma::tmem_ld_wait();
-  epilogue_values_m<MODE>(v, q, bias, bound, hi, lo, r);
-}
-// two neighbouring blocks q, q + 1 with both Tensor Memory loads in flight before the one wait
-template <int MODE>
-__device__ __forceinline__ void epilogue_pair_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
-  uint32_t v0[32], v1[32];
-  umma::tmem_ld32(taddr + 32u * q, v0);
-  umma::tmem_ld32(taddr + 32u * q + 32u, v1);
-  umma::tmem_ld_wait();
-  epilogue_values_m<MODE>(v0, q, bias, bound, hi, lo, r);
-  epilogue_values_m<MODE>(v1, q + 1, bias, bound, hi, lo, r);
-}
-__device__ __forceinline__ void epilogue_pair(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
-                                              int mode = 0) {
-  if (mode == 0) epilogue_pair_m<0>(taddr, q, bias, bound, hi, lo, r);
-  else if (mode == 1) epilogue_pair_m<1>(taddr, q, bias, bound, hi, lo, r);
-  else epilogue_pair_m<2>(taddr, q, bias, bound, hi, lo, r);
-}
-// the same for a 16-column block: D[:, 16q .. 16q+15] -> core columns 2q, 2q+1
-template <int MODE>
-__device__ __forceinline__ void epilogue_half_m(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r) {
-  uint32_t v[16];
-  umma::tmem_ld16(taddr + 16u * q, v);
-  umma::tmem_ld_wait();
-  const float4* b4 = reinterpret_cast<const float4*>(bias + 16 * q);
-#pragma unroll
-  for (int g = 0; g < 2; g++) {
-    const float4 ba = b4[2 * g], bb = b4[2 * g + 1];
-    const float x0 = epi_act<MODE>(__uint_as_float(v[8 * g + 0]), ba.x, bound);
-    const float x1 = epi_act<MODE>(__uint_as_float(v[8 * g + 1]), ba.y, bound);
-    const float x2 = epi_act<MODE>(__uint_as_float(v[8 * g + 2]), ba.z, bound);
-    const float x3 = epi_act<MODE>(__uint_as_float(v[8 * g + 3]), ba.w, bound);
-    const float x4 = epi_act<MODE>(__uint_as_float(v[8 * g + 4]), bb.x, bound);
-    const float x5 = epi_act<MODE>(__uint_as_float(v[8 * g + 5]), bb.y, bound);
-    const float x6 = epi_act<MODE>(__uint_as_float(v[8 * g + 6]), bb.z, bound);
-    const float x7 = epi_act<MODE>(__uint_as_float(v[8 * g + 7]), bb.w, bound);
-    uint32_t h0, h1, h2, h3, l0, l1, l2, l3;
-    split2(x0, x1, h0, l0);
-    split2(x2, x3, h1, l1);
-    split2(x4, x5, h2, l2);
-    split2(x6, x7, h3, l3);
-    const uint32_t o = (uint32_t)(((2 * q + g) * ROWS + r) << 4);
-    stv4(hi + o, h0, h1, h2, h3);
-    stv4(lo + o, l0, l1, l2, l3);
-  }
-}
-__device__ __forceinline__ void epilogue_half(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
-                                              int mode = 0) {
-  if (mode == 0) epilogue_half_m<0>(taddr, q, bias, bound, hi, lo, r);
-  else if (mode == 1) epilogue_half_m<1>(taddr, q, bias, bound, hi, lo, r);
-  else epilogue_half_m<2>(taddr, q, bias, bound, hi, lo, r);
 }
 // In-place epilogue (see tmem_operand): NC = 16 j fp32 accumulator columns at t0 -> + bias, activation (MODE as epi_act)
 // -> hi plane in columns [t0, t0 + NC / 2), lo plane in [t0 + NC / 2, t0 + NC). hp_col in [0, NC): that K element is the
@@ -502,21 +423,6 @@ __device__ __forceinline__ void epilogue_inplace(uint32_t t0, const float* bias,
   else if (mode == 1) epilogue_inplace_m<1, NC>(t0, bias, bound, hp_col, hp);
   else epilogue_inplace_m<2, NC>(t0, bias, bound, hp_col, hp);
 }
-// mode is warp-uniform (a property of the loaded network)
-__device__ __forceinline__ void epilogue_block(uint32_t taddr, int q, const float* bias, float bound, uint32_t hi, uint32_t lo, int r,
-                                               int mode = 0) {
-  if (mode == 0) epilogue_block_m<0>(taddr, q, bias, bound, hi, lo, r);
-  else if (mode == 1) epilogue_block_m<1>(taddr, q, bias, bound, hi, lo, r);
-  else epilogue_block_m<2>(taddr, q, bias, bound, hi, lo, r);
-}
-// the hp / max-hp column of an embedding operand (written after the block stores of the same thread)
-__device__ __forceinline__ void put_hp(uint32_t hi, uint32_t lo, int r, int col, float hp) {
-  uint32_t h, l;
-  umma::split_bf16(hp, h, l);
-  st16(elem(hi, r, col), h);
-  st16(elem(lo, r, col), l);
-}
-
 // CL = CTAs per cluster. CL = 2: the two CTAs of a cluster walk the chunk program in step on two different tiles, and
 // each weight chunk is read from L2 ONCE for both — each CTA's streamer fetches one half and multicasts it into both
 // rings — because the L2 -> SM weight stream (2.2 MB per tile, every SM asking for the same lines) is what bounds the
@@ -897,17 +803,6 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
       }
     };
     auto workers_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(WORKERS) : "memory"); };
-    // accumulator columns [c0, c1) of D (multiples of 16; 32-column blocks where aligned) -> activation -> operand planes
-    auto epi = [&](uint32_t dcol, int c0, int c1, const float* bias, float bound, uint32_t hi, uint32_t lo, int mode) {
-      int c = c0;
-#ifdef OAKB200_TC_NO_EPI  // timing experiment only: hand-overs without the epilogue work, results are garbage
-      c = c1;
-#endif
-      for (; c + 64 <= c1; c += 64) epilogue_pair(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
-      for (; c + 32 <= c1; c += 32) epilogue_block(tl + dcol, c >> 5, bias, bound, hi, lo, r, mode);
-      if (c < c1) epilogue_half(tl + dcol, c >> 4, bias, bound, hi, lo, r, mode);
-      WT_LAP(1);
-    };
 #ifdef OAKB200_TC_TRACE
     long long tr_w[96];
     int tr_wn = 0, tr_wtile = 0;
