@@ -772,14 +772,22 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #else
 #define WT_LAP(k) do { } while (0)
 #endif
-    auto publish_on = [&](uint32_t which) {  // operand written / TMEM read: hand over to the MMA issuer
+    // hand-over to the MMA issuer, one arrival per warp. An operand in Tensor Memory needs the tcgen05 fence only (the stores
+    // were waited for in the epilogue); the feature block was written through the generic proxy and is read by the async
+    // proxy, hence the proxy fence there.
+    auto publish_on = [&](uint32_t which) {
       umma::tc_fence_before();
-      umma::fence_proxy_async();
-      __syncwarp();  // one arrival per warp
+      __syncwarp();
       if (lane == 0) umma::mbar_arrive(which);
       WT_LAP(2);
     };
-    auto publish = [&]() { publish_on(bar_a); };
+    auto publish = [&]() {
+      umma::tc_fence_before();
+      umma::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(bar_a);
+      WT_LAP(2);
+    };
     uint32_t ephase = 0;
     auto wait_e = [&]() {
       OAKB200_TC_WAIT(bar_e, ephase & 1);
@@ -900,24 +908,14 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
         WT_LAP(3);
       }
       t_pending = true;
-      // ---- trunk (main-net.h:66-107)
-      wait_t();
-      // both trunk layers' activations become the next layer's A operand where their accumulator was (tmem_operand)
-      epilogue_inplace<EMB_NC>(tl + D_TRUNK + (uint32_t)(EMB_NC * grp), cst + C_FC0 + EMB_NC * grp, act_bound, m_main);
-      WT_LAP(1);
-      publish();
-      wait_d();
-      epilogue_inplace<EMB_NC>(tl + D_WORK + (uint32_t)(EMB_NC * grp), cst + C_FC1 + EMB_NC * grp, act_bound, m_main);
-      WT_LAP(1);
       // The head warps read the previous tile's head accumulators and row indices while this tile runs; both are rewritten
       // from here on (a fresh barrier passes the parity-1 wait of the first tile).
       umma::mbar_wait(bar_hfree, (iter + 1) & 1);
       WT_LAP(6);
-      publish();
-      wait_d();
-      // Policy heads (policy.h:29-58), worker part: legal choices -> row indices of the last layer. The dot products
-      // themselves (one 256-byte weight row per legal choice, gathered from L2) are latency-bound, 15 % of the tile time
-      // when the workers did them (profiles/r1o_eval_tc_timing.txt): the head warps run them off the critical path.
+      // Policy heads (policy.h:29-58), worker part, done under the last trunk product: legal choices -> row indices of the
+      // last layer. The dot products themselves (one 256-byte weight row per legal choice, gathered from L2) are
+      // latency-bound, 15 % of the tile time when the workers did them (profiles/r1o_eval_tc_timing.txt): the head warps
+      // run them off the critical path.
       if (grp < 2) {
         const int s = grp;
         const uint32_t res = results[ec];
@@ -946,6 +944,20 @@ eval_tc_kernel(Params P, const uint8_t* __restrict__ battles, const uint8_t* __r
 #pragma unroll
         for (int k = 0; k < 6; k++) asm volatile("st.shared.u32 [%0], %1;" ::"r"(ia + 4 * k), "r"(idx[2 * k] | (idx[2 * k + 1] << 16)) : "memory");
         if (e < n) counts[(size_t)e * 2 + s] = (uint8_t)cnt;
+      }
+      WT_LAP(5);
+      // ---- trunk (main-net.h:66-107)
+      wait_t();
+      // both trunk layers' activations become the next layer's A operand where their accumulator was (tmem_operand)
+      epilogue_inplace<EMB_NC>(tl + D_TRUNK + (uint32_t)(EMB_NC * grp), cst + C_FC0 + EMB_NC * grp, act_bound, m_main);
+      WT_LAP(1);
+      publish_on(bar_a);
+      wait_d();
+      epilogue_inplace<EMB_NC>(tl + D_WORK + (uint32_t)(EMB_NC * grp), cst + C_FC1 + EMB_NC * grp, act_bound, m_main);
+      WT_LAP(1);
+      publish_on(bar_a);
+      wait_d();
+      if (grp < 2) {  // head accumulators and row indices of this tile are ready
         umma::tc_fence_before();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bar_h);
