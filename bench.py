@@ -365,16 +365,52 @@ def main():
     pel = torch.empty((EV, 2, 9), dtype=torch.float32).pin_memory()
     pec = torch.empty((EV, 2), dtype=torch.uint8).pin_memory()
 
-    def eval_e2e():
-        rc = lib.oakb200_eval_host(h, EV, peb.data_ptr(), ped.data_ptr(), per_.data_ptr(), pev.data_ptr(), pel.data_ptr(), pec.data_ptr())
+    def eval_e2e(k=0):
+        e_, (o_v, o_l, o_c) = ev_engs[k], ev_out[k]
+        rc = lib.oakb200_eval_host(e_._h, EV, peb.data_ptr(), ped.data_ptr(), per_.data_ptr(), o_v.data_ptr(), o_l.data_ptr(), o_c.data_ptr())
         if rc:
-            raise RuntimeError(lib.oakb200_last_error(h).decode())
+            raise RuntimeError(lib.oakb200_last_error(e_._h).decode())
+    # one caller: the calls follow one another, each ends with its own download
+    ev_engs, ev_out = [eng], [(pev, pel, pec)]
     eval_e2e()
     t0 = time.perf_counter()
     for _ in range(5):
         eval_e2e()
-    eval_e2e_s = (time.perf_counter() - t0) / 5
+    eval_e2e_one_s = (time.perf_counter() - t0) / 5
     launches += 6
+    # two callers (host threads with a context each, as two search threads of one process would be): one call's upload
+    # runs under the other's kernels and download, so the PCIe link stays busy. This is the leg's headline figure.
+    ev2 = _BE(EV, device=local)
+    ev2.load_network(blob)
+    ev_engs.append(ev2)
+    ev_out.append((torch.empty(EV, dtype=torch.float32).pin_memory(), torch.empty((EV, 2, 9), dtype=torch.float32).pin_memory(),
+                   torch.empty((EV, 2), dtype=torch.uint8).pin_memory()))
+
+    def eval_e2e_run(total):
+        errs = []
+
+        def worker(k, count):
+            try:
+                for _ in range(count):
+                    eval_e2e(k)
+            except Exception as ex:  # surfaced below
+                errs.append(ex)
+        ts_ = [threading.Thread(target=worker, args=(k, total // 2)) for k in range(2)]
+        for t_ in ts_:
+            t_.start()
+        for t_ in ts_:
+            t_.join()
+        if errs:
+            raise errs[0]
+    EV_CALLS = 20
+    eval_e2e_run(4)
+    l0 = sum(e_.launch_count for e_ in ev_engs)
+    t0 = time.perf_counter()
+    eval_e2e_run(EV_CALLS)
+    eval_e2e_s = (time.perf_counter() - t0) / EV_CALLS
+    launches += sum(e_.launch_count for e_ in ev_engs) - l0
+    assert torch.equal(ev_out[0][0], ev_out[1][0]) and torch.equal(ev_out[0][2], ev_out[1][2]), "the two evaluation contexts disagree"
+    ev2.close()
     # ---- secondary: self-play generation (BASELINE configs[4]): lockstep games, network policy, frames recorded and
     # packed on the device, drained per rank into page-locked shared-memory rings the writer (rank 0) reads — no collective
     import json as _json
@@ -685,7 +721,8 @@ def main():
                           "kernel": "eval_tc_kernel (tcgen05.mma kind::f16 on split-bf16 operand pairs, fp32 accumulate in TMEM; "
                                     "one-hot first layers as dense tiles)",
                           "e2e_evals_per_s": world * EV / eval_e2e_s,
-                          "e2e_note": "pinned host records in (393 B/eval H2D), value + logits + counts out (78 B/eval D2H), wall clock around oakb200_eval_host (chunked upload / kernel / download on three streams)",
+                          "e2e_evals_per_s_one_caller": world * EV / eval_e2e_one_s,
+                          "e2e_note": "pinned host records in (393 B/eval H2D), value + logits + counts out (78 B/eval D2H), wall clock around oakb200_eval_host (chunked upload / kernel / download on three streams); e2e_evals_per_s = calls issued by two host threads on two contexts (one call's upload under the other's kernels and download), one_caller = calls one after another",
                           "fp32_cuda_core_kernel_evals_per_s": world * EV / (eval_ms_mode[1] * 1e-3),
                           "roofline": {"bound": "tensor", "achieved": F_EVAL_TC * EV / (eval_ms * 1e-3) / 1e12,
                                        "peak": pk["bf16_tflops"], "unit": "TFLOP/s",

@@ -106,7 +106,7 @@ OAK_HD_NOINLINE void mem_boost(M m, int p, uint32_t eff) {
       }
       return;
     }
-    const uint32_t v = m.stat_at(mem_unmodified_stats(m, p), ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
+    const uint32_t v = boost_scale(m.stat_at(mem_unmodified_stats(m, p), ST_ATK + 2 * which), nb);
     m.st16(s, so, v < 999 ? v : 999);
   }
   m.st32(s, A_BOOSTS, boost_set(b, which, nb));
@@ -154,7 +154,7 @@ OAK_HD_NOINLINE void mem_unboost(M m, int f, uint32_t eff) {
       }
       return;
     }
-    const uint32_t v = m.stat_at(mem_unmodified_stats(m, f), ST_ATK + 2 * which) * boost_num(nb) / boost_den(nb);
+    const uint32_t v = boost_scale(m.stat_at(mem_unmodified_stats(m, f), ST_ATK + 2 * which), nb);
     m.st16(s, so, v > 1 ? v : 1);
   }
   m.st32(s, A_BOOSTS, boost_set(b, which, nb));
@@ -291,51 +291,57 @@ OAK_HD_NOINLINE void mem_switch_in(M m, int p, int slot) {
 }
 
 // choices :3139-3251. Legal choices packed 5 bits each (type | data << 2), first in the low bits;
-// the count (1..9) in bits 60..63.
+// the count (1..9) in bits 60..63. Called twice per update by every lane (7.5 % of the playout kernel's instructions), so
+// the party order and the four {move, pp} pairs are read as two words each and the two partial lists (switches: at most
+// 25 bits, moves: at most 20) are built in 32-bit registers and joined by one 64-bit shift.
 template <class M>
 OAK_HD_NOINLINE uint64_t mem_choices(M m, int p, int request) {
-  uint64_t list = 0;
-  uint64_t k = 0;
   if (request == CH_PASS) return 1ull << 60;
   const H s = M::sb(p);
   const uint32_t lo = m.vlo(p);
   if (request == CH_MOVE && (lo & (VL_RECHARGING | VL_RAGE | VL_THRASHING | VL_CHARGING))) {
     return (1ull << 60) | (uint64_t)((1u << 2) | CH_MOVE);
   }
+  const uint32_t o0 = m.ld32(s, S_ORDER), o1 = m.ld32(s, S_ORDER + 4);  // order[0..3] | order[4], order[5], last_selected, last_used
+  uint32_t sw = 0, k = 0;
+#pragma unroll
   for (int slot = 2; slot <= 6; slot++) {
-    const uint32_t id = m.ld8(s, S_ORDER + slot - 1);
+    const uint32_t id = (slot <= 4 ? o0 >> (8 * (slot - 1)) : o1 >> (8 * (slot - 5))) & 255u;
     if (id == 0 || m.ld16(M::pokemon(p, (int)id - 1), PK_HP) == 0) continue;
-    list |= (uint64_t)(((uint32_t)slot << 2) | CH_SWITCH) << (5 * k);
+    sw |= (((uint32_t)slot << 2) | CH_SWITCH) << (5 * k);
     k++;
   }
-  if (request == CH_SWITCH) return list | ((k == 0 ? 1ull : k) << 60);
+  if (request == CH_SWITCH) return (uint64_t)sw | ((uint64_t)(k == 0 ? 1u : k) << 60);
   const uint32_t dm = m.vhi_field(p, VHI_DISABLE_MOVE);
+  const uint32_t mv0 = m.ld32(s, A_MOVES), mv1 = m.ld32(s, A_MOVES + 4);  // id0 pp0 id1 pp1 | id2 pp2 id3 pp3
   if (lo & (VL_BIDE | VL_BINDING)) {
-    const uint32_t want = (lo & VL_BIDE) ? (uint32_t)MOVE_Bide : m.last_selected(p);
+    const uint32_t want = (lo & VL_BIDE) ? (uint32_t)MOVE_Bide : (o1 >> 16) & 255u;  // last_selected
+#pragma unroll
     for (int slot = 1; slot <= 4; slot++) {
-      const uint32_t id = m.ld8(s, A_MOVES + 2 * (slot - 1));
+      const uint32_t e = (slot <= 2 ? mv0 >> (16 * (slot - 1)) : mv1 >> (16 * (slot - 3))) & 0xFFFFu;
+      const uint32_t id = e & 255u;
       if (id == MOVE_None) break;
       if (id == want) {
-        const bool struggle = id == MOVE_Bide && (m.ld8(s, A_MOVES + 2 * (slot - 1) + 1) == 0 || dm == (uint32_t)slot);
-        list |= (uint64_t)(((struggle ? 0u : (uint32_t)slot) << 2) | CH_MOVE) << (5 * k);
-        return list | ((k + 1) << 60);
+        const bool struggle = id == MOVE_Bide && ((e >> 8) == 0 || dm == (uint32_t)slot);
+        const uint32_t entry = ((struggle ? 0u : (uint32_t)slot) << 2) | CH_MOVE;
+        return (uint64_t)sw | ((uint64_t)entry << (5 * k)) | ((uint64_t)(k + 1) << 60);
       }
     }
   }
-  const uint64_t before = k;
+  uint32_t mvl = 0, km = 0;
+#pragma unroll
   for (int slot = 1; slot <= 4; slot++) {
-    const uint32_t id = m.ld8(s, A_MOVES + 2 * (slot - 1));
-    if (id == MOVE_None) break;
-    if (m.ld8(s, A_MOVES + 2 * (slot - 1) + 1) == 0) continue;
-    if (dm == (uint32_t)slot) continue;
-    list |= (uint64_t)(((uint32_t)slot << 2) | CH_MOVE) << (5 * k);
-    k++;
+    const uint32_t e = (slot <= 2 ? mv0 >> (16 * (slot - 1)) : mv1 >> (16 * (slot - 3))) & 0xFFFFu;
+    if ((e & 255u) == MOVE_None) break;
+    if ((e >> 8) == 0 || dm == (uint32_t)slot) continue;
+    mvl |= (((uint32_t)slot << 2) | CH_MOVE) << (5 * km);
+    km++;
   }
-  if (k == before) {
-    list |= (uint64_t)CH_MOVE << (5 * k);  // move 0 = Struggle
-    k++;
+  if (km == 0) {  // move 0 = Struggle
+    mvl = CH_MOVE;
+    km = 1;
   }
-  return list | (k << 60);
+  return (uint64_t)sw | ((uint64_t)mvl << (5 * k)) | ((uint64_t)(k + km) << 60);
 }
 OAK_HD uint32_t choice_at(uint64_t list, int i) { return (uint32_t)(list >> (5 * i)) & 31u; }
 OAK_HD int choice_count(uint64_t list) { return (int)(list >> 60); }

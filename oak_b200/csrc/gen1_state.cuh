@@ -158,6 +158,13 @@ OAK_HD uint32_t boost_den(int stage) {
   // 100 x6, 1, 10, 1, 10, 1, 10, 1
   return stage < 0 ? 100u : ((stage & 1) ? 10u : 1u);
 }
+// x * num / den of a stage with the three possible denominators as CONSTANT divisions (a multiply-high each) and a select,
+// instead of a division by a run-time value (~30 instructions, 5 % of the playout kernel's instructions when it was one)
+OAK_HD uint32_t boost_scale(uint32_t x, int stage) {
+  const uint32_t n = x * boost_num(stage);
+  const uint32_t q100 = n / 100u, q10 = n / 10u;
+  return stage < 0 ? q100 : ((stage & 1) ? q10 : n);
+}
 
 // volatile flag masks on the LOW word of the packed u64 (bits 0..17), fields confusion/attacks
 enum : uint32_t {

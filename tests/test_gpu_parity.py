@@ -29,9 +29,13 @@ def first_diff(a, b):
 
 
 def test_native_library_is_loaded(eng):
+    # the product path is the CUDA library: it is loaded from the tree and a call through the C ABI launches a kernel
     import oak_b200
-    assert oak_b200.load_library() is not None
-    assert eng.launch_count >= 0
+    lib = oak_b200.load_library()
+    assert lib is not None and "liboakb200" in lib._name
+    before = eng.launch_count
+    eng.build_battles(sample_teams(0, 128), sample_seeds(0, 128))
+    assert eng.launch_count > before
 
 
 def test_build_battles_matches_reference_construction(orc, eng):
