@@ -372,12 +372,14 @@ def main():
             raise RuntimeError(lib.oakb200_last_error(e_._h).decode())
     # one caller: the calls follow one another, each ends with its own download
     ev_engs, ev_out = [eng], [(pev, pel, pec)]
-    eval_e2e()
-    t0 = time.perf_counter()
-    for _ in range(5):
+    EV_ONE = 50
+    for _ in range(3):
         eval_e2e()
-    eval_e2e_one_s = (time.perf_counter() - t0) / 5
-    launches += 6
+    t0 = time.perf_counter()
+    for _ in range(EV_ONE):
+        eval_e2e()
+    eval_e2e_one_s = (time.perf_counter() - t0) / EV_ONE
+    launches += EV_ONE + 3
     # two callers (host threads with a context each, as two search threads of one process would be): one call's upload
     # runs under the other's kernels and download, so the PCIe link stays busy. This is the leg's headline figure.
     ev2 = _BE(EV, device=local)
@@ -402,8 +404,8 @@ def main():
             t_.join()
         if errs:
             raise errs[0]
-    EV_CALLS = 20
-    eval_e2e_run(4)
+    EV_CALLS = 200  # ~0.1 s: long enough that thread start-up does not show
+    eval_e2e_run(10)
     l0 = sum(e_.launch_count for e_ in ev_engs)
     t0 = time.perf_counter()
     eval_e2e_run(EV_CALLS)
