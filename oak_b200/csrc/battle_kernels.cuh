@@ -245,8 +245,11 @@ __device__ __forceinline__ bool wait_available(uint32_t* available, uint32_t i) 
 // "maybe refill, then exactly one update" so that all lanes re-converge once per update.
 // SPLIT: the on-chip column holds only the 48 words an update can write (gen1_state.cuh); stored stats, move ids, species,
 // types and level are read from the battle's record in global memory. 24 KB per CTA instead of 48: 8 CTAs = 32 warps per SM.
+#ifndef OAKB200_ROLLOUT_MINB
+#define OAKB200_ROLLOUT_MINB 8  // resident CTAs per SM the register budget is set for (A/B knob: 7 -> 72 registers, 6 -> 80)
+#endif
 template <int BLOCK, bool CHANCE, bool WRITE_STATE, bool SPLIT>
-__global__ void __launch_bounds__(BLOCK, SPLIT ? 8 : 3)
+__global__ void __launch_bounds__(BLOCK, SPLIT ? OAKB200_ROLLOUT_MINB : 3)
 rollout_kernel(uint8_t* battles, uint8_t* __restrict__ durations, uint8_t* __restrict__ results,
                const uint64_t* __restrict__ seeds, uint32_t max_steps, uint32_t n, uint32_t* __restrict__ ticket,
                uint8_t* __restrict__ score2_out, uint16_t* __restrict__ turns_out, uint32_t* __restrict__ steps_out,
