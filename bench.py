@@ -358,7 +358,33 @@ def main():
         eval_ms_mode[mode] = ee0.elapsed_time(ee1) / EVIT
         launches += EVIT + 3
     eng.set_eval_mode(0)
-    eval_ms = eval_ms_mode[2]
+    eval_ms_one = eval_ms_mode[2]
+    # The same batches issued alternately on two CUDA streams (a second context with the same parameters, its own outputs),
+    # as the two self-play lanes and the search's root groups issue them: 65 536 evaluations are 512 tiles on 148 SMs, i.e.
+    # 3.46 rounds run as 4, and the next launch's CTAs take the 80 SMs that have no fourth tile.
+    ev_eng_b = _BE(1, device=local)
+    ev_stream_b = torch.cuda.Stream(dev)
+    ev_eng_b.set_stream(ev_stream_b.cuda_stream)
+    ev_eng_b.load_network(blob)
+    ev_out_b = (torch.empty_like(ev_v), torch.empty_like(ev_l), torch.empty_like(ev_c))
+    ev_lanes = [(eng, stream, (ev_v, ev_l, ev_c)), (ev_eng_b, ev_stream_b, ev_out_b)]
+    EV2 = 20
+    for k in range(4):
+        ev_lanes[k & 1][0].evaluate_device(eb, ed, er, *ev_lanes[k & 1][2])
+    torch.cuda.synchronize(dev)
+    es0, es1, esb = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    es0.record(stream)
+    ev_stream_b.wait_event(es0)
+    for k in range(EV2):
+        ev_lanes[k & 1][0].evaluate_device(eb, ed, er, *ev_lanes[k & 1][2])
+    esb.record(ev_stream_b)
+    stream.wait_event(esb)
+    es1.record(stream)
+    torch.cuda.synchronize(dev)
+    eval_ms = es0.elapsed_time(es1) / EV2
+    launches += EV2 + 4
+    assert torch.equal(ev_v, ev_out_b[0]) and torch.equal(ev_c, ev_out_b[2]), "the two evaluation streams disagree"
+    ev_eng_b.close()
     # end to end through the C ABI with pinned HOST buffers: records in, value/logits/counts out
     peb, ped, per_ = (x.cpu().pin_memory() for x in (eb, ed, er))
     pev = torch.empty(EV, dtype=torch.float32).pin_memory()
@@ -718,7 +744,8 @@ def main():
                                      "achieved_gbs": B_STEP * n / (lock_ms * 1e-3) / 1e9,
                                      "frac_of_hbm_peak": B_STEP * n / (lock_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                                      "live_fraction_at_start": live_before / n},
-            "leaf_eval": {"evals_per_s": world * EV / (eval_ms * 1e-3), "batch_per_gpu": EV, "ms_per_batch": eval_ms,
+            "leaf_eval": {"evals_per_s": world * EV / (eval_ms * 1e-3), "batch_per_gpu": EV, "ms_per_batch": eval_ms, "ms_per_batch_one_stream": eval_ms_one,
+                          "streams": "batches issued alternately on two CUDA streams (the next launch's CTAs take the SMs that have no fourth tile); one_stream = launches back to back on one stream",
                           "network": "default dims 198/427->128->59/83, 768->64->64, value 32, policy 64->315 (legal rows), relu",
                           "kernel": "eval_tc_kernel (tcgen05.mma kind::f16 on split-bf16 operand pairs, fp32 accumulate in TMEM; "
                                     "one-hot first layers as dense tiles)",
