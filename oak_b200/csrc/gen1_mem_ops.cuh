@@ -171,7 +171,7 @@ OAK_HD void mem_build_rage(M m, int who) {
 
 // handleResidual :1585-1637
 template <class M>
-OAK_HD_NOINLINE void mem_handle_residual(M m, int p) {
+OAK_HD_NOINLINE void mem_handle_residual_slow(M m, int p) {
   const PH pk = m.stored(p);
   const uint32_t st = m.ld8(pk, PK_STATUS);
   const uint32_t lo = m.vlo(p);
@@ -210,6 +210,14 @@ OAK_HD_NOINLINE void mem_handle_residual(M m, int p) {
   }
 }
 
+// the common case (no burn / poison / Leech Seed) decided at the call site: no call, no argument moves
+template <class M>
+OAK_HD void mem_handle_residual(M m, int p) {
+  const uint32_t st = m.ld8(m.stored(p), PK_STATUS);
+  if (!(st & (SB_BRN | SB_PSN)) && !m.vflag(p, VL_LEECH_SEED)) return;
+  mem_handle_residual_slow(m, p);
+}
+
 template <class M>
 OAK_HD int mem_find_first_alive(M m, int p) {  // :99-102
   for (int i = 0; i < 6; i++)
@@ -219,8 +227,7 @@ OAK_HD int mem_find_first_alive(M m, int p) {  // :99-102
 
 // checkFaint :1507-1543 + faint :1545-1583. Returns the result byte or -1.
 template <class M>
-OAK_HD_NOINLINE int mem_check_faint(M m, int p) {
-  if (m.hp_of(m.stored(p)) > 0) return -1;
+OAK_HD_NOINLINE int mem_check_faint_slow(M m, int p) {
   const bool foe_fainted = m.hp_of(m.stored(p ^ 1)) == 0;
   const bool player_out = mem_find_first_alive(m, p) == 0;
   const bool foe_out = foe_fainted && mem_find_first_alive(m, p ^ 1) == 0;
@@ -259,6 +266,13 @@ OAK_HD_NOINLINE int mem_check_faint(M m, int p) {
   }
   const int fc = foe_fainted ? CH_SWITCH : CH_PASS;
   return p == 0 ? ((CH_SWITCH << 4) | (fc << 6)) : ((fc << 4) | (CH_SWITCH << 6));
+}
+
+// the common case (the active Pokémon has not fainted) decided at the call site
+template <class M>
+OAK_HD int mem_check_faint(M m, int p) {
+  if (m.hp_of(m.stored(p)) > 0) return -1;
+  return mem_check_faint_slow(m, p);
 }
 
 // switchIn :225-263 without the chance bookkeeping (done by the caller)
