@@ -242,6 +242,7 @@ struct Mem : ConstRecord<SPLIT> {
   OAK_HD uint32_t atv(int v) const { return sbase + (uint32_t)v; }
   OAK_HD uint32_t cld8(int off) const { return SPLIT ? (uint32_t)__ldg(crec_ptr() + off) : 0u; }
   OAK_HD uint32_t cld16(int off) const { return SPLIT ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(crec_ptr() + off)) : 0u; }
+  OAK_HD uint2 cld64(int off) const { return SPLIT ? __ldg(reinterpret_cast<const uint2*>(crec_ptr() + off)) : make_uint2(0u, 0u); }  // off % 8 == 0
 #else
   uint8_t* base;  // host (tests only): address of byte 0 of word 0 of this battle's column
   OAK_HD void set(uint8_t* column) { base = column; }
