@@ -148,6 +148,19 @@ struct Params {
 
 // AoS record (384 B, 16-byte aligned) -> column of the word-transposed tile; the four threads of a row take a quarter each
 __device__ __forceinline__ void load_record_part(uint32_t* col, const uint8_t* record, int part) {
+  if ((reinterpret_cast<uintptr_t>(record) & 31u) == 0) {  // whole 32-byte sectors with 256-bit loads (battle_kernels.cuh: load_column)
+    const int per8 = 12 / GROUPS;
+#pragma unroll
+    for (int k = per8 * part; k < per8 * part + per8; k++) {
+      uint32_t v[8];
+      asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                   : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                   : "l"(record + 32 * k));
+#pragma unroll
+      for (int j = 0; j < 8; j++) col[(8 * k + j) * ROWS] = v[j];
+    }
+    return;
+  }
   const uint4* src = reinterpret_cast<const uint4*>(record);
   const int per = 24 / GROUPS;
 #pragma unroll
