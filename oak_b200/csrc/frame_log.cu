@@ -57,39 +57,49 @@ __global__ void frames_begin_kernel(uint8_t* buf, uint32_t* used, uint16_t* nupd
   }
 }
 
-// one thread per slot: append the update of this step (before the battle is advanced)
+// one WARP per slot: append the update of this step (before the battle is advanced). Lane l writes bytes l, l + 32, l + 64
+// of the record (11 + 4 (m + k) <= 83 bytes), so a record is three coalesced byte stores of the warp; a thread per slot
+// made ~83 scattered byte stores each (56 us per 65 536 games, a seventh of a self-play step).
 __global__ void frames_record_kernel(uint8_t* buf, uint32_t* used, uint16_t* nupd, uint8_t* state, uint32_t cap, uint32_t max_updates,
                                      const uint8_t* __restrict__ results, const uint8_t* __restrict__ c1,
                                      const uint8_t* __restrict__ c2, const uint8_t* __restrict__ counts,
                                      const uint32_t* __restrict__ iterations, const float* __restrict__ emp_value,
                                      const float* __restrict__ nash_value, const float* __restrict__ emp,
                                      const float* __restrict__ nash, uint32_t n) {
-  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n || state[g] != FS_RECORDING || (results[g] & 15u) != 0) return;
+  const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (g >= n || state[g] != FS_RECORDING || (results[g] & 15u) != 0) return;  // uniform over the warp
   const uint32_t m = counts[2 * g], k = counts[2 * g + 1];
   const uint32_t sz = 11 + 4 * (m + k), at = used[g];
   if (m < 1 || k < 1 || m > 9 || k > 9 || nupd[g] >= max_updates || at + sz > cap) {
-    state[g] = FS_OVERFLOW;
+    __syncwarp();
+    if (lane == 0) state[g] = FS_OVERFLOW;
     return;
   }
   uint8_t* p = buf + (size_t)g * cap + at;
-  auto put16 = [&](uint32_t v) { *p++ = (uint8_t)v; *p++ = (uint8_t)(v >> 8); };
-  *p++ = (uint8_t)((m - 1) | ((k - 1) << 4));
-  *p++ = c1[g];
-  *p++ = c2[g];
   const uint32_t it = iterations ? iterations[g] : 0;
-  put16(it & 0xFFFFu);
-  put16(it >> 16);
-  put16(compress_prob(emp_value[g]));
-  put16(compress_prob(nash_value[g]));
   const float* e = emp + (size_t)g * 18;
   const float* q = nash + (size_t)g * 18;
-  for (uint32_t i = 0; i < m; i++) put16(compress_prob(e[i]));
-  for (uint32_t i = 0; i < m; i++) put16(compress_prob(q[i]));
-  for (uint32_t i = 0; i < k; i++) put16(compress_prob(e[9 + i]));
-  for (uint32_t i = 0; i < k; i++) put16(compress_prob(q[9 + i]));
-  used[g] = at + sz;
-  nupd[g] = (uint16_t)(nupd[g] + 1);
+#pragma unroll
+  for (uint32_t r = 0; r < 3; r++) {
+    const uint32_t b = lane + 32 * r;
+    if (b >= sz) break;
+    uint32_t v;
+    if (b < 11) {
+      const uint32_t ev = compress_prob(emp_value[g]), nv = compress_prob(nash_value[g]);
+      v = b == 0 ? ((m - 1) | ((k - 1) << 4)) : b == 1 ? c1[g] : b == 2 ? c2[g] : b < 7 ? it >> (8 * (b - 3))
+          : b < 9 ? ev >> (8 * (b - 7)) : nv >> (8 * (b - 9));
+    } else {
+      const uint32_t j = (b - 11) >> 1;  // 16-bit entry: m empirical p1, m nash p1, k empirical p2, k nash p2
+      const float x = j < m ? e[j] : j < 2 * m ? q[j - m] : j < 2 * m + k ? e[9 + j - 2 * m] : q[9 + j - 2 * m - k];
+      v = (uint32_t)compress_prob(x) >> (8 * ((b - 11) & 1));
+    }
+    p[b] = (uint8_t)v;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    used[g] = at + sz;
+    nupd[g] = (uint16_t)(nupd[g] + 1);
+  }
 }
 
 // one thread per slot: a recording game whose battle has ended gets its header and result
@@ -283,7 +293,7 @@ int oakb200_frames_record_device(oakb200_ctx* ctx, size_t n, const void* results
   if (n == 0) return OAKB200_OK;
   oakb200_frames* f = ctx->frames;
   CU(ctx, cudaSetDevice(ctx->device));
-  frames_record_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(
+  frames_record_kernel<<<(unsigned)((n * 32 + 127) / 128), 128, 0, ctx->stream>>>(
       f->buf, f->used, f->nupd, f->state, f->cap, f->max_updates, (const uint8_t*)results, (const uint8_t*)c1, (const uint8_t*)c2,
       (const uint8_t*)counts, (const uint32_t*)iterations, (const float*)empirical_value, (const float*)nash_value,
       (const float*)empirical, (const float*)nash, (uint32_t)n);
