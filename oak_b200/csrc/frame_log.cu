@@ -67,31 +67,41 @@ __global__ void frames_record_kernel(uint8_t* buf, uint32_t* used, uint16_t* nup
                                      const float* __restrict__ nash_value, const float* __restrict__ emp,
                                      const float* __restrict__ nash, uint32_t n) {
   const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (g >= n || state[g] != FS_RECORDING || (results[g] & 15u) != 0) return;  // uniform over the warp
-  const uint32_t m = counts[2 * g], k = counts[2 * g + 1];
-  const uint32_t sz = 11 + 4 * (m + k), at = used[g];
-  if (m < 1 || k < 1 || m > 9 || k > 9 || nupd[g] >= max_updates || at + sz > cap) {
+  if (g >= n) return;
+  // every input is asked for before the first decision: the kernel is a chain of dependent loads per warp, and a load
+  // behind a branch waits for the one the branch tests
+  const float* e = emp + (size_t)g * 18;
+  const float* q = nash + (size_t)g * 18;
+  const uint32_t st = state[g], res = results[g], m = counts[2 * g], k = counts[2 * g + 1], at = used[g], nu = nupd[g];
+  const uint32_t it = iterations ? iterations[g] : 0;
+  const uint32_t ca = c1[g], cb = c2[g];
+  const float fev = emp_value[g], fnv = nash_value[g];
+  const float xe = lane < 18 ? e[lane] : 0.0f, xq = lane < 18 ? q[lane] : 0.0f;  // lane j holds entry j of both tables
+  if (st != FS_RECORDING || (res & 15u) != 0) return;  // uniform over the warp
+  const uint32_t sz = 11 + 4 * (m + k);
+  if (m < 1 || k < 1 || m > 9 || k > 9 || nu >= max_updates || at + sz > cap) {
     __syncwarp();
     if (lane == 0) state[g] = FS_OVERFLOW;
     return;
   }
   uint8_t* p = buf + (size_t)g * cap + at;
-  const uint32_t it = iterations ? iterations[g] : 0;
-  const float* e = emp + (size_t)g * 18;
-  const float* q = nash + (size_t)g * 18;
+  const uint32_t ce = compress_prob(xe), cq = compress_prob(xq);  // 16-bit forms of this lane's two entries
 #pragma unroll
   for (uint32_t r = 0; r < 3; r++) {
     const uint32_t b = lane + 32 * r;
-    if (b >= sz) break;
+    // 16-bit entry j of the record: m empirical p1, m nash p1, k empirical p2, k nash p2 -> (table, index) -> owning lane
+    const uint32_t j = b >= 11 ? (b - 11) >> 1 : 0;
+    const bool from_q = (j >= m && j < 2 * m) || j >= 2 * m + k;
+    const uint32_t src = j < m ? j : j < 2 * m ? j - m : j < 2 * m + k ? 9 + j - 2 * m : 9 + j - 2 * m - k;
+    const uint32_t ve = __shfl_sync(0xFFFFFFFFu, ce, (int)(src & 31u)), vq = __shfl_sync(0xFFFFFFFFu, cq, (int)(src & 31u));
+    if (b >= sz) continue;
     uint32_t v;
     if (b < 11) {
-      const uint32_t ev = compress_prob(emp_value[g]), nv = compress_prob(nash_value[g]);
-      v = b == 0 ? ((m - 1) | ((k - 1) << 4)) : b == 1 ? c1[g] : b == 2 ? c2[g] : b < 7 ? it >> (8 * (b - 3))
+      const uint32_t ev = compress_prob(fev), nv = compress_prob(fnv);
+      v = b == 0 ? ((m - 1) | ((k - 1) << 4)) : b == 1 ? ca : b == 2 ? cb : b < 7 ? it >> (8 * (b - 3))
           : b < 9 ? ev >> (8 * (b - 7)) : nv >> (8 * (b - 9));
     } else {
-      const uint32_t j = (b - 11) >> 1;  // 16-bit entry: m empirical p1, m nash p1, k empirical p2, k nash p2
-      const float x = j < m ? e[j] : j < 2 * m ? q[j - m] : j < 2 * m + k ? e[9 + j - 2 * m] : q[9 + j - 2 * m - k];
-      v = (uint32_t)compress_prob(x) >> (8 * ((b - 11) & 1));
+      v = (from_q ? vq : ve) >> (8 * ((b - 11) & 1));
     }
     p[b] = (uint8_t)v;
   }
