@@ -278,3 +278,37 @@ def test_pipelined_host_rollout_beyond_32_default_chunks(orc):
     for a, w in zip(got, want):
         assert np.array_equal(a, w[idx])
     eng.close()
+
+
+def test_records_aligned_to_16_bytes_only(orc):
+    """The one-update kernels and the evaluation read a 32-byte-aligned record with 256-bit accesses and any other
+    16-byte-aligned one with 128-bit accesses (include/oakb200.h asks for 16): both forms give the same bytes."""
+    import torch
+    import oak_b200
+    n = 4096
+    dev = torch.device("cuda:0")
+    e = oak_b200.BattleEngine(n)
+    b, d, r = oracle_sample_batch(orc, 0, n)
+    seeds = torch.from_numpy(sample_seeds(0, n).view(np.int64)).to(dev)
+    raw = torch.zeros(n * 384 + 64, dtype=torch.uint8, device=dev)
+    outs = []
+    for shift in (0, 16):  # torch allocations are 512-byte aligned: shift 16 leaves every record on 16 (mod 32)
+        tb = raw[shift:shift + n * 384].view(n, 384)
+        assert tb.data_ptr() % 32 == shift
+        tb.copy_(torch.from_numpy(b).to(dev))
+        td = torch.from_numpy(d).to(dev)
+        tr = torch.from_numpy(r).to(dev)
+        for s in range(24):
+            e.step_random_device(tb, td, tr, seeds, s)
+        torch.cuda.synchronize()
+        outs.append((tb.cpu().numpy().copy(), td.cpu().numpy(), tr.cpu().numpy()))
+    for x, y in zip(outs[0], outs[1]):
+        assert np.array_equal(x, y)
+    ob, od, orr = b.copy(), d.copy(), r.copy()  # and both equal the oracle's 24 playout steps
+    sd = sample_seeds(0, n)
+    for i in range(0, n, 64):
+        for s in range(24):
+            if (orr[i] & 15) == 0:
+                orr[i], _, _, _ = orc.step(ob[i], od[i], int(orr[i]), pick_word(int(sd[i]), s))
+        assert np.array_equal(outs[0][0][i], ob[i]) and outs[0][2][i] == orr[i], first_diff(outs[0][0][i:i + 1], ob[i:i + 1])
+    e.close()
