@@ -694,6 +694,17 @@ def main():
         value = tot_steps / (ms_total_max * 1e-3)
         kern_s = ms_total_max / args.steps * 1e-3  # time per launch over the timed region (launches overlap only at their tails)
         achieved = B_ROLLOUT * n / kern_s / 1e9
+        # DRAM traffic of one launch: from the newest `ncu --set full` summary when it is of the bench configuration (2^20
+        # playouts per launch), else the round-1 capture of the same configuration; scaled to this n
+        iss_ = issue_stats()
+        if iss_ and "2^20" in iss_.get("command", "") and iss_.get("dram_bytes"):
+            traffic_bytes = int(iss_["dram_bytes"] * n / (1 << 20))
+            traffic_src = (f"dram__bytes_read.sum + dram__bytes_write.sum of one launch of 2^20 playouts (ncu --set full, {iss_['file']}, "
+                           f"captured {iss_.get('captured')}), scaled to this n")
+        else:
+            traffic_bytes = int(424_100_608 * n / (1 << 20))
+            traffic_src = ("dram__bytes_read.sum + dram__bytes_write.sum = 414.9 + 9.2 MB for one launch of 2^20 playouts (ncu --set full, "
+                           "profiles/r1m_rollout_kernel_ncu_summary.txt), scaled to this n")
         cpu = None
         if not args.no_cpu_baseline:
             from oak_ref import Oracle
@@ -730,9 +741,7 @@ def main():
                     "iters": e2e_iters, "timing": "wall clock around oakb200_rollout_host calls (pinned host records in, score/turns/steps out; chunked upload pipelined behind the playouts) issued alternately by two host threads on two contexts, so one call's upload and tail overlap the other's playouts"},
             "roofline": {"bound": "hbm", "kernel": "rollout_kernel<128,false,false,SPLIT>", "achieved": achieved, "peak": pk["hbm_gbs"],
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                         "traffic": int(424_100_608 * n / (1 << 20)), "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum = 414.9 + 9.2 MB "
-                         "for one launch of 2^20 playouts (ncu --set full, profiles/r1m_rollout_kernel_ncu_summary.txt; the SPLIT kernel "
-                         "reads the same records once: profiles/r2c_rollout_issue.json has 106.9 MB for 2^18), scaled to this n",
+                         "traffic": traffic_bytes, "traffic_source": traffic_src,
                          "peak_source": pk_src,
                          "algorithmic_bytes_per_launch": B_ROLLOUT * n, "kernel_ms": ms_total_max / args.steps,
                          "launch_ms_on_own_stream": statistics.mean(kernel_ms), "launch_ms_alone": alone_ms,
