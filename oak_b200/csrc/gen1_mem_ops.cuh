@@ -22,24 +22,28 @@ OAK_HD void mem_status_modify(M m, uint32_t status, H stats) {
   }
 }
 
-// applyDamage :1314-1349. Returns new last_damage | (substitute broke ? 1u << 31 : 0)
+// applyDamage :1314-1349. Returns new last_damage | (substitute broke ? 1u << 31 : 0). The common case (no Substitute up)
+// is inline at the call sites — a call costs about as much as the four instructions it would save — the Substitute branch
+// stays out of line.
+template <class M>
+OAK_HD_NOINLINE uint32_t mem_apply_damage_substitute(M m, int subp, uint32_t last_damage) {
+  const uint32_t lo = m.vlo(subp);
+  if (!(lo & VL_SUBSTITUTE)) return last_damage;
+  const uint32_t hi = m.vhi(subp);
+  const uint32_t shp = bf_get(hi, VHI_SUBSTITUTE);
+  if (last_damage >= shp) {
+    m.set_vhi(subp, bf_set(hi, VHI_SUBSTITUTE, 0));
+    m.set_vlo(subp, lo & ~VL_SUBSTITUTE);
+    m.lg3(LG_End, m.ident(subp), END_Substitute);
+    return last_damage | 0x80000000u;
+  }
+  m.set_vhi(subp, bf_set(hi, VHI_SUBSTITUTE, shp - last_damage));
+  m.lg3(LG_Activate, m.ident(subp), ACT_Substitute);
+  return last_damage;
+}
 template <class M>
 OAK_HD uint32_t mem_apply_damage_impl(M m, int t, int subp, uint32_t last_damage, uint32_t reason) {
-  if (m.vflag(t, VL_SUBSTITUTE)) {
-    const uint32_t lo = m.vlo(subp);
-    if (!(lo & VL_SUBSTITUTE)) return last_damage;
-    const uint32_t hi = m.vhi(subp);
-    const uint32_t shp = bf_get(hi, VHI_SUBSTITUTE);
-    if (last_damage >= shp) {
-      m.set_vhi(subp, bf_set(hi, VHI_SUBSTITUTE, 0));
-      m.set_vlo(subp, lo & ~VL_SUBSTITUTE);
-      m.lg3(LG_End, m.ident(subp), END_Substitute);
-      return last_damage | 0x80000000u;
-    }
-    m.set_vhi(subp, bf_set(hi, VHI_SUBSTITUTE, shp - last_damage));
-    m.lg3(LG_Activate, m.ident(subp), ACT_Substitute);
-    return last_damage;
-  }
+  if (m.vflag(t, VL_SUBSTITUTE)) return mem_apply_damage_substitute(m, subp, last_damage);
   const PH pk = m.stored(t);
   const uint32_t hp = m.ld16(pk, PK_HP);
   if (last_damage > hp) last_damage = hp;
@@ -48,12 +52,12 @@ OAK_HD uint32_t mem_apply_damage_impl(M m, int t, int subp, uint32_t last_damage
   return last_damage;
 }
 template <class M>
-OAK_HD_NOINLINE uint32_t mem_apply_damage(M m, int t, int subp, uint32_t last_damage) {
+OAK_HD uint32_t mem_apply_damage(M m, int t, int subp, uint32_t last_damage) {
   return mem_apply_damage_impl(m, t, subp, last_damage, DMG_None);
 }
 // with the |-damage| reason of the log (only the confusion self-hit has one, mechanics.zig:624); LOG builds only
 template <class M>
-OAK_HD_NOINLINE uint32_t mem_apply_damage_reason(M m, int t, int subp, uint32_t last_damage, uint32_t reason) {
+OAK_HD uint32_t mem_apply_damage_reason(M m, int t, int subp, uint32_t last_damage, uint32_t reason) {
   return mem_apply_damage_impl(m, t, subp, last_damage, reason);
 }
 
@@ -424,7 +428,7 @@ OAK_HD_NOINLINE void mem_haze(M m, int p) {
 
 // Effects.heal :2084-2106
 template <class M>
-OAK_HD_NOINLINE void mem_heal(M m, int p) {
+OAK_HD void mem_heal(M m, int p) {  // one call site, and a frequent one in random play (Recover / Softboiled / Rest): inline
   const PH pk = m.stored(p);
   const uint32_t hp = m.ld16(pk, PK_HP), maxhp = m.ld16(pk, PK_STATS + ST_HP);
   const uint32_t delta = (maxhp - hp) & 0xFFFFu;
